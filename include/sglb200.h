@@ -1,0 +1,169 @@
+/* sglb200.h -- C ABI of libsglb200.so, the sm_100a implementation of the quantized fused-MoE expert
+ * path that mingfeima/sgl-cpu-tests drives through torch.ops.sgl_kernel.
+ *
+ * Plain pointers and sizes only: every pointer is a DEVICE pointer unless stated, every call is
+ * asynchronous on the given CUDA stream (a cudaStream_t passed as void*), nothing here touches
+ * torch.  A call returns SGLB_OK or a negative status; sglb_last_error() then holds a
+ * thread-local message (the Python layer turns it into RuntimeError, the way the reference's
+ * TORCH_CHECK surfaces).  The library keeps no global state apart from that message: the caller
+ * owns all buffers including the workspace.
+ *
+ * Each entry point cites the reference interface it stands behind (paths are relative to the
+ * reference checkout, /root/reference in the build container).
+ */
+#ifndef SGLB200_H_
+#define SGLB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* sglb_stream_t; /* cudaStream_t */
+
+enum {
+  SGLB_OK = 0,
+  SGLB_ERR_INVALID = -1, /* bad argument / unsupported shape */
+  SGLB_ERR_CUDA = -2     /* CUDA runtime error */
+};
+
+/* element types of caller tensors */
+enum { SGLB_DT_BF16 = 0, SGLB_DT_F32 = 1, SGLB_DT_F16 = 2 };
+
+/* weight formats; numbering follows CPUQuantMethod (test_moe.py:4,86) */
+enum {
+  SGLB_FMT_BF16 = 0,      /* UNQUANT   : w bf16                                         */
+  SGLB_FMT_INT8_W8A8 = 1, /* INT8_W8A8 : w s8, f32 per-output-channel scale, dynamic    */
+                          /*             per-token s8 activations (test_moe_int8.py)    */
+  SGLB_FMT_FP8_W8A16 = 2, /* FP8_W8A16 : w e4m3, f32 scale per [block_n, block_k] block */
+  SGLB_FMT_MXFP4 = 4      /* MXFP4     : w e2m1 nibbles (low nibble = even k), e8m0/32  */
+};
+
+/* which GEMM implementation sglb_fused_experts uses */
+enum { SGLB_PATH_AUTO = 0, SGLB_PATH_STREAM = 1, SGLB_PATH_UMMA = 2 };
+
+int sglb_version(void);
+const char* sglb_last_error(void);
+/* number of kernels this library has launched in the calling process (bench.py reports it) */
+uint64_t sglb_launch_count(void);
+
+/* ---- K1 router ------------------------------------------------------------------------------
+ * grouped_topk_cpu          (test_grouped_topk.py:61-69, test_moe.py:61-70)  : bias == NULL
+ * biased_grouped_topk_cpu   (test_biased_grouped_topk.py:71-80)              : bias != NULL
+ * gating [M,E] (gating_dtype), bias [E] (bias_dtype); out topk_weights [M,topk] f32,
+ * topk_ids [M,topk] i32, picks in descending score order, ties to the lowest expert index. */
+int sglb_grouped_topk(const void* gating, int gating_dtype, const void* bias, int bias_dtype,
+                      int64_t M, int E, int topk, int num_expert_group, int topk_group,
+                      int renormalize, float routed_scaling_factor, float* topk_weights,
+                      int32_t* topk_ids, sglb_stream_t stream);
+
+/* ---- K2 moe_align -----------------------------------------------------------------------------
+ * The sort/align pass inside fused_experts_cpu; layout documented in csrc/align.cu.
+ * S = M*topk.  chunk_list / tile_list may be NULL. */
+typedef struct sglb_align_out {
+  int32_t* expert_count;  /* [E]   */
+  int32_t* expert_offset; /* [E+1] */
+  int32_t* sorted_slot;   /* [S]   */
+  int32_t* slot_pos;      /* [S]   */
+  int32_t* chunk_list;    /* [3 * sglb_moe_align_max_items(M,topk,E,chunk_rows)] */
+  int32_t* tile_list;     /* [3 * sglb_moe_align_max_items(M,topk,E,tile_rows)]  */
+  int32_t* counters;      /* [4] num_valid, num_chunks, num_tiles, num_active_experts */
+} sglb_align_out;
+
+size_t sglb_moe_align_scratch_bytes(int64_t M, int topk, int E);
+int64_t sglb_moe_align_max_items(int64_t M, int topk, int E, int rows);
+int sglb_moe_align(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows,
+                   int tile_rows, const sglb_align_out* out, void* scratch, sglb_stream_t stream);
+
+/* ---- K3-K5 fused_experts ------------------------------------------------------------------------
+ * fused_experts_cpu (test_moe.py:79-92, test_moe_int8.py:129, test_moe_fp8_ext.py:118,
+ * test_moe_offloading_cpu.py:103-117, bench_moe.py:65-130).
+ * Weights are row-major ("is_vnni = False" layout): w13 [E, 2I, H] with rows 0..I-1 = gate and
+ * I..2I-1 = up, w2 [E, H, I]; mxfp4 rows hold K/2 bytes.  The VNNI-packed layout produced by
+ * convert_weight_packed is turned into this one by sglb_unpack_weight.
+ *   out[m] = sum_j topk_weights[m,j] * W2[e_j] . silu_and_mul(W13[e_j] . x[m]),  e_j = topk_ids[m,j]
+ * ids outside [0,E) contribute nothing.  out may alias hidden (the reference's inplace=True). */
+typedef struct sglb_moe_problem {
+  int64_t M;
+  int32_t topk, E, H, I;
+  int32_t fmt;  /* SGLB_FMT_* */
+  int32_t path; /* SGLB_PATH_* */
+  const void* hidden; /* [M,H] bf16 */
+  const void* w13;
+  const void* w2;
+  const float* topk_weights; /* [M,topk] */
+  const int32_t* topk_ids;   /* [M,topk] */
+  const void* w13_scale; /* int8: f32 [E,2I]; fp8: f32 [E,ceil(2I/bn),ceil(H/bk)]; mxfp4: u8 [E,2I,H/32] */
+  const void* w2_scale;  /* int8: f32 [E,H];  fp8: f32 [E,ceil(H/bn),ceil(I/bk)];  mxfp4: u8 [E,H,I/32]  */
+  int32_t block_n, block_k; /* fp8 only */
+  void* out;                /* [M,H] bf16 */
+  void* workspace;
+  size_t workspace_bytes; /* >= sglb_fused_experts_workspace_bytes(...) */
+} sglb_moe_problem;
+
+size_t sglb_fused_experts_workspace_bytes(int64_t M, int topk, int E, int H, int I, int fmt);
+int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t stream);
+
+/* ---- K6 shared_expert -----------------------------------------------------------------------------
+ * shared_expert_cpu (test_shared_experts.py:68,78; test_moe_fp8_ext.py:60-61; test_moe_fp8.py:87-88):
+ *   out = silu_and_mul(x . W1^T) . W2^T + fused_out * routed_scaling_factor
+ * w1 [2I,H], w2 [H,I]; same formats and scale layouts as above with E = 1. */
+typedef struct sglb_shared_problem {
+  int64_t M;
+  int32_t H, I;
+  int32_t fmt;
+  int32_t path;
+  const void* hidden; /* [M,H] bf16 */
+  const void* w1;
+  const void* w2;
+  const void* w1_scale;
+  const void* w2_scale;
+  int32_t block_n, block_k;
+  const void* fused_out; /* [M,H] bf16 */
+  float routed_scaling_factor;
+  void* out; /* [M,H] bf16, may alias hidden */
+  void* workspace;
+  size_t workspace_bytes; /* >= sglb_fused_experts_workspace_bytes(M, 1, 1, H, I, fmt) */
+} sglb_shared_problem;
+
+int sglb_shared_expert(const sglb_shared_problem* p, sglb_stream_t stream);
+
+/* ---- K9 mxfp4 linear ------------------------------------------------------------------------------
+ * mxfp4_scaled_mm_cpu (test_mxfp4.py:167,196): out[M,N] bf16 = A[M,K] bf16 . dequant(Bq,Bs)^T + bias
+ * Bq [N,K/2] u8 row-major, Bs [N,K/32] u8 row-major, bias f32 [N] or NULL.
+ * workspace >= sglb_fused_experts_workspace_bytes(M, 1, 1, K, N, SGLB_FMT_MXFP4). */
+int sglb_mxfp4_mm(const void* A, const void* Bq, const void* Bs, const float* bias, int64_t M, int N,
+                  int K, void* out, void* workspace, size_t workspace_bytes, sglb_stream_t stream);
+
+/* ---- K7 prepack ---------------------------------------------------------------------------------
+ * convert_weight_packed (test_moe.py:75-76,115-124; test_gemm.py:36-46; test_gemm_int8.py:80-93)
+ * and convert_scale_packed (test_mxfp4.py:160,182-185) define a CPU (AMX/VNNI) tile layout.  These
+ * kernels convert between the row-major layout the sm_100a kernels consume and that layout, so
+ * tensors produced for / by the reference stay interchangeable:
+ *   row-major [E, N, K] elements of elem_bytes  <->  [E, N/32, K/vnni, 32, vnni]
+ *   bf16: elem_bytes 2, vnni 2 (pinned by test_gemm.py:38-44, test_moe.py:117-124)
+ *   int8: elem_bytes 1, vnni 4, int8_comp 1 -- every 32-row block is followed by 32 int32
+ *         compensation values 128 * sum_k w[n,k] (test_gemm_int8.py:84-93), so the packed buffer
+ *         holds N*(K+4) bytes per expert
+ *   fp8 / packed-fp4 bytes: elem_bytes 1, vnni 4, int8_comp 0 (layout not pinned by the reference)
+ * to_packed != 0: row-major -> packed, else packed -> row-major (compensation is dropped). */
+int sglb_repack_weight(const void* src, void* dst, int elem_bytes, int vnni, int64_t E, int64_t N,
+                       int64_t K, int int8_comp, int to_packed, sglb_stream_t stream);
+/* e8m0 scales [E, N, G] <-> [E, N/32, G, 32]  (G = K/32), test_mxfp4.py:185 */
+int sglb_repack_scale(const void* src, void* dst, int64_t E, int64_t N, int64_t G, int to_packed,
+                      sglb_stream_t stream);
+
+/* ---- building blocks exposed for tests and for the expert-parallel layer --------------------------
+ * per-row dynamic int8 quantisation (test_moe_int8.py:23-31): q = round(x * 127/absmax), scale = absmax/127 */
+int sglb_quant_rows_int8(const void* x_bf16, int64_t rows, int K, int8_t* q, float* scale,
+                         sglb_stream_t stream);
+/* K5: out[m] = bf16( sum_j ic2[slot_pos[m*topk+j]] ) over valid slots, in slot order */
+int sglb_topk_reduce(const void* ic2_bf16, const int32_t* slot_pos, int64_t M, int topk, int H,
+                     void* out_bf16, sglb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SGLB200_H_ */

@@ -1,0 +1,343 @@
+"""CPU oracle for the fused-MoE path.  TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import
+this module; nothing under sgl_cpu_tests_b200/ does (tests/test_boundary.py greps for that).
+
+What it restates.  The reference checkout contains no kernel source: the arithmetic of
+fused_experts_cpu & co. lives in the sgl-kernel CPU extension of sgl-project/sglang
+(sgl-kernel/csrc/cpu/*), version unpinned by the reference (no requirements/lock file) and absent
+from /root/reference.  What the reference does hold, and what pins results at the operator boundary,
+are the torch-native oracles inside its test scripts.  Each function below restates one of them and
+cites it (paths relative to /root/reference).  The restatements are pinned against the reference's
+own functions, executed in the build container by tests/golden/make_golden.py, through the
+fixtures under tests/golden/ (tests/test_oracle.py).
+
+Three things have no pin in the reference and are defined here -- "parity unpinned"
+for exactly these: (1) router tie-break and output order: descending score, ties to the lowest
+expert index; (2) the moe_align index layout; (3) mxfp4 *fused MoE* (only the single GEMM is tested
+upstream): composed from the mxfp4 dequantiser + the fp32 MoE oracle.
+"""
+import math
+
+import torch
+import torch.nn.functional as F
+
+# ---------------------------------------------------------------------------------------------------
+# activation / quantisation helpers
+
+
+def silu_and_mul(x):
+    """test_moe.py:17-19, test_moe_fp8_ext.py:18-20 (dtype-preserving)."""
+    d = x.shape[-1] // 2
+    return F.silu(x[..., :d]) * x[..., d:]
+
+
+def silu_and_mul_f32(x):
+    """test_moe_int8.py:16-21 (computes in f32, casts back)."""
+    dtype = x.dtype
+    x = x.to(torch.float32)
+    d = x.shape[-1] // 2
+    return (F.silu(x[..., :d]) * x[..., d:]).to(dtype)
+
+
+def per_token_quant_int8(x):
+    """test_moe_int8.py:23-31."""
+    x = x.float()
+    absmax = x.abs().max(dim=-1).values
+    absmax = absmax.clamp_min(1e-7).unsqueeze(-1)
+    scale_x = absmax / 127
+    x_q = x.mul(127 / absmax)
+    x_q = torch.round(x_q).to(torch.int8)
+    return x_q, scale_x
+
+
+def native_w8a8_per_token_matmul(A, B, As, Bs, output_dtype=torch.float32):
+    """test_moe_int8.py:37-56: C = As * (A @ B^T) * Bs, f32 accumulate."""
+    A = A.to(torch.float32)
+    B = B.to(torch.float32)
+    C = torch.matmul(A, B.t())
+    C = As * C * Bs.view(1, -1)
+    return C.to(output_dtype)
+
+
+def scaled_weight(weight, scales, block_n, block_k):
+    """test_moe_fp8_ext.py:22-25 generalised to ragged edges (test_moe_fp8.py:15-62 pads the same way):
+    w[e, n, k] * scales[e, n // block_n, k // block_k] in f32."""
+    squeeze = weight.dim() == 2
+    if squeeze:
+        weight, scales = weight.unsqueeze(0), scales.unsqueeze(0)
+    E, N, K = weight.shape
+    s = scales.float().repeat_interleave(block_n, dim=1)[:, :N]
+    s = s.repeat_interleave(block_k, dim=2)[:, :, :K]
+    out = weight.float() * s
+    return out.squeeze(0) if squeeze else out
+
+
+# ---------------------------------------------------------------------------------------------------
+# MXFP4 (test_mxfp4.py:15-128)
+
+E2M1_VALUES = [0, 0.5, 1, 1.5, 2, 3, 4, 6]
+E2M1_BOUNDS = torch.tensor([0.25, 0.75, 1.25, 1.75, 2.5, 3.5, 5])
+MX_BLOCK = 32
+
+
+def mxfp4_quantize(x):
+    """test_mxfp4.py:21-63.  Returns (packed nibbles u8 [..., K/2], e8m0 u8 [numel/32, 1])."""
+    original_shape = x.shape
+    x = x.reshape(-1, MX_BLOCK)
+    amax = x.abs().max(dim=-1, keepdim=True).values
+    descale = amax / 6.0
+    e8m0 = torch.ceil(torch.maximum(torch.log2(descale), torch.tensor(-127.0)))
+    x = (x / torch.exp2(e8m0)).view(original_shape)
+    sign = torch.sign(x)
+    sign_bit = (2 - sign) // 2
+    ord_ = torch.sum((x.abs().unsqueeze(-1) - E2M1_BOUNDS) > 0, dim=-1)
+    q = (sign_bit * 0b1000 + ord_).to(torch.uint8)
+    packed = (q[..., 1::2] << 4) + q[..., 0::2]  # low nibble = even index
+    return packed, (e8m0 + 127).to(torch.uint8)
+
+
+def mxfp4_dequantize(packed, dtype, scale):
+    """test_mxfp4.py:65-128."""
+    lo = packed & 0x0F
+    hi = (packed >> 4) & 0x0F
+    shape = list(packed.shape)
+    shape[-1] *= 2
+    q = torch.zeros(shape, dtype=torch.uint8)
+    q[..., 0::2] = lo
+    q[..., 1::2] = hi
+    sign = 1 - 2 * ((q & 0b1000) >> 3).to(torch.float32)
+    mag = (q & 0b0111).to(torch.long)
+    vals = torch.tensor(E2M1_VALUES, dtype=torch.float32)
+    x = sign * vals[mag.reshape(-1)].reshape(mag.shape)
+    x = x.reshape(-1, MX_BLOCK) * torch.exp2(scale.float() - 127).reshape(-1, 1)
+    return x.reshape(shape).to(dtype)
+
+
+def mxfp4_scaled_mm(A, Bq, Bs, bias=None):
+    """test_mxfp4.py:162-168: bf16(A.f32 @ dequant(B).f32^T) (+ bias added in bf16)."""
+    Bdq = mxfp4_dequantize(Bq, A.dtype, Bs)
+    out = torch.matmul(A.float(), Bdq.float().t()).bfloat16()
+    if bias is not None:
+        out.add_(bias.view(1, -1))
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# routers
+
+
+def _topk_lowest_index(scores, k):
+    """top-k in descending score order, ties to the lowest index (the build's stated rule)."""
+    order = torch.sort(scores, dim=-1, descending=True, stable=True).indices
+    ids = order[..., :k]
+    return torch.gather(scores, -1, ids), ids
+
+
+def grouped_topk(gating_output, topk, renormalize, num_expert_group, topk_group):
+    """test_grouped_topk.py:9-39 with the tie-break made explicit.  gating_output: any float dtype,
+    math in f32 (the script feeds .float() inputs, :49-50)."""
+    scores = torch.softmax(gating_output.float(), dim=-1)
+    n, E = scores.shape
+    G = max(1, num_expert_group)
+    group_scores = scores.view(n, G, -1).max(dim=-1).values
+    _, group_idx = _topk_lowest_index(group_scores, topk_group if topk_group > 0 else G)
+    group_mask = torch.zeros_like(group_scores)
+    group_mask.scatter_(1, group_idx, 1)
+    score_mask = group_mask.unsqueeze(-1).expand(n, G, E // G).reshape(n, -1)
+    tmp = scores.masked_fill(~score_mask.bool(), 0.0)
+    w, ids = _topk_lowest_index(tmp, topk)
+    if renormalize:
+        w = w / w.sum(dim=-1, keepdim=True)
+    return w.to(torch.float32), ids.to(torch.int32)
+
+
+def biased_grouped_topk(gating_output, correction_bias, topk, renormalize, num_expert_group, topk_group):
+    """test_biased_grouped_topk.py:9-47 with the tie-break made explicit."""
+    scores = gating_output.float().sigmoid()
+    n, E = scores.shape
+    G = max(1, num_expert_group)
+    choice = scores + correction_bias.float().unsqueeze(0)
+    gsz = E // G
+    if gsz >= 2:
+        group_scores = choice.view(n, G, -1).topk(2, dim=-1)[0].sum(dim=-1)
+    else:
+        group_scores = choice.view(n, G, -1).sum(dim=-1)
+    _, group_idx = _topk_lowest_index(group_scores, topk_group if topk_group > 0 else G)
+    group_mask = torch.zeros_like(group_scores)
+    group_mask.scatter_(1, group_idx, 1)
+    score_mask = group_mask.unsqueeze(-1).expand(n, G, gsz).reshape(n, -1)
+    tmp = choice.masked_fill(~score_mask.bool(), float("-inf"))
+    _, ids = _topk_lowest_index(tmp, topk)
+    w = scores.gather(1, ids)
+    if renormalize:
+        w = w / w.sum(dim=-1, keepdim=True)
+    return w.to(torch.float32), ids.to(torch.int32)
+
+
+# ---------------------------------------------------------------------------------------------------
+# moe_align (layout of csrc/align.cu; SURVEY.md 3b for where it sits)
+
+
+def moe_align(topk_ids, num_experts, chunk_rows=8, tile_rows=128):
+    ids = topk_ids.reshape(-1).to(torch.int64)
+    S = ids.numel()
+    valid = (ids >= 0) & (ids < num_experts)
+    slots = torch.arange(S)
+    key = torch.where(valid, ids, torch.full_like(ids, num_experts))
+    order = torch.sort(key, stable=True).indices
+    nvalid = int(valid.sum())
+    sorted_slot = torch.full((S,), S, dtype=torch.int32)
+    sorted_slot[:nvalid] = order[:nvalid].to(torch.int32)
+    slot_pos = torch.full((S,), -1, dtype=torch.int32)
+    slot_pos[order[:nvalid]] = torch.arange(nvalid, dtype=torch.int32)
+    count = torch.bincount(ids[valid], minlength=num_experts).to(torch.int32)
+    offset = torch.zeros(num_experts + 1, dtype=torch.int32)
+    offset[1:] = torch.cumsum(count, 0)
+
+    def items(rows):
+        out = []
+        for e in range(num_experts):
+            c, o = int(count[e]), int(offset[e])
+            for r0 in range(0, c, rows):
+                out.append((e, o + r0, min(rows, c - r0)))
+        return torch.tensor(out, dtype=torch.int32).reshape(-1, 3)
+
+    chunks, tiles = items(chunk_rows), items(tile_rows)
+    counters = torch.tensor([nvalid, chunks.shape[0], tiles.shape[0], int((count > 0).sum())], dtype=torch.int32)
+    return dict(expert_count=count, expert_offset=offset, sorted_slot=sorted_slot, slot_pos=slot_pos,
+                chunk_list=chunks, tile_list=tiles, counters=counters)
+
+
+# ---------------------------------------------------------------------------------------------------
+# fused MoE oracles
+
+
+def _masked_rows(topk_ids, i):
+    return topk_ids.reshape(-1) == i
+
+
+def torch_naive_moe(a, w1, w2, topk_weight, topk_ids):
+    """test_moe.py:22-54 with the routing passed in (the script recomputes softmax+topk inline):
+    bf16 matmuls, bf16 silu_and_mul, weights applied in a.dtype, sum over topk."""
+    B, D = a.shape
+    topk = topk_ids.shape[1]
+    a_rep = a.view(B, -1, D).repeat(1, topk, 1).reshape(-1, D)
+    out = torch.zeros(B * topk, w2.shape[1], dtype=a.dtype)
+    for i in range(w1.shape[0]):
+        mask = _masked_rows(topk_ids, i)
+        if mask.sum():
+            out[mask] = silu_and_mul(a_rep[mask] @ w1[i].transpose(0, 1)) @ w2[i].transpose(0, 1)
+    return (out.view(B, -1, w2.shape[1]) * topk_weight.view(B, -1, 1).to(out.dtype)).sum(dim=1)
+
+
+def native_fused_moe(a, w1, w2, topk_weight, topk_ids):
+    """test_moe_fp8_ext.py:70-91 / test_moe_offloading_cpu.py:28-52: f32 everywhere, ids == -1 (or any
+    id without an expert) contribute zero rows; result cast to a.dtype."""
+    B, D = a.shape
+    topk = topk_ids.shape[1]
+    old = a.dtype
+    a_rep = a.view(B, -1, D).repeat(1, topk, 1).reshape(-1, D).float()
+    out = torch.zeros(B * topk, w2.shape[1], dtype=torch.float32)
+    for i in range(w1.shape[0]):
+        mask = _masked_rows(topk_ids, i)
+        if mask.sum():
+            ic1 = silu_and_mul(torch.matmul(a_rep[mask], w1[i].float().transpose(0, 1)))
+            out[mask] = torch.matmul(ic1, w2[i].float().transpose(0, 1))
+    return (out.view(B, -1, w2.shape[1]) * topk_weight.view(B, -1, 1).to(out.dtype)).sum(dim=1).to(old)
+
+
+def torch_w8a8_per_column_moe(a, w1, w2, w1_s, w2_s, topk_weight, topk_ids):
+    """test_moe_int8.py:59-94."""
+    B, D = a.shape
+    topk = topk_ids.shape[1]
+    a_q, a_s = per_token_quant_int8(a)
+    a_q = a_q.view(B, -1, D).repeat(1, topk, 1).reshape(-1, D)
+    a_s = a_s.view(B, -1, 1).repeat(1, topk, 1).reshape(-1, 1)
+    out = torch.zeros(B * topk, w2.shape[1], dtype=torch.float32)
+    for i in range(w1.shape[0]):
+        mask = _masked_rows(topk_ids, i)
+        if mask.sum():
+            inter = native_w8a8_per_token_matmul(a_q[mask], w1[i], a_s[mask], w1_s[i])
+            act = silu_and_mul_f32(inter)
+            act_q, act_s = per_token_quant_int8(act)
+            out[mask] = native_w8a8_per_token_matmul(act_q, w2[i], act_s, w2_s[i])
+    return (out.view(B, -1, w2.shape[1]) * topk_weight.view(B, -1, 1).to(out.dtype)).sum(dim=1).to(a.dtype)
+
+
+def fused_experts(a, w1, w2, topk_weight, topk_ids, fmt, w1_scale=None, w2_scale=None, block_size=None):
+    """One entry point per weight format; fmt in {"bf16", "int8", "fp8", "mxfp4"}.
+    Weights are row-major (unpacked)."""
+    if fmt == "bf16":
+        return native_fused_moe(a, w1, w2, topk_weight, topk_ids)
+    if fmt == "int8":
+        return torch_w8a8_per_column_moe(a, w1, w2, w1_scale, w2_scale, topk_weight, topk_ids)
+    if fmt == "fp8":
+        bn, bk = block_size
+        return native_fused_moe(a, scaled_weight(w1, w1_scale, bn, bk), scaled_weight(w2, w2_scale, bn, bk),
+                                topk_weight, topk_ids)
+    if fmt == "mxfp4":
+        w1d = mxfp4_dequantize(w1, torch.float32, w1_scale)
+        w2d = mxfp4_dequantize(w2, torch.float32, w2_scale)
+        return native_fused_moe(a, w1d, w2d, topk_weight, topk_ids)
+    raise ValueError(fmt)
+
+
+# ---------------------------------------------------------------------------------------------------
+# shared expert
+
+
+def shared_expert(a, w1, w2, fused_out, routed_scaling_factor, fmt, w1_scale=None, w2_scale=None,
+                  block_size=None):
+    """bf16: test_shared_experts.py:34-40 (f32 inputs, :64); int8: :42-53; fp8: test_moe_fp8_ext.py:51-56."""
+    dtype = a.dtype
+    if fmt == "int8":
+        a_q, a_s = per_token_quant_int8(a.float())
+        ic1 = native_w8a8_per_token_matmul(a_q, w1, a_s, w1_scale)
+        ic2 = silu_and_mul(ic1)
+        q2, s2 = per_token_quant_int8(ic2)
+        ic3 = native_w8a8_per_token_matmul(q2, w2, s2, w2_scale)
+        return (ic3 + fused_out.float() * routed_scaling_factor).to(dtype)
+    if fmt == "fp8":
+        bn, bk = block_size
+        w1, w2 = scaled_weight(w1, w1_scale, bn, bk), scaled_weight(w2, w2_scale, bn, bk)
+    ic1 = silu_and_mul(torch.matmul(a.float(), w1.float().t()))
+    out = torch.matmul(ic1, w2.float().t()) + fused_out.float() * routed_scaling_factor
+    return out.to(dtype)
+
+
+# ---------------------------------------------------------------------------------------------------
+# prepack layouts
+
+
+def pack_weight_vnni(w):
+    """bf16/fp16: test_gemm.py:38-44, test_moe.py:117-124 -> [E, N/32, K/2, 32, 2], same shape.
+    int8: test_gemm_int8.py:84-93 -> per 32-row block [K/4, 32, 4] bytes followed by 32 int32
+    compensation values 128*sum_k w[n,k] (behind-the-block placement follows the upstream kernel;
+    the reference pins it for N = 32 only); returned as [.., N, K+4] int8.
+    fp8 / uint8: same byte tiling as int8 without compensation (not pinned by the reference)."""
+    squeeze = w.dim() == 2
+    if squeeze:
+        w = w.unsqueeze(0)
+    E, N, K = w.shape
+    if w.dtype in (torch.bfloat16, torch.float16):
+        out = w.view(E, N // 32, 32, K // 2, 2).permute(0, 1, 3, 2, 4).contiguous().view(E, N, K)
+    elif w.dtype == torch.int8:
+        body = w.view(E, N // 32, 32, K // 4, 4).permute(0, 1, 3, 2, 4).contiguous().view(E, N // 32, 32 * K)
+        comp = (128 * w.to(torch.int32).sum(dim=-1)).to(torch.int32).view(E, N // 32, 32)
+        comp_bytes = comp.contiguous().view(torch.int8).view(E, N // 32, 128)
+        out = torch.cat([body, comp_bytes], dim=-1).view(E, N, K + 4)
+    else:
+        b = w.view(torch.uint8)
+        out = b.view(E, N // 32, 32, K // 4, 4).permute(0, 1, 3, 2, 4).contiguous().view(E, N, K).view(w.dtype)
+    return out.squeeze(0) if squeeze else out
+
+
+def pack_scale(s):
+    """test_mxfp4.py:185: Bs.view(N/32, 32, K/32).transpose(1, 2), flat order, same shape."""
+    squeeze = s.dim() == 2
+    if squeeze:
+        s = s.unsqueeze(0)
+    E, N, G = s.shape
+    out = s.view(E, N // 32, 32, G).transpose(2, 3).contiguous().view(E, N, G)
+    return out.squeeze(0) if squeeze else out

@@ -1,0 +1,224 @@
+// K2: moe_align -- stable counting sort of the M*topk routed slots by expert.
+//
+// Stands where the reference kernel's internal moe_align_block_size pass stands (SURVEY.md 3b;
+// not exposed by any op in /root/reference, so the layout below is this build's own contract,
+// stated identically in oracle/moe_oracle.py::moe_align and held bit-exact by tests):
+//
+//   slot            = m*topk + j                    (flat index into topk_ids)
+//   valid slot      = 0 <= topk_ids[slot] < E       (-1 and any other id contribute nothing,
+//                                                    test_moe_offloading_cpu.py:57-68)
+//   sorted_slot[p]  = valid slots ordered by (expert, slot) ascending; tail filled with S=M*topk
+//   slot_pos[slot]  = p, or -1 for an invalid slot
+//   expert_offset   = exclusive scan of per-expert counts, E+1 entries
+//   chunk_list      = (expert, row_start, rows<=chunk_rows) work items for the streaming GEMM
+//   tile_list       = (expert, row_start, rows<=tile_rows)  work items for the tcgen05 GEMM
+//   counters        = {num_valid, num_chunks, num_tiles, num_active_experts}
+#include "common.cuh"
+
+namespace sglb {
+
+constexpr int kAlignThreads = 1024;
+
+__device__ __forceinline__ int block_exclusive_scan(int v, int* warp_sums, int* total) {
+  // 1024 threads.  Returns exclusive prefix of v over threadIdx.x; *total = sum.
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    int o = __shfl_up_sync(0xffffffffu, inc, off);
+    if (lane >= off) inc += o;
+  }
+  __syncthreads();  // protect warp_sums reuse
+  if (lane == 31) warp_sums[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    int w = warp_sums[lane];
+    int winc = w;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      int o = __shfl_up_sync(0xffffffffu, winc, off);
+      if (lane >= off) winc += o;
+    }
+    warp_sums[lane] = winc - w;  // exclusive
+    if (lane == 31) warp_sums[32] = winc;
+  }
+  __syncthreads();
+  int res = warp_sums[warp] + inc - v;
+  *total = warp_sums[32];
+  return res;
+}
+
+// Per-block stable ranks.  On return: rank = number of earlier slots of this block with the same
+// expert; warp_cnt[w*E + e] has been turned into the exclusive prefix over warps; block_total[e]
+// (smem) = slots of expert e in this block.
+__device__ __forceinline__ void block_rank(int e, bool valid, int E, uint16_t* warp_cnt,
+                                           int* block_total, int& rank_in_block) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < 32 * E; i += kAlignThreads) warp_cnt[i] = 0;
+  __syncthreads();
+  unsigned peers = __match_any_sync(0xffffffffu, valid ? e : -1 - lane);
+  int rank_in_warp = __popc(peers & ((1u << lane) - 1u));
+  if (valid && rank_in_warp == 0) warp_cnt[warp * E + e] = (uint16_t)__popc(peers);
+  __syncthreads();
+  for (int x = threadIdx.x; x < E; x += kAlignThreads) {
+    int run = 0;
+    for (int w = 0; w < 32; ++w) {
+      int c = warp_cnt[w * E + x];
+      warp_cnt[w * E + x] = (uint16_t)run;
+      run += c;
+    }
+    block_total[x] = run;
+  }
+  __syncthreads();
+  rank_in_block = valid ? (int)warp_cnt[warp * E + e] + rank_in_warp : 0;
+}
+
+__global__ void __launch_bounds__(kAlignThreads) align_count_kernel(const int32_t* __restrict__ ids,
+                                                                   int S, int E,
+                                                                   int32_t* __restrict__ block_hist) {
+  extern __shared__ int smem_i[];
+  int* hist = smem_i;
+  for (int x = threadIdx.x; x < E; x += kAlignThreads) hist[x] = 0;
+  __syncthreads();
+  int slot = blockIdx.x * kAlignThreads + threadIdx.x;
+  if (slot < S) {
+    int e = ids[slot];
+    if (e >= 0 && e < E) atomicAdd(&hist[e], 1);
+  }
+  __syncthreads();
+  for (int x = threadIdx.x; x < E; x += kAlignThreads) block_hist[(size_t)blockIdx.x * E + x] = hist[x];
+}
+
+__global__ void __launch_bounds__(kAlignThreads)
+    align_scatter_kernel(const int32_t* __restrict__ ids, int S, int E, int nb,
+                         const int32_t* __restrict__ block_hist, int chunk_rows, int tile_rows,
+                         int32_t* __restrict__ expert_count, int32_t* __restrict__ expert_offset,
+                         int32_t* __restrict__ sorted_slot, int32_t* __restrict__ slot_pos,
+                         int32_t* __restrict__ chunk_list, int32_t* __restrict__ tile_list,
+                         int32_t* __restrict__ counters) {
+  extern __shared__ int smem_i[];
+  int* block_total = smem_i;            // [E]
+  int* base = block_total + E;          // [E]  expert_offset + slots in earlier blocks
+  int* warp_sums = base + E;            // [33]
+  uint16_t* warp_cnt = reinterpret_cast<uint16_t*>(warp_sums + 34);  // [32*E]
+
+  const int slot = blockIdx.x * kAlignThreads + threadIdx.x;
+  int e = -1;
+  if (slot < S) e = ids[slot];
+  const bool valid = (e >= 0 && e < E);
+  int rank;
+  block_rank(e, valid, E, warp_cnt, block_total, rank);
+
+  // totals over all blocks + slots of the same expert in earlier blocks
+  int total_valid = 0;
+  for (int x0 = 0; x0 < E; x0 += kAlignThreads) {  // E <= 1024 -> a single pass
+    int x = x0 + threadIdx.x;
+    int tot = 0, before = 0;
+    if (x < E) {
+      if (nb == 1) {
+        tot = block_total[x];
+      } else {
+        for (int b = 0; b < nb; ++b) {
+          int c = block_hist[(size_t)b * E + x];
+          if (b < (int)blockIdx.x) before += c;
+          tot += c;
+        }
+      }
+    }
+    int off = block_exclusive_scan(tot, warp_sums, &total_valid);
+    if (x < E) {
+      base[x] = off + before;
+      if (blockIdx.x == 0) {
+        expert_count[x] = tot;
+        expert_offset[x] = off;
+      }
+    }
+    __syncthreads();
+
+    if (blockIdx.x == 0) {
+      if (threadIdx.x == 0) {
+        expert_offset[E] = total_valid;
+        counters[0] = total_valid;
+      }
+      // work lists
+      int nact = 0;
+      for (int pass = 0; pass < 2; ++pass) {
+        const int rows = pass == 0 ? chunk_rows : tile_rows;
+        int32_t* list = pass == 0 ? chunk_list : tile_list;
+        int n = (x < E && rows > 0) ? (tot + rows - 1) / rows : 0;
+        int ntot;
+        int first = block_exclusive_scan(n, warp_sums, &ntot);
+        if (list != nullptr) {
+          for (int i = 0; i < n; ++i) {
+            int r0 = i * rows;
+            list[3 * (first + i) + 0] = x;
+            list[3 * (first + i) + 1] = off + r0;
+            list[3 * (first + i) + 2] = min(rows, tot - r0);
+          }
+        }
+        if (threadIdx.x == 0) counters[1 + pass] = (list != nullptr) ? ntot : 0;
+        __syncthreads();
+      }
+      int act = (x < E && tot > 0) ? 1 : 0;
+      block_exclusive_scan(act, warp_sums, &nact);
+      if (threadIdx.x == 0) counters[3] = nact;
+    }
+  }
+  __syncthreads();
+
+  if (slot < S) {
+    if (valid) {
+      int p = base[e] + rank;
+      sorted_slot[p] = slot;
+      slot_pos[slot] = p;
+    } else {
+      slot_pos[slot] = -1;
+    }
+  }
+  // sentinel tail
+  for (int p = total_valid + blockIdx.x * kAlignThreads + threadIdx.x; p < S;
+       p += nb * kAlignThreads)
+    sorted_slot[p] = S;
+}
+
+}  // namespace sglb
+
+using namespace sglb;
+
+extern "C" size_t sglb_moe_align_scratch_bytes(int64_t M, int topk, int E) {
+  int64_t S = M * topk;
+  int64_t nb = ceil_div64(S > 0 ? S : 1, kAlignThreads);
+  return (size_t)(nb * E) * sizeof(int32_t);
+}
+
+extern "C" int sglb_moe_align(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows,
+                              int tile_rows, const sglb_align_out* out, void* scratch,
+                              sglb_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  SGLB_CHECK(out != nullptr, "moe_align: null output struct");
+  SGLB_CHECK(E >= 1 && E <= 1024, "moe_align: E=%d must be in [1,1024]", E);
+  SGLB_CHECK(M >= 0 && topk >= 1, "moe_align: bad shape");
+  SGLB_CHECK(M * (int64_t)topk < (1ll << 30), "moe_align: M*topk too large");
+  const int S = (int)(M * topk);
+  SGLB_CHECK(out->expert_count && out->expert_offset && out->sorted_slot && out->slot_pos &&
+                 out->counters,
+             "moe_align: null output pointer");
+  const int nb = S > 0 ? ceil_div(S, kAlignThreads) : 1;
+  if (nb > 1) {
+    SGLB_CHECK(scratch != nullptr, "moe_align: scratch required for M*topk > %d", kAlignThreads);
+    align_count_kernel<<<nb, kAlignThreads, E * sizeof(int), stream>>>(topk_ids, S, E,
+                                                                     (int32_t*)scratch);
+    SGLB_LAUNCH_CHECK();
+  }
+  size_t smem = (size_t)(2 * E + 34) * sizeof(int) + (size_t)32 * E * sizeof(uint16_t);
+  if (smem > 48 * 1024) {
+    SGLB_CUDA(cudaFuncSetAttribute(align_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)smem));
+  }
+  align_scatter_kernel<<<nb, kAlignThreads, smem, stream>>>(
+      topk_ids, S, E, nb, (const int32_t*)scratch, chunk_rows, tile_rows, out->expert_count,
+      out->expert_offset, out->sorted_slot, out->slot_pos, out->chunk_list, out->tile_list,
+      out->counters);
+  SGLB_LAUNCH_CHECK();
+  return SGLB_OK;
+}

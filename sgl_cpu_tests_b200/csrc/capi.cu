@@ -1,0 +1,340 @@
+// C-ABI entry points that orchestrate the kernels: fused_experts, shared_expert, mxfp4_mm.
+#include <atomic>
+#include <math.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "stream_gemm.cuh"
+
+namespace sglb {
+
+static thread_local char g_err[1024] = "";
+static std::atomic<uint64_t> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+void count_launch(int n = 1) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+int launch_shared_axpy(const void* y, const void* fused, float rsf, int64_t n, void* out,
+                       cudaStream_t stream);
+int umma_supported(int fmt, int64_t M, int topk, int E, int H, int I);
+int launch_umma_moe(const sglb_moe_problem* p, const struct MoeWorkspace& ws, cudaStream_t stream);
+
+// ---- workspace carving -------------------------------------------------------------------------
+struct MoeWorkspace {
+  int32_t *expert_count, *expert_offset, *counters, *sorted_slot, *slot_pos, *chunk_list, *tile_list;
+  int32_t* align_scratch;
+  int32_t* zero_ids;          // [M] (shared expert / dense callers)
+  __nv_bfloat16* act;         // [S, I]
+  __nv_bfloat16* ic2;         // [S, H]
+  int8_t* xq;                 // [M, H]
+  float* xs;                  // [M]
+  int8_t* actq;               // [S, I]
+  float* acts;                // [S]
+  size_t bytes;
+};
+
+constexpr int kMinChunkRows = 8;
+constexpr int kTileRows = 128;
+
+static int64_t max_items(int64_t S, int E, int rows) {
+  return (S < E ? S : E) + S / rows + 1;
+}
+
+static MoeWorkspace carve(void* base, int64_t M, int topk, int E, int H, int I, int fmt) {
+  MoeWorkspace w;
+  const int64_t S = M * topk;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = base ? (char*)base + off : nullptr;
+    off += align_up(bytes ? bytes : 1, 256);
+    return p;
+  };
+  w.expert_count = (int32_t*)take(sizeof(int32_t) * E);
+  w.expert_offset = (int32_t*)take(sizeof(int32_t) * (E + 1));
+  w.counters = (int32_t*)take(sizeof(int32_t) * 4);
+  w.sorted_slot = (int32_t*)take(sizeof(int32_t) * S);
+  w.slot_pos = (int32_t*)take(sizeof(int32_t) * S);
+  w.chunk_list = (int32_t*)take(sizeof(int32_t) * 3 * max_items(S, E, kMinChunkRows));
+  w.tile_list = (int32_t*)take(sizeof(int32_t) * 3 * max_items(S, E, kTileRows));
+  w.align_scratch = (int32_t*)take(sglb_moe_align_scratch_bytes(M, topk, E));
+  w.zero_ids = (int32_t*)take(sizeof(int32_t) * M);
+  // +kTileRows rows of slack: the tcgen05 path reads whole 128-row tiles past the last expert
+  w.act = (__nv_bfloat16*)take(sizeof(__nv_bfloat16) * (S + kTileRows) * I);
+  w.ic2 = (__nv_bfloat16*)take(sizeof(__nv_bfloat16) * S * H);
+  if (fmt == SGLB_FMT_INT8_W8A8) {
+    w.xq = (int8_t*)take((size_t)M * H);
+    w.xs = (float*)take(sizeof(float) * M);
+    w.actq = (int8_t*)take((size_t)(S + kTileRows) * I);
+    w.acts = (float*)take(sizeof(float) * (S + kTileRows));
+  } else {
+    w.xq = nullptr;
+    w.xs = nullptr;
+    w.actq = nullptr;
+    w.acts = nullptr;
+  }
+  w.bytes = off;
+  return w;
+}
+
+// ---- plan for the streaming kernels ---------------------------------------------------------------
+static StreamPlan make_plan(int64_t M, int topk, int E, int n_rows_stage, int stage) {
+  StreamPlan p;
+  const double S = (double)M * topk;
+  double active = E * (1.0 - pow(1.0 - (double)(topk < E ? topk : E) / E, (double)M));
+  if (E == 1) active = 1;
+  if (active < 1) active = 1;
+  const double avg = S / active;
+  p.ng = avg <= 6.0 ? 1 : (avg <= 12.0 ? 2 : 4);
+  const double chunks = active + S / (8.0 * p.ng);
+  const int per_warp = stage == 1 ? 16 : 32;
+  auto ctas = [&](int wn) { return chunks * ceil_div(n_rows_stage, per_warp * wn); };
+  p.cfg = ctas(8) >= 2 * 148 ? 0 : (ctas(2) >= 2 * 148 ? 1 : 2);
+  p.max_chunks = 0;  // filled by caller
+  return p;
+}
+
+template <int STAGE>
+static int dispatch_stream(int fmt, const StreamArgs& a, const StreamPlan& plan, cudaStream_t s) {
+  int rc;
+  switch (fmt) {
+    case SGLB_FMT_BF16: rc = launch_stream_gemm<SGLB_FMT_BF16, STAGE>(a, plan, s); break;
+    case SGLB_FMT_INT8_W8A8: rc = launch_stream_gemm<SGLB_FMT_INT8_W8A8, STAGE>(a, plan, s); break;
+    case SGLB_FMT_FP8_W8A16: rc = launch_stream_gemm<SGLB_FMT_FP8_W8A16, STAGE>(a, plan, s); break;
+    case SGLB_FMT_MXFP4: rc = launch_stream_gemm<SGLB_FMT_MXFP4, STAGE>(a, plan, s); break;
+    default: set_error("unsupported weight format %d", fmt); return SGLB_ERR_INVALID;
+  }
+  if (rc == SGLB_OK) count_launch();
+  return rc;
+}
+
+static int check_format(const char* who, int fmt, int H, int I, const void* s13, const void* s2,
+                        int bn, int bk) {
+  switch (fmt) {
+    case SGLB_FMT_BF16:
+      SGLB_CHECK(H % 8 == 0 && I % 8 == 0, "%s: bf16 needs H,I multiples of 8 (H=%d I=%d)", who, H, I);
+      break;
+    case SGLB_FMT_INT8_W8A8:
+      SGLB_CHECK(H % 16 == 0 && I % 16 == 0, "%s: int8 needs H,I multiples of 16 (H=%d I=%d)", who, H, I);
+      SGLB_CHECK(s13 && s2, "%s: int8 w8a8 needs w1_scale and w2_scale", who);
+      break;
+    case SGLB_FMT_FP8_W8A16:
+      SGLB_CHECK(H % 16 == 0 && I % 16 == 0, "%s: fp8 needs H,I multiples of 16 (H=%d I=%d)", who, H, I);
+      SGLB_CHECK(s13 && s2, "%s: fp8 w8a16 needs w1_scale and w2_scale", who);
+      SGLB_CHECK(bn >= 8 && bn % 8 == 0 && bk >= 64 && bk % 64 == 0,
+                 "%s: fp8 block_size [%d,%d] unsupported (block_n %% 8 == 0, block_k %% 64 == 0)", who, bn, bk);
+      break;
+    case SGLB_FMT_MXFP4:
+      SGLB_CHECK(H % 32 == 0 && I % 32 == 0, "%s: mxfp4 needs H,I multiples of 32 (H=%d I=%d)", who, H, I);
+      SGLB_CHECK(s13 && s2, "%s: mxfp4 needs e8m0 scales", who);
+      break;
+    default:
+      set_error("%s: unsupported weight format %d", who, fmt);
+      return SGLB_ERR_INVALID;
+  }
+  return SGLB_OK;
+}
+
+// Two streaming GEMMs over an existing alignment.  `row_scale` = topk weights or NULL.
+static int run_stream_mlp(int fmt, int64_t M, int topk, int E, int H, int I, const void* hidden,
+                          const void* w13, const void* w2, const void* s13, const void* s2, int bn,
+                          int bk, const float* row_scale, const MoeWorkspace& ws, void* ic2_out,
+                          cudaStream_t stream) {
+  const int64_t S = M * topk;
+  StreamArgs a;
+  memset(&a, 0, sizeof(a));
+  a.chunk_list = ws.chunk_list;
+  a.counters = ws.counters;
+  a.sorted_slot = ws.sorted_slot;
+  a.topk = topk;
+  a.block_n = bn;
+  a.block_k = bk;
+
+  StreamPlan plan = make_plan(M, topk, E, I, 1);
+  plan.max_chunks = (int)max_items(S, E, 8 * plan.ng);
+  SGLB_CHECK(plan.max_chunks <= 65535, "fused_experts(stream path): too many row chunks (%d)", plan.max_chunks);
+
+  // stage 1
+  a.W = w13;
+  a.Wscale = s13;
+  a.K = H;
+  a.N = I;
+  a.rows_per_expert = 2 * I;
+  a.gather = 1;
+  a.out = ws.act;
+  a.row_scale = nullptr;
+  a.scale_cols = fmt == SGLB_FMT_FP8_W8A16 ? ceil_div(H, bk) : H / 32;
+  if (fmt == SGLB_FMT_INT8_W8A8) {
+    int rc = sglb_quant_rows_int8(hidden, M, H, ws.xq, ws.xs, stream);
+    if (rc) return rc;
+    a.X = ws.xq;
+    a.Xscale = ws.xs;
+  } else {
+    a.X = hidden;
+  }
+  int rc = dispatch_stream<1>(fmt, a, plan, stream);
+  if (rc) return rc;
+
+  // stage 2
+  StreamPlan plan2 = make_plan(M, topk, E, H, 2);
+  plan2.ng = plan.ng;  // same chunk list
+  plan2.max_chunks = plan.max_chunks;
+  a.W = w2;
+  a.Wscale = s2;
+  a.K = I;
+  a.N = H;
+  a.rows_per_expert = H;
+  a.gather = 0;
+  a.out = ic2_out;
+  a.row_scale = row_scale;
+  a.scale_cols = fmt == SGLB_FMT_FP8_W8A16 ? ceil_div(I, bk) : I / 32;
+  if (fmt == SGLB_FMT_INT8_W8A8) {
+    rc = sglb_quant_rows_int8(ws.act, S, I, ws.actq, ws.acts, stream);
+    if (rc) return rc;
+    a.X = ws.actq;
+    a.Xscale = ws.acts;
+  } else {
+    a.X = ws.act;
+  }
+  return dispatch_stream<2>(fmt, a, plan2, stream);
+}
+
+static int run_align(const int32_t* ids, int64_t M, int topk, int E, int chunk_rows,
+                     const MoeWorkspace& ws, cudaStream_t stream) {
+  sglb_align_out ao;
+  ao.expert_count = ws.expert_count;
+  ao.expert_offset = ws.expert_offset;
+  ao.sorted_slot = ws.sorted_slot;
+  ao.slot_pos = ws.slot_pos;
+  ao.chunk_list = ws.chunk_list;
+  ao.tile_list = ws.tile_list;
+  ao.counters = ws.counters;
+  int rc = sglb_moe_align(ids, M, topk, E, chunk_rows, kTileRows, &ao, ws.align_scratch, stream);
+  return rc;
+}
+
+}  // namespace sglb
+
+using namespace sglb;
+
+extern "C" int sglb_version(void) { return 100; }
+extern "C" const char* sglb_last_error(void) { return g_err; }
+extern "C" uint64_t sglb_launch_count(void) { return g_launches.load(); }
+
+extern "C" int64_t sglb_moe_align_max_items(int64_t M, int topk, int E, int rows) {
+  if (rows <= 0) return 0;
+  return max_items(M * topk, E, rows);
+}
+
+extern "C" size_t sglb_fused_experts_workspace_bytes(int64_t M, int topk, int E, int H, int I,
+                                                     int fmt) {
+  return carve(nullptr, M, topk, E, H, I, fmt).bytes;
+}
+
+extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  SGLB_CHECK(p != nullptr, "fused_experts: null problem");
+  SGLB_CHECK(p->M >= 0 && p->topk >= 1 && p->E >= 1 && p->H > 0 && p->I > 0,
+             "fused_experts: bad shape M=%lld topk=%d E=%d H=%d I=%d", (long long)p->M, p->topk, p->E, p->H, p->I);
+  SGLB_CHECK(p->hidden && p->w13 && p->w2 && p->topk_weights && p->topk_ids && p->out,
+             "fused_experts: null tensor pointer");
+  int rc = check_format("fused_experts", p->fmt, p->H, p->I, p->w13_scale, p->w2_scale, p->block_n, p->block_k);
+  if (rc) return rc;
+  if (p->M == 0) return SGLB_OK;
+  const size_t need = sglb_fused_experts_workspace_bytes(p->M, p->topk, p->E, p->H, p->I, p->fmt);
+  SGLB_CHECK(p->workspace && p->workspace_bytes >= need, "fused_experts: workspace too small (%zu < %zu)",
+             p->workspace_bytes, need);
+  SGLB_CHECK(((uintptr_t)p->workspace & 255) == 0, "fused_experts: workspace must be 256-byte aligned");
+  MoeWorkspace ws = carve(p->workspace, p->M, p->topk, p->E, p->H, p->I, p->fmt);
+
+  int path = p->path;
+  if (path == SGLB_PATH_AUTO) {
+    const double rows_per_expert = (double)p->M * p->topk / p->E;
+    path = (rows_per_expert >= 24.0 && umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I))
+               ? SGLB_PATH_UMMA
+               : SGLB_PATH_STREAM;
+  }
+  if (path == SGLB_PATH_UMMA) {
+    SGLB_CHECK(umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I),
+               "fused_experts: tcgen05 path does not support fmt=%d H=%d I=%d", p->fmt, p->H, p->I);
+    rc = run_align(p->topk_ids, p->M, p->topk, p->E, 0, ws, stream);
+    if (rc) return rc;
+    count_launch(p->M * p->topk > 1024 ? 2 : 1);
+    rc = launch_umma_moe(p, ws, stream);
+    if (rc) return rc;
+  } else {
+    StreamPlan plan = make_plan(p->M, p->topk, p->E, p->I, 1);
+    rc = run_align(p->topk_ids, p->M, p->topk, p->E, 8 * plan.ng, ws, stream);
+    if (rc) return rc;
+    count_launch(p->M * p->topk > 1024 ? 2 : 1);
+    rc = run_stream_mlp(p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2, p->w13_scale,
+                        p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, ws.ic2, stream);
+    if (rc) return rc;
+  }
+  return sglb_topk_reduce(ws.ic2, ws.slot_pos, p->M, p->topk, p->H, p->out, stream);
+}
+
+extern "C" int sglb_shared_expert(const sglb_shared_problem* p, sglb_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  SGLB_CHECK(p != nullptr, "shared_expert: null problem");
+  SGLB_CHECK(p->M >= 0 && p->H > 0 && p->I > 0, "shared_expert: bad shape");
+  SGLB_CHECK(p->hidden && p->w1 && p->w2 && p->fused_out && p->out, "shared_expert: null tensor pointer");
+  int rc = check_format("shared_expert", p->fmt, p->H, p->I, p->w1_scale, p->w2_scale, p->block_n, p->block_k);
+  if (rc) return rc;
+  if (p->M == 0) return SGLB_OK;
+  const size_t need = sglb_fused_experts_workspace_bytes(p->M, 1, 1, p->H, p->I, p->fmt);
+  SGLB_CHECK(p->workspace && p->workspace_bytes >= need, "shared_expert: workspace too small (%zu < %zu)",
+             p->workspace_bytes, need);
+  MoeWorkspace ws = carve(p->workspace, p->M, 1, 1, p->H, p->I, p->fmt);
+  SGLB_CUDA(cudaMemsetAsync(ws.zero_ids, 0, sizeof(int32_t) * p->M, stream));
+  StreamPlan plan = make_plan(p->M, 1, 1, p->I, 1);
+  rc = run_align(ws.zero_ids, p->M, 1, 1, 8 * plan.ng, ws, stream);
+  if (rc) return rc;
+  count_launch(p->M > 1024 ? 2 : 1);
+  rc = run_stream_mlp(p->fmt, p->M, 1, 1, p->H, p->I, p->hidden, p->w1, p->w2, p->w1_scale, p->w2_scale,
+                      p->block_n, p->block_k, nullptr, ws, ws.ic2, stream);
+  if (rc) return rc;
+  return launch_shared_axpy(ws.ic2, p->fused_out, p->routed_scaling_factor, p->M * (int64_t)p->H, p->out, stream);
+}
+
+extern "C" int sglb_mxfp4_mm(const void* A, const void* Bq, const void* Bs, const float* bias, int64_t M,
+                             int N, int K, void* out, void* workspace, size_t workspace_bytes,
+                             sglb_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  SGLB_CHECK(A && Bq && Bs && out, "mxfp4_mm: null tensor pointer");
+  SGLB_CHECK(M >= 0 && N > 0 && K > 0 && K % 32 == 0, "mxfp4_mm: bad shape M=%lld N=%d K=%d (K %% 32 == 0)",
+             (long long)M, N, K);
+  if (M == 0) return SGLB_OK;
+  const size_t need = sglb_fused_experts_workspace_bytes(M, 1, 1, K, N, SGLB_FMT_MXFP4);
+  SGLB_CHECK(workspace && workspace_bytes >= need, "mxfp4_mm: workspace too small (%zu < %zu)", workspace_bytes, need);
+  MoeWorkspace ws = carve(workspace, M, 1, 1, K, N, SGLB_FMT_MXFP4);
+  SGLB_CUDA(cudaMemsetAsync(ws.zero_ids, 0, sizeof(int32_t) * M, stream));
+  StreamPlan plan = make_plan(M, 1, 1, N, 2);
+  plan.max_chunks = (int)max_items(M, 1, 8 * plan.ng);
+  SGLB_CHECK(plan.max_chunks <= 65535, "mxfp4_mm: M too large for the streaming path");
+  int rc = run_align(ws.zero_ids, M, 1, 1, 8 * plan.ng, ws, stream);
+  if (rc) return rc;
+  count_launch(M > 1024 ? 2 : 1);
+  StreamArgs a;
+  memset(&a, 0, sizeof(a));
+  a.chunk_list = ws.chunk_list;
+  a.counters = ws.counters;
+  a.sorted_slot = ws.sorted_slot;
+  a.topk = 1;
+  a.W = Bq;
+  a.Wscale = Bs;
+  a.X = A;
+  a.K = K;
+  a.N = N;
+  a.rows_per_expert = N;
+  a.gather = 0;
+  a.out = out;
+  a.bias = bias;
+  a.scale_cols = K / 32;
+  return dispatch_stream<2>(SGLB_FMT_MXFP4, a, plan, stream);
+}

@@ -1,0 +1,274 @@
+// K1: grouped top-k router, one warp per token.
+//
+// Replaces the reference ops grouped_topk_cpu (test_grouped_topk.py:61-69, oracle :20-39) and
+// biased_grouped_topk_cpu (test_biased_grouped_topk.py:71-80, oracle :20-47).
+//
+// Tie-break rule (the reference leaves it open): among equal scores the lowest
+// index wins; picks are emitted in descending score order.  oracle/moe_oracle.py states the
+// same rule and the tests hold this kernel bit-exact on ids to it.
+#include "common.cuh"
+
+namespace sglb {
+
+constexpr int kMaxPerLane = 32;  // E <= 1024
+
+struct ValIdx {
+  float v;
+  int i;
+};
+
+__device__ __forceinline__ bool better(float v, int i, float bv, int bi) {
+  // NaNs never win; equal values -> lower index.
+  return (v > bv) || (v == bv && i < bi);
+}
+
+__device__ __forceinline__ ValIdx warp_argmax(float v, int i) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    float ov = __shfl_xor_sync(0xffffffffu, v, off);
+    int oi = __shfl_xor_sync(0xffffffffu, i, off);
+    if (better(ov, oi, v, i)) {
+      v = ov;
+      i = oi;
+    }
+  }
+  return {v, i};
+}
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, off));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+  return v;
+}
+
+// PER = ceil(E/32) rounded up to a compiled size.  Lane l owns experts l, l+32, ...
+template <int PER, typename TG, typename TB, bool BIASED>
+__global__ void __launch_bounds__(128) router_kernel(const TG* __restrict__ gating,
+                                                    const TB* __restrict__ bias, int64_t M, int E,
+                                                    int topk, int G, int topk_group, int renorm,
+                                                    float routed_scale, float* __restrict__ out_w,
+                                                    int32_t* __restrict__ out_id) {
+  const int lane = threadIdx.x & 31;
+  const int64_t tok = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (tok >= M) return;
+  const TG* row = gating + tok * E;
+  const float NEG = -INFINITY;
+
+  float s[PER];  // weight source: softmax prob or sigmoid
+  float c[PER];  // choice score
+#pragma unroll
+  for (int k = 0; k < PER; ++k) {
+    int e = lane + 32 * k;
+    s[k] = (e < E) ? load_as_float<TG>(row + e) : NEG;
+  }
+  if (!BIASED) {
+    float mx = NEG;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) mx = fmaxf(mx, s[k]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+      int e = lane + 32 * k;
+      s[k] = (e < E) ? expf(s[k] - mx) : 0.f;
+      sum += s[k];
+    }
+    sum = warp_sum(sum);
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+      s[k] = s[k] / sum;
+      c[k] = s[k];
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+      int e = lane + 32 * k;
+      if (e < E) {
+        s[k] = 1.0f / (1.0f + expf(-s[k]));
+        c[k] = s[k] + load_as_float<TB>(bias + e);
+      } else {
+        s[k] = 0.f;
+        c[k] = NEG;
+      }
+    }
+  }
+
+  // ---- group scores: lane g ends up holding the score of group g (G <= 32) ----
+  const int gs = E / G;
+  uint32_t group_mask = 0xffffffffu;
+  if (G > 1 && topk_group < G) {
+    float my_group_score = NEG;
+    for (int g = 0; g < G; ++g) {
+      float m1 = NEG, m2 = NEG;  // top-2 of the group (biased) / max (softmax)
+#pragma unroll
+      for (int k = 0; k < PER; ++k) {
+        int e = lane + 32 * k;
+        if (e < E && e / gs == g) {
+          float v = c[k];
+          if (v > m1) {
+            m2 = m1;
+            m1 = v;
+          } else if (v > m2) {
+            m2 = v;
+          }
+        }
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        float o1 = __shfl_xor_sync(0xffffffffu, m1, off);
+        float o2 = __shfl_xor_sync(0xffffffffu, m2, off);
+        float n1 = fmaxf(m1, o1);
+        float n2 = fmaxf(fminf(m1, o1), fmaxf(m2, o2));
+        m1 = n1;
+        m2 = n2;
+      }
+      float score = (BIASED && gs >= 2) ? (m1 + m2) : m1;
+      if (lane == g) my_group_score = score;
+    }
+    group_mask = 0u;
+    float v = (lane < G) ? my_group_score : NEG;
+    int idx = (lane < G) ? lane : 0x7fffffff;
+    for (int r = 0; r < topk_group; ++r) {
+      ValIdx b = warp_argmax(v, idx);
+      group_mask |= (1u << b.i);
+      if (lane == b.i) {
+        v = NEG;
+        idx = 0x7fffffff;  // taken: can no longer win a tie between -inf entries
+      }
+    }
+  }
+
+  // ---- mask: softmax variant fills 0.0 (test_grouped_topk.py:33), biased fills -inf (:41-43) ----
+  bool taken[PER];
+#pragma unroll
+  for (int k = 0; k < PER; ++k) {
+    int e = lane + 32 * k;
+    taken[k] = !(e < E);
+    if (e < E && !((group_mask >> (e / gs)) & 1u)) c[k] = BIASED ? NEG : 0.0f;
+  }
+
+  // ---- top-k by repeated warp argmax ----
+  float wsum = 0.f;
+  float my_w = 0.f;
+  int my_id = 0;
+  for (int r = 0; r < topk; ++r) {
+    float bv = NEG;
+    int bi = 0x7fffffff;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+      int e = lane + 32 * k;
+      if (!taken[k] && (bi == 0x7fffffff || better(c[k], e, bv, bi))) {
+        bv = c[k];
+        bi = e;
+      }
+    }
+    ValIdx b = warp_argmax(bv, bi);
+    // weight of the winner lives in its owner lane
+    float w = 0.f;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+      int e = lane + 32 * k;
+      if (e == b.i) {
+        taken[k] = true;
+        w = BIASED ? s[k] : c[k];
+      }
+    }
+    w = __shfl_sync(0xffffffffu, w, b.i & 31);
+    wsum += w;
+    if (lane == r) {
+      my_w = w;
+      my_id = b.i;
+    }
+  }
+  if (lane < topk) {
+    float w = my_w;
+    if (renorm) w = w / wsum;
+    w *= routed_scale;
+    out_w[tok * topk + lane] = w;
+    out_id[tok * topk + lane] = my_id;
+  }
+}
+
+template <typename TG, typename TB, bool BIASED>
+static int launch_router(const void* gating, const void* bias, int64_t M, int E, int topk, int G,
+                         int topk_group, int renorm, float routed_scale, float* out_w,
+                         int32_t* out_id, cudaStream_t stream) {
+  const int warps = 4;
+  dim3 grid((unsigned)ceil_div64(M, warps)), block(warps * 32);
+  const int per = ceil_div(E, 32);
+#define SGLB_ROUTER_CASE(P)                                                                      \
+  router_kernel<P, TG, TB, BIASED><<<grid, block, 0, stream>>>(                                  \
+      (const TG*)gating, (const TB*)bias, M, E, topk, G, topk_group, renorm, routed_scale, out_w, \
+      out_id)
+  if (per <= 1) SGLB_ROUTER_CASE(1);
+  else if (per <= 2) SGLB_ROUTER_CASE(2);
+  else if (per <= 4) SGLB_ROUTER_CASE(4);
+  else if (per <= 8) SGLB_ROUTER_CASE(8);
+  else if (per <= 16) SGLB_ROUTER_CASE(16);
+  else SGLB_ROUTER_CASE(32);
+#undef SGLB_ROUTER_CASE
+  SGLB_LAUNCH_CHECK();
+  return SGLB_OK;
+}
+
+template <typename TG, bool BIASED>
+static int dispatch_bias(int bias_dtype, const void* gating, const void* bias, int64_t M, int E,
+                         int topk, int G, int topk_group, int renorm, float routed_scale,
+                         float* out_w, int32_t* out_id, cudaStream_t stream) {
+  switch (bias_dtype) {
+    case SGLB_DT_BF16:
+      return launch_router<TG, __nv_bfloat16, BIASED>(gating, bias, M, E, topk, G, topk_group,
+                                                      renorm, routed_scale, out_w, out_id, stream);
+    case SGLB_DT_F32:
+      return launch_router<TG, float, BIASED>(gating, bias, M, E, topk, G, topk_group, renorm,
+                                              routed_scale, out_w, out_id, stream);
+    case SGLB_DT_F16:
+      return launch_router<TG, __half, BIASED>(gating, bias, M, E, topk, G, topk_group, renorm,
+                                               routed_scale, out_w, out_id, stream);
+  }
+  set_error("router: unsupported bias dtype %d", bias_dtype);
+  return SGLB_ERR_INVALID;
+}
+
+}  // namespace sglb
+
+using namespace sglb;
+
+extern "C" int sglb_grouped_topk(const void* gating, int gating_dtype, const void* bias,
+                                 int bias_dtype, int64_t M, int E, int topk, int num_expert_group,
+                                 int topk_group, int renormalize, float routed_scaling_factor,
+                                 float* topk_weights, int32_t* topk_ids, sglb_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  SGLB_CHECK(M >= 0 && E > 0, "router: bad shape M=%lld E=%d", (long long)M, E);
+  SGLB_CHECK(E <= 32 * kMaxPerLane, "router: E=%d exceeds %d", E, 32 * kMaxPerLane);
+  SGLB_CHECK(topk >= 1 && topk <= 32 && topk <= E, "router: topk=%d must be in [1, min(32,E)]", topk);
+  if (num_expert_group <= 0) num_expert_group = 1;
+  if (topk_group <= 0) topk_group = num_expert_group;
+  SGLB_CHECK(num_expert_group <= 32 && E % num_expert_group == 0,
+             "router: num_expert_group=%d must divide E=%d and be <= 32", num_expert_group, E);
+  SGLB_CHECK(topk_group <= num_expert_group, "router: topk_group=%d > num_expert_group=%d",
+             topk_group, num_expert_group);
+  SGLB_CHECK(gating && topk_weights && topk_ids, "router: null pointer");
+  if (M == 0) return SGLB_OK;
+  const bool biased = bias != nullptr;
+#define SGLB_R(TG)                                                                                 \
+  (biased ? dispatch_bias<TG, true>(bias_dtype, gating, bias, M, E, topk, num_expert_group,        \
+                                    topk_group, renormalize, routed_scaling_factor, topk_weights,  \
+                                    topk_ids, stream)                                              \
+          : launch_router<TG, float, false>(gating, nullptr, M, E, topk, num_expert_group,         \
+                                            topk_group, renormalize, routed_scaling_factor,        \
+                                            topk_weights, topk_ids, stream))
+  switch (gating_dtype) {
+    case SGLB_DT_BF16: return SGLB_R(__nv_bfloat16);
+    case SGLB_DT_F32: return SGLB_R(float);
+    case SGLB_DT_F16: return SGLB_R(__half);
+  }
+#undef SGLB_R
+  set_error("router: unsupported gating dtype %d", gating_dtype);
+  return SGLB_ERR_INVALID;
+}

@@ -1,0 +1,72 @@
+"""Drop-in `sgl_kernel`: importing it makes torch.ops.sgl_kernel.<op> resolve to the sm_100a
+implementation, exactly as `import sgl_kernel` does for the reference scripts (test_moe.py:5-8).
+
+Ops are registered with the PyTorch dispatcher under namespace `sgl_kernel`; fused_experts_cpu and
+shared_expert_cpu carry one overload per signature vintage found in the reference,
+selected by arity.  The implementation key is CompositeExplicitAutograd so the same op accepts the
+CPU tensors the reference scripts build and CUDA tensors.
+"""
+import os
+import sys
+
+import torch
+
+_root = os.path.abspath(os.path.join(os.path.dirname(__file__), "..", "..", ".."))
+if _root not in sys.path:
+    sys.path.insert(0, _root)
+
+from sgl_cpu_tests_b200 import ops as _ops  # noqa: E402
+
+_ops.L.load()  # fail loudly at import if libsglb200.so is missing
+
+_lib = torch.library.Library("sgl_kernel", "DEF")
+_KEY = "CompositeExplicitAutograd"
+
+
+def _def(schema, fn):
+    name = schema.split("(")[0]
+    _lib.define(schema)
+    _lib.impl(name, fn, _KEY)
+
+
+_T, _TO = "Tensor", "Tensor?"
+_def("convert_weight_packed(Tensor weight) -> Tensor", _ops.convert_weight_packed)
+_def("convert_scale_packed(Tensor scale) -> Tensor", _ops.convert_scale_packed)
+_def("grouped_topk_cpu(Tensor hidden_states, Tensor gating_output, int topk, bool renormalize, "
+     "int num_expert_group, int topk_group, int num_fused_shared_experts, float? routed_scaling_factor, "
+     "Tensor? num_token_non_padded) -> (Tensor, Tensor)", _ops.grouped_topk)
+_def("biased_grouped_topk_cpu(Tensor hidden_states, Tensor gating_output, Tensor correction_bias, int topk, "
+     "bool renormalize, int num_expert_group, int topk_group, int num_fused_shared_experts, "
+     "float? routed_scaling_factor, Tensor? num_token_non_padded) -> (Tensor, Tensor)",
+     _ops.biased_grouped_topk)
+
+# fused_experts_cpu: 14-arg (default overload), 13-arg and 17-arg vintages
+_def("fused_experts_cpu(Tensor hidden_states, Tensor w1, Tensor w2, Tensor topk_weights, Tensor topk_ids, "
+     "bool inplace, bool use_int8_w8a8, bool use_fp8_w8a16, Tensor? w1_scale, Tensor? w2_scale, "
+     "int[]? block_size, Tensor? a1_scale, Tensor? a2_scale, bool is_vnni) -> Tensor",
+     lambda *a: _ops.fused_experts(*a))
+_def("fused_experts_cpu.quant_method(Tensor hidden_states, Tensor w1, Tensor w2, Tensor topk_weights, "
+     "Tensor topk_ids, bool inplace, int quant_method, Tensor? w1_scale, Tensor? w2_scale, Tensor? w1_zero, "
+     "Tensor? w2_zero, int[]? block_size, bool is_vnni) -> Tensor",
+     lambda *a: _ops.fused_experts(*a))
+_def("fused_experts_cpu.bias(Tensor hidden_states, Tensor w1, Tensor w2, Tensor topk_weights, "
+     "Tensor topk_ids, bool inplace, int quant_method, Tensor? w1_scale, Tensor? w2_scale, Tensor? w1_zero, "
+     "Tensor? w2_zero, int[]? block_size, Tensor? w1_bias, Tensor? w2_bias, float? alpha, float? limit, "
+     "bool is_vnni) -> Tensor",
+     lambda *a: _ops.fused_experts(*a))
+
+_def("shared_expert_cpu(Tensor hidden_states, Tensor w1, Tensor w2, Tensor fused_experts_out, "
+     "float routed_scaling_factor, bool inplace, bool use_int8_w8a8, bool use_fp8_w8a16, Tensor? w1_scale, "
+     "Tensor? w2_scale, int[]? block_size, Tensor? a1_scale, Tensor? a2_scale, bool is_vnni) -> Tensor",
+     lambda *a: _ops.shared_expert(*a))
+_def("shared_expert_cpu.v12(Tensor hidden_states, Tensor w1, Tensor w2, Tensor fused_experts_out, "
+     "float routed_scaling_factor, bool inplace, bool use_int8_w8a8, bool use_fp8_w8a16, Tensor? w1_scale, "
+     "Tensor? w2_scale, int[]? block_size, bool is_vnni) -> Tensor",
+     lambda *a: _ops.shared_expert(*a))
+
+_def("mxfp4_scaled_mm_cpu(Tensor mat1, Tensor mat2, Tensor scales2, Tensor? bias, bool is_vnni) -> Tensor",
+     _ops.mxfp4_scaled_mm)
+
+from . import common_ops  # noqa: E402,F401
+
+__all__ = ["common_ops"]

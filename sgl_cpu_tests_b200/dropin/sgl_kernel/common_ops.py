@@ -1,0 +1,24 @@
+"""`sgl_kernel.common_ops`: the older import style of the reference scripts
+(test_grouped_topk.py:2, test_biased_grouped_topk.py:2, test_moe_fp8.py:4-5).  Routers are the
+out-variants those scripts call; a functional call (9 / 10 positional args) is accepted too."""
+import torch
+
+from sgl_cpu_tests_b200 import ops as _ops
+
+convert_weight_packed = _ops.convert_weight_packed
+convert_scale_packed = _ops.convert_scale_packed
+fused_experts_cpu = _ops.fused_experts
+shared_expert_cpu = _ops.shared_expert
+mxfp4_scaled_mm_cpu = _ops.mxfp4_scaled_mm
+
+
+def grouped_topk_cpu(*args):
+    if len(args) == 8:
+        return _ops.grouped_topk_out(*args)
+    return _ops.grouped_topk(*args)
+
+
+def biased_grouped_topk_cpu(*args):
+    if len(args) == 9 and args[0].dtype == torch.float32 and args[1].dtype == torch.int32:
+        return _ops.biased_grouped_topk_out(*args)
+    return _ops.biased_grouped_topk(*args)

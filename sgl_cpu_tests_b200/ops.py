@@ -1,0 +1,556 @@
+"""Host-side mirror of the reference operator interface for the fused-MoE path.
+
+Same op names, positional argument lists and error behaviour as the ops the reference scripts
+resolve through ``torch.ops.sgl_kernel`` / ``sgl_kernel.common_ops``; every
+function here ends in a call into libsglb200.so.  PyTorch is used for memory, streams and dtype
+bookkeeping only -- there is no torch compute on this path and no CPU fallback.
+
+Tensors may live on the CPU (what the reference scripts allocate) or on a CUDA device:
+  * CUDA tensors are used in place.
+  * CPU activations / routing tensors are staged to the current CUDA device for the call and the
+    result is copied back (into ``hidden_states`` itself when ``inplace=True``).
+  * CPU weights are uploaded once and kept resident in HBM in a registry keyed on the host
+    buffer (pointer, shape, dtype, version, sampled fingerprint), so later calls move no weights.
+"""
+import math
+import os
+import weakref
+from enum import IntEnum
+
+import torch
+
+from . import _lib as L
+
+
+class CPUQuantMethod(IntEnum):  # test_moe.py:4,86 (sglang.srt.layers.amx_utils.CPUQuantMethod)
+    UNQUANT = 0
+    INT8_W8A8 = 1
+    FP8_W8A16 = 2
+    INT4_W4A8 = 3
+    MXFP4 = 4
+
+
+_FP8 = torch.float8_e4m3fn
+_DT = {torch.bfloat16: L.DT_BF16, torch.float32: L.DT_F32, torch.float16: L.DT_F16}
+
+
+def _device():
+    if not torch.cuda.is_available():
+        raise RuntimeError("sgl_cpu_tests_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _to_dev(t, dev, dtype=None):
+    if t is None:
+        return None
+    if t.device != dev:
+        t = t.to(dev, non_blocking=False)
+    if dtype is not None and t.dtype != dtype:
+        t = t.to(dtype)
+    return t.contiguous()
+
+
+# ---- workspace: one growing buffer per (device, stream) ---------------------------------------------
+_workspaces = {}
+
+
+def _workspace(nbytes, dev):
+    key = (dev.index, _stream())
+    buf = _workspaces.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=dev)
+        _workspaces[key] = buf
+    return buf
+
+
+# ---- weight registry ------------------------------------------------------------------------------------
+_WEIGHT_CACHE_BYTES = int(float(os.environ.get("SGLB_WEIGHT_CACHE_GB", "140")) * (1 << 30))
+_registry = {}
+_registry_bytes = 0
+
+
+def _fingerprint(t):
+    """A few sampled 8-byte words of a CPU tensor: guards against pointer reuse after free."""
+    if t.is_cuda:
+        return 0
+    b = t.reshape(-1).view(torch.uint8)
+    n = b.numel()
+    if n <= 256:
+        return hash(bytes(b.numpy().tobytes()))
+    idx = [0, n // 7, n // 3, n // 2, (2 * n) // 3, n - 64]
+    return hash(b"".join(bytes(b[i:i + 64].numpy().tobytes()) for i in idx))
+
+
+def _registry_key(t, is_vnni, kind):
+    return (t.device.type, t.device.index, t.data_ptr(), tuple(t.shape), t.dtype, bool(is_vnni), kind,
+            t._version)
+
+
+def _registry_put(key, fp, dev_tensor):
+    global _registry_bytes
+    nbytes = dev_tensor.numel() * dev_tensor.element_size()
+    while _registry and _registry_bytes + nbytes > _WEIGHT_CACHE_BYTES:
+        oldest = next(iter(_registry))  # dicts keep insertion order: evict the oldest entry
+        _, old = _registry.pop(oldest)
+        _registry_bytes -= old.numel() * old.element_size()
+    _registry[key] = (fp, dev_tensor)
+    _registry_bytes += nbytes
+
+
+def clear_weight_cache():
+    global _registry_bytes
+    _registry.clear()
+    _registry_bytes = 0
+
+
+def _rows_k(w, is_int8_packed):
+    """[..., N, K] geometry; an int8 packed tensor carries 4 compensation bytes per row."""
+    N, K = w.shape[-2], w.shape[-1]
+    if is_int8_packed:
+        K -= 4
+    E = 1
+    for d in w.shape[:-2]:
+        E *= d
+    return E, N, K
+
+
+def _repack(src, dst, elem_bytes, vnni, E, N, K, comp, to_packed):
+    L.check(L.load().sglb_repack_weight(src.data_ptr(), dst.data_ptr(), elem_bytes, vnni, E, N, K,
+                                        int(comp), int(to_packed), _stream()))
+
+
+def _layout_of(dtype):
+    """(elem_bytes, vnni, has_compensation) of convert_weight_packed for a weight dtype."""
+    if dtype in (torch.bfloat16, torch.float16):
+        return 2, 2, False
+    if dtype == torch.int8:
+        return 1, 4, True
+    if dtype in (_FP8, torch.uint8):
+        return 1, 4, False
+    raise RuntimeError(f"convert_weight_packed: unsupported weight dtype {dtype}")
+
+
+def _resident_weight(w, is_vnni, dev):
+    """Row-major, device-resident view of a weight the caller passed (CPU or CUDA, packed or not)."""
+    if w.is_cuda and not is_vnni:
+        return w if w.is_contiguous() else w.contiguous()
+    key = _registry_key(w, is_vnni, "w")
+    hit = _registry.get(key)
+    fp = _fingerprint(w)
+    if hit is not None and hit[0] == fp:
+        return hit[1]
+    wd = _to_dev(w, dev)
+    if is_vnni:
+        eb, vnni, comp = _layout_of(w.dtype)
+        E, N, K = _rows_k(w, comp)
+        out_shape = list(w.shape)
+        out_shape[-1] = K
+        rm = torch.empty(out_shape, dtype=w.dtype, device=dev)
+        _repack(wd, rm, eb, vnni, E, N, K, comp, False)
+        wd = rm
+    _registry_put(key, fp, wd)
+    return wd
+
+
+def _resident_aux(t, dev, dtype, kind="s"):
+    """Scales / bias: tiny next to the weights but cached the same way when they come from the CPU."""
+    if t is None:
+        return None
+    if t.is_cuda:
+        return _to_dev(t, dev, dtype)
+    key = _registry_key(t, False, kind)
+    hit = _registry.get(key)
+    fp = _fingerprint(t)
+    if hit is not None and hit[0] == fp:
+        return hit[1]
+    td = _to_dev(t, dev, dtype)
+    _registry_put(key, fp, td)
+    return td
+
+
+# ---- K7: convert_weight_packed / convert_scale_packed --------------------------------------------------
+def convert_weight_packed(weight):
+    """convert_weight_packed(Tensor) -> Tensor   (test_moe.py:75-76, test_mxfp4.py:159).
+
+    Returns the reference's VNNI tile layout (bit-identical where the reference pins it: bf16
+    test_gemm.py:38-44 / test_moe.py:117-124, int8 + compensation test_gemm_int8.py:84-93) on the
+    device of the input, and registers the row-major HBM-resident twin the sm_100a kernels read,
+    so a later fused_experts(..., is_vnni=True) on the returned tensor moves no weight bytes.
+    """
+    if weight.dim() not in (2, 3):
+        raise RuntimeError(f"convert_weight_packed: expect a 2-D or 3-D weight, got {weight.dim()}-D")
+    dev = _device() if not weight.is_cuda else weight.device
+    eb, vnni, comp = _layout_of(weight.dtype)
+    E, N, K = _rows_k(weight, False)
+    if N % 32 != 0:
+        raise RuntimeError(f"convert_weight_packed: N={N} must be a multiple of 32")
+    if K % vnni != 0:
+        raise RuntimeError(f"convert_weight_packed: K={K} must be a multiple of {vnni}")
+    with torch.cuda.device(dev):
+        wd = _to_dev(weight, dev)
+        out_shape = list(weight.shape)
+        if comp:
+            out_shape[-1] = K + 4
+        packed = torch.empty(out_shape, dtype=weight.dtype, device=dev)
+        _repack(wd, packed, eb, vnni, E, N, K, comp, True)
+        result = packed if weight.is_cuda else packed.cpu()
+        _registry_put(_registry_key(result, True, "w"), _fingerprint(result), wd)
+    return result
+
+
+def convert_scale_packed(scale):
+    """convert_scale_packed(Tensor) -> Tensor   (test_mxfp4.py:160,182-185): e8m0 scales
+    [.., N, K/32] u8 -> [.., N/32, K/32, 32] (flat order), same shape and device as the input."""
+    if scale.dtype != torch.uint8 or scale.dim() not in (2, 3):
+        raise RuntimeError("convert_scale_packed: expect a 2-D or 3-D uint8 (e8m0) tensor")
+    dev = _device() if not scale.is_cuda else scale.device
+    E, N, G = _rows_k(scale, False)
+    if N % 32 != 0:
+        raise RuntimeError(f"convert_scale_packed: N={N} must be a multiple of 32")
+    with torch.cuda.device(dev):
+        sd = _to_dev(scale, dev)
+        packed = torch.empty_like(sd)
+        L.check(L.load().sglb_repack_scale(sd.data_ptr(), packed.data_ptr(), E, N, G, 1, _stream()))
+        result = packed if scale.is_cuda else packed.cpu()
+        _registry_put(_registry_key(result, True, "ms"), _fingerprint(result), sd)
+    return result
+
+
+def _resident_mx_scale(s, is_vnni, dev):
+    """Row-major device copy of an e8m0 scale tensor (packed by convert_scale_packed or not)."""
+    if s.is_cuda and not is_vnni:
+        return s.contiguous()
+    key = _registry_key(s, is_vnni, "ms")
+    hit = _registry.get(key)
+    fp = _fingerprint(s)
+    if hit is not None and hit[0] == fp:
+        return hit[1]
+    sd = _to_dev(s, dev)
+    if is_vnni:
+        E, N, G = _rows_k(s, False)
+        rm = torch.empty_like(sd)
+        L.check(L.load().sglb_repack_scale(sd.data_ptr(), rm.data_ptr(), E, N, G, 0, _stream()))
+        sd = rm
+    _registry_put(key, fp, sd)
+    return sd
+
+
+# ---- K1: routers -----------------------------------------------------------------------------------------
+def _router(gating_output, correction_bias, topk, renormalize, num_expert_group, topk_group,
+            routed_scaling_factor, out_w=None, out_ids=None):
+    if gating_output.dim() != 2:
+        raise RuntimeError("grouped_topk: gating_output must be [num_tokens, num_experts]")
+    if gating_output.dtype not in _DT:
+        raise RuntimeError(f"grouped_topk: unsupported gating dtype {gating_output.dtype}")
+    M, E = gating_output.shape
+    dev = gating_output.device if gating_output.is_cuda else _device()
+    with torch.cuda.device(dev):
+        g = _to_dev(gating_output, dev)
+        b = _to_dev(correction_bias, dev) if correction_bias is not None else None
+        if b is not None and (b.dim() != 1 or b.numel() != E or b.dtype not in _DT):
+            raise RuntimeError("biased_grouped_topk: correction_bias must be [num_experts] bf16/f16/f32")
+        w = torch.empty(M, topk, dtype=torch.float32, device=dev)
+        ids = torch.empty(M, topk, dtype=torch.int32, device=dev)
+        L.check(L.load().sglb_grouped_topk(
+            g.data_ptr(), _DT[g.dtype], _ptr(b), _DT[b.dtype] if b is not None else 0, M, E, int(topk),
+            int(num_expert_group), int(topk_group), int(bool(renormalize)),
+            float(1.0 if routed_scaling_factor is None else routed_scaling_factor),
+            w.data_ptr(), ids.data_ptr(), _stream()))
+    if out_w is not None:
+        out_w.copy_(w)
+        out_ids.copy_(ids)
+        return None
+    if not gating_output.is_cuda:
+        return w.cpu(), ids.cpu()
+    return w, ids
+
+
+def _check_tokens(hidden_states, gating_output):
+    if hidden_states.shape[0] != gating_output.shape[0]:
+        raise RuntimeError("Number of tokens mismatch")  # test_grouped_topk.py:18
+
+
+def grouped_topk(hidden_states, gating_output, topk, renormalize, num_expert_group, topk_group,
+                 num_fused_shared_experts=0, routed_scaling_factor=None, num_token_non_padded=None):
+    """grouped_topk_cpu, 9-arg functional form (test_moe.py:61-70) -> (topk_weights f32, topk_ids i32)."""
+    _check_tokens(hidden_states, gating_output)
+    if num_fused_shared_experts not in (0, None):
+        raise RuntimeError("grouped_topk: num_fused_shared_experts != 0 is not supported")
+    if num_token_non_padded is not None:
+        raise RuntimeError("grouped_topk: num_token_non_padded is not supported")
+    return _router(gating_output, None, topk, renormalize, num_expert_group, topk_group,
+                   routed_scaling_factor)
+
+
+def grouped_topk_out(topk_weights, topk_ids, hidden_states, gating_output, topk, renormalize,
+                     num_expert_group, topk_group):
+    """grouped_topk_cpu, 8-arg out-variant (test_grouped_topk.py:57-69) -> None."""
+    _check_tokens(hidden_states, gating_output)
+    return _router(gating_output, None, topk, renormalize, num_expert_group, topk_group, None,
+                   topk_weights, topk_ids)
+
+
+def biased_grouped_topk(hidden_states, gating_output, correction_bias, topk, renormalize,
+                        num_expert_group, topk_group, num_fused_shared_experts=0,
+                        routed_scaling_factor=None, num_token_non_padded=None):
+    """biased_grouped_topk_cpu, functional form (by analogy with grouped_topk_cpu)."""
+    _check_tokens(hidden_states, gating_output)
+    if num_fused_shared_experts not in (0, None) or num_token_non_padded is not None:
+        raise RuntimeError("biased_grouped_topk: fused shared experts / token padding are not supported")
+    return _router(gating_output, correction_bias, topk, renormalize, num_expert_group, topk_group,
+                   routed_scaling_factor)
+
+
+def biased_grouped_topk_out(topk_weights, topk_ids, hidden_states, gating_output, correction_bias, topk,
+                            renormalize, num_expert_group, topk_group):
+    """biased_grouped_topk_cpu, 9-arg out-variant (test_biased_grouped_topk.py:67-80) -> None."""
+    _check_tokens(hidden_states, gating_output)
+    return _router(gating_output, correction_bias, topk, renormalize, num_expert_group, topk_group, None,
+                   topk_weights, topk_ids)
+
+
+# ---- K2: moe_align (exposed for tests and the expert-parallel layer) -------------------------------------
+def moe_align(topk_ids, num_experts, chunk_rows=8, tile_rows=128):
+    """Returns a dict of int32 CUDA tensors; layout documented in csrc/align.cu."""
+    dev = topk_ids.device if topk_ids.is_cuda else _device()
+    with torch.cuda.device(dev):
+        ids = _to_dev(topk_ids, dev, torch.int32)
+        M, topk = ids.shape
+        S = M * topk
+        lib = L.load()
+        i32 = dict(dtype=torch.int32, device=dev)
+        out = {
+            "expert_count": torch.empty(num_experts, **i32),
+            "expert_offset": torch.empty(num_experts + 1, **i32),
+            "sorted_slot": torch.empty(max(S, 1), **i32),
+            "slot_pos": torch.empty(max(S, 1), **i32),
+            "chunk_list": torch.zeros(3 * max(1, lib.sglb_moe_align_max_items(M, topk, num_experts, chunk_rows)), **i32),
+            "tile_list": torch.zeros(3 * max(1, lib.sglb_moe_align_max_items(M, topk, num_experts, tile_rows)), **i32),
+            "counters": torch.zeros(4, **i32),
+        }
+        scratch = torch.empty(max(1, lib.sglb_moe_align_scratch_bytes(M, topk, num_experts)), dtype=torch.uint8, device=dev)
+        ao = L.AlignOut(**{k: v.data_ptr() for k, v in out.items()})
+        L.check(lib.sglb_moe_align(ids.data_ptr(), M, topk, num_experts, chunk_rows, tile_rows, ao,
+                                   scratch.data_ptr(), _stream()))
+        out["sorted_slot"] = out["sorted_slot"][:S]
+        out["slot_pos"] = out["slot_pos"][:S]
+    return out
+
+
+# ---- K3-K5: fused_experts ---------------------------------------------------------------------------------
+def _weight_geometry(w1, w2, fmt, is_vnni):
+    if w1.dim() != 3 or w2.dim() != 3:
+        raise RuntimeError("fused_experts: w1 and w2 must be 3-D [E, N, K]")
+    int8_packed = is_vnni and fmt == L.FMT_INT8_W8A8
+    E, N2, K1 = _rows_k(w1, int8_packed)
+    E2, H, K2 = _rows_k(w2, int8_packed)
+    if fmt == L.FMT_MXFP4:
+        K1, K2 = 2 * K1, 2 * K2
+    if E != E2 or N2 % 2 != 0 or K1 != H or K2 * 2 != N2:
+        raise RuntimeError(f"fused_experts: inconsistent weight shapes w1={tuple(w1.shape)} w2={tuple(w2.shape)}")
+    return E, H, N2 // 2
+
+
+_WDT = {L.FMT_BF16: (torch.bfloat16,), L.FMT_INT8_W8A8: (torch.int8,), L.FMT_FP8_W8A16: (_FP8,),
+        L.FMT_MXFP4: (torch.uint8,)}
+
+
+def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, fmt, w1_scale, w2_scale,
+                       block_size, is_vnni, path=L.PATH_AUTO):
+    """Format-explicit core behind every fused_experts_cpu signature vintage."""
+    if hidden_states.dim() != 2 or hidden_states.dtype != torch.bfloat16:
+        raise RuntimeError("fused_experts: hidden_states must be a 2-D bfloat16 tensor")
+    if w1.dtype not in _WDT[fmt] or w2.dtype != w1.dtype:
+        raise RuntimeError(f"fused_experts: weight dtype {w1.dtype} does not match the quantization method")
+    M, H = hidden_states.shape
+    E, Hw, I = _weight_geometry(w1, w2, fmt, is_vnni)
+    if Hw != H:
+        raise RuntimeError(f"fused_experts: hidden size {H} does not match weights ({Hw})")
+    if topk_weights.shape != topk_ids.shape or topk_ids.dim() != 2 or topk_ids.shape[0] != M:
+        raise RuntimeError("fused_experts: topk_weights / topk_ids must both be [num_tokens, topk]")
+    topk = topk_ids.shape[1]
+    bn = bk = 0
+    if fmt == L.FMT_FP8_W8A16:
+        if block_size is None or len(block_size) != 2:
+            raise RuntimeError("fused_experts: fp8 w8a16 needs block_size = [block_n, block_k]")
+        bn, bk = int(block_size[0]), int(block_size[1])
+    if fmt != L.FMT_BF16 and (w1_scale is None or w2_scale is None):
+        raise RuntimeError("fused_experts: quantized weights need w1_scale and w2_scale")
+
+    on_cuda = hidden_states.is_cuda
+    dev = hidden_states.device if on_cuda else _device()
+    lib = L.load()
+    with torch.cuda.device(dev):
+        x = _to_dev(hidden_states, dev)
+        tw = _to_dev(topk_weights, dev, torch.float32)
+        ids = _to_dev(topk_ids, dev, torch.int32)
+        w13 = _resident_weight(w1, is_vnni, dev)
+        w2d = _resident_weight(w2, is_vnni, dev)
+        s13 = s2 = None
+        if fmt == L.FMT_MXFP4:
+            s13 = _resident_mx_scale(w1_scale, is_vnni, dev)
+            s2 = _resident_mx_scale(w2_scale, is_vnni, dev)
+        elif fmt != L.FMT_BF16:
+            s13 = _resident_aux(w1_scale, dev, torch.float32)
+            s2 = _resident_aux(w2_scale, dev, torch.float32)
+        if on_cuda and inplace and x.data_ptr() == hidden_states.data_ptr():
+            out = x
+        else:
+            out = torch.empty_like(x)
+        nws = lib.sglb_fused_experts_workspace_bytes(M, topk, E, H, I, fmt)
+        ws = _workspace(nws, dev)
+        p = L.MoeProblem(M=M, topk=topk, E=E, H=H, I=I, fmt=fmt, path=path, hidden=x.data_ptr(),
+                         w13=w13.data_ptr(), w2=w2d.data_ptr(), topk_weights=tw.data_ptr(),
+                         topk_ids=ids.data_ptr(), w13_scale=_ptr(s13), w2_scale=_ptr(s2), block_n=bn,
+                         block_k=bk, out=out.data_ptr(), workspace=ws.data_ptr(),
+                         workspace_bytes=ws.numel())
+        L.check(lib.sglb_fused_experts(p, _stream()))
+        if on_cuda:
+            if inplace and out is not hidden_states:
+                hidden_states.copy_(out)
+                return hidden_states
+            return out
+        if inplace:
+            hidden_states.copy_(out)  # D2H into the caller's buffer ("fused moe mutates content in hs")
+            return hidden_states
+        return out.cpu()
+
+
+def fused_experts(*args):
+    """fused_experts_cpu with the reference's three positional signature vintages:
+      14 args (bench_moe.py:65-82, test_moe_int8.py:129, test_moe_fp8_ext.py:118):
+         hs, w1, w2, topk_w, topk_ids, inplace, use_int8_w8a8, use_fp8_w8a16, w1_scale, w2_scale,
+         block_size, a1_scale, a2_scale, is_vnni
+      13 args (test_moe.py:79-92):
+         hs, w1, w2, topk_w, topk_ids, inplace, quant_method, w1_scale, w2_scale, w1_zero, w2_zero,
+         block_size, is_vnni
+      17 args (vllm cpu_moe.py:308-326): the 13-arg list + w1_bias, w2_bias, alpha, limit before is_vnni
+    """
+    n = len(args)
+    if n == 14:
+        hs, w1, w2, tw, ids, inplace, use_int8, use_fp8, s1, s2, block, a1s, a2s, is_vnni = args
+        if use_int8 and use_fp8:
+            raise RuntimeError("fused_experts: use_int8_w8a8 and use_fp8_w8a16 are mutually exclusive")
+        if a1s is not None or a2s is not None:
+            raise RuntimeError("fused_experts: static activation scales (a1_scale/a2_scale) are not supported")
+        fmt = L.FMT_INT8_W8A8 if use_int8 else (L.FMT_FP8_W8A16 if use_fp8 else L.FMT_BF16)
+    elif n in (13, 17):
+        hs, w1, w2, tw, ids, inplace, method, s1, s2, z1, z2, block = args[:12]
+        is_vnni = args[-1]
+        fmt = int(method)
+        if fmt == int(CPUQuantMethod.INT4_W4A8) or z1 is not None or z2 is not None:
+            raise RuntimeError("fused_experts: int4 w4a8 (zero points) is not supported")
+        if fmt not in (L.FMT_BF16, L.FMT_INT8_W8A8, L.FMT_FP8_W8A16, L.FMT_MXFP4):
+            raise RuntimeError(f"fused_experts: unknown quant method {fmt}")
+        if n == 17:
+            b1, b2, alpha, limit = args[12:16]
+            if b1 is not None or b2 is not None or alpha is not None or limit is not None:
+                raise RuntimeError("fused_experts: expert bias / clamped swiglu (alpha, limit) are not supported yet")
+    else:
+        raise RuntimeError(f"fused_experts_cpu: expected 13, 14 or 17 positional arguments, got {n}")
+    return fused_experts_impl(hs, w1, w2, tw, ids, bool(inplace), fmt, s1, s2, block, bool(is_vnni))
+
+
+# ---- K6: shared_expert -------------------------------------------------------------------------------------
+def shared_expert(*args):
+    """shared_expert_cpu: 14 args (test_moe_fp8_ext.py:60-61, test_moe_fp8.py:87-88)
+         hs, w1, w2, fused_experts_out, routed_scaling_factor, inplace, use_int8_w8a8, use_fp8_w8a16,
+         w1_scale, w2_scale, block_size, a1_scale, a2_scale, is_vnni
+       or 12 args (test_shared_experts.py:68,78): ... w1_scale, w2_scale, block_size, is_vnni."""
+    n = len(args)
+    if n == 14:
+        hs, w1, w2, fused_out, rsf, inplace, use_int8, use_fp8, s1, s2, block, a1s, a2s, is_vnni = args
+        if a1s is not None or a2s is not None:
+            raise RuntimeError("shared_expert: static activation scales are not supported")
+    elif n == 12:
+        hs, w1, w2, fused_out, rsf, inplace, use_int8, use_fp8, s1, s2, block, is_vnni = args
+    else:
+        raise RuntimeError(f"shared_expert_cpu: expected 12 or 14 positional arguments, got {n}")
+    if use_int8 and use_fp8:
+        raise RuntimeError("shared_expert: use_int8_w8a8 and use_fp8_w8a16 are mutually exclusive")
+    fmt = L.FMT_INT8_W8A8 if use_int8 else (L.FMT_FP8_W8A16 if use_fp8 else L.FMT_BF16)
+    if hs.dim() != 2 or hs.dtype != torch.bfloat16:
+        raise RuntimeError("shared_expert: hidden_states must be a 2-D bfloat16 tensor")
+    if w1.dim() != 2 or w2.dim() != 2 or w1.dtype not in _WDT[fmt] or w2.dtype != w1.dtype:
+        raise RuntimeError("shared_expert: w1/w2 must be 2-D and match the quantization method")
+    if fused_out.shape != hs.shape or fused_out.dtype != torch.bfloat16:
+        raise RuntimeError("shared_expert: fused_experts_out must match hidden_states")
+    M, H = hs.shape
+    packed8 = bool(is_vnni) and fmt == L.FMT_INT8_W8A8
+    _, N2, K1 = _rows_k(w1, packed8)
+    _, Hw, I = _rows_k(w2, packed8)
+    if K1 != H or Hw != H or N2 != 2 * I:
+        raise RuntimeError(f"shared_expert: inconsistent shapes hs={tuple(hs.shape)} w1={tuple(w1.shape)} w2={tuple(w2.shape)}")
+    bn = bk = 0
+    if fmt == L.FMT_FP8_W8A16:
+        if block is None or len(block) != 2:
+            raise RuntimeError("shared_expert: fp8 w8a16 needs block_size = [block_n, block_k]")
+        bn, bk = int(block[0]), int(block[1])
+    if fmt != L.FMT_BF16 and (s1 is None or s2 is None):
+        raise RuntimeError("shared_expert: quantized weights need w1_scale and w2_scale")
+    on_cuda = hs.is_cuda
+    dev = hs.device if on_cuda else _device()
+    lib = L.load()
+    with torch.cuda.device(dev):
+        x = _to_dev(hs, dev)
+        fo = _to_dev(fused_out, dev)
+        w1d = _resident_weight(w1, bool(is_vnni), dev)
+        w2d = _resident_weight(w2, bool(is_vnni), dev)
+        s1d = _resident_aux(s1, dev, torch.float32)
+        s2d = _resident_aux(s2, dev, torch.float32)
+        out = x if (on_cuda and inplace and x.data_ptr() == hs.data_ptr()) else torch.empty_like(x)
+        nws = lib.sglb_fused_experts_workspace_bytes(M, 1, 1, H, I, fmt)
+        ws = _workspace(nws, dev)
+        p = L.SharedProblem(M=M, H=H, I=I, fmt=fmt, path=L.PATH_AUTO, hidden=x.data_ptr(), w1=w1d.data_ptr(),
+                            w2=w2d.data_ptr(), w1_scale=_ptr(s1d), w2_scale=_ptr(s2d), block_n=bn, block_k=bk,
+                            fused_out=fo.data_ptr(), routed_scaling_factor=float(rsf), out=out.data_ptr(),
+                            workspace=ws.data_ptr(), workspace_bytes=ws.numel())
+        L.check(lib.sglb_shared_expert(p, _stream()))
+        if on_cuda:
+            if inplace and out is not hs:
+                hs.copy_(out)
+                return hs
+            return out
+        if inplace:
+            hs.copy_(out)
+            return hs
+        return out.cpu()
+
+
+# ---- K9: mxfp4 linear --------------------------------------------------------------------------------------
+def mxfp4_scaled_mm(mat1, mat2, scales2, bias, is_vnni):
+    """mxfp4_scaled_mm_cpu(A, B_packed, Bs_packed, bias?, is_vnni) -> Tensor (test_mxfp4.py:167,196)."""
+    if mat1.dim() != 2 or mat1.dtype != torch.bfloat16:
+        raise RuntimeError("mxfp4_scaled_mm: mat1 must be a 2-D bfloat16 tensor")
+    if mat2.dim() != 2 or mat2.dtype != torch.uint8 or scales2.dtype != torch.uint8:
+        raise RuntimeError("mxfp4_scaled_mm: mat2 / scales2 must be 2-D uint8 tensors")
+    M, K = mat1.shape
+    N = mat2.shape[0]
+    if mat2.shape[1] * 2 != K or tuple(scales2.shape) != (N, K // 32) or K % 32 != 0:
+        raise RuntimeError(f"mxfp4_scaled_mm: inconsistent shapes A={tuple(mat1.shape)} B={tuple(mat2.shape)} Bs={tuple(scales2.shape)}")
+    on_cuda = mat1.is_cuda
+    dev = mat1.device if on_cuda else _device()
+    lib = L.load()
+    with torch.cuda.device(dev):
+        a = _to_dev(mat1, dev)
+        bq = _resident_weight(mat2, bool(is_vnni), dev)
+        bs = _resident_mx_scale(scales2, bool(is_vnni), dev)
+        bd = _resident_aux(bias, dev, torch.float32, "b")
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+        nws = lib.sglb_fused_experts_workspace_bytes(M, 1, 1, K, N, L.FMT_MXFP4)
+        ws = _workspace(nws, dev)
+        L.check(lib.sglb_mxfp4_mm(a.data_ptr(), bq.data_ptr(), bs.data_ptr(), _ptr(bd), M, N, K, out.data_ptr(),
+                                  ws.data_ptr(), ws.numel(), _stream()))
+    return out if on_cuda else out.cpu()
+
+
+def launch_count():
+    return int(L.load().sglb_launch_count())

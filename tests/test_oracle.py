@@ -1,0 +1,160 @@
+"""The CPU oracle against fixtures produced by the reference's own oracle code
+(tests/golden/make_golden.py).  No GPU, no CUDA library."""
+import torch
+
+from oracle import moe_oracle as O
+from conftest import load_golden
+
+
+def dense(ids, w, E):
+    out = torch.zeros(ids.shape[0], E)
+    out.scatter_(1, ids.long(), w)
+    return out
+
+
+def tie_rows(choice, group_scores, topk, topk_group, fill=0.0):
+    """Rows where the reference leaves the pick open: equal scores straddling a selection boundary
+    (torch.topk(sorted=False) has no stated tie-break).  Happens with the scripts' own
+    bf16 * 2M logits, never with well-conditioned f32 logits."""
+    gs = group_scores.sort(dim=1, descending=True).values
+    t = torch.zeros(choice.shape[0], dtype=torch.bool)
+    n, G = group_scores.shape
+    if topk_group < G:
+        t |= gs[:, topk_group - 1] == gs[:, topk_group]
+        _, gidx = O._topk_lowest_index(group_scores, topk_group)
+        gm = torch.zeros_like(group_scores).scatter_(1, gidx, 1).bool()
+        keep = gm.unsqueeze(-1).expand(n, G, choice.shape[1] // G).reshape(n, -1)
+        choice = choice.masked_fill(~keep, fill)
+    cs = choice.sort(dim=1, descending=True).values
+    if topk < cs.shape[1]:
+        t |= (cs[:, topk - 1] == cs[:, topk]) & (cs[:, topk - 1] != 0)
+    return t
+
+
+def rows_close(a, b, open_rows):
+    ok = torch.isclose(a, b, rtol=1e-5, atol=1e-6).all(dim=1)
+    return bool((ok | open_rows).all())
+
+
+def test_router_softmax_matches_reference():
+    n_open = 0
+    for c in load_golden("router_softmax"):
+        w, ids = O.grouped_topk(c["gating"], c["topk"], c["renormalize"], c["G"], c["topk_group"])
+        sc = torch.softmax(c["gating"].float(), dim=-1)
+        open_rows = tie_rows(sc, sc.view(sc.shape[0], c["G"], -1).max(dim=-1).values, c["topk"], c["topk_group"])
+        if c["gating"].dtype == torch.float32:
+            assert not open_rows.any()
+        n_open += int(open_rows.sum())
+        # the reference's own criterion: dense scatter compare (test_grouped_topk.py:71-75)
+        assert rows_close(dense(ids, w, c["E"]), dense(c["ref_ids"], c["ref_weights"], c["E"]), open_rows)
+        if c["gating"].dtype == torch.float32:  # well conditioned: no ties, no saturation -> same id sets
+            assert torch.equal(ids.sort(dim=1).values, c["ref_ids"].sort(dim=1).values)
+            assert (w[:, :-1] >= w[:, 1:]).all()  # our stated order: descending
+
+
+def test_router_biased_matches_reference():
+    for c in load_golden("router_biased"):
+        w, ids = O.biased_grouped_topk(c["gating"], c["bias"], c["topk"], c["renormalize"], c["G"], c["topk_group"])
+        ch = c["gating"].float().sigmoid() + c["bias"].float()
+        gsc = ch.view(ch.shape[0], c["G"], -1).topk(2, dim=-1)[0].sum(dim=-1)
+        open_rows = tie_rows(ch, gsc, c["topk"], c["topk_group"], float("-inf"))
+        if c["gating"].dtype == torch.float32:
+            assert not open_rows.any()
+        assert rows_close(dense(ids, w, c["E"]), dense(c["ref_ids"], c["ref_weights"], c["E"]), open_rows)
+        if c["gating"].dtype == torch.float32:
+            assert torch.equal(ids.sort(dim=1).values, c["ref_ids"].sort(dim=1).values)
+
+
+def _routing(c):
+    score = torch.softmax(c["score"], dim=-1, dtype=torch.float32)
+    w, ids = torch.topk(score, c["topk"])
+    if c["renormalize"]:
+        w = w / w.sum(dim=-1, keepdim=True)
+    return w, ids.to(torch.int32)
+
+
+def test_moe_bf16_matches_reference():
+    for c in load_golden("moe_bf16"):
+        w, ids = _routing(c)
+        out = O.torch_naive_moe(c["a"], c["w1"], c["w2"], w, ids)
+        assert torch.equal(out, c["ref_out"])  # same bf16 op sequence -> bit-exact
+        out32 = O.native_fused_moe(c["a"], c["w1"], c["w2"], w, ids)
+        assert torch.allclose(out32.float(), c["ref_out"].float(), rtol=1e-2, atol=1e-2)
+
+
+def test_moe_int8_matches_reference():
+    g = load_golden("moe_int8")
+    q, s = O.per_token_quant_int8(g["quant"]["x"])
+    assert torch.equal(q, g["quant"]["q"]) and torch.equal(s, g["quant"]["scale"])
+    for c in g["cases"]:
+        out = O.fused_experts(c["a"], c["w1"], c["w2"], c["topk_weight"], c["topk_ids"], "int8", c["w1_s"], c["w2_s"])
+        assert torch.equal(out, c["ref_out"])
+
+
+def test_moe_fp8_matches_reference():
+    g = load_golden("moe_fp8")
+    for c in g["cases"]:
+        out = O.fused_experts(c["a"], c["w1"], c["w2"], c["topk_weight"], c["topk_ids"], "fp8", c["w1s"], c["w2s"], c["block"])
+        assert torch.equal(out.bfloat16(), c["ref_out"])
+    assert len(g["shared"]) >= 2
+    for c in g["shared"]:
+        out = O.shared_expert(c["a"], c["w1"], c["w2"], c["fused_out"], c["rsf"], "fp8", c["w1s"], c["w2s"], c["block"])
+        assert torch.allclose(out.float(), c["ref_out"].float(), rtol=1e-2, atol=1e-2)
+        assert (out.float() - c["ref_out"].float()).abs().max() <= 2 ** -7 * c["ref_out"].float().abs().max()
+
+
+def test_moe_offload_masked_ids_match_reference():
+    for c in load_golden("moe_offload"):
+        assert (c["topk_ids"] == -1).any()
+        out = O.fused_experts(c["a"], c["w1"], c["w2"], c["topk_weight"], c["topk_ids"], "fp8", c["w1s"], c["w2s"], c["block"])
+        assert torch.equal(out.bfloat16(), c["ref_out"])
+
+
+def test_shared_expert_matches_reference():
+    for c in load_golden("shared_expert"):
+        out = O.shared_expert(c["hs"], c["w1"], c["w2"], c["fused_out"], c["rsf"], "bf16")
+        assert torch.equal(out, c["ref_bf16"])
+        out8 = O.shared_expert(c["hs"], c["w1_q"], c["w2_q"], c["fused_out"], c["rsf"], "int8", c["w1_s"], c["w2_s"])
+        assert torch.equal(out8, c["ref_int8"])
+
+
+def test_fp8_block_quantizer_fixture():
+    g = load_golden("moe_fp8_quantizer")
+    r = g["ragged"]
+    dq = O.scaled_weight(r["q"], r["scales"], *r["block"])
+    assert torch.equal(dq.to(torch.bfloat16), r["dq"])  # ragged edges: 96x200 with [64,128] blocks
+    for c in g["shared"]:
+        out = O.shared_expert(c["a"], c["w1"], c["w2"], c["fused_out"], c["rsf"], "fp8", c["w1s"], c["w2s"], c["block"])
+        assert torch.allclose(out.float(), c["ref_out"].float(), rtol=1e-2, atol=1e-2)
+
+
+def test_mxfp4_matches_reference():
+    g = load_golden("mxfp4")
+    q, s = O.mxfp4_quantize(g["quant"]["x"])
+    assert torch.equal(q, g["quant"]["q"]) and torch.equal(s, g["quant"]["scale"])
+    assert torch.equal(O.mxfp4_dequantize(q, torch.float32, s), g["quant"]["dq"])
+    c = g["codes"]
+    assert torch.equal(O.mxfp4_dequantize(c["q"], torch.float32, c["scale"]), c["dq"])
+    assert len(g["gemms"]) == 5
+    for m in g["gemms"]:
+        assert torch.equal(O.pack_scale(m["Bs"]), m["Bs_packed"])  # test_mxfp4.py:185
+        assert torch.equal(O.mxfp4_scaled_mm(m["A"], m["Bq"], m["Bs"], m["bias"]), m["ref_out"])
+
+
+def test_moe_align_properties():
+    torch.manual_seed(0)
+    for (M, topk, E) in [(1, 2, 4), (14, 8, 8), (300, 8, 256), (129, 1, 1)]:
+        ids = torch.randint(-1, E, (M, topk), dtype=torch.int32)
+        al = O.moe_align(ids, E, 8, 128)
+        S = M * topk
+        nv = int(al["counters"][0])
+        assert nv == int((ids >= 0).sum())
+        ss = al["sorted_slot"][:nv].long()
+        e_sorted = ids.reshape(-1)[ss]
+        assert (e_sorted[1:] >= e_sorted[:-1]).all()                       # grouped by expert
+        same = e_sorted[1:] == e_sorted[:-1]
+        assert (ss[1:][same] > ss[:-1][same]).all()                        # stable inside an expert
+        assert (al["sorted_slot"][nv:] == S).all()
+        assert torch.equal(al["slot_pos"][ss], torch.arange(nv, dtype=torch.int32))
+        assert int(al["chunk_list"][:, 2].sum()) == nv and int(al["tile_list"][:, 2].sum()) == nv
+        assert (al["chunk_list"][:, 2] <= 8).all()
