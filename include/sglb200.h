@@ -49,6 +49,12 @@ const char* sglb_last_error(void);
 /* number of kernels this library has launched in the calling process (bench.py reports it) */
 uint64_t sglb_launch_count(void);
 
+/* Optional per-stage timing with CUDA events on the launching stream (used by bench.py for the
+ * roofline figure).  Stages: 0 align, 1 quant_x, 2 w13 GEMM, 3 quant_act, 4 w2 GEMM, 5 topk reduce.
+ * sglb_profile_read sums ms and sample counts per stage since the last read; synchronise first. */
+void sglb_profile_enable(int on);
+int sglb_profile_read(float* ms_out, int* calls_out, int n);
+
 /* ---- K1 router ------------------------------------------------------------------------------
  * grouped_topk_cpu          (test_grouped_topk.py:61-69, test_moe.py:61-70)  : bias == NULL
  * biased_grouped_topk_cpu   (test_biased_grouped_topk.py:71-80)              : bias != NULL

@@ -41,6 +41,8 @@ SIGNATURES = {
     "sglb_version": (C.c_int, []),
     "sglb_last_error": (C.c_char_p, []),
     "sglb_launch_count": (C.c_uint64, []),
+    "sglb_profile_enable": (None, [C.c_int]),
+    "sglb_profile_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_int), C.c_int]),
     "sglb_grouped_topk": (C.c_int, [_vp, C.c_int, _vp, C.c_int, _i64, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.c_int, _f32, _vp, _vp, _vp]),
     "sglb_moe_align_scratch_bytes": (_sz, [_i64, C.c_int, C.c_int]),

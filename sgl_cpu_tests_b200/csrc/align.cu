@@ -220,5 +220,6 @@ extern "C" int sglb_moe_align(const int32_t* topk_ids, int64_t M, int topk, int 
       out->expert_offset, out->sorted_slot, out->slot_pos, out->chunk_list, out->tile_list,
       out->counters);
   SGLB_LAUNCH_CHECK();
+  count_launch(nb > 1 ? 2 : 1);
   return SGLB_OK;
 }

@@ -1,5 +1,6 @@
 // C-ABI entry points that orchestrate the kernels: fused_experts, shared_expert, mxfp4_mm.
 #include <atomic>
+#include <vector>
 #include <math.h>
 #include <stdarg.h>
 #include <string.h>
@@ -18,7 +19,39 @@ void set_error(const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
-void count_launch(int n = 1) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+// ---- optional per-stage CUDA-event timing (bench.py's roofline leg) ------------------------------
+// When enabled, fused_experts brackets each stage with events on the launching stream; the events
+// are resolved by sglb_profile_read() after the caller has synchronised.
+enum { ST_ALIGN = 0, ST_QUANT_X, ST_GEMM1, ST_QUANT_ACT, ST_GEMM2, ST_REDUCE, ST_COUNT };
+struct StageEvents {
+  cudaEvent_t a, b;
+  int stage;
+};
+static bool g_profile = false;
+static std::vector<StageEvents> g_events;
+static size_t g_events_used = 0;
+
+struct StageTimer {
+  cudaStream_t s;
+  int idx = -1;
+  StageTimer(int stage, cudaStream_t stream) : s(stream) {
+    if (!g_profile) return;
+    if (g_events_used == g_events.size()) {
+      StageEvents e;
+      cudaEventCreate(&e.a);
+      cudaEventCreate(&e.b);
+      g_events.push_back(e);
+    }
+    idx = (int)g_events_used++;
+    g_events[idx].stage = stage;
+    cudaEventRecord(g_events[idx].a, s);
+  }
+  ~StageTimer() {
+    if (idx >= 0) cudaEventRecord(g_events[idx].b, s);
+  }
+};
 
 int launch_shared_axpy(const void* y, const void* fused, float rsf, int64_t n, void* out,
                        cudaStream_t stream);
@@ -169,15 +202,20 @@ static int run_stream_mlp(int fmt, int64_t M, int topk, int E, int H, int I, con
   a.out = ws.act;
   a.row_scale = nullptr;
   a.scale_cols = fmt == SGLB_FMT_FP8_W8A16 ? ceil_div(H, bk) : H / 32;
+  int rc;
   if (fmt == SGLB_FMT_INT8_W8A8) {
-    int rc = sglb_quant_rows_int8(hidden, M, H, ws.xq, ws.xs, stream);
+    StageTimer t(ST_QUANT_X, stream);
+    rc = sglb_quant_rows_int8(hidden, M, H, ws.xq, ws.xs, stream);
     if (rc) return rc;
     a.X = ws.xq;
     a.Xscale = ws.xs;
   } else {
     a.X = hidden;
   }
-  int rc = dispatch_stream<1>(fmt, a, plan, stream);
+  {
+    StageTimer t(ST_GEMM1, stream);
+    rc = dispatch_stream<1>(fmt, a, plan, stream);
+  }
   if (rc) return rc;
 
   // stage 2
@@ -194,6 +232,7 @@ static int run_stream_mlp(int fmt, int64_t M, int topk, int E, int H, int I, con
   a.row_scale = row_scale;
   a.scale_cols = fmt == SGLB_FMT_FP8_W8A16 ? ceil_div(I, bk) : I / 32;
   if (fmt == SGLB_FMT_INT8_W8A8) {
+    StageTimer t(ST_QUANT_ACT, stream);
     rc = sglb_quant_rows_int8(ws.act, S, I, ws.actq, ws.acts, stream);
     if (rc) return rc;
     a.X = ws.actq;
@@ -201,6 +240,7 @@ static int run_stream_mlp(int fmt, int64_t M, int topk, int E, int H, int I, con
   } else {
     a.X = ws.act;
   }
+  StageTimer t(ST_GEMM2, stream);
   return dispatch_stream<2>(fmt, a, plan2, stream);
 }
 
@@ -214,6 +254,7 @@ static int run_align(const int32_t* ids, int64_t M, int topk, int E, int chunk_r
   ao.chunk_list = ws.chunk_list;
   ao.tile_list = ws.tile_list;
   ao.counters = ws.counters;
+  StageTimer t(ST_ALIGN, stream);
   int rc = sglb_moe_align(ids, M, topk, E, chunk_rows, kTileRows, &ao, ws.align_scratch, stream);
   return rc;
 }
@@ -225,6 +266,29 @@ using namespace sglb;
 extern "C" int sglb_version(void) { return 100; }
 extern "C" const char* sglb_last_error(void) { return g_err; }
 extern "C" uint64_t sglb_launch_count(void) { return g_launches.load(); }
+
+extern "C" void sglb_profile_enable(int on) {
+  g_profile = on != 0;
+  g_events_used = 0;
+}
+// Sums the recorded stage durations (ms) into ms_out[0..n) and the number of samples into
+// calls_out[0..n); the caller must have synchronised the stream(s).  Resets the recording.
+extern "C" int sglb_profile_read(float* ms_out, int* calls_out, int n) {
+  for (int i = 0; i < n; ++i) {
+    ms_out[i] = 0.f;
+    calls_out[i] = 0;
+  }
+  for (size_t i = 0; i < g_events_used; ++i) {
+    float ms = 0.f;
+    SGLB_CUDA(cudaEventElapsedTime(&ms, g_events[i].a, g_events[i].b));
+    if (g_events[i].stage < n) {
+      ms_out[g_events[i].stage] += ms;
+      calls_out[g_events[i].stage] += 1;
+    }
+  }
+  g_events_used = 0;
+  return SGLB_OK;
+}
 
 extern "C" int64_t sglb_moe_align_max_items(int64_t M, int topk, int E, int rows) {
   if (rows <= 0) return 0;
@@ -264,18 +328,17 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
                "fused_experts: tcgen05 path does not support fmt=%d H=%d I=%d", p->fmt, p->H, p->I);
     rc = run_align(p->topk_ids, p->M, p->topk, p->E, 0, ws, stream);
     if (rc) return rc;
-    count_launch(p->M * p->topk > 1024 ? 2 : 1);
     rc = launch_umma_moe(p, ws, stream);
     if (rc) return rc;
   } else {
     StreamPlan plan = make_plan(p->M, p->topk, p->E, p->I, 1);
     rc = run_align(p->topk_ids, p->M, p->topk, p->E, 8 * plan.ng, ws, stream);
     if (rc) return rc;
-    count_launch(p->M * p->topk > 1024 ? 2 : 1);
     rc = run_stream_mlp(p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2, p->w13_scale,
                         p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, ws.ic2, stream);
     if (rc) return rc;
   }
+  StageTimer t(ST_REDUCE, stream);
   return sglb_topk_reduce(ws.ic2, ws.slot_pos, p->M, p->topk, p->H, p->out, stream);
 }
 
@@ -295,7 +358,6 @@ extern "C" int sglb_shared_expert(const sglb_shared_problem* p, sglb_stream_t st
   StreamPlan plan = make_plan(p->M, 1, 1, p->I, 1);
   rc = run_align(ws.zero_ids, p->M, 1, 1, 8 * plan.ng, ws, stream);
   if (rc) return rc;
-  count_launch(p->M > 1024 ? 2 : 1);
   rc = run_stream_mlp(p->fmt, p->M, 1, 1, p->H, p->I, p->hidden, p->w1, p->w2, p->w1_scale, p->w2_scale,
                       p->block_n, p->block_k, nullptr, ws, ws.ic2, stream);
   if (rc) return rc;
@@ -319,7 +381,6 @@ extern "C" int sglb_mxfp4_mm(const void* A, const void* Bq, const void* Bs, cons
   SGLB_CHECK(plan.max_chunks <= 65535, "mxfp4_mm: M too large for the streaming path");
   int rc = run_align(ws.zero_ids, M, 1, 1, 8 * plan.ng, ws, stream);
   if (rc) return rc;
-  count_launch(M > 1024 ? 2 : 1);
   StreamArgs a;
   memset(&a, 0, sizeof(a));
   a.chunk_list = ws.chunk_list;

@@ -13,6 +13,7 @@ namespace sglb {
 
 // ---- error plumbing (thread-local message behind sglb_last_error) -------------------------
 void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
 
 #define SGLB_CHECK(cond, ...)                 \
   do {                                        \

@@ -4,7 +4,7 @@
 
 namespace sglb {
 
-void count_launch(int n = 1);
+
 
 // ---- per-row dynamic int8 quantisation (test_moe_int8.py:23-31) ---------------------------------
 // One CTA per row.  absmax is taken over the bf16 values, scale = absmax.clamp_min(1e-7)/127,

@@ -213,6 +213,7 @@ static int launch_router(const void* gating, const void* bias, int64_t M, int E,
   else SGLB_ROUTER_CASE(32);
 #undef SGLB_ROUTER_CASE
   SGLB_LAUNCH_CHECK();
+  count_launch();
   return SGLB_OK;
 }
 

@@ -1,0 +1,350 @@
+"""GPU parity tests: the CUDA path (through the C ABI, via the host mirror) against the CPU oracle on
+the same seeded inputs, against the reference-generated golden fixtures, and through
+size-independent properties at the BASELINE.json shapes.  Run with `-m gpu` on the B200 box."""
+import math
+
+import pytest
+import torch
+
+from conftest import load_golden
+from oracle import moe_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+BF16_TOL = dict(rtol=1e-2, atol=1e-2)  # utils.py:3-12 of the reference
+
+
+@pytest.fixture(scope="module")
+def K():
+    import sgl_cpu_tests_b200 as K
+    assert torch.cuda.is_available()
+    return K
+
+
+def dense(ids, w, E):
+    out = torch.zeros(ids.shape[0], E)
+    out.scatter_(1, ids.long().cpu(), w.float().cpu())
+    return out
+
+
+def routing(m, e, topk, dtype=torch.bfloat16):
+    score = torch.softmax(torch.randn((m, e), dtype=dtype), dim=-1, dtype=torch.float32)
+    w, ids = torch.topk(score, topk)
+    return w, ids.to(torch.int32)
+
+
+# ------------------------------------------------------------------------------------------ routers
+ROUTER_SHAPES = [(123, 8, 2, 2, 1), (123, 16, 4, 3, 2), (123, 32, 4, 3, 2), (1123, 32, 4, 3, 2), (123, 64, 1, 6, 1),
+                 (123, 256, 8, 4, 8), (123, 160, 8, 6, 2), (64, 128, 1, 8, 1), (3, 384, 1, 8, 1), (5, 1024, 8, 8, 4)]
+
+
+@pytest.mark.parametrize("renorm", [True, False])
+@pytest.mark.parametrize("shape", ROUTER_SHAPES)
+def test_grouped_topk_bit_exact_ids(K, shape, renorm):
+    M, E, G, topk, tg = shape
+    torch.manual_seed(111)
+    for gating in (torch.randn(M, E), torch.randn(M, E, dtype=torch.bfloat16),
+                   torch.randn(M, E, dtype=torch.bfloat16) * 2 * M):  # last: test_grouped_topk.py:44-46
+        w_ref, id_ref = O.grouped_topk(gating, topk, renorm, G, tg)
+        w, ids = K.grouped_topk(torch.zeros(M, 4), gating.cuda(), topk, renorm, G, tg, 0, None, None)
+        ids, w = ids.cpu(), w.cpu()
+        # softmax is monotone in the logit, so picks (ids AND order) are bit-exact for every input
+        # style, ties included: both sides break ties towards the lowest expert index.  Only picks
+        # whose probability underflowed to (sub)zero may differ between expf implementations.
+        live = (w_ref > 1e-30) & (w > 1e-30)
+        assert torch.equal(ids[live], id_ref[live])
+        if gating.dtype == torch.float32:
+            assert torch.equal(ids, id_ref)
+        assert torch.allclose(dense(ids, w, E), dense(id_ref, w_ref, E), rtol=1e-4, atol=1e-6)
+
+
+def test_grouped_topk_out_variant_and_golden(K):
+    for c in load_golden("router_softmax"):
+        M, topk = c["M"], c["topk"]
+        w = torch.empty(M, topk, dtype=torch.float32)
+        ids = torch.empty(M, topk, dtype=torch.int32)
+        K.grouped_topk_out(w, ids, torch.zeros(M, 4), c["gating"], topk, c["renormalize"], c["G"], c["topk_group"])
+        w_o, id_o = O.grouped_topk(c["gating"], topk, c["renormalize"], c["G"], c["topk_group"])
+        if c["gating"].dtype == torch.float32:
+            assert torch.equal(ids, id_o)
+            assert torch.allclose(w, w_o, rtol=1e-5, atol=1e-7)
+            assert torch.allclose(dense(ids, w, c["E"]), dense(c["ref_ids"], c["ref_weights"], c["E"]), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("renorm", [True, False])
+def test_biased_grouped_topk(K, renorm):
+    torch.manual_seed(1111)
+    for (M, E, G, topk, tg) in [(122, 256, 8, 8, 2), (33, 64, 4, 4, 2), (7, 32, 8, 3, 3), (2048, 256, 8, 8, 4)]:
+        for dt in (torch.float32, torch.bfloat16):
+            gating = torch.randn(M, E, dtype=dt)
+            bias = torch.randn(E, dtype=dt)
+            w_ref, id_ref = O.biased_grouped_topk(gating, bias, topk, renorm, G, tg)
+            w = torch.empty(M, topk, dtype=torch.float32)
+            ids = torch.empty(M, topk, dtype=torch.int32)
+            K.biased_grouped_topk_out(w, ids, torch.zeros(M, 4), gating, bias, topk, renorm, G, tg)
+            # sigmoid + bias is not monotone-safe across two exp implementations: a 1-ulp difference can
+            # flip a near-tie.  f32 logits: at most a stray row; bf16 logits collide far more often.
+            mism = (ids != id_ref).any(dim=1).float().mean()
+            assert mism <= (0.01 if dt == torch.float32 else 0.25), float(mism)
+            ok = (ids == id_ref).all(dim=1)
+            assert torch.allclose(w[ok], w_ref[ok], rtol=1e-5, atol=1e-7)
+    for c in load_golden("router_biased"):
+        if c["gating"].dtype != torch.float32:
+            continue
+        w, ids = K.biased_grouped_topk(torch.zeros(c["M"], 4), c["gating"].cuda(), c["bias"].cuda(), c["topk"],
+                                       c["renormalize"], c["G"], c["topk_group"])
+        assert torch.allclose(dense(ids, w, c["E"]), dense(c["ref_ids"], c["ref_weights"], c["E"]), rtol=1e-5, atol=1e-6)
+
+
+# ------------------------------------------------------------------------------------------ moe_align
+@pytest.mark.parametrize("shape", [(1, 1, 1), (1, 8, 128), (14, 8, 8), (128, 8, 128), (129, 8, 256), (1024, 8, 256),
+                                   (8192, 8, 256), (4096, 8, 128), (1000, 4, 1024), (5000, 1, 1), (0, 2, 8)])
+def test_moe_align_bit_exact(K, shape):
+    M, topk, E = shape
+    torch.manual_seed(M + E)
+    ids = torch.randint(-1, E, (M, topk), dtype=torch.int32)
+    for chunk_rows in (8, 32):
+        ref = O.moe_align(ids, E, chunk_rows, 128)
+        got = K.moe_align(ids.cuda(), E, chunk_rows, 128)
+        for k in ("expert_count", "expert_offset", "sorted_slot", "slot_pos", "counters"):
+            assert torch.equal(got[k].cpu(), ref[k]), k
+        for k, n in (("chunk_list", int(ref["counters"][1])), ("tile_list", int(ref["counters"][2]))):
+            assert torch.equal(got[k].cpu()[:3 * n].view(-1, 3), ref[k]), k
+
+
+# ------------------------------------------------------------------------------------------ fused experts
+def check_close(out, ref, what=""):
+    out, ref = out.float().cpu(), ref.float().cpu()
+    assert torch.isfinite(out).all(), what
+    assert torch.allclose(out, ref, **BF16_TOL), f"{what}: max diff {(out - ref).abs().max():.5f}"
+
+
+def mean_rel(out, ref):
+    out, ref = out.float().cpu(), ref.float().cpu()
+    return float((out - ref).abs().mean() / ref.abs().mean())
+
+
+@pytest.mark.parametrize("prepack", [False, True])
+@pytest.mark.parametrize("shape", [(4, 32, 32, 4, 2), (2, 128, 32, 4, 2), (33, 64, 128, 8, 3), (224, 512, 1056, 8, 2),
+                                   (128, 768, 2048, 128, 8), (1, 768, 2048, 128, 8), (17, 96, 72, 8, 8)])
+def test_fused_experts_bf16(K, shape, prepack):
+    m, n, k, e, topk = shape
+    if prepack and ((2 * n) % 32 != 0 or k % 32 != 0):
+        pytest.skip("prepack needs N % 32 == 0")
+    torch.manual_seed(1111)
+    a = torch.randn((m, k), dtype=torch.bfloat16) / 10           # test_moe.py:96-99
+    w1 = torch.randn((e, 2 * n, k), dtype=torch.bfloat16) / 10
+    w2 = torch.randn((e, k, n), dtype=torch.bfloat16) / 10
+    score = torch.randn((m, e), dtype=torch.bfloat16)
+    tw, ids = K.grouped_topk(a, score, topk, True, 1, 1, 0, None, None)
+    ref = O.native_fused_moe(a, w1, w2, tw, ids)
+    p1 = K.convert_weight_packed(w1) if prepack else w1
+    p2 = K.convert_weight_packed(w2) if prepack else w2
+    hs = a.clone()
+    out = K.fused_experts(hs, p1, p2, tw, ids, True, K.CPUQuantMethod.UNQUANT, None, None, None, None, None, prepack)
+    assert out.data_ptr() == hs.data_ptr()  # inplace: mutates and returns hidden_states
+    check_close(out, ref, f"bf16 {shape}")
+
+
+def test_fused_experts_bf16_golden(K):
+    for c in load_golden("moe_bf16"):
+        score = torch.softmax(c["score"], dim=-1, dtype=torch.float32)
+        w, ids = torch.topk(score, c["topk"])
+        if c["renormalize"]:
+            w = w / w.sum(dim=-1, keepdim=True)
+        out = K.fused_experts(c["a"].clone(), c["w1"], c["w2"], w, ids.to(torch.int32), False, False, False, None, None,
+                              None, None, None, False)
+        check_close(out, c["ref_out"], "bf16 golden")
+
+
+@pytest.mark.parametrize("case", [(1, 128, 256, 8, 2, False), (39, 1280, 1024, 8, 3, True), (1024, 1280, 1024, 8, 3, True),
+                                  (5, 64, 32, 4, 2, False), (64, 768, 2048, 128, 8, True)])
+def test_fused_experts_int8(K, case):
+    M, N, Kd, E, topk, prepack = case
+    torch.manual_seed(1111)
+    a = torch.randn((M, Kd), dtype=torch.bfloat16) / math.sqrt(Kd)   # test_moe_int8.py:97-122
+    w1 = ((torch.rand((E, 2 * N, Kd)) - 0.5) * 2 * 127).clamp(-128, 127).to(torch.int8)
+    w2 = ((torch.rand((E, Kd, N)) - 0.5) * 2 * 127).clamp(-128, 127).to(torch.int8)
+    w1_s, w2_s = torch.rand(E, 2 * N) * 1e-2, torch.rand(E, Kd) * 1e-2
+    tw, ids = routing(M, E, topk)
+    ref = O.fused_experts(a, w1, w2, tw, ids, "int8", w1_s, w2_s)
+    p1 = K.convert_weight_packed(w1) if prepack else w1
+    p2 = K.convert_weight_packed(w2) if prepack else w2
+    out = K.fused_experts(a.clone(), p1, p2, tw, ids, True, True, False, w1_s, w2_s, None, None, None, prepack)
+    assert mean_rel(out, ref) < 0.01                 # test_moe_int8.py:134-137
+    if M <= 64:
+        check_close(out, ref, f"int8 {case}")        # the reference itself warns this may fail at large shapes (:131)
+
+
+def test_fused_experts_int8_golden_and_quant(K):
+    g = load_golden("moe_int8")
+    for c in g["cases"]:
+        out = K.fused_experts(c["a"].clone(), c["w1"], c["w2"], c["topk_weight"], c["topk_ids"], False, True, False,
+                              c["w1_s"], c["w2_s"], None, None, None, False)
+        check_close(out, c["ref_out"], "int8 golden")
+        assert mean_rel(out, c["ref_out"]) < 0.01
+
+
+@pytest.mark.parametrize("block", [[64, 128], [128, 128]])
+@pytest.mark.parametrize("shape", [(2, 128, 128, 8, 4), (121, 512, 1024, 8, 2), (1212, 512, 1024, 8, 2), (16, 2048, 7168, 4, 2)])
+def test_fused_experts_fp8(K, shape, block):
+    M, N, Kd, E, topk = shape
+    bn, bk = block
+    torch.manual_seed(1111)
+    a = torch.randn(M, Kd, dtype=torch.bfloat16) / math.sqrt(Kd)     # test_moe_fp8_ext.py:96-105
+    w1 = (torch.randn(E, 2 * N, Kd) * 400).clamp(-400, 400).to(torch.float8_e4m3fn)
+    w2 = (torch.randn(E, Kd, N) * 400).clamp(-400, 400).to(torch.float8_e4m3fn)
+    w1s = torch.randn(E, 2 * N // bn, Kd // bk) * 1e-3
+    w2s = torch.randn(E, Kd // bn, N // bk) * 1e-3
+    tw, ids = routing(M, E, topk)
+    ref = O.fused_experts(a, w1, w2, tw, ids, "fp8", w1s, w2s, block)
+    out = K.fused_experts(a, K.convert_weight_packed(w1), K.convert_weight_packed(w2), tw, ids, False, False, True, w1s,
+                          w2s, block, None, None, True)
+    check_close(out, ref.bfloat16(), f"fp8 {shape} {block}")
+
+
+def test_fused_experts_fp8_golden_and_offload(K):
+    for c in load_golden("moe_fp8")["cases"] + load_golden("moe_offload"):
+        out = K.fused_experts(c["a"], c["w1"], c["w2"], c["topk_weight"], c["topk_ids"], False, False, True, c["w1s"],
+                              c["w2s"], c["block"], None, None, False)
+        check_close(out, c["ref_out"], "fp8 golden")
+    # bf16 weights with -1 ids and duplicate experts in a row (test_moe_offloading_cpu.py:123-137)
+    c = load_golden("moe_offload")[0]
+    w1d = O.scaled_weight(c["w1"], c["w1s"], *c["block"]).bfloat16()
+    w2d = O.scaled_weight(c["w2"], c["w2s"], *c["block"]).bfloat16()
+    out = K.fused_experts(c["a"], w1d, w2d, c["topk_weight"], c["topk_ids"], False, False, False, None, None, None, None,
+                          None, False)
+    check_close(out, O.native_fused_moe(c["a"], w1d, w2d, c["topk_weight"], c["topk_ids"]), "bf16 offload")
+
+
+def test_fused_experts_all_masked_and_empty(K):
+    a = torch.randn(3, 64, dtype=torch.bfloat16)
+    w1 = torch.randn(4, 64, 64, dtype=torch.bfloat16)
+    w2 = torch.randn(4, 64, 32, dtype=torch.bfloat16)
+    ids = torch.full((3, 2), -1, dtype=torch.int32)
+    out = K.fused_experts(a, w1, w2, torch.ones(3, 2), ids, False, False, False, None, None, None, None, None, False)
+    assert torch.equal(out, torch.zeros_like(out))
+    out = K.fused_experts(a[:0], w1, w2, torch.ones(0, 2), ids[:0], False, False, False, None, None, None, None, None, False)
+    assert out.shape == (0, 64)
+
+
+@pytest.mark.parametrize("shape", [(3, 64, 64, 4, 2), (37, 96, 352, 8, 4), (16, 2880, 2880, 8, 4)])
+def test_fused_experts_mxfp4(K, shape):
+    M, N, Kd, E, topk = shape
+    torch.manual_seed(1111)
+    a = torch.randn(M, Kd, dtype=torch.bfloat16) / 10
+    w1q, w1s = O.mxfp4_quantize((torch.rand(E, 2 * N, Kd) - 0.5) * 2e-1)
+    w2q, w2s = O.mxfp4_quantize((torch.rand(E, Kd, N) - 0.5) * 2e-1)
+    w1s, w2s = w1s.view(E, 2 * N, Kd // 32), w2s.view(E, Kd, N // 32)
+    tw, ids = routing(M, E, topk)
+    ref = O.fused_experts(a, w1q, w2q, tw, ids, "mxfp4", w1s, w2s)
+    for vnni in (False, True):
+        if vnni and N % 32:
+            continue
+        args = (w1q, w2q, w1s, w2s) if not vnni else (K.convert_weight_packed(w1q), K.convert_weight_packed(w2q),
+                                                      K.convert_scale_packed(w1s), K.convert_scale_packed(w2s))
+        out = K.fused_experts(a, args[0], args[1], tw, ids, False, K.CPUQuantMethod.MXFP4, args[2], args[3], None, None,
+                              None, vnni)
+        check_close(out, ref, f"mxfp4 {shape} vnni={vnni}")
+
+
+# ------------------------------------------------------------------------------------------ shared expert
+@pytest.mark.parametrize("shape", [(2, 32, 32, 16), (121, 128, 64, 16), (1211, 128, 64, 16)])
+def test_shared_expert_bf16_int8(K, shape):
+    m, n, k, rsf = shape
+    torch.manual_seed(1111)
+    hs = torch.randn(m, k, dtype=torch.bfloat16) / k                  # test_shared_experts.py:57-60
+    w1 = torch.randn(2 * n, k, dtype=torch.bfloat16)
+    w2 = torch.randn(k, n, dtype=torch.bfloat16)
+    fo = torch.randn(m, k, dtype=torch.bfloat16) / k
+    hs2 = hs.clone()
+    ref = O.shared_expert(hs, w1, w2, fo, rsf, "bf16")
+    res = K.shared_expert(hs, w1, w2, fo, rsf, True, False, False, None, None, None, False)
+    assert res.data_ptr() == hs.data_ptr()
+    check_close(res, ref, "shared bf16")
+    w1_q, w1_s = O.per_token_quant_int8(w1)
+    w2_q, w2_s = O.per_token_quant_int8(w2)
+    ref2 = O.shared_expert(hs2, w1_q, w2_q, fo, rsf, "int8", w1_s, w2_s)
+    res2 = K.shared_expert(hs2, w1_q, w2_q, fo, rsf, True, True, False, w1_s, w2_s, None, False)
+    check_close(res2, ref2, "shared int8")
+
+
+def test_shared_expert_golden(K):
+    for c in load_golden("shared_expert"):
+        out = K.shared_expert(c["hs"].clone(), c["w1"], c["w2"], c["fused_out"], c["rsf"], False, False, False, None, None,
+                              None, False)
+        check_close(out, c["ref_bf16"], "shared golden bf16")
+        out = K.shared_expert(c["hs"].clone(), c["w1_q"], c["w2_q"], c["fused_out"], c["rsf"], False, True, False,
+                              c["w1_s"], c["w2_s"], None, None, None, False)
+        check_close(out, c["ref_int8"], "shared golden int8")
+    for c in load_golden("moe_fp8")["shared"] + load_golden("moe_fp8_quantizer")["shared"]:
+        for vnni in (False, True):
+            w1 = K.convert_weight_packed(c["w1"]) if vnni else c["w1"]
+            w2 = K.convert_weight_packed(c["w2"]) if vnni else c["w2"]
+            out = K.shared_expert(c["a"].clone(), w1, w2, c["fused_out"], c["rsf"], True, False, True, c["w1s"], c["w2s"],
+                                  c["block"], None, None, vnni)
+            check_close(out, c["ref_out"], "shared golden fp8")
+
+
+# ------------------------------------------------------------------------------------------ mxfp4 linear + prepack
+def test_mxfp4_scaled_mm_golden(K):
+    for m in load_golden("mxfp4")["gemms"]:
+        Bp = K.convert_weight_packed(m["Bq"])
+        Sp = K.convert_scale_packed(m["Bs"])
+        assert torch.equal(Sp, m["Bs_packed"])                       # test_mxfp4.py:185
+        out = K.mxfp4_scaled_mm(m["A"], Bp, Sp, m["bias"], True)
+        check_close(out, m["ref_out"], "mxfp4 mm")
+
+
+def test_mxfp4_all_codes(K):
+    c = load_golden("mxfp4")["codes"]          # every nibble pair x extreme e8m0 scales, as a GEMM against identity
+    q, sc = c["q"], c["scale"]                 # [8, 32] bytes -> 64 values per row; scales [16,1] -> [8,2]
+    dq = c["dq"]                               # [8, 64] f32
+    rows = [i for i in range(8) if torch.isfinite(dq[i]).all() and dq[i].abs().max() < 1e30 and
+            (dq[i] == 0).logical_or(dq[i].abs() > 1e-30).all()]
+    eye = torch.eye(64, dtype=torch.bfloat16)
+    out = K.mxfp4_scaled_mm(eye, q, sc.view(8, 2), None, False)     # out[k, n] = dq[n, k]
+    got = out.float().t()
+    assert torch.equal(got[rows], dq[rows].bfloat16().float())
+
+
+def test_prepack_layouts_bit_exact(K):
+    g = load_golden("prepack")
+    for k in ("bf16", "int8", "fp8"):
+        for dev in ("cpu", "cuda"):
+            w = g[k]["w"].to(dev)
+            p = K.convert_weight_packed(w)
+            assert p.device == w.device
+            assert torch.equal(p.cpu().view(torch.uint8), g[k]["packed"].view(torch.uint8)), k
+    assert torch.equal(K.convert_scale_packed(g["scale"]["s"]), g["scale"]["packed"])
+    w = torch.randn(256, 16 * 8, 32 * 24).to(torch.bfloat16)  # test_moe.py:126 (commented call), test_gemm.py:46 shape
+    assert torch.equal(K.convert_weight_packed(w), O.pack_weight_vnni(w))
+
+
+def test_building_blocks(K):
+    import ctypes
+    from sgl_cpu_tests_b200 import _lib as L
+    lib = L.load()
+    g = load_golden("moe_int8")["quant"]
+    x = g["x"].cuda()
+    q = torch.empty(x.shape, dtype=torch.int8, device="cuda")
+    s = torch.empty(x.shape[0], dtype=torch.float32, device="cuda")
+    L.check(lib.sglb_quant_rows_int8(x.data_ptr(), x.shape[0], x.shape[1], q.data_ptr(), s.data_ptr(), None))
+    torch.cuda.synchronize()
+    assert torch.equal(q.cpu(), g["q"]) and torch.equal(s.cpu(), g["scale"].view(-1))   # bit-exact
+
+
+def test_errors_surface_as_runtime_error(K):
+    a = torch.randn(4, 64, dtype=torch.bfloat16)
+    w1 = torch.randn(4, 64, 64, dtype=torch.bfloat16)
+    w2 = torch.randn(4, 64, 32, dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError):
+        K.fused_experts(a, w1, w2, torch.ones(4, 2), torch.zeros(4, 2, dtype=torch.int32), False, True, False, None, None,
+                        None, None, None, False)     # int8 flag with bf16 weights / no scales
+    with pytest.raises(RuntimeError):
+        K.fused_experts(a, w1, w2[:, :32], torch.ones(4, 2), torch.zeros(4, 2, dtype=torch.int32), False, False, False,
+                        None, None, None, None, None, False)
+    with pytest.raises(RuntimeError):
+        K.grouped_topk(a, torch.randn(5, 8), 2, False, 1, 1, 0, None, None)  # token count mismatch
+    with pytest.raises(RuntimeError):
+        K.grouped_topk(a, torch.randn(4, 8), 2, False, 3, 1, 0, None, None)  # G does not divide E
