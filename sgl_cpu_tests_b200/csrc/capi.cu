@@ -55,6 +55,8 @@ struct StageTimer {
 
 int launch_shared_axpy(const void* y, const void* fused, float rsf, int64_t n, void* out,
                        cudaStream_t stream);
+int launch_quant_rows_f32(const float* x, int64_t rows, int K, int8_t* q, float* scale,
+                          cudaStream_t stream);
 int umma_supported(int fmt, int64_t M, int topk, int E, int H, int I);
 int launch_umma_moe(const sglb_moe_problem* p, const struct MoeWorkspace& ws, cudaStream_t stream);
 
@@ -98,7 +100,8 @@ static MoeWorkspace carve(void* base, int64_t M, int topk, int E, int H, int I, 
   w.align_scratch = (int32_t*)take(sglb_moe_align_scratch_bytes(M, topk, E));
   w.zero_ids = (int32_t*)take(sizeof(int32_t) * M);
   // +kTileRows rows of slack: the tcgen05 path reads whole 128-row tiles past the last expert
-  w.act = (__nv_bfloat16*)take(sizeof(__nv_bfloat16) * (S + kTileRows) * I);
+  // int8 keeps the silu_and_mul output in f32 until it is re-quantised
+  w.act = (__nv_bfloat16*)take((fmt == SGLB_FMT_INT8_W8A8 ? sizeof(float) : sizeof(__nv_bfloat16)) * (S + kTileRows) * I);
   w.ic2 = (__nv_bfloat16*)take(sizeof(__nv_bfloat16) * S * H);
   if (fmt == SGLB_FMT_INT8_W8A8) {
     w.xq = (int8_t*)take((size_t)M * H);
@@ -233,7 +236,7 @@ static int run_stream_mlp(int fmt, int64_t M, int topk, int E, int H, int I, con
   a.scale_cols = fmt == SGLB_FMT_FP8_W8A16 ? ceil_div(I, bk) : I / 32;
   if (fmt == SGLB_FMT_INT8_W8A8) {
     StageTimer t(ST_QUANT_ACT, stream);
-    rc = sglb_quant_rows_int8(ws.act, S, I, ws.actq, ws.acts, stream);
+    rc = launch_quant_rows_f32((const float*)ws.act, S, I, ws.actq, ws.acts, stream);
     if (rc) return rc;
     a.X = ws.actq;
     a.Xscale = ws.acts;
@@ -305,11 +308,11 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
   SGLB_CHECK(p != nullptr, "fused_experts: null problem");
   SGLB_CHECK(p->M >= 0 && p->topk >= 1 && p->E >= 1 && p->H > 0 && p->I > 0,
              "fused_experts: bad shape M=%lld topk=%d E=%d H=%d I=%d", (long long)p->M, p->topk, p->E, p->H, p->I);
-  SGLB_CHECK(p->hidden && p->w13 && p->w2 && p->topk_weights && p->topk_ids && p->out,
-             "fused_experts: null tensor pointer");
   int rc = check_format("fused_experts", p->fmt, p->H, p->I, p->w13_scale, p->w2_scale, p->block_n, p->block_k);
   if (rc) return rc;
-  if (p->M == 0) return SGLB_OK;
+  SGLB_CHECK(p->w13 && p->w2, "fused_experts: null weight pointer");
+  if (p->M == 0) return SGLB_OK;  // empty batch: activation pointers may legitimately be null
+  SGLB_CHECK(p->hidden && p->topk_weights && p->topk_ids && p->out, "fused_experts: null tensor pointer");
   const size_t need = sglb_fused_experts_workspace_bytes(p->M, p->topk, p->E, p->H, p->I, p->fmt);
   SGLB_CHECK(p->workspace && p->workspace_bytes >= need, "fused_experts: workspace too small (%zu < %zu)",
              p->workspace_bytes, need);
@@ -346,10 +349,11 @@ extern "C" int sglb_shared_expert(const sglb_shared_problem* p, sglb_stream_t st
   cudaStream_t stream = (cudaStream_t)stream_;
   SGLB_CHECK(p != nullptr, "shared_expert: null problem");
   SGLB_CHECK(p->M >= 0 && p->H > 0 && p->I > 0, "shared_expert: bad shape");
-  SGLB_CHECK(p->hidden && p->w1 && p->w2 && p->fused_out && p->out, "shared_expert: null tensor pointer");
   int rc = check_format("shared_expert", p->fmt, p->H, p->I, p->w1_scale, p->w2_scale, p->block_n, p->block_k);
   if (rc) return rc;
+  SGLB_CHECK(p->w1 && p->w2, "shared_expert: null weight pointer");
   if (p->M == 0) return SGLB_OK;
+  SGLB_CHECK(p->hidden && p->fused_out && p->out, "shared_expert: null tensor pointer");
   const size_t need = sglb_fused_experts_workspace_bytes(p->M, 1, 1, p->H, p->I, p->fmt);
   SGLB_CHECK(p->workspace && p->workspace_bytes >= need, "shared_expert: workspace too small (%zu < %zu)",
              p->workspace_bytes, need);
@@ -368,10 +372,11 @@ extern "C" int sglb_mxfp4_mm(const void* A, const void* Bq, const void* Bs, cons
                              int N, int K, void* out, void* workspace, size_t workspace_bytes,
                              sglb_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
-  SGLB_CHECK(A && Bq && Bs && out, "mxfp4_mm: null tensor pointer");
+  SGLB_CHECK(Bq && Bs, "mxfp4_mm: null weight pointer");
   SGLB_CHECK(M >= 0 && N > 0 && K > 0 && K % 32 == 0, "mxfp4_mm: bad shape M=%lld N=%d K=%d (K %% 32 == 0)",
              (long long)M, N, K);
   if (M == 0) return SGLB_OK;
+  SGLB_CHECK(A && out, "mxfp4_mm: null tensor pointer");
   const size_t need = sglb_fused_experts_workspace_bytes(M, 1, 1, K, N, SGLB_FMT_MXFP4);
   SGLB_CHECK(workspace && workspace_bytes >= need, "mxfp4_mm: workspace too small (%zu < %zu)", workspace_bytes, need);
   MoeWorkspace ws = carve(workspace, M, 1, 1, K, N, SGLB_FMT_MXFP4);

@@ -9,27 +9,43 @@ namespace sglb {
 // ---- per-row dynamic int8 quantisation (test_moe_int8.py:23-31) ---------------------------------
 // One CTA per row.  absmax is taken over the bf16 values, scale = absmax.clamp_min(1e-7)/127,
 // q = rint(x * (127/absmax)) -- the same two f32 expressions the reference oracle evaluates.
-__global__ void __launch_bounds__(256) quant_rows_kernel(const __nv_bfloat16* __restrict__ x, int K,
+template <typename TIN>
+__device__ __forceinline__ void load8(const TIN* p, float (&v)[8]);
+template <>
+__device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[8]) {
+  int4 r = *reinterpret_cast<const int4*>(p);
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(&r);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    v[2 * j] = bf16_bits_to_float(w[j] & 0xffffu);
+    v[2 * j + 1] = bf16_bits_to_float(w[j] >> 16);
+  }
+}
+template <>
+__device__ __forceinline__ void load8<float>(const float* p, float (&v)[8]) {
+  float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w, v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
+}
+
+template <typename TIN>
+__global__ void __launch_bounds__(256) quant_rows_kernel(const TIN* __restrict__ x, int K,
                                                          int8_t* __restrict__ q,
                                                          float* __restrict__ scale) {
   const int64_t row = blockIdx.x;
-  const __nv_bfloat16* xr = x + row * K;
+  const TIN* xr = x + row * K;
   int8_t* qr = q + row * K;
   __shared__ float warp_max_s[8];
   float amax = 0.f;
   const bool vec = (K % 8 == 0);
   if (vec) {
     for (int i = threadIdx.x * 8; i < K; i += 256 * 8) {
-      int4 v = *reinterpret_cast<const int4*>(xr + i);
-      const uint32_t* w = reinterpret_cast<const uint32_t*>(&v);
+      float v[8];
+      load8<TIN>(xr + i, v);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        amax = fmaxf(amax, fabsf(bf16_bits_to_float(w[j] & 0xffffu)));
-        amax = fmaxf(amax, fabsf(bf16_bits_to_float(w[j] >> 16)));
-      }
+      for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(v[j]));
     }
   } else {
-    for (int i = threadIdx.x; i < K; i += 256) amax = fmaxf(amax, fabsf(__bfloat162float(xr[i])));
+    for (int i = threadIdx.x; i < K; i += 256) amax = fmaxf(amax, fabsf(load_as_float<TIN>(xr + i)));
   }
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
@@ -39,19 +55,18 @@ __global__ void __launch_bounds__(256) quant_rows_kernel(const __nv_bfloat16* __
 #pragma unroll
   for (int w = 1; w < 8; ++w) amax = fmaxf(amax, warp_max_s[w]);
   amax = fmaxf(amax, 1e-7f);
-  const float inv = 127.0f / amax;
+  // torch evaluates `127 / absmax` (Tensor.__rtruediv__) as reciprocal(absmax) * 127: two roundings
+  const float inv = __fmul_rn(__frcp_rn(amax), 127.0f);
   if (threadIdx.x == 0) scale[row] = amax / 127.0f;
   if (vec) {
     for (int i = threadIdx.x * 8; i < K; i += 256 * 8) {
-      int4 v = *reinterpret_cast<const int4*>(xr + i);
-      const uint32_t* w = reinterpret_cast<const uint32_t*>(&v);
+      float v[8];
+      load8<TIN>(xr + i, v);
       uint32_t o[2];
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
-        int q0 = __float2int_rn(bf16_bits_to_float(w[2 * j] & 0xffffu) * inv);
-        int q1 = __float2int_rn(bf16_bits_to_float(w[2 * j] >> 16) * inv);
-        int q2 = __float2int_rn(bf16_bits_to_float(w[2 * j + 1] & 0xffffu) * inv);
-        int q3 = __float2int_rn(bf16_bits_to_float(w[2 * j + 1] >> 16) * inv);
+        int q0 = __float2int_rn(v[4 * j] * inv), q1 = __float2int_rn(v[4 * j + 1] * inv);
+        int q2 = __float2int_rn(v[4 * j + 2] * inv), q3 = __float2int_rn(v[4 * j + 3] * inv);
         o[j] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) |
                ((uint32_t)(q3 & 0xff) << 24);
       }
@@ -59,7 +74,7 @@ __global__ void __launch_bounds__(256) quant_rows_kernel(const __nv_bfloat16* __
     }
   } else {
     for (int i = threadIdx.x; i < K; i += 256)
-      qr[i] = (int8_t)__float2int_rn(__bfloat162float(xr[i]) * inv);
+      qr[i] = (int8_t)__float2int_rn(load_as_float<TIN>(xr + i) * inv);
   }
 }
 
@@ -178,12 +193,24 @@ extern "C" int sglb_quant_rows_int8(const void* x_bf16, int64_t rows, int K, int
   SGLB_CHECK(x_bf16 && q && scale, "quant_rows: null pointer");
   SGLB_CHECK(K > 0 && rows >= 0, "quant_rows: bad shape");
   if (rows == 0) return SGLB_OK;
-  quant_rows_kernel<<<(unsigned)rows, 256, 0, (cudaStream_t)stream>>>(
+  quant_rows_kernel<__nv_bfloat16><<<(unsigned)rows, 256, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)x_bf16, K, q, scale);
   SGLB_LAUNCH_CHECK();
   count_launch();
   return SGLB_OK;
 }
+
+namespace sglb {
+// f32 rows (the int8 path keeps silu_and_mul in f32 until it is re-quantised, test_moe_int8.py:84-90)
+int launch_quant_rows_f32(const float* x, int64_t rows, int K, int8_t* q, float* scale,
+                          cudaStream_t stream) {
+  if (rows == 0) return SGLB_OK;
+  quant_rows_kernel<float><<<(unsigned)rows, 256, 0, stream>>>(x, K, q, scale);
+  SGLB_LAUNCH_CHECK();
+  count_launch();
+  return SGLB_OK;
+}
+}  // namespace sglb
 
 extern "C" int sglb_topk_reduce(const void* ic2, const int32_t* slot_pos, int64_t M, int topk,
                                 int H, void* out, sglb_stream_t stream) {

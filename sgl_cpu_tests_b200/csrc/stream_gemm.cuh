@@ -29,7 +29,7 @@ struct StreamArgs {
   const int32_t* sorted_slot;
   const float* row_scale;  // stage 2: topk_weights flat [S] (indexed by slot), else nullptr
   const float* bias;       // stage 2 optional f32 [N]
-  void* out;               // bf16 [*, N]  (stage 1: N = I)
+  void* out;               // bf16 [*, N]  (stage 1: N = I; f32 for int8 stage 1)
   int K;
   int N;                   // outputs per row: I (stage 1), H (stage 2)
   int rows_per_expert;     // 2I (stage 1), H (stage 2)
@@ -327,7 +327,10 @@ __global__ void __launch_bounds__(WN* WK * 32)
           gate = xs * gate * ws[n];
           up = xs * up * ws[a.N + n];
         }
-        out[(size_t)p * a.N + n] = __float2bfloat16_rn(silu_f(gate) * up);
+        if (FMT == SGLB_FMT_INT8_W8A8)
+          reinterpret_cast<float*>(a.out)[(size_t)p * a.N + n] = silu_f(gate) * up;
+        else
+          out[(size_t)p * a.N + n] = __float2bfloat16_rn(silu_f(gate) * up);
       } else {
         float rs = 1.f;
         if (a.row_scale != nullptr) rs = a.row_scale[a.sorted_slot[p]];

@@ -388,6 +388,8 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
     on_cuda = hidden_states.is_cuda
     dev = hidden_states.device if on_cuda else _device()
     lib = L.load()
+    if M == 0:
+        return hidden_states if inplace else torch.empty_like(hidden_states)
     with torch.cuda.device(dev):
         x = _to_dev(hidden_states, dev)
         tw = _to_dev(topk_weights, dev, torch.float32)
@@ -534,15 +536,24 @@ def mxfp4_scaled_mm(mat1, mat2, scales2, bias, is_vnni):
         raise RuntimeError("mxfp4_scaled_mm: mat2 / scales2 must be 2-D uint8 tensors")
     M, K = mat1.shape
     N = mat2.shape[0]
-    if mat2.shape[1] * 2 != K or tuple(scales2.shape) != (N, K // 32) or K % 32 != 0:
+    if mat2.shape[1] * 2 != K or K % 32 != 0 or scales2.numel() != N * (K // 32):
         raise RuntimeError(f"mxfp4_scaled_mm: inconsistent shapes A={tuple(mat1.shape)} B={tuple(mat2.shape)} Bs={tuple(scales2.shape)}")
+    scale_vnni = bool(is_vnni)
+    if tuple(scales2.shape) != (N, K // 32):
+        # MXFP4QuantizeUtil.quantize (test_mxfp4.py:69-88) returns the scales flattened to
+        # [N*K/32, 1]; convert_scale_packed of that shape re-tiles with G = 1, i.e. not at all
+        # (test_mxfp4.py:200-201), so the bytes are still row-major [N, K/32].
+        if scales2.dim() != 2 or scales2.shape[1] != 1:
+            raise RuntimeError(f"mxfp4_scaled_mm: scales must be [N, K/32] or [N*K/32, 1], got {tuple(scales2.shape)}")
+        scales2 = scales2.reshape(N, K // 32)
+        scale_vnni = False
     on_cuda = mat1.is_cuda
     dev = mat1.device if on_cuda else _device()
     lib = L.load()
     with torch.cuda.device(dev):
         a = _to_dev(mat1, dev)
         bq = _resident_weight(mat2, bool(is_vnni), dev)
-        bs = _resident_mx_scale(scales2, bool(is_vnni), dev)
+        bs = _resident_mx_scale(scales2, scale_vnni, dev)
         bd = _resident_aux(bias, dev, torch.float32, "b")
         out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
         nws = lib.sglb_fused_experts_workspace_bytes(M, 1, 1, K, N, L.FMT_MXFP4)
