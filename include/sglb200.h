@@ -161,6 +161,27 @@ int sglb_repack_weight(const void* src, void* dst, int elem_bytes, int vnni, int
 int sglb_repack_scale(const void* src, void* dst, int64_t E, int64_t N, int64_t G, int to_packed,
                       sglb_stream_t stream);
 
+/* ---- K8 expert-parallel dispatch / combine ---------------------------------------------------------
+ * Nothing in the reference shards experts; its hook is that fused_experts_cpu ignores ids == -1
+ * (test_moe_offloading_cpu.py:57-68), which is what a rank sees for experts it does not own.
+ * Rank r owns experts [r*E/world, (r+1)*E/world).  These three kernels are the device side of the
+ * exchange; the collective itself (NCCL all-to-all) is issued by the host layer (ep.py).
+ *   plan:    dest_row[m*world + r] = row of token m in the segment sent to rank r (token order) or -1;
+ *            send_count[r] = rows in that segment
+ *   pack:    send_x[seg(r) + dest_row] = hidden[m];  send_meta[row] = {topk local ids (-1 if not owned
+ *            by r), topk weights as f32 bits};  seg(r) = r*cap if cap > 0 (fixed-capacity exchange,
+ *            padding rows read as all -1) else exclusive scan of send_count;  send_rows = total rows
+ *            of the send buffers (cap*world, or sum of send_count)
+ *   combine: out[m] = bf16( sum over r of ret[seg(r) + dest_row[m,r]] ), f32, rank order */
+int sglb_ep_plan(const int32_t* topk_ids, int64_t M, int topk, int E, int world, int32_t* dest_row,
+                 int32_t* send_count, sglb_stream_t stream);
+int sglb_ep_pack(const void* hidden, const int32_t* topk_ids, const float* topk_weights,
+                 const int32_t* dest_row, const int32_t* send_count, int64_t M, int topk, int E,
+                 int world, int H, int cap, int64_t send_rows, void* send_x, int32_t* send_meta,
+                 sglb_stream_t stream);
+int sglb_ep_combine(const void* ret, const int32_t* dest_row, const int32_t* send_count, int64_t M,
+                    int world, int H, int cap, void* out, sglb_stream_t stream);
+
 /* ---- building blocks exposed for tests and for the expert-parallel layer --------------------------
  * per-row dynamic int8 quantisation (test_moe_int8.py:23-31): q = round(x * 127/absmax), scale = absmax/127 */
 int sglb_quant_rows_int8(const void* x_bf16, int64_t rows, int K, int8_t* q, float* scale,

@@ -341,3 +341,63 @@ def pack_scale(s):
     E, N, G = s.shape
     out = s.view(E, N // 32, 32, G).transpose(2, 3).contiguous().view(E, N, G)
     return out.squeeze(0) if squeeze else out
+
+
+# ---------------------------------------------------------------------------------------------------
+# expert-parallel exchange (no counterpart in the reference; "parity unpinned": the layout is this
+# build's own contract, stated identically in csrc/ep.cu.  The only reference hook is that
+# fused_experts_cpu ignores ids == -1, test_moe_offloading_cpu.py:57-68.)
+
+
+def ep_plan(topk_ids, num_experts, world):
+    """dest_row[m, r] = index of token m in the segment sent to rank r (token order) or -1;
+    send_count[r] = rows in that segment.  Rank r owns experts [r*E/world, (r+1)*E/world)."""
+    M = topk_ids.shape[0]
+    e_local = num_experts // world
+    dest_row = torch.full((M, world), -1, dtype=torch.int32)
+    send_count = torch.zeros(world, dtype=torch.int32)
+    ids = topk_ids.long()
+    for r in range(world):
+        flag = ((ids >= r * e_local) & (ids < (r + 1) * e_local)).any(dim=1)
+        n = int(flag.sum())
+        dest_row[flag, r] = torch.arange(n, dtype=torch.int32)
+        send_count[r] = n
+    return dest_row, send_count
+
+
+def ep_seg_start(send_count, world, cap):
+    if cap > 0:
+        return [r * cap for r in range(world)]
+    c = [int(v) for v in send_count]
+    return [sum(c[:r]) for r in range(world)]
+
+
+def ep_pack(x, topk_ids, topk_weights, dest_row, send_count, num_experts, world, cap):
+    """send_x [rows, H], send_meta [rows, 2*topk] int32 (local ids | weight bits); padding rows = -1."""
+    M, topk = topk_ids.shape
+    e_local = num_experts // world
+    rows = cap * world if cap > 0 else int(send_count.sum())
+    seg = ep_seg_start(send_count, world, cap)
+    send_x = torch.zeros(rows, x.shape[1], dtype=x.dtype)
+    meta = torch.full((rows, 2 * topk), -1, dtype=torch.int32)
+    wbits = topk_weights.float().contiguous().view(torch.int32)
+    for r in range(world):
+        sel = dest_row[:, r] >= 0
+        pos = seg[r] + dest_row[sel, r].long()
+        send_x[pos] = x[sel]
+        ids = topk_ids[sel].to(torch.int32)
+        mine = (ids >= r * e_local) & (ids < (r + 1) * e_local)
+        meta[pos, :topk] = torch.where(mine, ids - r * e_local, torch.full_like(ids, -1))
+        meta[pos, topk:] = torch.where(mine, wbits[sel], torch.zeros_like(ids))
+    return send_x, meta
+
+
+def ep_combine(ret, dest_row, send_count, world, cap):
+    """out[m] = bf16(sum_r ret[seg(r) + dest_row[m, r]]) in f32, rank order."""
+    M = dest_row.shape[0]
+    seg = ep_seg_start(send_count, world, cap)
+    acc = torch.zeros(M, ret.shape[1], dtype=torch.float32)
+    for r in range(world):
+        sel = dest_row[:, r] >= 0
+        acc[sel] += ret[seg[r] + dest_row[sel, r].long()].float()
+    return acc.to(ret.dtype)

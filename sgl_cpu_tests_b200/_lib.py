@@ -55,6 +55,10 @@ SIGNATURES = {
     "sglb_repack_weight": (C.c_int, [_vp, _vp, C.c_int, C.c_int, _i64, _i64, _i64, C.c_int, C.c_int, _vp]),
     "sglb_repack_scale": (C.c_int, [_vp, _vp, _i64, _i64, _i64, C.c_int, _vp]),
     "sglb_quant_rows_int8": (C.c_int, [_vp, _i64, C.c_int, _vp, _vp, _vp]),
+    "sglb_ep_plan": (C.c_int, [_vp, _i64, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp]),
+    "sglb_ep_pack": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _i64, _vp,
+                               _vp, _vp]),
+    "sglb_ep_combine": (C.c_int, [_vp, _vp, _vp, _i64, C.c_int, C.c_int, C.c_int, _vp, _vp]),
     "sglb_topk_reduce": (C.c_int, [_vp, _vp, _i64, C.c_int, C.c_int, _vp, _vp]),
 }
 
