@@ -7,6 +7,7 @@
 
 #include "common.cuh"
 #include "stream_gemm.cuh"
+#include "umma_gemm.cuh"
 
 namespace sglb {
 
@@ -57,8 +58,6 @@ int launch_shared_axpy(const void* y, const void* fused, float rsf, int64_t n, v
                        cudaStream_t stream);
 int launch_quant_rows_f32(const float* x, int64_t rows, int K, int8_t* q, float* scale,
                           cudaStream_t stream);
-int umma_supported(int fmt, int64_t M, int topk, int E, int H, int I);
-int launch_umma_moe(const sglb_moe_problem* p, const struct MoeWorkspace& ws, cudaStream_t stream);
 
 // ---- workspace carving -------------------------------------------------------------------------
 struct MoeWorkspace {
@@ -75,7 +74,7 @@ struct MoeWorkspace {
 };
 
 constexpr int kMinChunkRows = 8;
-constexpr int kTileRows = 128;
+constexpr int kTileRows = kUmmaTileRows;
 
 static int64_t max_items(int64_t S, int E, int rows) {
   return (S < E ? S : E) + S / rows + 1;
@@ -176,8 +175,33 @@ static int check_format(const char* who, int fmt, int H, int I, const void* s13,
   return SGLB_OK;
 }
 
-// Two streaming GEMMs over an existing alignment.  `row_scale` = topk weights or NULL.
-static int run_stream_mlp(int fmt, int64_t M, int topk, int E, int H, int I, const void* hidden,
+// One GEMM stage on the tcgen05 path over the tile list of an existing alignment.
+static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64_t S, const MoeWorkspace& ws,
+                          cudaStream_t stream) {
+  UmmaArgs u;
+  memset(&u, 0, sizeof(u));
+  u.W = sa.W;
+  u.Wscale = sa.Wscale;
+  u.X = sa.X;
+  u.Xscale = sa.Xscale;
+  u.tile_list = ws.tile_list;
+  u.counters = ws.counters;
+  u.sorted_slot = ws.sorted_slot;
+  u.row_scale = sa.row_scale;
+  u.out = sa.out;
+  u.K = sa.K;
+  u.N = sa.N;
+  u.rows_per_expert = sa.rows_per_expert;
+  u.E = E;
+  u.topk = sa.topk;
+  u.gather = sa.gather;
+  u.max_tiles = (int)max_items(S, E, kTileRows);
+  return launch_umma_gemm(fmt, stage, u, stream);
+}
+
+// Two grouped GEMMs over an existing alignment (path = SGLB_PATH_STREAM or SGLB_PATH_UMMA).
+// `row_scale` = topk weights or NULL.
+static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, const void* hidden,
                           const void* w13, const void* w2, const void* s13, const void* s2, int bn,
                           int bk, const float* row_scale, const MoeWorkspace& ws, void* ic2_out,
                           cudaStream_t stream) {
@@ -193,7 +217,8 @@ static int run_stream_mlp(int fmt, int64_t M, int topk, int E, int H, int I, con
 
   StreamPlan plan = make_plan(M, topk, E, I, 1);
   plan.max_chunks = (int)max_items(S, E, 8 * plan.ng);
-  SGLB_CHECK(plan.max_chunks <= 65535, "fused_experts(stream path): too many row chunks (%d)", plan.max_chunks);
+  SGLB_CHECK(path == SGLB_PATH_UMMA || plan.max_chunks <= 65535,
+             "fused_experts(stream path): too many row chunks (%d)", plan.max_chunks);
 
   // stage 1
   a.W = w13;
@@ -217,7 +242,8 @@ static int run_stream_mlp(int fmt, int64_t M, int topk, int E, int H, int I, con
   }
   {
     StageTimer t(ST_GEMM1, stream);
-    rc = dispatch_stream<1>(fmt, a, plan, stream);
+    rc = path == SGLB_PATH_UMMA ? run_umma_stage(fmt, 1, a, E, S, ws, stream)
+                                : dispatch_stream<1>(fmt, a, plan, stream);
   }
   if (rc) return rc;
 
@@ -244,7 +270,8 @@ static int run_stream_mlp(int fmt, int64_t M, int topk, int E, int H, int I, con
     a.X = ws.act;
   }
   StageTimer t(ST_GEMM2, stream);
-  return dispatch_stream<2>(fmt, a, plan2, stream);
+  return path == SGLB_PATH_UMMA ? run_umma_stage(fmt, 2, a, E, S, ws, stream)
+                                : dispatch_stream<2>(fmt, a, plan2, stream);
 }
 
 static int run_align(const int32_t* ids, int64_t M, int topk, int E, int chunk_rows,
@@ -331,14 +358,15 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
                "fused_experts: tcgen05 path does not support fmt=%d H=%d I=%d", p->fmt, p->H, p->I);
     rc = run_align(p->topk_ids, p->M, p->topk, p->E, 0, ws, stream);
     if (rc) return rc;
-    rc = launch_umma_moe(p, ws, stream);
+    rc = run_mlp(SGLB_PATH_UMMA, p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2,
+                 p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, ws.ic2, stream);
     if (rc) return rc;
   } else {
     StreamPlan plan = make_plan(p->M, p->topk, p->E, p->I, 1);
     rc = run_align(p->topk_ids, p->M, p->topk, p->E, 8 * plan.ng, ws, stream);
     if (rc) return rc;
-    rc = run_stream_mlp(p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2, p->w13_scale,
-                        p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, ws.ic2, stream);
+    rc = run_mlp(SGLB_PATH_STREAM, p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2,
+                 p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, ws.ic2, stream);
     if (rc) return rc;
   }
   StageTimer t(ST_REDUCE, stream);
@@ -362,8 +390,8 @@ extern "C" int sglb_shared_expert(const sglb_shared_problem* p, sglb_stream_t st
   StreamPlan plan = make_plan(p->M, 1, 1, p->I, 1);
   rc = run_align(ws.zero_ids, p->M, 1, 1, 8 * plan.ng, ws, stream);
   if (rc) return rc;
-  rc = run_stream_mlp(p->fmt, p->M, 1, 1, p->H, p->I, p->hidden, p->w1, p->w2, p->w1_scale, p->w2_scale,
-                      p->block_n, p->block_k, nullptr, ws, ws.ic2, stream);
+  rc = run_mlp(SGLB_PATH_STREAM, p->fmt, p->M, 1, 1, p->H, p->I, p->hidden, p->w1, p->w2, p->w1_scale,
+               p->w2_scale, p->block_n, p->block_k, nullptr, ws, ws.ic2, stream);
   if (rc) return rc;
   return launch_shared_axpy(ws.ic2, p->fused_out, p->routed_scaling_factor, p->M * (int64_t)p->H, p->out, stream);
 }

@@ -1,0 +1,33 @@
+// K3/K4 (prefill regime): interface of the tcgen05 / TMEM / TMA grouped GEMM (umma_gemm.cu).
+#pragma once
+#include "common.cuh"
+
+namespace sglb {
+
+struct UmmaArgs {
+  const void* W;           // [E, rows_per_expert, K] row-major, K contiguous (bf16 or s8)
+  const void* Wscale;      // int8: f32 [E, rows_per_expert]
+  const void* X;           // routed rows, row stride K elements (bf16 or s8)
+  const float* Xscale;     // int8: per X row
+  const int32_t* tile_list;   // (expert, row_start, rows <= 128) from moe_align
+  const int32_t* counters;    // counters[2] = number of tiles
+  const int32_t* sorted_slot;
+  const float* row_scale;  // stage 2: topk_weights flat [S] (indexed by slot) or nullptr
+  void* out;               // stage 1: act [*, I] (bf16; f32 for int8); stage 2: ic2 [*, H] bf16
+  int K;                   // reduction length in elements
+  int N;                   // outputs per routed row: I (stage 1), H (stage 2)
+  int rows_per_expert;     // 2I (stage 1), H (stage 2)
+  int E;
+  int topk;
+  int gather;              // 1: X row = sorted_slot[p] / topk; 0: X row = p
+  int max_tiles;           // host upper bound on counters[2]
+};
+
+constexpr int kUmmaTileRows = 128;  // routed rows per tile (tile_rows handed to moe_align)
+
+// 1 if the tcgen05 path handles this problem (format and divisibility), else 0.
+int umma_supported(int fmt, int64_t M, int topk, int E, int H, int I);
+// stage 1: out = silu(X W13_gate^T) * (X W13_up^T);  stage 2: out = (X W2^T) * row_scale
+int launch_umma_gemm(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream);
+
+}  // namespace sglb

@@ -14,7 +14,7 @@ Tensors may live on the CPU (what the reference scripts allocate) or on a CUDA d
 """
 import math
 import os
-import weakref
+import threading
 from enum import IntEnum
 
 import torch
@@ -59,7 +59,11 @@ def _to_dev(t, dev, dtype=None):
 
 
 # ---- workspace: one growing buffer per (device, stream) ---------------------------------------------
+# Calls that share a stream share its workspace; that is safe because their kernels are stream-ordered,
+# provided the launches of one call are not interleaved with another thread's.  _launch_lock is held
+# from taking the workspace until the (asynchronous) C call has enqueued everything.
 _workspaces = {}
+_launch_lock = threading.RLock()
 
 
 def _workspace(nbytes, dev):
@@ -408,13 +412,14 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
         else:
             out = torch.empty_like(x)
         nws = lib.sglb_fused_experts_workspace_bytes(M, topk, E, H, I, fmt)
-        ws = _workspace(nws, dev)
-        p = L.MoeProblem(M=M, topk=topk, E=E, H=H, I=I, fmt=fmt, path=path, hidden=x.data_ptr(),
-                         w13=w13.data_ptr(), w2=w2d.data_ptr(), topk_weights=tw.data_ptr(),
-                         topk_ids=ids.data_ptr(), w13_scale=_ptr(s13), w2_scale=_ptr(s2), block_n=bn,
-                         block_k=bk, out=out.data_ptr(), workspace=ws.data_ptr(),
-                         workspace_bytes=ws.numel())
-        L.check(lib.sglb_fused_experts(p, _stream()))
+        with _launch_lock:
+            ws = _workspace(nws, dev)
+            p = L.MoeProblem(M=M, topk=topk, E=E, H=H, I=I, fmt=fmt, path=path, hidden=x.data_ptr(),
+                             w13=w13.data_ptr(), w2=w2d.data_ptr(), topk_weights=tw.data_ptr(),
+                             topk_ids=ids.data_ptr(), w13_scale=_ptr(s13), w2_scale=_ptr(s2), block_n=bn,
+                             block_k=bk, out=out.data_ptr(), workspace=ws.data_ptr(),
+                             workspace_bytes=ws.numel())
+            L.check(lib.sglb_fused_experts(p, _stream()))
         if on_cuda:
             if inplace and out is not hidden_states:
                 hidden_states.copy_(out)
@@ -510,12 +515,13 @@ def shared_expert(*args):
         s2d = _resident_aux(s2, dev, torch.float32)
         out = x if (on_cuda and inplace and x.data_ptr() == hs.data_ptr()) else torch.empty_like(x)
         nws = lib.sglb_fused_experts_workspace_bytes(M, 1, 1, H, I, fmt)
-        ws = _workspace(nws, dev)
-        p = L.SharedProblem(M=M, H=H, I=I, fmt=fmt, path=L.PATH_AUTO, hidden=x.data_ptr(), w1=w1d.data_ptr(),
-                            w2=w2d.data_ptr(), w1_scale=_ptr(s1d), w2_scale=_ptr(s2d), block_n=bn, block_k=bk,
-                            fused_out=fo.data_ptr(), routed_scaling_factor=float(rsf), out=out.data_ptr(),
-                            workspace=ws.data_ptr(), workspace_bytes=ws.numel())
-        L.check(lib.sglb_shared_expert(p, _stream()))
+        with _launch_lock:
+            ws = _workspace(nws, dev)
+            p = L.SharedProblem(M=M, H=H, I=I, fmt=fmt, path=L.PATH_AUTO, hidden=x.data_ptr(), w1=w1d.data_ptr(),
+                                w2=w2d.data_ptr(), w1_scale=_ptr(s1d), w2_scale=_ptr(s2d), block_n=bn, block_k=bk,
+                                fused_out=fo.data_ptr(), routed_scaling_factor=float(rsf), out=out.data_ptr(),
+                                workspace=ws.data_ptr(), workspace_bytes=ws.numel())
+            L.check(lib.sglb_shared_expert(p, _stream()))
         if on_cuda:
             if inplace and out is not hs:
                 hs.copy_(out)
@@ -557,9 +563,10 @@ def mxfp4_scaled_mm(mat1, mat2, scales2, bias, is_vnni):
         bd = _resident_aux(bias, dev, torch.float32, "b")
         out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
         nws = lib.sglb_fused_experts_workspace_bytes(M, 1, 1, K, N, L.FMT_MXFP4)
-        ws = _workspace(nws, dev)
-        L.check(lib.sglb_mxfp4_mm(a.data_ptr(), bq.data_ptr(), bs.data_ptr(), _ptr(bd), M, N, K, out.data_ptr(),
-                                  ws.data_ptr(), ws.numel(), _stream()))
+        with _launch_lock:
+            ws = _workspace(nws, dev)
+            L.check(lib.sglb_mxfp4_mm(a.data_ptr(), bq.data_ptr(), bs.data_ptr(), _ptr(bd), M, N, K, out.data_ptr(),
+                                      ws.data_ptr(), ws.numel(), _stream()))
     return out if on_cuda else out.cpu()
 
 

@@ -1,0 +1,107 @@
+"""GPU parity of the tcgen05 (UMMA) grouped-GEMM path: forced with path=PATH_UMMA and compared with the
+CPU oracle and with the weight-streaming path on the same inputs (the two CUDA paths share the align
+pass, the int8 quantisation kernels and the top-k reduce, so they must agree far inside the bf16
+tolerance).  Run with `-m gpu` on the B200 box."""
+import math
+
+import pytest
+import torch
+
+from oracle import moe_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+BF16_TOL = dict(rtol=1e-2, atol=1e-2)  # utils.py:3-12 of the reference
+
+
+@pytest.fixture(scope="module")
+def K():
+    import sgl_cpu_tests_b200 as K
+    assert torch.cuda.is_available()
+    return K
+
+
+def describe(out, ref):
+    d = (out.float() - ref.float()).abs()
+    bad = d > (1e-2 + 1e-2 * ref.float().abs())
+    rows = bad.any(dim=1).nonzero().flatten().tolist()
+    cols = bad.any(dim=0).nonzero().flatten().tolist()
+    return (f"max diff {d.max():.5f}, {int(bad.sum())}/{bad.numel()} bad, bad rows {rows[:12]}... ({len(rows)}), "
+            f"bad cols {cols[:12]}... ({len(cols)}), out[0,:4]={out[0, :4].tolist()} ref[0,:4]={ref[0, :4].tolist()}")
+
+
+def make_ids(M, E, topk, style, gen):
+    if style == "uniform":
+        score = torch.rand(M, E, generator=gen)
+        return torch.topk(score, topk).indices.to(torch.int32)
+    if style == "skewed":      # a few hot experts (many tiles each) + masked slots + duplicates in a row
+        ids = torch.randint(0, max(1, E // 4), (M, topk), generator=gen, dtype=torch.int32)
+        ids[torch.rand(M, topk, generator=gen) < 0.1] = -1
+        return ids
+    if style == "one":         # everything on one expert: rows = M*topk, several full 128-row tiles
+        return torch.full((M, topk), E - 1, dtype=torch.int32)
+    raise ValueError(style)
+
+
+CASES = [  # M, I, H, E, topk, style
+    (64, 128, 128, 4, 2, "uniform"),
+    (300, 128, 256, 8, 2, "uniform"),
+    (257, 192, 320, 8, 4, "skewed"),      # partial weight blocks in both stages, ragged tiles, -1 ids
+    (130, 256, 128, 4, 2, "one"),
+    (1, 128, 128, 2, 1, "uniform"),       # a single routed row
+    (148, 128, 256, 4, 4, "skewed"),      # the expert-parallel local shape: one hot expert, masked ids
+    (1024, 768, 2048, 128, 8, "uniform"),  # Qwen3-30B-A3B layer shape
+]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_umma_bf16(K, case):
+    M, I, H, E, topk, style = case
+    g = torch.Generator().manual_seed(1111)
+    a = torch.randn(M, H, generator=g).bfloat16() / 10
+    w1 = (torch.randn(E, 2 * I, H, generator=g) / 10).bfloat16()
+    w2 = (torch.randn(E, H, I, generator=g) / 10).bfloat16()
+    ids = make_ids(M, E, topk, style, g)
+    tw = torch.rand(M, topk, generator=g)
+    ref = O.native_fused_moe(a, w1, w2, tw, ids)
+    ad, w1d, w2d, twd, idd = a.cuda(), w1.cuda(), w2.cuda(), tw.cuda(), ids.cuda()
+    out_s = K.fused_experts_impl(ad, w1d, w2d, twd, idd, False, K.FMT_BF16, None, None, None, False, path=K.PATH_STREAM)
+    out_u = K.fused_experts_impl(ad, w1d, w2d, twd, idd, False, K.FMT_BF16, None, None, None, False, path=K.PATH_UMMA)
+    torch.cuda.synchronize()
+    out_s, out_u = out_s.cpu(), out_u.cpu()
+    assert torch.isfinite(out_u).all(), describe(out_u, ref)
+    assert torch.allclose(out_u.float(), ref.float(), **BF16_TOL), "vs oracle: " + describe(out_u, ref)
+    assert torch.allclose(out_u.float(), out_s.float(), **BF16_TOL), "vs stream: " + describe(out_u, out_s)
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_umma_int8(K, case):
+    M, I, H, E, topk, style = case
+    g = torch.Generator().manual_seed(1111)
+    a = (torch.randn(M, H, generator=g) / math.sqrt(H)).bfloat16()
+    w1 = torch.randint(-127, 128, (E, 2 * I, H), generator=g, dtype=torch.int8)
+    w2 = torch.randint(-127, 128, (E, H, I), generator=g, dtype=torch.int8)
+    s1, s2 = torch.rand(E, 2 * I, generator=g) * 1e-2, torch.rand(E, H, generator=g) * 1e-2
+    ids = make_ids(M, E, topk, style, g)
+    tw = torch.rand(M, topk, generator=g)
+    ad, w1d, w2d, twd, idd, s1d, s2d = (t.cuda() for t in (a, w1, w2, tw, ids, s1, s2))
+    out_s = K.fused_experts_impl(ad, w1d, w2d, twd, idd, False, K.FMT_INT8_W8A8, s1d, s2d, None, False, path=K.PATH_STREAM)
+    out_u = K.fused_experts_impl(ad, w1d, w2d, twd, idd, False, K.FMT_INT8_W8A8, s1d, s2d, None, False, path=K.PATH_UMMA)
+    torch.cuda.synchronize()
+    out_s, out_u = out_s.cpu(), out_u.cpu()
+    assert torch.isfinite(out_u).all(), describe(out_u, out_s)
+    # integer accumulation is exact on both paths and the epilogues use the same f32 expressions
+    assert torch.equal(out_u, out_s), "vs stream: " + describe(out_u, out_s)
+    if M * topk * H * I <= 300 * 2 * 256 * 128 * 8:
+        ref = O.fused_experts(a, w1, w2, tw, ids, "int8", s1, s2)
+        rel = float((out_u.float() - ref.float()).abs().mean() / ref.float().abs().mean().clamp_min(1e-12))
+        assert rel < 0.01, f"mean rel {rel}: " + describe(out_u, ref)      # test_moe_int8.py:134-137
+
+
+def test_umma_unsupported_shape_raises(K):
+    a = torch.randn(8, 96, dtype=torch.bfloat16, device="cuda")    # 96 * 2 B is not a whole 128-B K slab
+    w1 = torch.randn(2, 64, 96, dtype=torch.bfloat16, device="cuda")
+    w2 = torch.randn(2, 96, 32, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(RuntimeError):
+        K.fused_experts_impl(a, w1, w2, torch.ones(8, 1, device="cuda"), torch.zeros(8, 1, dtype=torch.int32, device="cuda"),
+                             False, K.FMT_BF16, None, None, None, False, path=K.PATH_UMMA)
