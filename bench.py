@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--sweep", default="1,16,128,1024,4096", help="extra M values reported under 'sweep'")
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--path", default="auto", choices=["auto", "stream", "umma"], help="GEMM path (auto = by rows/expert)")
     ap.add_argument("--copies", type=int, default=2, help="weight copies rotated between steps (bench_moe.py:50-58)")
     return ap.parse_args()
 
@@ -156,6 +157,19 @@ def dist_env():
 
 
 FMT_ID = {"bf16": 0, "int8": 1, "fp8": 2, "mxfp4": 4}
+PATHS = {"auto": 0, "stream": 1, "umma": 2}
+
+
+def path_used(args, fmt, M, topk, E, H, I):
+    """Mirrors the SGLB_PATH_AUTO rule of capi.cu (rows/expert >= 24 and a supported shape)."""
+    if args.path != "auto":
+        return args.path
+    eb = {"bf16": 2, "int8": 1}.get(fmt)
+    ok = eb is not None and (H * eb) % 128 == 0 and (I * eb) % 128 == 0
+    return "umma" if ok and M * topk / E >= 24.0 else "stream"
+
+
+PATH_DESC = {"stream": "stream (mma.sync weight streaming)", "umma": "umma (tcgen05 + TMEM + TMA)"}
 
 
 def time_steps(fn, steps, warmup, world):
@@ -215,7 +229,8 @@ def run_b200(args):
             w = layer_sets[i % len(layer_sets)]
             if world > 1:
                 return w.forward(x, tw, ids)
-            return K.fused_experts_impl(x, w["w1"], w["w2"], tw, ids, False, FMT_ID[fmt], w["s1"], w["s2"], w["block"], False)
+            return K.fused_experts_impl(x, w["w1"], w["w2"], tw, ids, False, FMT_ID[fmt], w["s1"], w["s2"], w["block"], False,
+                                        path=PATHS[args.path])
         return step
 
     x, tw, ids = make_batch(M, E, topk, H, dev, gen)
@@ -243,7 +258,7 @@ def run_b200(args):
         "config": {"workload": f"{args.shape} MoE layer {fmt}: E={E} topk={topk} H={H} I={I}, M={M} tokens/step/GPU",
                    "tokens_per_step_per_gpu": M, "parallelism": "single GPU" if world == 1 else f"ep{world}",
                    "l2_policy": f"inputs larger than L2: {args.copies} weight copies rotated between steps",
-                   "path": "stream (mma.sync weight streaming)"},
+                   "path": PATH_DESC[path_used(args, fmt, M, topk, E, H, I)]},
         "clocks": clk, "gpu_launches": int(launches),
     }
 

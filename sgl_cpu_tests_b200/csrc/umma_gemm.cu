@@ -38,13 +38,16 @@ constexpr int kWSub = 128;                           // weight rows per accumula
 constexpr int kWTileBytes = kWSub * kRowBytes;       // 16 KB
 constexpr int kXTileBytes = kUmmaTileRows * kRowBytes;
 constexpr int kStageBytes = 2 * kWTileBytes + kXTileBytes;  // 48 KB
-constexpr int kThreads = 320;
 constexpr int kGatherThreads = 128;
-constexpr int kEpiThreads = 128;
-constexpr int kLag = 2;                              // cp.async groups in flight per gather thread
+constexpr int kEpiWarps = 8;                         // two per TMEM lane quadrant (one per 16-column parity)
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kFirstEpiWarp = 6;
+constexpr int kThreads = (kFirstEpiWarp + kEpiWarps) * 32;  // 448
 constexpr int kTmemCols = 512;
 constexpr int kAccCols = 256;                        // per accumulator buffer: 2 sub-tiles x 128
-constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int kEpiBufBytes = 16 * 32 * 4;            // per epilogue warp: 16 tokens x 32 outputs, f32 worst case
+constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBufBytes + 1024 /*alignment slack*/ +
+                           256 /*barriers*/;
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -95,12 +98,10 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() {
-  asm volatile("cp.async.commit_group;" ::: "memory");
-}
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+// mbarrier arrive (counted in the barrier's expected arrivals) once all cp.async issued so far by this
+// thread have landed: the gather producers never block on their own loads
+__device__ __forceinline__ void cp_async_arrive_noinc(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
 // D[tmem] (+)= A[smem desc] * B[smem desc]; issued by one thread on behalf of the CTA
 template <int FMT>
@@ -187,7 +188,8 @@ __global__ void __launch_bounds__(kThreads, 1)
     umma_moe_kernel(const __grid_constant__ CUtensorMap tmap_w, const UmmaArgs a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B: 1 KB aligned
-  const uint32_t bar_base = smem_base + kStages * kStageBytes;
+  const uint32_t epi_base = smem_base + kStages * kStageBytes;
+  const uint32_t bar_base = epi_base + kEpiWarps * kEpiBufBytes;
   auto w_tile = [&](int s) { return smem_base + s * kStageBytes; };
   auto x_tile = [&](int s) { return smem_base + s * kStageBytes + 2 * kWTileBytes; };
   auto full_bar = [&](int s) { return bar_base + 8 * s; };
@@ -261,6 +263,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int s = it % kStages;
           mbar_wait(full_bar(s), (it / kStages) & 1);
+          fence_proxy_async();  // routed rows were written by cp.async (generic proxy)
           tc_fence_after();
 #pragma unroll
           for (int sub = 0; sub < 2; ++sub) {
@@ -301,23 +304,25 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           if (rbase + 16 * j < n_eff) cp_async16(dst + j * 16 * kRowBytes, src[j] + kb * kRowBytes);
-        cp_async_commit();
-        if (it >= kLag) {
-          cp_async_wait<kLag>();
-          fence_proxy_async();
-          mbar_arrive(full_bar((it - kLag) % kStages));
-        }
+        cp_async_arrive_noinc(full_bar(s));
       }
     }
-    cp_async_wait<0>();
-    fence_proxy_async();
-    for (uint32_t d = (it < (uint32_t)kLag ? it : (uint32_t)kLag); d > 0; --d)
-      mbar_arrive(full_bar((it - d) % kStages));
   } else {
     // ================= epilogue =================
-    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    // Eight warps: warp (q, par) owns TMEM lanes [32q, 32q+32) (= 32 consecutive outputs n) and the
+    // 16-column (= 16-token) chunks of parity par.  A chunk is transposed through a private smem
+    // buffer so that global stores are 16 B per lane and whole 64/128-B row segments per token.
+    const int ew = warp - kFirstEpiWarp;
+    const int q = warp & 3, par = ew >> 2;
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
     constexpr bool kInt8 = FMT == SGLB_FMT_INT8_W8A8;
+    constexpr int OB = (kInt8 && STAGE == 1) ? 4 : 2;  // output element bytes (f32 act for int8 stage 1)
+    constexpr int ROWB = 32 * OB;                      // bytes per token row in the transpose buffer
+    constexpr int SEGS = ROWB / 16;                    // lanes per token row on the read side
+    constexpr int TPI = 32 / SEGS;                     // token rows per read instruction
+    constexpr int NRD = 16 / TPI;                      // read instructions per chunk
+    uint8_t* ebuf = smem_raw + (epi_base + ew * kEpiBufBytes - smem_u32(smem_raw));
+    const int rd_tok = lane / SEGS, rd_seg = lane % SEGS;
     uint32_t li = 0;
     for (int w = blockIdx.x; w < total; w += gridDim.x, ++li) {
       const WorkItem wi = get_item(a, w, n_blocks);
@@ -344,19 +349,21 @@ __global__ void __launch_bounds__(kThreads, 1)
       mbar_wait(tfull_bar(buf), (li >> 1) & 1);
       tc_fence_after();
       const uint32_t acc = tmem_base + lane_off + buf * kAccCols;
-      if constexpr (STAGE == 1) {
-        const int n = wi.nb * kWSub + q * 32 + lane;
-        const bool n_ok = n < a.N;
-        float wsg = 1.f, wsu = 1.f;
-        if (kInt8 && n_ok) {
+      constexpr int kSubs = STAGE == 1 ? 1 : 2;
+#pragma unroll 1
+      for (int sub = 0; sub < kSubs; ++sub) {
+        const int nbase = STAGE == 1 ? wi.nb * kWSub + q * 32 : wi.nb * 2 * kWSub + sub * kWSub + q * 32;
+        const int n = nbase + lane;
+        float ws0 = 1.f, ws1 = 1.f;
+        if (kInt8 && n < a.N) {
           const float* ws = (const float*)a.Wscale + (size_t)wi.e * a.rows_per_expert;
-          wsg = ws[n];
-          wsu = ws[a.N + n];
+          ws0 = ws[n];
+          if (STAGE == 1) ws1 = ws[a.N + n];
         }
 #pragma unroll 1
-        for (int c0 = 0; c0 < n_eff; c0 += 16) {  // n_eff is warp-uniform
-          {
-            const float xsel = sel4(xs_r, c0 >> 5);
+        for (int c0 = 16 * par; c0 < n_eff; c0 += 32) {  // n_eff is warp-uniform
+          const float xsel = sel4(xs_r, c0 >> 5), rsel = sel4(rs_r, c0 >> 5);
+          if constexpr (STAGE == 1) {
             uint32_t gv[16], uv[16];
             tmem_ld16(acc + c0, gv);
             tmem_ld16(acc + kWSub + c0, uv);
@@ -364,51 +371,45 @@ __global__ void __launch_bounds__(kThreads, 1)
             tmem_ld_wait(uv);
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
-              const float xs = kInt8 ? __shfl_sync(0xffffffffu, xsel, (c0 & 16) + j) : 1.f;
-              if (c0 + j < wi.rows && n_ok) {
-                const size_t o = (size_t)(wi.row_start + c0 + j) * a.N + n;
-                if constexpr (kInt8) {
-                  const float gate = xs * (float)(int)gv[j] * wsg;
-                  const float up = xs * (float)(int)uv[j] * wsu;
-                  reinterpret_cast<float*>(a.out)[o] = silu_f(gate) * up;
-                } else {
-                  const float gate = __uint_as_float(gv[j]), up = __uint_as_float(uv[j]);
-                  reinterpret_cast<__nv_bfloat16*>(a.out)[o] = __float2bfloat16_rn(silu_f(gate) * up);
-                }
+              if constexpr (kInt8) {
+                const float xs = __shfl_sync(0xffffffffu, xsel, 16 * par + j);
+                const float gate = xs * (float)(int)gv[j] * ws0;
+                const float up = xs * (float)(int)uv[j] * ws1;
+                *reinterpret_cast<float*>(ebuf + j * ROWB + lane * 4) = silu_f(gate) * up;
+              } else {
+                const float gate = __uint_as_float(gv[j]), up = __uint_as_float(uv[j]);
+                *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) =
+                    __float2bfloat16_rn(silu_f(gate) * up);
               }
             }
-          }
-        }
-      } else {
-#pragma unroll 1
-        for (int sub = 0; sub < 2; ++sub) {
-          const int n = wi.nb * 2 * kWSub + sub * kWSub + q * 32 + lane;
-          const bool n_ok = n < a.N;
-          float wsn = 1.f;
-          if (kInt8 && n_ok) wsn = ((const float*)a.Wscale)[(size_t)wi.e * a.rows_per_expert + n];
-#pragma unroll 1
-          for (int c0 = 0; c0 < n_eff; c0 += 16) {  // n_eff is warp-uniform
-            {
-              const float xsel = sel4(xs_r, c0 >> 5), rsel = sel4(rs_r, c0 >> 5);
-              uint32_t v[16];
-              tmem_ld16(acc + sub * kWSub + c0, v);
-              tmem_ld_wait(v);
+          } else {
+            uint32_t v[16];
+            tmem_ld16(acc + sub * kWSub + c0, v);
+            tmem_ld_wait(v);
 #pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                const float xs = kInt8 ? __shfl_sync(0xffffffffu, xsel, (c0 & 16) + j) : 1.f;
-                const float rs = __shfl_sync(0xffffffffu, rsel, (c0 & 16) + j);
-                if (c0 + j < wi.rows && n_ok) {
-                  float val;
-                  if constexpr (kInt8)
-                    val = xs * (float)(int)v[j] * wsn;
-                  else
-                    val = __uint_as_float(v[j]);
-                  reinterpret_cast<__nv_bfloat16*>(a.out)[(size_t)(wi.row_start + c0 + j) * a.N + n] =
-                      __float2bfloat16_rn(val * rs);
-                }
+            for (int j = 0; j < 16; ++j) {
+              const float rs = __shfl_sync(0xffffffffu, rsel, 16 * par + j);
+              float val;
+              if constexpr (kInt8) {
+                const float xs = __shfl_sync(0xffffffffu, xsel, 16 * par + j);
+                val = xs * (float)(int)v[j] * ws0;
+              } else {
+                val = __uint_as_float(v[j]);
               }
+              *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(val * rs);
             }
           }
+          __syncwarp();
+          const int nn = nbase + rd_seg * (16 / OB);  // first output held by this lane's 16 bytes
+#pragma unroll
+          for (int i = 0; i < NRD; ++i) {
+            const int tok = rd_tok + TPI * i;
+            const int4 piece = *reinterpret_cast<const int4*>(ebuf + tok * ROWB + rd_seg * 16);
+            if (c0 + tok < wi.rows && nn < a.N)
+              *reinterpret_cast<int4*>((char*)a.out +
+                                       ((size_t)(wi.row_start + c0 + tok) * a.N + nn) * OB) = piece;
+          }
+          __syncwarp();
         }
       }
       tc_fence_before();

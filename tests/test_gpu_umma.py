@@ -74,7 +74,12 @@ def test_umma_bf16(K, case):
     assert torch.allclose(out_u.float(), out_s.float(), **BF16_TOL), "vs stream: " + describe(out_u, out_s)
 
 
-@pytest.mark.parametrize("case", CASES)
+INT8_CASES = [c for c in CASES if c[1] % 128 == 0 and c[2] % 128 == 0] + [
+    (257, 256, 384, 8, 4, "skewed"),      # partial weight block in stage 2 (H = 384 = 256 + 128)
+]
+
+
+@pytest.mark.parametrize("case", INT8_CASES)
 def test_umma_int8(K, case):
     M, I, H, E, topk, style = case
     g = torch.Generator().manual_seed(1111)
