@@ -161,12 +161,12 @@ PATHS = {"auto": 0, "stream": 1, "umma": 2}
 
 
 def path_used(args, fmt, M, topk, E, H, I):
-    """Mirrors the SGLB_PATH_AUTO rule of capi.cu (rows/expert >= 24 and a supported shape)."""
+    """Mirrors the SGLB_PATH_AUTO rule of capi.cu (rows/expert >= 4 and a supported shape)."""
     if args.path != "auto":
         return args.path
     eb = {"bf16": 2, "int8": 1}.get(fmt)
     ok = eb is not None and (H * eb) % 128 == 0 and (I * eb) % 128 == 0
-    return "umma" if ok and M * topk / E >= 24.0 else "stream"
+    return "umma" if ok and M * topk / E >= 4.0 else "stream"
 
 
 PATH_DESC = {"stream": "stream (mma.sync weight streaming)", "umma": "umma (tcgen05 + TMEM + TMA)"}
@@ -277,7 +277,10 @@ def run_b200(args):
         stage_us = {STAGES[i]: (msv[i] / cnt[i] * 1e3 if cnt[i] else 0.0) for i in range(6)}
         k_us = stage_us["w13_gemm"]
         achieved = ab["w13"] / (k_us * 1e-6) / 1e9 if k_us > 0 else 0.0
-        out["roofline"] = {"bound": "hbm", "kernel": "stream_gemm_kernel<stage 1> (w13 GEMM + silu_and_mul)",
+        used = path_used(args, fmt, M, topk, E, H, I)
+        kname = ("umma_moe_kernel<stage 1> (tcgen05 w13 GEMM + silu_and_mul)" if used == "umma"
+                 else "stream_gemm_kernel<stage 1> (mma.sync w13 GEMM + silu_and_mul)")
+        out["roofline"] = {"bound": "hbm", "kernel": kname,
                            "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                            "peak_source": peak_src, "traffic": None, "kernel_us": k_us,
                            "algorithmic_bytes": ab["w13"], "active_experts": ab["e_act"],

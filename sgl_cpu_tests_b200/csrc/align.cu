@@ -78,6 +78,8 @@ __global__ void __launch_bounds__(kAlignThreads) align_count_kernel(const int32_
                                                                    int32_t* __restrict__ block_hist) {
   extern __shared__ int smem_i[];
   int* hist = smem_i;
+  pdl_wait();
+  pdl_trigger();
   for (int x = threadIdx.x; x < E; x += kAlignThreads) hist[x] = 0;
   __syncthreads();
   int slot = blockIdx.x * kAlignThreads + threadIdx.x;
@@ -101,6 +103,8 @@ __global__ void __launch_bounds__(kAlignThreads)
   int* base = block_total + E;          // [E]  expert_offset + slots in earlier blocks
   int* warp_sums = base + E;            // [33]
   uint16_t* warp_cnt = reinterpret_cast<uint16_t*>(warp_sums + 34);  // [32*E]
+  pdl_wait();
+  pdl_trigger();
 
   const int slot = blockIdx.x * kAlignThreads + threadIdx.x;
   int e = -1;
@@ -206,20 +210,18 @@ extern "C" int sglb_moe_align(const int32_t* topk_ids, int64_t M, int topk, int 
   const int nb = S > 0 ? ceil_div(S, kAlignThreads) : 1;
   if (nb > 1) {
     SGLB_CHECK(scratch != nullptr, "moe_align: scratch required for M*topk > %d", kAlignThreads);
-    align_count_kernel<<<nb, kAlignThreads, E * sizeof(int), stream>>>(topk_ids, S, E,
-                                                                     (int32_t*)scratch);
-    SGLB_LAUNCH_CHECK();
+    SGLB_CUDA(launch_pdl(align_count_kernel, dim3(nb), dim3(kAlignThreads), E * sizeof(int), stream,
+                         topk_ids, S, E, (int32_t*)scratch));
   }
   size_t smem = (size_t)(2 * E + 34) * sizeof(int) + (size_t)32 * E * sizeof(uint16_t);
   if (smem > 48 * 1024) {
     SGLB_CUDA(cudaFuncSetAttribute(align_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)smem));
   }
-  align_scatter_kernel<<<nb, kAlignThreads, smem, stream>>>(
-      topk_ids, S, E, nb, (const int32_t*)scratch, chunk_rows, tile_rows, out->expert_count,
-      out->expert_offset, out->sorted_slot, out->slot_pos, out->chunk_list, out->tile_list,
-      out->counters);
-  SGLB_LAUNCH_CHECK();
+  SGLB_CUDA(launch_pdl(align_scatter_kernel, dim3(nb), dim3(kAlignThreads), smem, stream, topk_ids, S, E,
+                       nb, (const int32_t*)scratch, chunk_rows, tile_rows, out->expert_count,
+                       out->expert_offset, out->sorted_slot, out->slot_pos, out->chunk_list,
+                       out->tile_list, out->counters));
   count_launch(nb > 1 ? 2 : 1);
   return SGLB_OK;
 }

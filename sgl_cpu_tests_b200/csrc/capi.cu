@@ -74,6 +74,9 @@ struct MoeWorkspace {
 };
 
 constexpr int kMinChunkRows = 8;
+// Measured on B200 (Qwen3 shape): the persistent TMA-fed tcgen05 kernel streams weights faster than the
+// mma.sync kernel from about 4 routed rows per expert upwards and ties below.
+constexpr double kUmmaMinRowsPerExpert = 4.0;
 constexpr int kTileRows = kUmmaTileRows;
 
 static int64_t max_items(int64_t S, int E, int rows) {
@@ -349,7 +352,7 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
   int path = p->path;
   if (path == SGLB_PATH_AUTO) {
     const double rows_per_expert = (double)p->M * p->topk / p->E;
-    path = (rows_per_expert >= 24.0 && umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I))
+    path = (rows_per_expert >= kUmmaMinRowsPerExpert && umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I))
                ? SGLB_PATH_UMMA
                : SGLB_PATH_STREAM;
   }

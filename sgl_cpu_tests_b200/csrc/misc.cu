@@ -31,6 +31,8 @@ template <typename TIN>
 __global__ void __launch_bounds__(256) quant_rows_kernel(const TIN* __restrict__ x, int K,
                                                          int8_t* __restrict__ q,
                                                          float* __restrict__ scale) {
+  pdl_wait();
+  pdl_trigger();
   const int64_t row = blockIdx.x;
   const TIN* xr = x + row * K;
   int8_t* qr = q + row * K;
@@ -84,6 +86,8 @@ __global__ void __launch_bounds__(256) quant_rows_kernel(const TIN* __restrict__
 __global__ void __launch_bounds__(256)
     topk_reduce_kernel(const __nv_bfloat16* __restrict__ ic2, const int32_t* __restrict__ slot_pos,
                        int topk, int H, __nv_bfloat16* __restrict__ out) {
+  pdl_wait();
+  pdl_trigger();
   const int64_t m = blockIdx.y;
   const int h0 = (blockIdx.x * 256 + threadIdx.x) * 8;
   if (h0 >= H) return;
@@ -120,6 +124,8 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     shared_axpy_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ fused,
                        float rsf, int64_t n, __nv_bfloat16* __restrict__ out) {
+  pdl_wait();
+  pdl_trigger();
   int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (i < n) out[i] = __float2bfloat16_rn(__bfloat162float(y[i]) + __bfloat162float(fused[i]) * rsf);
 }
@@ -193,9 +199,8 @@ extern "C" int sglb_quant_rows_int8(const void* x_bf16, int64_t rows, int K, int
   SGLB_CHECK(x_bf16 && q && scale, "quant_rows: null pointer");
   SGLB_CHECK(K > 0 && rows >= 0, "quant_rows: bad shape");
   if (rows == 0) return SGLB_OK;
-  quant_rows_kernel<__nv_bfloat16><<<(unsigned)rows, 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)x_bf16, K, q, scale);
-  SGLB_LAUNCH_CHECK();
+  SGLB_CUDA(launch_pdl(quant_rows_kernel<__nv_bfloat16>, dim3((unsigned)rows), dim3(256), 0,
+                       (cudaStream_t)stream, (const __nv_bfloat16*)x_bf16, K, q, scale));
   count_launch();
   return SGLB_OK;
 }
@@ -205,8 +210,7 @@ namespace sglb {
 int launch_quant_rows_f32(const float* x, int64_t rows, int K, int8_t* q, float* scale,
                           cudaStream_t stream) {
   if (rows == 0) return SGLB_OK;
-  quant_rows_kernel<float><<<(unsigned)rows, 256, 0, stream>>>(x, K, q, scale);
-  SGLB_LAUNCH_CHECK();
+  SGLB_CUDA(launch_pdl(quant_rows_kernel<float>, dim3((unsigned)rows), dim3(256), 0, stream, x, K, q, scale));
   count_launch();
   return SGLB_OK;
 }
@@ -221,9 +225,9 @@ extern "C" int sglb_topk_reduce(const void* ic2, const int32_t* slot_pos, int64_
   for (int64_t m0 = 0; m0 < M; m0 += 65535) {
     int64_t mm = M - m0 < 65535 ? M - m0 : 65535;
     dim3 grid((unsigned)ceil_div(ceil_div(H, 8), 256), (unsigned)mm);
-    topk_reduce_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
-        (const __nv_bfloat16*)ic2, slot_pos + m0 * topk, topk, H, (__nv_bfloat16*)out + m0 * H);
-    SGLB_LAUNCH_CHECK();
+    SGLB_CUDA(launch_pdl(topk_reduce_kernel, grid, dim3(256), 0, (cudaStream_t)stream,
+                         (const __nv_bfloat16*)ic2, slot_pos + m0 * topk, topk, H,
+                         (__nv_bfloat16*)out + m0 * H));
     count_launch();
   }
   return SGLB_OK;
@@ -233,9 +237,8 @@ namespace sglb {
 int launch_shared_axpy(const void* y, const void* fused, float rsf, int64_t n, void* out,
                        cudaStream_t stream) {
   if (n == 0) return SGLB_OK;
-  shared_axpy_kernel<<<(unsigned)ceil_div64(n, 256), 256, 0, stream>>>(
-      (const __nv_bfloat16*)y, (const __nv_bfloat16*)fused, rsf, n, (__nv_bfloat16*)out);
-  SGLB_LAUNCH_CHECK();
+  SGLB_CUDA(launch_pdl(shared_axpy_kernel, dim3((unsigned)ceil_div64(n, 256)), dim3(256), 0, stream,
+                       (const __nv_bfloat16*)y, (const __nv_bfloat16*)fused, rsf, n, (__nv_bfloat16*)out));
   count_launch();
   return SGLB_OK;
 }

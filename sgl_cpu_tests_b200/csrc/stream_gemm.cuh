@@ -86,6 +86,8 @@ __global__ void __launch_bounds__(WN* WK * 32)
   constexpr int U = 4 * PE;  // k elements per unit (one 16-B load per lane and weight row)
   constexpr int XV = T::XV;
 
+  pdl_wait();
+  pdl_trigger();
   const int chunk = blockIdx.y;
   if (chunk >= a.counters[1]) return;
   const int e = a.chunk_list[3 * chunk + 0];
@@ -377,8 +379,7 @@ static int stream_launch_one(const StreamArgs& a, int max_chunks, cudaStream_t s
   constexpr int PD = stream_prefetch_depth<FMT, NG>();
   const int rows_per_cta = (STAGE == 1 ? 16 : 32) * WN;
   dim3 grid((unsigned)ceil_div(a.N, rows_per_cta), (unsigned)max_chunks);
-  stream_gemm_kernel<FMT, STAGE, NG, WN, WK, PD><<<grid, WN * WK * 32, 0, stream>>>(a);
-  SGLB_LAUNCH_CHECK();
+  SGLB_CUDA(launch_pdl(stream_gemm_kernel<FMT, STAGE, NG, WN, WK, PD>, grid, dim3(WN * WK * 32), 0, stream, a));
   return SGLB_OK;
 }
 

@@ -205,7 +205,6 @@ __global__ void __launch_bounds__(kThreads, 1)
   const int k_bytes = a.K * EB;
   const int num_kb = k_bytes / kRowBytes;
   const int n_blocks = num_weight_blocks<STAGE>(a);
-  const int total = a.counters[2] * n_blocks;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_w)) : "memory");
@@ -229,6 +228,10 @@ __global__ void __launch_bounds__(kThreads, 1)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  // Everything above overlapped the previous kernel's tail; its outputs are read from here on.
+  pdl_wait();
+  pdl_trigger();
+  const int total = a.counters[2] * n_blocks;
 
   if (warp == 0) {
     // ================= TMA producer: weights =================
@@ -513,8 +516,7 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   const int n_blocks = STAGE == 1 ? ceil_div(a.N, kWSub) : ceil_div(a.N, 2 * kWSub);
   const int64_t max_items = (int64_t)a.max_tiles * n_blocks;
   const int grid = (int)(max_items < sm_count() ? (max_items > 0 ? max_items : 1) : sm_count());
-  umma_moe_kernel<FMT, STAGE><<<grid, kThreads, kSmemBytes, stream>>>(map, a);
-  SGLB_LAUNCH_CHECK();
+  SGLB_CUDA(launch_pdl(umma_moe_kernel<FMT, STAGE>, dim3(grid), dim3(kThreads), kSmemBytes, stream, map, a));
   return SGLB_OK;
 }
 

@@ -52,7 +52,9 @@ def _to_dev(t, dev, dtype=None):
     if t is None:
         return None
     if t.device != dev:
-        t = t.to(dev, non_blocking=False)
+        # pinned host memory: stream-ordered async copy (every entry point ends with a blocking D2H of
+        # its result or returns device tensors ordered on the same stream, so the source stays valid)
+        t = t.to(dev, non_blocking=(t.device.type == "cpu" and t.is_pinned()))
     if dtype is not None and t.dtype != dtype:
         t = t.to(dtype)
     return t.contiguous()
