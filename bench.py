@@ -280,9 +280,14 @@ def run_b200(args):
         used = path_used(args, fmt, M, topk, E, H, I)
         kname = ("umma_moe_kernel<stage 1> (tcgen05 w13 GEMM + silu_and_mul)" if used == "umma"
                  else "stream_gemm_kernel<stage 1> (mma.sync w13 GEMM + silu_and_mul)")
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            ent = json.load(open(tpath)).get(f"{args.shape}/{fmt}/M={M}/{used}_stage1")
+            traffic = ent["bytes"] if ent else None
         out["roofline"] = {"bound": "hbm", "kernel": kname,
                            "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                           "peak_source": peak_src, "traffic": None, "kernel_us": k_us,
+                           "peak_source": peak_src, "traffic": traffic, "kernel_us": k_us,
                            "algorithmic_bytes": ab["w13"], "active_experts": ab["e_act"],
                            "kernel_timing": "second pass over the same steps with per-stage CUDA events on the launching stream"}
         step_gbs = ab["total"] / (ms_per_step * 1e-3) / 1e9
