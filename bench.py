@@ -164,12 +164,17 @@ def path_used(args, fmt, M, topk, E, H, I):
     """Mirrors the SGLB_PATH_AUTO rule of capi.cu (rows/expert >= 4 and a supported shape)."""
     if args.path != "auto":
         return args.path
-    eb = {"bf16": 2, "int8": 1}.get(fmt)
-    ok = eb is not None and (H * eb) % 128 == 0 and (I * eb) % 128 == 0
+    if fmt in ("fp8", "mxfp4"):
+        ok = H % 64 == 0 and I % 64 == 0
+    else:
+        eb = {"bf16": 2, "int8": 1}[fmt]
+        ok = (H * eb) % 128 == 0 and (I * eb) % 128 == 0
     return "umma" if ok and M * topk / E >= 4.0 else "stream"
 
 
 PATH_DESC = {"stream": "stream (mma.sync weight streaming)", "umma": "umma (tcgen05 + TMEM + TMA)"}
+KERNEL_DESC = {("umma", "bf16"): "umma_moe_kernel", ("umma", "int8"): "umma_moe_kernel", ("umma", "fp8"): "umma_dq_kernel",
+               ("umma", "mxfp4"): "umma_dq_kernel"}
 
 
 def time_steps(fn, steps, warmup, world):
@@ -278,7 +283,7 @@ def run_b200(args):
         k_us = stage_us["w13_gemm"]
         achieved = ab["w13"] / (k_us * 1e-6) / 1e9 if k_us > 0 else 0.0
         used = path_used(args, fmt, M, topk, E, H, I)
-        kname = ("umma_moe_kernel<stage 1> (tcgen05 w13 GEMM + silu_and_mul)" if used == "umma"
+        kname = (f"{KERNEL_DESC[(used, fmt)]}<stage 1> (tcgen05 w13 GEMM + silu_and_mul)" if used == "umma"
                  else "stream_gemm_kernel<stage 1> (mma.sync w13 GEMM + silu_and_mul)")
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")

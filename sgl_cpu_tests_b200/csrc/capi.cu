@@ -199,6 +199,9 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.topk = sa.topk;
   u.gather = sa.gather;
   u.max_tiles = (int)max_items(S, E, kTileRows);
+  u.block_n = sa.block_n;
+  u.block_k = sa.block_k;
+  u.scale_cols = sa.scale_cols;
   return launch_umma_gemm(fmt, stage, u, stream);
 }
 

@@ -1,0 +1,318 @@
+// Shared pieces of the tcgen05 grouped-GEMM kernels (umma_gemm.cu: operands straight from HBM;
+// umma_dq.cu: weights dequantised to bf16 on the way): PTX wrappers, descriptors, the work-item
+// decode, the routed-row gather producers and the epilogue warps.
+#pragma once
+#include <cuda.h>  // CUtensorMap and enums only; the encoder is resolved through cudart, no -lcuda
+
+#include "umma_gemm.cuh"
+
+namespace sglb {
+namespace ummak {
+
+
+constexpr int kRowBytes = 128;                       // bytes of K per operand row per stage
+constexpr int kWSub = 128;                           // weight rows per accumulator (UMMA M)
+constexpr int kWTileBytes = kWSub * kRowBytes;       // 16 KB
+constexpr int kXTileBytes = kUmmaTileRows * kRowBytes;
+constexpr int kGatherThreads = 128;
+constexpr int kEpiWarps = 8;                         // two per TMEM lane quadrant (one per 16-column parity)
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kTmemCols = 512;
+constexpr int kAccCols = 256;                        // per accumulator buffer: 2 sub-tiles x 128
+constexpr int kEpiBufBytes = 16 * 32 * 4;            // per epilogue warp: 16 tokens x 32 outputs, f32 worst case
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                            int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, "
+      "%4, %5}], [%2];" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+// mbarrier arrive (counted in the barrier's expected arrivals) once all cp.async issued so far by this
+// thread have landed: the gather producers never block on their own loads
+__device__ __forceinline__ void cp_async_arrive_noinc(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]; issued by one thread on behalf of the CTA
+template <int FMT>
+__device__ __forceinline__ void umma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                     uint32_t accumulate) {
+  if constexpr (FMT == SGLB_FMT_INT8_W8A8) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
+}
+// mbarrier arrive once every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, "
+      "%13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]),
+        "=r"(v[15])
+      : "r"(taddr));
+}
+// The loaded registers are threaded through the wait as "+r" operands so the compiler cannot
+// schedule a use of them above it.
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[16]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]),
+                 "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]),
+                 "+r"(v[14]), "+r"(v[15])
+               :
+               : "memory");
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (sm_100 format): start address >> 4,
+// LBO = 1 (unused for swizzled K-major), SBO = 1024 B between 8-row groups, version 1, layout 2.
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr) {
+  return (uint64_t)((addr >> 4) & 0x3FFFu) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) |
+         (1ull << 46) | (2ull << 61);
+}
+// instruction descriptor: D f32 (or s32), A and B K-major, M = 128, N = n
+template <int FMT>
+__device__ __forceinline__ uint32_t instr_desc(int n) {
+  const uint32_t cfmt = FMT == SGLB_FMT_INT8_W8A8 ? 2u : 1u;  // S32 : F32
+  const uint32_t abfmt = 1u;                                  // kind::f16: BF16; kind::i8: signed
+  return (cfmt << 4) | (abfmt << 7) | (abfmt << 10) | ((uint32_t)(n >> 3) << 17) |
+         ((uint32_t)(kWSub >> 4) << 24);
+}
+
+__device__ __forceinline__ float sel4(const float (&v)[4], int i) {
+  return i == 0 ? v[0] : (i == 1 ? v[1] : (i == 2 ? v[2] : v[3]));
+}
+
+struct WorkItem {
+  int e, row_start, rows, nb;
+};
+
+template <int STAGE>
+__device__ __forceinline__ int num_weight_blocks(const UmmaArgs& a) {
+  return STAGE == 1 ? ceil_div(a.N, kWSub) : ceil_div(a.N, 2 * kWSub);
+}
+__device__ __forceinline__ WorkItem get_item(const UmmaArgs& a, int w, int n_blocks) {
+  WorkItem it;
+  const int t = w / n_blocks;
+  it.nb = w - t * n_blocks;
+  it.e = a.tile_list[3 * t + 0];
+  it.row_start = a.tile_list[3 * t + 1];
+  it.rows = a.tile_list[3 * t + 2];
+  return it;
+}
+
+
+// ---- gather producers: routed rows -> 128-B-swizzled K-major smem tiles ------------------------------
+// 128 threads (g = 0..127).  Thread g owns the 16-B chunk c = g & 7 of rows rbase + 16 j.  Stage s of the
+// ring lives at x_tile0 + s * x_stride; full/empty barriers at xfull0 + 8 s / xempty0 + 8 s.
+__device__ __forceinline__ void gather_role(const UmmaArgs& a, int total, int n_blocks, int num_kb,
+                                            int k_bytes, int g, uint32_t x_tile0, uint32_t x_stride,
+                                            uint32_t xfull0, uint32_t xempty0, int nstages) {
+  auto x_tile = [&](int s) { return x_tile0 + s * x_stride; };
+  auto full_bar = [&](int s) { return xfull0 + 8 * s; };
+  auto empty_bar = [&](int s) { return xempty0 + 8 * s; };
+  const int kStages = nstages;
+    const int c = g & 7, rbase = g >> 3;  // 16-B chunk of the 128-B row; rows rbase + 16*j
+    const uint32_t dst0 = rbase * kRowBytes + ((c ^ (rbase & 7)) << 4);
+    uint32_t it = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x) {
+      const WorkItem wi = get_item(a, w, n_blocks);
+      const int n_eff = (wi.rows + 15) & ~15;
+      const char* src[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int r = rbase + 16 * j;
+        const int p = wi.row_start + min(r, wi.rows - 1);
+        const int xr = a.gather ? (a.sorted_slot[p] / a.topk) : p;
+        src[j] = (const char*)a.X + (size_t)xr * k_bytes + c * 16;
+      }
+      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const int s = it % kStages;
+        mbar_wait(empty_bar(s), ((it / kStages) & 1) ^ 1);
+        const uint32_t dst = x_tile(s) + dst0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (rbase + 16 * j < n_eff) cp_async16(dst + j * 16 * kRowBytes, src[j] + kb * kRowBytes);
+        cp_async_arrive_noinc(full_bar(s));
+      }
+    }
+}
+
+// ---- epilogue warps -------------------------------------------------------------------------------------
+// kEpiWarps warps; `ew` = index among them, `warp` = warp index in the CTA (its TMEM lane quadrant is
+// warp & 3).  INT8: s32 accumulators with activation / weight scales; otherwise f32 accumulators.
+template <bool kInt8, int STAGE>
+__device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int n_blocks, uint8_t* smem_raw,
+                                              uint32_t epi_base, uint32_t tfull0, uint32_t tempty0,
+                                              uint32_t tmem_base, int warp, int ew, int lane) {
+  auto tfull_bar = [&](int b) { return tfull0 + 8 * b; };
+  auto tempty_bar = [&](int b) { return tempty0 + 8 * b; };
+    // ================= epilogue =================
+    // Eight warps: warp (q, par) owns TMEM lanes [32q, 32q+32) (= 32 consecutive outputs n) and the
+    // 16-column (= 16-token) chunks of parity par.  A chunk is transposed through a private smem
+    // buffer so that global stores are 16 B per lane and whole 64/128-B row segments per token.
+    const int q = warp & 3, par = ew >> 2;
+    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+    constexpr int OB = (kInt8 && STAGE == 1) ? 4 : 2;  // output element bytes (f32 act for int8 stage 1)
+    constexpr int ROWB = 32 * OB;                      // bytes per token row in the transpose buffer
+    constexpr int SEGS = ROWB / 16;                    // lanes per token row on the read side
+    constexpr int TPI = 32 / SEGS;                     // token rows per read instruction
+    constexpr int NRD = 16 / TPI;                      // read instructions per chunk
+    uint8_t* ebuf = smem_raw + (epi_base + ew * kEpiBufBytes - smem_u32(smem_raw));
+    const int rd_tok = lane / SEGS, rd_seg = lane % SEGS;
+    uint32_t li = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x, ++li) {
+      const WorkItem wi = get_item(a, w, n_blocks);
+      const int n_eff = (wi.rows + 15) & ~15;
+      const int buf = li & 1;
+      // Per-token scalars of this tile (activation scale, topk weight): lane l keeps tokens
+      // l, l+32, l+64, l+96.  Fetched before the accumulator wait so the dependent loads
+      // (sorted_slot -> scale) hide under the MMAs; broadcast with shuffles in the column loop.
+      float xs_r[4], rs_r[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        xs_r[i] = 1.f;
+        rs_r[i] = 1.f;
+        const int p = wi.row_start + min(lane + 32 * i, wi.rows - 1);
+        if (32 * i < n_eff) {
+          if constexpr (STAGE == 1) {
+            if (kInt8) xs_r[i] = a.Xscale[a.sorted_slot[p] / a.topk];
+          } else {
+            if (kInt8) xs_r[i] = a.Xscale[p];
+            if (a.row_scale != nullptr) rs_r[i] = a.row_scale[a.sorted_slot[p]];
+          }
+        }
+      }
+      mbar_wait(tfull_bar(buf), (li >> 1) & 1);
+      tc_fence_after();
+      const uint32_t acc = tmem_base + lane_off + buf * kAccCols;
+      constexpr int kSubs = STAGE == 1 ? 1 : 2;
+#pragma unroll 1
+      for (int sub = 0; sub < kSubs; ++sub) {
+        const int nbase = STAGE == 1 ? wi.nb * kWSub + q * 32 : wi.nb * 2 * kWSub + sub * kWSub + q * 32;
+        const int n = nbase + lane;
+        float ws0 = 1.f, ws1 = 1.f;
+        if (kInt8 && n < a.N) {
+          const float* ws = (const float*)a.Wscale + (size_t)wi.e * a.rows_per_expert;
+          ws0 = ws[n];
+          if (STAGE == 1) ws1 = ws[a.N + n];
+        }
+#pragma unroll 1
+        for (int c0 = 16 * par; c0 < n_eff; c0 += 32) {  // n_eff is warp-uniform
+          const float xsel = sel4(xs_r, c0 >> 5), rsel = sel4(rs_r, c0 >> 5);
+          if constexpr (STAGE == 1) {
+            uint32_t gv[16], uv[16];
+            tmem_ld16(acc + c0, gv);
+            tmem_ld16(acc + kWSub + c0, uv);
+            tmem_ld_wait(gv);
+            tmem_ld_wait(uv);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              if constexpr (kInt8) {
+                const float xs = __shfl_sync(0xffffffffu, xsel, 16 * par + j);
+                const float gate = xs * (float)(int)gv[j] * ws0;
+                const float up = xs * (float)(int)uv[j] * ws1;
+                *reinterpret_cast<float*>(ebuf + j * ROWB + lane * 4) = silu_f(gate) * up;
+              } else {
+                const float gate = __uint_as_float(gv[j]), up = __uint_as_float(uv[j]);
+                *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) =
+                    __float2bfloat16_rn(silu_f(gate) * up);
+              }
+            }
+          } else {
+            uint32_t v[16];
+            tmem_ld16(acc + sub * kWSub + c0, v);
+            tmem_ld_wait(v);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float rs = __shfl_sync(0xffffffffu, rsel, 16 * par + j);
+              float val;
+              if constexpr (kInt8) {
+                const float xs = __shfl_sync(0xffffffffu, xsel, 16 * par + j);
+                val = xs * (float)(int)v[j] * ws0;
+              } else {
+                val = __uint_as_float(v[j]);
+              }
+              *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(val * rs);
+            }
+          }
+          __syncwarp();
+          const int nn = nbase + rd_seg * (16 / OB);  // first output held by this lane's 16 bytes
+#pragma unroll
+          for (int i = 0; i < NRD; ++i) {
+            const int tok = rd_tok + TPI * i;
+            const int4 piece = *reinterpret_cast<const int4*>(ebuf + tok * ROWB + rd_seg * 16);
+            if (c0 + tok < wi.rows && nn < a.N)
+              *reinterpret_cast<int4*>((char*)a.out +
+                                       ((size_t)(wi.row_start + c0 + tok) * a.N + nn) * OB) = piece;
+          }
+          __syncwarp();
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(tempty_bar(buf));
+    }
+}
+
+}  // namespace ummak
+
+// host helpers shared by the two tcgen05 translation units (defined in umma_gemm.cu)
+int weight_tensor_map(const void* W, uint64_t kbytes, uint64_t rows, uint64_t E, uint32_t box_bytes,
+                      uint32_t box_rows, int swizzle128, CUtensorMap* out);
+int sm_count();
+
+}  // namespace sglb

@@ -6,7 +6,7 @@ namespace sglb {
 
 struct UmmaArgs {
   const void* W;           // [E, rows_per_expert, K] row-major, K contiguous (bf16 or s8)
-  const void* Wscale;      // int8: f32 [E, rows_per_expert]
+  const void* Wscale;      // int8: f32 [E, rows_per_expert]; fp8: f32 [E, rows/bn, K/bk]; mxfp4: u8 [E, rows, K/32]
   const void* X;           // routed rows, row stride K elements (bf16 or s8)
   const float* Xscale;     // int8: per X row
   const int32_t* tile_list;   // (expert, row_start, rows <= 128) from moe_align
@@ -21,6 +21,8 @@ struct UmmaArgs {
   int topk;
   int gather;              // 1: X row = sorted_slot[p] / topk; 0: X row = p
   int max_tiles;           // host upper bound on counters[2]
+  int block_n, block_k;    // fp8 scale block
+  int scale_cols;          // fp8: ceil(K/bk); mxfp4: K/32
 };
 
 constexpr int kUmmaTileRows = 128;  // routed rows per tile (tile_rows handed to moe_align)
@@ -29,5 +31,7 @@ constexpr int kUmmaTileRows = 128;  // routed rows per tile (tile_rows handed to
 int umma_supported(int fmt, int64_t M, int topk, int E, int H, int I);
 // stage 1: out = silu(X W13_gate^T) * (X W13_up^T);  stage 2: out = (X W2^T) * row_scale
 int launch_umma_gemm(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream);
+// fp8 w8a16 / mxfp4: weights dequantised to bf16 inside the kernel (umma_dq.cu)
+int launch_umma_dq(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream);
 
 }  // namespace sglb

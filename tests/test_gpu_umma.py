@@ -110,3 +110,60 @@ def test_umma_unsupported_shape_raises(K):
     with pytest.raises(RuntimeError):
         K.fused_experts_impl(a, w1, w2, torch.ones(8, 1, device="cuda"), torch.zeros(8, 1, dtype=torch.int32, device="cuda"),
                              False, K.FMT_BF16, None, None, None, False, path=K.PATH_UMMA)
+
+
+DQ_CASES = [  # M, I, H, E, topk, style
+    (64, 128, 128, 4, 2, "uniform"),
+    (300, 128, 256, 8, 2, "uniform"),
+    (257, 192, 320, 8, 4, "skewed"),       # K = 320 / 192: 5 and 3 stages of 64; partial weight blocks
+    (130, 256, 128, 4, 2, "one"),
+    (148, 128, 256, 4, 4, "skewed"),
+    (512, 512, 1024, 16, 4, "uniform"),
+]
+
+
+@pytest.mark.parametrize("block", [[128, 128], [64, 128], [64, 64]])
+@pytest.mark.parametrize("case", DQ_CASES)
+def test_umma_fp8(K, case, block):
+    M, I, H, E, topk, style = case
+    bn, bk = block
+    g = torch.Generator().manual_seed(1111)
+    a = (torch.randn(M, H, generator=g) / math.sqrt(H)).bfloat16()
+    w1 = (torch.randn(E, 2 * I, H, generator=g) * 400).clamp(-448, 448).to(torch.float8_e4m3fn)
+    w2 = (torch.randn(E, H, I, generator=g) * 400).clamp(-448, 448).to(torch.float8_e4m3fn)
+    w1.view(torch.uint8)[0, :4, :8] = torch.arange(32, dtype=torch.uint8).view(4, 8)   # e4m3 subnormals / tiny codes
+    cd = lambda x, y: (x + y - 1) // y
+    w1s = torch.randn(E, cd(2 * I, bn), cd(H, bk), generator=g) * 1e-3
+    w2s = torch.randn(E, cd(H, bn), cd(I, bk), generator=g) * 1e-3
+    ids = make_ids(M, E, topk, style, g)
+    tw = torch.rand(M, topk, generator=g) / topk     # keeps |out| < 1 so one bf16 ulp stays inside atol
+    ref = O.fused_experts(a, w1, w2, tw, ids, "fp8", w1s, w2s, block)
+    dev = [t.cuda() for t in (a, w1, w2, tw, ids, w1s, w2s)]
+    outs = {}
+    for name, path in (("stream", K.PATH_STREAM), ("umma", K.PATH_UMMA)):
+        outs[name] = K.fused_experts_impl(dev[0], dev[1], dev[2], dev[3], dev[4], False, K.FMT_FP8_W8A16, dev[5], dev[6],
+                                          block, False, path=path).cpu()
+    assert torch.isfinite(outs["umma"]).all(), describe(outs["umma"], ref)
+    assert torch.allclose(outs["umma"].float(), ref.float(), **BF16_TOL), "vs oracle: " + describe(outs["umma"], ref)
+    assert torch.allclose(outs["umma"].float(), outs["stream"].float(), **BF16_TOL), "vs stream: " + describe(outs["umma"], outs["stream"])
+
+
+@pytest.mark.parametrize("case", DQ_CASES + [(64, 2880, 2880, 4, 2, "uniform")])
+def test_umma_mxfp4(K, case):
+    M, I, H, E, topk, style = case
+    g = torch.Generator().manual_seed(1111)
+    a = torch.randn(M, H, generator=g).bfloat16() / 10
+    w1q, w1s = O.mxfp4_quantize((torch.rand(E, 2 * I, H, generator=g) - 0.5) * 2e-1)
+    w2q, w2s = O.mxfp4_quantize((torch.rand(E, H, I, generator=g) - 0.5) * 2e-1)
+    w1s, w2s = w1s.view(E, 2 * I, H // 32).contiguous(), w2s.view(E, H, I // 32).contiguous()
+    ids = make_ids(M, E, topk, style, g)
+    tw = torch.rand(M, topk, generator=g)
+    ref = O.fused_experts(a, w1q, w2q, tw, ids, "mxfp4", w1s, w2s)
+    dev = [t.cuda() for t in (a, w1q, w2q, tw, ids, w1s, w2s)]
+    outs = {}
+    for name, path in (("stream", K.PATH_STREAM), ("umma", K.PATH_UMMA)):
+        outs[name] = K.fused_experts_impl(dev[0], dev[1], dev[2], dev[3], dev[4], False, K.FMT_MXFP4, dev[5], dev[6],
+                                          None, False, path=path).cpu()
+    assert torch.isfinite(outs["umma"]).all(), describe(outs["umma"], ref)
+    assert torch.allclose(outs["umma"].float(), ref.float(), **BF16_TOL), "vs oracle: " + describe(outs["umma"], ref)
+    assert torch.allclose(outs["umma"].float(), outs["stream"].float(), **BF16_TOL), "vs stream: " + describe(outs["umma"], outs["stream"])
