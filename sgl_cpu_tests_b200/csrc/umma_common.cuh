@@ -40,6 +40,25 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "memory");
   } while (!ok);
 }
+// Wait of a role that is not on the critical path (producers waiting for a free slot, the MMA
+// issuer and the epilogue waiting for data in the HBM-bound regime).  A failed poll sleeps so the
+// spinning warp stops competing for issue slots with the warps doing ALU work (ncu, r1d: try_wait
+// spin loops were 49 % of all issued instructions of the fp8 kernel); the try_wait itself carries a
+// suspend-time hint so the hardware may park the warp until the phase completes.
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(100000u)
+        : "memory");
+    if (ok) break;
+    __nanosleep(32);
+  }
+}
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
@@ -159,6 +178,7 @@ __device__ __forceinline__ WorkItem get_item(const UmmaArgs& a, int w, int n_blo
 // ---- gather producers: routed rows -> 128-B-swizzled K-major smem tiles ------------------------------
 // 128 threads (g = 0..127).  Thread g owns the 16-B chunk c = g & 7 of rows rbase + 16 j.  Stage s of the
 // ring lives at x_tile0 + s * x_stride; full/empty barriers at xfull0 + 8 s / xempty0 + 8 s.
+template <bool kRelaxed>
 __device__ __forceinline__ void gather_role(const UmmaArgs& a, int total, int n_blocks, int num_kb,
                                             int k_bytes, int g, uint32_t x_tile0, uint32_t x_stride,
                                             uint32_t xfull0, uint32_t xempty0, int nstages) {
@@ -182,7 +202,8 @@ __device__ __forceinline__ void gather_role(const UmmaArgs& a, int total, int n_
       }
       for (int kb = 0; kb < num_kb; ++kb, ++it) {
         const int s = it % kStages;
-        mbar_wait(empty_bar(s), ((it / kStages) & 1) ^ 1);
+        if (kRelaxed) mbar_wait_relaxed(empty_bar(s), ((it / kStages) & 1) ^ 1);
+        else mbar_wait(empty_bar(s), ((it / kStages) & 1) ^ 1);
         const uint32_t dst = x_tile(s) + dst0;
 #pragma unroll
         for (int j = 0; j < 8; ++j)
@@ -195,7 +216,7 @@ __device__ __forceinline__ void gather_role(const UmmaArgs& a, int total, int n_
 // ---- epilogue warps -------------------------------------------------------------------------------------
 // kEpiWarps warps; `ew` = index among them, `warp` = warp index in the CTA (its TMEM lane quadrant is
 // warp & 3).  INT8: s32 accumulators with activation / weight scales; otherwise f32 accumulators.
-template <bool kInt8, int STAGE>
+template <bool kInt8, int STAGE, bool kRelaxed>
 __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int n_blocks, uint8_t* smem_raw,
                                               uint32_t epi_base, uint32_t tfull0, uint32_t tempty0,
                                               uint32_t tmem_base, int warp, int ew, int lane) {
@@ -237,7 +258,8 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
           }
         }
       }
-      mbar_wait(tfull_bar(buf), (li >> 1) & 1);
+      if (kRelaxed) mbar_wait_relaxed(tfull_bar(buf), (li >> 1) & 1);
+      else mbar_wait(tfull_bar(buf), (li >> 1) & 1);
       tc_fence_after();
       const uint32_t acc = tmem_base + lane_off + buf * kAccCols;
       constexpr int kSubs = STAGE == 1 ? 1 : 2;

@@ -50,22 +50,37 @@ constexpr int smem_bytes() {
          kEpiWarps * kEpiBufBytes + 1024 /*alignment slack*/ + 512 /*barriers*/;
 }
 
-// four e4m3 bytes of a word -> four bf16(f32(w) * scale) packed as two bf16x2.  The byte s.eeee.mmm
-// placed at f32 bits [31|26:20] is the value times 2^-120 (subnormals included); `pre` * `s` must
-// equal 2^120 * scale: (2^120 * scale, 1) in the common case, (scale, 2^120) when folding would overflow.
-__device__ __forceinline__ void e4m3x4_scale_to_bf16x4(uint32_t w, float s, float pre, uint32_t& lo,
-                                                       uint32_t& hi) {
-  const float f0 = __uint_as_float(((w << 20) & 0x07F00000u) | ((w << 24) & 0x80000000u));
-  const float f1 = __uint_as_float(((w << 12) & 0x07F00000u) | ((w << 16) & 0x80000000u));
-  const float f2 = __uint_as_float(((w << 4) & 0x07F00000u) | ((w << 8) & 0x80000000u));
-  const float f3 = __uint_as_float(((w >> 4) & 0x07F00000u) | (w & 0x80000000u));
-  lo = pack_bf16x2(f0 * pre * s, f1 * pre * s);
-  hi = pack_bf16x2(f2 * pre * s, f3 * pre * s);
+// four e4m3 bytes of a word -> four bf16(f32(w) * scale) packed as two bf16x2.  The hardware converter
+// (cvt.rn.f16x2.e4m3x2, exact: f16 holds every e4m3 value) replaces the shift/mask arithmetic; the
+// product is the same single-rounded f32 multiply the reference oracle does, then one RN to bf16.
+__device__ __forceinline__ void e4m3x4_scale_to_bf16x4(uint32_t w, float s, uint32_t& lo, uint32_t& hi) {
+  uint32_t h01, h23;
+  asm("{\n\t.reg .b16 l, h;\n\tmov.b32 {l, h}, %2;\n\t"
+      "cvt.rn.f16x2.e4m3x2 %0, l;\n\tcvt.rn.f16x2.e4m3x2 %1, h;\n\t}"
+      : "=r"(h01), "=r"(h23)
+      : "r"(w));
+  const float2 f01 = __half22float2(*reinterpret_cast<const __half2*>(&h01));
+  const float2 f23 = __half22float2(*reinterpret_cast<const __half2*>(&h23));
+  lo = pack_bf16x2(f01.x * s, f01.y * s);
+  hi = pack_bf16x2(f23.x * s, f23.y * s);
 }
-// byte b = (n_lo | n_hi << 4) of e2m1 nibbles -> raw bf16x2 (value * 2^-126), low half = n_lo (even k)
-__device__ __forceinline__ uint32_t e2m1x2_to_raw_bf16x2(uint32_t b) {
-  const uint32_t t = (b & 0x0Fu) | ((b & 0xF0u) << 12);
-  return ((t & 0x00080008u) << 12) | ((t & 0x00070007u) << 6);
+// word w of e2m1 nibbles n0..n7 (n0 lowest = lowest k) -> raw bf16x2 words (value * 2^-126) in k
+// order: r[0] = (n0,n1) ... r[3] = (n6,n7).  Pairs (n_i, n_{i+4}) come out of one mask/shift each
+// (see e2m1x8_to_raw_bf16 in common.cuh); two byte permutes per pair of words restore the k order.
+__device__ __forceinline__ void e2m1x8_to_raw_bf16_korder(uint32_t w, uint32_t (&r)[4]) {
+  uint32_t p[4];
+  e2m1x8_to_raw_bf16(w, p);                  // p[i] = (n_i, n_{i+4})
+  r[0] = __byte_perm(p[0], p[1], 0x5410);    // (n0, n1)
+  r[2] = __byte_perm(p[0], p[1], 0x7632);    // (n4, n5)
+  r[1] = __byte_perm(p[2], p[3], 0x5410);    // (n2, n3)
+  r[3] = __byte_perm(p[2], p[3], 0x7632);    // (n6, n7)
+}
+// A raw e2m1 pair (value * 2^-126) times 2^(e-1) is value * 2^(e8m0-127).  The bf16 code of 2^(e-1)
+// has biased exponent e + 126, valid for e <= 128 (e = 0 included: 2^-1); larger scales (> 2) take a
+// second exact factor 2^(e-128).  bf16x2_pow2(b) = the bf16 number with biased exponent b, both halves.
+__device__ __forceinline__ uint32_t bf16x2_pow2(int biased) {  // 1 <= biased <= 254
+  const uint32_t b = (uint32_t)biased << 7;
+  return b | (b << 16);
 }
 
 template <int FMT, int STAGE>
@@ -144,7 +159,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int wrow1 = STAGE == 1 ? a.N + wi.nb * kWSub : wrow0 + kWSub;
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int s = it % RAWS;
-          mbar_wait(raw_empty(s), ((it / RAWS) & 1) ^ 1);
+          mbar_wait_relaxed(raw_empty(s), ((it / RAWS) & 1) ^ 1);
           mbar_arrive_expect_tx(raw_full(s), kRawStageBytes);
           const uint32_t dst = raw_base + s * kRawStageBytes;
           tma_load_3d(dst, &tmap_w, raw_full(s), kb * RB, wrow0, wi.e);
@@ -162,13 +177,13 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int n_eff = (wi.rows + 15) & ~15;
         const uint32_t idesc = instr_desc<SGLB_FMT_BF16>(n_eff);
         const int buf = li & 1;
-        mbar_wait(tempty_bar(buf), ((li >> 1) & 1) ^ 1);
+        mbar_wait_relaxed(tempty_bar(buf), ((li >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t acc = tmem_base + buf * kAccCols;
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int sx = it % kXStages, sw = it % kWopStages;
-          mbar_wait(x_full(sx), (it / kXStages) & 1);
-          mbar_wait(wop_full(sw), (it / kWopStages) & 1);
+          mbar_wait_relaxed(x_full(sx), (it / kXStages) & 1);
+          mbar_wait_relaxed(wop_full(sw), (it / kWopStages) & 1);
           fence_proxy_async();
           tc_fence_after();
           const uint32_t wt = wop_base + sw * kWopBytes, xt = x_base + sx * kXTileBytes;
@@ -189,10 +204,10 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
     __syncwarp();
   } else if (warp < kFirstEpiWarp) {
-    gather_role(a, total, n_blocks, num_kb, a.K * 2, threadIdx.x - 64, x_base, kXTileBytes, x_full(0),
+    gather_role<true>(a, total, n_blocks, num_kb, a.K * 2, threadIdx.x - 64, x_base, kXTileBytes, x_full(0),
                 x_empty(0), kXStages);
   } else if (warp < kFirstDqWarp) {
-    epilogue_role<false, STAGE>(a, total, n_blocks, smem_raw, epi_base, tfull_bar(0), tempty_bar(0), tmem_base,
+    epilogue_role<false, STAGE, true>(a, total, n_blocks, smem_raw, epi_base, tfull_bar(0), tempty_bar(0), tmem_base,
                                 warp, warp - kFirstEpiWarp, lane);
   } else {
     // ================= dequant warps: raw ring -> bf16 operand ring =================
@@ -222,15 +237,24 @@ __global__ void __launch_bounds__(kThreads, 1)
           srow[i] = (const uint8_t*)a.Wscale + ((size_t)wi.e * a.rows_per_expert + wr) * a.scale_cols;
         }
       }
-      for (int kb = 0; kb < num_kb; ++kb, ++it) {
-        // scales of this k block first: their latency hides behind the barrier waits
-        float sc[TASKS];
+      // scales are fetched one k block ahead (registers), so their HBM/L2 latency overlaps the
+      // conversion of the current block instead of stalling every stage
+      auto load_scale = [&](int i, int kb) -> uint32_t {
+        if constexpr (FMT == SGLB_FMT_FP8_W8A16)
+          return __float_as_uint(__ldg((const float*)srow[i] + (kb * kKPerStage) / a.block_k));
+        else
+          return (uint32_t)__ldg((const uint8_t*)srow[i] + kb * 2 + chunk);
+      };
+      uint32_t sc_next[TASKS];
 #pragma unroll
-        for (int i = 0; i < TASKS; ++i) {
-          if constexpr (FMT == SGLB_FMT_FP8_W8A16)
-            sc[i] = __ldg((const float*)srow[i] + (kb * kKPerStage) / a.block_k);
-          else
-            sc[i] = __uint_as_float((uint32_t)__ldg((const uint8_t*)srow[i] + kb * 2 + chunk));
+      for (int i = 0; i < TASKS; ++i) sc_next[i] = load_scale(i, 0);
+      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        uint32_t sc[TASKS];
+#pragma unroll
+        for (int i = 0; i < TASKS; ++i) sc[i] = sc_next[i];
+        if (kb + 1 < num_kb) {
+#pragma unroll
+          for (int i = 0; i < TASKS; ++i) sc_next[i] = load_scale(i, kb + 1);
         }
         const int sr = it % RAWS, sw = it % kWopStages;
         mbar_wait(raw_full(sr), (it / RAWS) & 1);
@@ -245,22 +269,23 @@ __global__ void __launch_bounds__(kThreads, 1)
           const uint32_t* qw = reinterpret_cast<const uint32_t*>(&q);
           uint32_t o[16 / CPR * 2];  // 8 (fp8) or 16 (mxfp4) bf16x2 words
           if constexpr (FMT == SGLB_FMT_FP8_W8A16) {
-            constexpr float k2p120 = 1.329227995784916e36f;
-            if (fabsf(sc[i]) < 64.f) {  // fold 2^120 into the scale: one multiply per element
-              const float s = sc[i] * k2p120;
+            const float sf = __uint_as_float(sc[i]);
 #pragma unroll
-              for (int k = 0; k < 4; ++k) e4m3x4_scale_to_bf16x4(qw[k], s, 1.f, o[2 * k], o[2 * k + 1]);
-            } else {
-#pragma unroll
-              for (int k = 0; k < 4; ++k) e4m3x4_scale_to_bf16x4(qw[k], sc[i], k2p120, o[2 * k], o[2 * k + 1]);
-            }
+            for (int k = 0; k < 4; ++k) e4m3x4_scale_to_bf16x4(qw[k], sf, o[2 * k], o[2 * k + 1]);
           } else {
-            const uint32_t s2 = e8m0_to_bf16x2(__float_as_uint(sc[i]));
+            const int e = (int)sc[i];
+            const uint32_t m1 = bf16x2_pow2((e < 128 ? e : 128) + 126);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
+              uint32_t rr[4];
+              e2m1x8_to_raw_bf16_korder(qw[k], rr);
 #pragma unroll
-              for (int b = 0; b < 4; ++b)
-                o[4 * k + b] = mxfp4_finish(e2m1x2_to_raw_bf16x2((qw[k] >> (8 * b)) & 0xFFu), s2);
+              for (int b = 0; b < 4; ++b) o[4 * k + b] = bf16x2_mul(rr[b], m1);
+            }
+            if (e > 128) {  // rare: scales above 2 need a second exact factor 2^(e-128)
+              const uint32_t m2 = bf16x2_pow2(e - 1);
+#pragma unroll
+              for (int k = 0; k < 16; ++k) o[k] = bf16x2_mul(o[k], m2);
             }
           }
           uint8_t* orow = wop + (r >> 7) * kWTileBytes + (r & 127) * kRowBytes;
