@@ -55,6 +55,11 @@ uint64_t sglb_launch_count(void);
 void sglb_profile_enable(int on);
 int sglb_profile_read(float* ms_out, int* calls_out, int n);
 
+/* fp8 w8a16 on the tcgen05 path: 1 (default) = weights stay e4m3 and run on the fp8 tensor cores with
+ * the activations split into two e4m3 pieces (csrc/umma_f8.cu); 0 = weights dequantised to bf16 in
+ * the kernel (csrc/umma_dq.cu).  Process-wide switch, used by the parity tests to cover both. */
+void sglb_set_fp8_native(int on);
+
 /* ---- K1 router ------------------------------------------------------------------------------
  * grouped_topk_cpu          (test_grouped_topk.py:61-69, test_moe.py:61-70)  : bias == NULL
  * biased_grouped_topk_cpu   (test_biased_grouped_topk.py:71-80)              : bias != NULL
@@ -185,6 +190,10 @@ int sglb_ep_combine(const void* ret, const int32_t* dest_row, const int32_t* sen
 /* ---- building blocks exposed for tests and for the expert-parallel layer --------------------------
  * per-row dynamic int8 quantisation (test_moe_int8.py:23-31): q = round(x * 127/absmax), scale = absmax/127 */
 int sglb_quant_rows_int8(const void* x_bf16, int64_t rows, int K, int8_t* q, float* scale,
+                         sglb_stream_t stream);
+/* bf16 rows -> two e4m3 pieces for the tensor-native fp8 path: x ~= (hi + lo) * rexp, rexp = 2^(e-7) with
+ * e = floor(log2(rowmax)); exact for elements within 2^-9 of the row maximum (csrc/umma_f8.cu) */
+int sglb_split_rows_e4m3(const void* x_bf16, int64_t rows, int K, void* hi_e4m3, void* lo_e4m3, float* rexp,
                          sglb_stream_t stream);
 /* K5: out[m] = bf16( sum_j ic2[slot_pos[m*topk+j]] ) over valid slots, in slot order */
 int sglb_topk_reduce(const void* ic2_bf16, const int32_t* slot_pos, int64_t M, int topk, int H,

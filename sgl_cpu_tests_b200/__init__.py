@@ -13,7 +13,7 @@ from . import _lib
 from .ops import (CPUQuantMethod, biased_grouped_topk, biased_grouped_topk_out, clear_weight_cache,
                   convert_scale_packed, convert_weight_packed, fused_experts, fused_experts_impl,
                   grouped_topk, grouped_topk_out, launch_count, moe_align, mxfp4_scaled_mm,
-                  shared_expert)
+                  shared_expert, split_rows_e4m3)
 
 DROPIN_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "dropin")
 FMT_BF16, FMT_INT8_W8A8, FMT_FP8_W8A16, FMT_MXFP4 = (_lib.FMT_BF16, _lib.FMT_INT8_W8A8,

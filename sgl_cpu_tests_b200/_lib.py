@@ -42,6 +42,7 @@ SIGNATURES = {
     "sglb_last_error": (C.c_char_p, []),
     "sglb_launch_count": (C.c_uint64, []),
     "sglb_profile_enable": (None, [C.c_int]),
+    "sglb_set_fp8_native": (None, [C.c_int]),
     "sglb_profile_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_int), C.c_int]),
     "sglb_grouped_topk": (C.c_int, [_vp, C.c_int, _vp, C.c_int, _i64, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.c_int, _f32, _vp, _vp, _vp]),
@@ -55,6 +56,7 @@ SIGNATURES = {
     "sglb_repack_weight": (C.c_int, [_vp, _vp, C.c_int, C.c_int, _i64, _i64, _i64, C.c_int, C.c_int, _vp]),
     "sglb_repack_scale": (C.c_int, [_vp, _vp, _i64, _i64, _i64, C.c_int, _vp]),
     "sglb_quant_rows_int8": (C.c_int, [_vp, _i64, C.c_int, _vp, _vp, _vp]),
+    "sglb_split_rows_e4m3": (C.c_int, [_vp, _i64, C.c_int, _vp, _vp, _vp, _vp]),
     "sglb_ep_plan": (C.c_int, [_vp, _i64, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp]),
     "sglb_ep_pack": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _i64, _vp,
                                _vp, _vp]),

@@ -31,6 +31,7 @@ struct StageEvents {
   int stage;
 };
 static bool g_profile = false;
+static bool g_f8_native = true;  // fp8: tensor-native kernel (umma_f8.cu) vs dequantising kernel (umma_dq.cu)
 static std::vector<StageEvents> g_events;
 static size_t g_events_used = 0;
 
@@ -70,6 +71,7 @@ struct MoeWorkspace {
   float* xs;                  // [M]
   int8_t* actq;               // [S, I]
   float* acts;                // [S]
+  int8_t *xq2, *actq2;        // fp8 tensor-native path: lo pieces (xq / actq hold the hi pieces)
   size_t bytes;
 };
 
@@ -85,6 +87,8 @@ static int64_t max_items(int64_t S, int E, int rows) {
 
 static MoeWorkspace carve(void* base, int64_t M, int topk, int E, int H, int I, int fmt) {
   MoeWorkspace w;
+  w.xq2 = nullptr;
+  w.actq2 = nullptr;
   const int64_t S = M * topk;
   size_t off = 0;
   auto take = [&](size_t bytes) {
@@ -109,6 +113,13 @@ static MoeWorkspace carve(void* base, int64_t M, int topk, int E, int H, int I, 
     w.xq = (int8_t*)take((size_t)M * H);
     w.xs = (float*)take(sizeof(float) * M);
     w.actq = (int8_t*)take((size_t)(S + kTileRows) * I);
+    w.acts = (float*)take(sizeof(float) * (S + kTileRows));
+  } else if (fmt == SGLB_FMT_FP8_W8A16) {
+    w.xq = (int8_t*)take((size_t)M * H);
+    w.xq2 = (int8_t*)take((size_t)M * H);
+    w.xs = (float*)take(sizeof(float) * M);
+    w.actq = (int8_t*)take((size_t)(S + kTileRows) * I);
+    w.actq2 = (int8_t*)take((size_t)(S + kTileRows) * I);
     w.acts = (float*)take(sizeof(float) * (S + kTileRows));
   } else {
     w.xq = nullptr;
@@ -180,7 +191,7 @@ static int check_format(const char* who, int fmt, int H, int I, const void* s13,
 
 // One GEMM stage on the tcgen05 path over the tile list of an existing alignment.
 static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64_t S, const MoeWorkspace& ws,
-                          cudaStream_t stream) {
+                          cudaStream_t stream, bool f8_native = false) {
   UmmaArgs u;
   memset(&u, 0, sizeof(u));
   u.W = sa.W;
@@ -202,6 +213,8 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.block_n = sa.block_n;
   u.block_k = sa.block_k;
   u.scale_cols = sa.scale_cols;
+  u.X2 = sa.X2;
+  if (f8_native) return launch_umma_f8(stage, u, stream);
   return launch_umma_gemm(fmt, stage, u, stream);
 }
 
@@ -237,18 +250,28 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   a.row_scale = nullptr;
   a.scale_cols = fmt == SGLB_FMT_FP8_W8A16 ? ceil_div(H, bk) : H / 32;
   int rc;
+  // fp8 w8a16 on the fp8 tensor cores: activations split into two e4m3 pieces (umma_f8.cu)
+  const bool f8 = path == SGLB_PATH_UMMA && fmt == SGLB_FMT_FP8_W8A16 && g_f8_native &&
+                  umma_f8_supported(H, I, bn, bk);
   if (fmt == SGLB_FMT_INT8_W8A8) {
     StageTimer t(ST_QUANT_X, stream);
     rc = sglb_quant_rows_int8(hidden, M, H, ws.xq, ws.xs, stream);
     if (rc) return rc;
     a.X = ws.xq;
     a.Xscale = ws.xs;
+  } else if (f8) {
+    StageTimer t(ST_QUANT_X, stream);
+    rc = launch_split_rows_e4m3(hidden, M, H, ws.xq, ws.xq2, ws.xs, stream);
+    if (rc) return rc;
+    a.X = ws.xq;
+    a.X2 = ws.xq2;
+    a.Xscale = ws.xs;
   } else {
     a.X = hidden;
   }
   {
     StageTimer t(ST_GEMM1, stream);
-    rc = path == SGLB_PATH_UMMA ? run_umma_stage(fmt, 1, a, E, S, ws, stream)
+    rc = path == SGLB_PATH_UMMA ? run_umma_stage(fmt, 1, a, E, S, ws, stream, f8)
                                 : dispatch_stream<1>(fmt, a, plan, stream);
   }
   if (rc) return rc;
@@ -272,11 +295,18 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
     if (rc) return rc;
     a.X = ws.actq;
     a.Xscale = ws.acts;
+  } else if (f8) {
+    StageTimer t(ST_QUANT_ACT, stream);
+    rc = launch_split_rows_e4m3(ws.act, S, I, ws.actq, ws.actq2, ws.acts, stream);
+    if (rc) return rc;
+    a.X = ws.actq;
+    a.X2 = ws.actq2;
+    a.Xscale = ws.acts;
   } else {
     a.X = ws.act;
   }
   StageTimer t(ST_GEMM2, stream);
-  return path == SGLB_PATH_UMMA ? run_umma_stage(fmt, 2, a, E, S, ws, stream)
+  return path == SGLB_PATH_UMMA ? run_umma_stage(fmt, 2, a, E, S, ws, stream, f8)
                                 : dispatch_stream<2>(fmt, a, plan2, stream);
 }
 
@@ -324,6 +354,15 @@ extern "C" int sglb_profile_read(float* ms_out, int* calls_out, int n) {
   }
   g_events_used = 0;
   return SGLB_OK;
+}
+
+extern "C" void sglb_set_fp8_native(int on) { g_f8_native = on != 0; }
+extern "C" int sglb_split_rows_e4m3(const void* x_bf16, int64_t rows, int K, void* hi, void* lo, float* rexp,
+                                    sglb_stream_t stream) {
+  SGLB_CHECK(rows >= 0 && K > 0, "split_rows_e4m3: bad shape");
+  if (rows == 0) return SGLB_OK;
+  SGLB_CHECK(x_bf16 && hi && lo && rexp, "split_rows_e4m3: null pointer");
+  return launch_split_rows_e4m3(x_bf16, rows, K, hi, lo, rexp, (cudaStream_t)stream);
 }
 
 extern "C" int64_t sglb_moe_align_max_items(int64_t M, int topk, int E, int rows) {

@@ -37,6 +37,7 @@ struct StreamArgs {
   int gather;              // 1: X row = sorted_slot[p] / topk ; 0: X row = p
   int block_n, block_k;    // fp8 scale block
   int scale_cols;          // fp8: ceil(K/bk); mxfp4: K/32
+  const void* X2;          // tcgen05 fp8 path only (see UmmaArgs)
 };
 
 template <int FMT>

@@ -23,6 +23,7 @@ struct UmmaArgs {
   int max_tiles;           // host upper bound on counters[2]
   int block_n, block_k;    // fp8 scale block
   int scale_cols;          // fp8: ceil(K/bk); mxfp4: K/32
+  const void* X2;          // fp8 tensor-native path: lo pieces of the routed rows (X = hi pieces, e4m3)
 };
 
 constexpr int kUmmaTileRows = 128;  // routed rows per tile (tile_rows handed to moe_align)
@@ -33,5 +34,10 @@ int umma_supported(int fmt, int64_t M, int topk, int E, int H, int I);
 int launch_umma_gemm(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream);
 // fp8 w8a16 / mxfp4: weights dequantised to bf16 inside the kernel (umma_dq.cu)
 int launch_umma_dq(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream);
+// fp8 w8a16 on the fp8 tensor cores (umma_f8.cu): X/X2 = hi/lo e4m3 pieces, Xscale = per-row 2^e factor
+int umma_f8_supported(int H, int I, int block_n, int block_k);
+int launch_umma_f8(int stage, const UmmaArgs& a, cudaStream_t stream);
+int launch_split_rows_e4m3(const void* x_bf16, int64_t rows, int K, void* hi, void* lo, float* rexp,
+                           cudaStream_t stream);
 
 }  // namespace sglb

@@ -572,5 +572,18 @@ def mxfp4_scaled_mm(mat1, mat2, scales2, bias, is_vnni):
     return out if on_cuda else out.cpu()
 
 
+def split_rows_e4m3(x):
+    """bf16 rows -> (hi, lo, rexp): two e4m3 pieces (uint8 storage) and the per-row power-of-two factor with
+    x ~= (hi + lo) * rexp -- the activation format of the tensor-native fp8 path (csrc/umma_f8.cu)."""
+    dev = _device()
+    x = _to_dev(x, dev, torch.bfloat16)
+    rows, K = x.shape
+    hi = torch.empty(rows, K, dtype=torch.uint8, device=dev)
+    lo = torch.empty_like(hi)
+    rexp = torch.empty(rows, dtype=torch.float32, device=dev)
+    L.check(L.load().sglb_split_rows_e4m3(_ptr(x), rows, K, _ptr(hi), _ptr(lo), _ptr(rexp), _stream()))
+    return hi, lo, rexp
+
+
 def launch_count():
     return int(L.load().sglb_launch_count())

@@ -122,13 +122,32 @@ DQ_CASES = [  # M, I, H, E, topk, style
 ]
 
 
-@pytest.mark.parametrize("block", [[128, 128], [64, 128], [64, 64]])
-@pytest.mark.parametrize("case", DQ_CASES)
-def test_umma_fp8(K, case, block):
+F8_CASES = [  # shapes the tensor-native fp8 kernel takes (H, I multiples of 128); M, I, H, E, topk, style
+    (1, 128, 128, 2, 1, "uniform"),
+    (33, 256, 384, 4, 2, "uniform"),       # K = 384 / 256: 3 and 2 scale blocks; partial weight block in stage 2
+    (300, 128, 256, 8, 2, "uniform"),
+    (130, 256, 128, 4, 2, "one"),          # 260 rows on one expert: two full tiles + a 4-row tile
+    (148, 128, 256, 4, 4, "skewed"),
+    (64, 2048, 7168, 4, 2, "uniform"),     # DeepSeek-V3 expert shape, 56 scale blocks along K
+]
+
+
+@pytest.mark.parametrize("native", [0, 1])
+@pytest.mark.parametrize("block", [[128, 128], [64, 128], [64, 64], [128, 256]])
+@pytest.mark.parametrize("case", DQ_CASES + F8_CASES)
+def test_umma_fp8(K, case, block, native):
+    """native = 1: e4m3 weights on the fp8 tensor cores with hi/lo-split activations (umma_f8.cu) wherever
+    the shape allows (H, I % 128 == 0, block_k % 128 == 0, block_n % 32 == 0), else the dequantising kernel;
+    native = 0: always the dequantising kernel (umma_dq.cu)."""
     M, I, H, E, topk, style = case
     bn, bk = block
+    if native and (case in DQ_CASES) and not (H % 128 == 0 and I % 128 == 0 and bk % 128 == 0):
+        pytest.skip("falls back to the dequantising kernel, covered by native = 0")
+    if not native and case in F8_CASES and case[2] >= 4096:
+        pytest.skip("large shape covered once")
     g = torch.Generator().manual_seed(1111)
     a = (torch.randn(M, H, generator=g) / math.sqrt(H)).bfloat16()
+    a[0, :8] *= 2.0 ** -12                                                                 # far below the row maximum
     w1 = (torch.randn(E, 2 * I, H, generator=g) * 400).clamp(-448, 448).to(torch.float8_e4m3fn)
     w2 = (torch.randn(E, H, I, generator=g) * 400).clamp(-448, 448).to(torch.float8_e4m3fn)
     w1.view(torch.uint8)[0, :4, :8] = torch.arange(32, dtype=torch.uint8).view(4, 8)   # e4m3 subnormals / tiny codes
@@ -140,12 +159,35 @@ def test_umma_fp8(K, case, block):
     ref = O.fused_experts(a, w1, w2, tw, ids, "fp8", w1s, w2s, block)
     dev = [t.cuda() for t in (a, w1, w2, tw, ids, w1s, w2s)]
     outs = {}
-    for name, path in (("stream", K.PATH_STREAM), ("umma", K.PATH_UMMA)):
-        outs[name] = K.fused_experts_impl(dev[0], dev[1], dev[2], dev[3], dev[4], False, K.FMT_FP8_W8A16, dev[5], dev[6],
-                                          block, False, path=path).cpu()
+    lib = K._lib.load()
+    lib.sglb_set_fp8_native(native)
+    try:
+        for name, path in (("stream", K.PATH_STREAM), ("umma", K.PATH_UMMA)):
+            outs[name] = K.fused_experts_impl(dev[0], dev[1], dev[2], dev[3], dev[4], False, K.FMT_FP8_W8A16, dev[5], dev[6],
+                                              block, False, path=path).cpu()
+    finally:
+        lib.sglb_set_fp8_native(1)
     assert torch.isfinite(outs["umma"]).all(), describe(outs["umma"], ref)
     assert torch.allclose(outs["umma"].float(), ref.float(), **BF16_TOL), "vs oracle: " + describe(outs["umma"], ref)
     assert torch.allclose(outs["umma"].float(), outs["stream"].float(), **BF16_TOL), "vs stream: " + describe(outs["umma"], outs["stream"])
+
+
+def test_split_rows_e4m3_is_exact_near_the_row_maximum(K):
+    """The hi/lo split behind the tensor-native fp8 path: (hi + lo) * 2^e reproduces every bf16 element
+    within 2^-9 of its row maximum exactly, and the rest to 2^-17 of the row maximum."""
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(64, 512, generator=g).bfloat16()
+    x[1] *= 1e-6
+    x[2] *= 1e6
+    x[3] = 0
+    x[4, ::2] *= 2.0 ** -11
+    hi, lo, rexp = K.split_rows_e4m3(x.cuda())
+    rec = (hi.cpu().view(torch.float8_e4m3fn).float() + lo.cpu().view(torch.float8_e4m3fn).float()) * rexp.cpu()[:, None]
+    xf = x.float()
+    rowmax = xf.abs().amax(dim=1, keepdim=True)
+    near = xf.abs() >= rowmax * 2.0 ** -9
+    assert torch.equal(rec[near], xf[near])
+    assert ((rec - xf).abs() <= rowmax * 2.0 ** -17).all()
 
 
 @pytest.mark.parametrize("case", DQ_CASES + [(64, 2880, 2880, 4, 2, "uniform")])
