@@ -164,6 +164,8 @@ def path_used(args, fmt, M, topk, E, H, I):
     """Mirrors the SGLB_PATH_AUTO rule of capi.cu (rows/expert >= 4 and a supported shape)."""
     if args.path != "auto":
         return args.path
+    if fmt == "fp8" and H % 128 == 0 and I % 128 == 0:
+        return "umma"          # tensor-native fp8 kernel at every M (capi.cu AUTO rule)
     if fmt in ("fp8", "mxfp4"):
         ok = H % 64 == 0 and I % 64 == 0
     else:
@@ -173,7 +175,7 @@ def path_used(args, fmt, M, topk, E, H, I):
 
 
 PATH_DESC = {"stream": "stream (mma.sync weight streaming)", "umma": "umma (tcgen05 + TMEM + TMA)"}
-KERNEL_DESC = {("umma", "bf16"): "umma_moe_kernel", ("umma", "int8"): "umma_moe_kernel", ("umma", "fp8"): "umma_dq_kernel",
+KERNEL_DESC = {("umma", "bf16"): "umma_moe_kernel", ("umma", "int8"): "umma_moe_kernel", ("umma", "fp8"): "umma_f8_kernel",
                ("umma", "mxfp4"): "umma_dq_kernel"}
 
 

@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   if (warp == 0) {
     // ================= TMA producer: raw weights =================
-    if (lane == 0) {
+    {
       uint32_t it = 0;
       for (int w = blockIdx.x; w < total; w += gridDim.x) {
         const WorkItem wi = get_item(a, w, n_blocks);
@@ -160,33 +160,36 @@ __global__ void __launch_bounds__(kThreads, 1)
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int s = it % RAWS;
           mbar_wait_relaxed(raw_empty(s), ((it / RAWS) & 1) ^ 1);
-          mbar_arrive_expect_tx(raw_full(s), kRawStageBytes);
-          const uint32_t dst = raw_base + s * kRawStageBytes;
-          tma_load_3d(dst, &tmap_w, raw_full(s), kb * RB, wrow0, wi.e);
-          tma_load_3d(dst + 128 * RB, &tmap_w, raw_full(s), kb * RB, wrow1, wi.e);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(raw_full(s), kRawStageBytes);
+            const uint32_t dst = raw_base + s * kRawStageBytes;
+            tma_load_3d(dst, &tmap_w, raw_full(s), kb * RB, wrow0, wi.e);
+            tma_load_3d(dst + 128 * RB, &tmap_w, raw_full(s), kb * RB, wrow1, wi.e);
+          }
+          __syncwarp();
         }
       }
     }
-    __syncwarp();
+      __syncwarp();
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
-      uint32_t it = 0, li = 0;
-      for (int w = blockIdx.x; w < total; w += gridDim.x, ++li) {
-        const WorkItem wi = get_item(a, w, n_blocks);
-        const int n_eff = (wi.rows + 15) & ~15;
-        const uint32_t idesc = instr_desc<SGLB_FMT_BF16>(n_eff);
-        const int buf = li & 1;
-        mbar_wait_relaxed(tempty_bar(buf), ((li >> 1) & 1) ^ 1);
+    // ================= MMA issuer (converged warp, one elected lane issues) =================
+    uint32_t it = 0, li = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x, ++li) {
+      const WorkItem wi = get_item(a, w, n_blocks);
+      const int n_eff = (wi.rows + 15) & ~15;
+      const uint32_t idesc = instr_desc<SGLB_FMT_BF16>(n_eff);
+      const int buf = li & 1;
+      mbar_wait_relaxed(tempty_bar(buf), ((li >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t acc = tmem_base + buf * kAccCols;
+      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const int sx = it % kXStages, sw = it % kWopStages;
+        mbar_wait_relaxed(x_full(sx), (it / kXStages) & 1);
+        mbar_wait_relaxed(wop_full(sw), (it / kWopStages) & 1);
+        fence_proxy_async();
         tc_fence_after();
-        const uint32_t acc = tmem_base + buf * kAccCols;
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
-          const int sx = it % kXStages, sw = it % kWopStages;
-          mbar_wait_relaxed(x_full(sx), (it / kXStages) & 1);
-          mbar_wait_relaxed(wop_full(sw), (it / kWopStages) & 1);
-          fence_proxy_async();
-          tc_fence_after();
-          const uint32_t wt = wop_base + sw * kWopBytes, xt = x_base + sx * kXTileBytes;
+        const uint32_t wt = wop_base + sw * kWopBytes, xt = x_base + sx * kXTileBytes;
+        if (elect_one()) {
 #pragma unroll
           for (int sub = 0; sub < 2; ++sub) {
 #pragma unroll
@@ -198,11 +201,11 @@ __global__ void __launch_bounds__(kThreads, 1)
           }
           umma_commit(x_empty(sx));
           umma_commit(wop_empty(sw));
+          if (kb == num_kb - 1) umma_commit(tfull_bar(buf));
         }
-        umma_commit(tfull_bar(buf));
+        __syncwarp();
       }
     }
-    __syncwarp();
   } else if (warp < kFirstEpiWarp) {
     gather_role<true>(a, total, n_blocks, num_kb, a.K * 2, threadIdx.x - 64, x_base, kXTileBytes, x_full(0),
                 x_empty(0), kXStages);

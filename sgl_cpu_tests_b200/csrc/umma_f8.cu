@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kProducerRegs));
     if (warp == 0) {
       // ================= TMA producer: e4m3 weights, untouched =================
-      if (lane == 0) {
+      {
         uint32_t it = 0;
         for (int w = blockIdx.x; w < total; w += gridDim.x) {
           const WorkItem wi = get_item(a, w, n_blocks);
@@ -117,34 +117,39 @@ __global__ void __launch_bounds__(kThreads, 1)
           const int wrow1 = STAGE == 1 ? a.N + wi.nb * kWSub : wrow0 + kWSub;
           for (int kb = 0; kb < num_kb; ++kb, ++it) {
             const int s = it % kStages;
-            mbar_wait_relaxed(empty_bar(s), ((it / kStages) & 1) ^ 1);
-            mbar_arrive_expect_tx(full_bar(s), 2 * kWTileBytes);
-            tma_load_3d(w_tile(s), &tmap_w, full_bar(s), kb * kRowBytes, wrow0, wi.e);
-            tma_load_3d(w_tile(s) + kWTileBytes, &tmap_w, full_bar(s), kb * kRowBytes, wrow1, wi.e);
+            mbar_wait(empty_bar(s), ((it / kStages) & 1) ^ 1);
+            if (elect_one()) {
+              mbar_arrive_expect_tx(full_bar(s), 2 * kWTileBytes);
+              tma_load_3d(w_tile(s), &tmap_w, full_bar(s), kb * kRowBytes, wrow0, wi.e);
+              tma_load_3d(w_tile(s) + kWTileBytes, &tmap_w, full_bar(s), kb * kRowBytes, wrow1, wi.e);
+            }
+            __syncwarp();
           }
         }
       }
       __syncwarp();
     } else if (warp == 1) {
       // ================= MMA issuer =================
-      if (lane == 0) {
-        uint32_t it = 0, gi = 0;
-        for (int w = blockIdx.x; w < total; w += gridDim.x) {
-          const WorkItem wi = get_item(a, w, n_blocks);
-          const int n_eff = (wi.rows + 15) & ~15;
-          const uint32_t idesc = instr_desc_f8(n_eff);
-          for (int kb = 0; kb < num_kb; ++kb, ++it) {
-            const bool first = (kb % G) == 0;
-            const int pb = gi & 1;
-            if (first) {
-              mbar_wait(pempty_bar(pb), ((gi >> 1) & 1) ^ 1);
-              tc_fence_after();
-            }
-            const int s = it % kStages;
-            mbar_wait(full_bar(s), (it / kStages) & 1);
-            fence_proxy_async();  // routed rows were written by cp.async (generic proxy)
+      // The whole warp runs the loop converged; one elected lane issues (see elect_one()).
+      uint32_t it = 0, gi = 0;
+      for (int w = blockIdx.x; w < total; w += gridDim.x) {
+        const WorkItem wi = get_item(a, w, n_blocks);
+        const int n_eff = (wi.rows + 15) & ~15;
+        const uint32_t idesc = instr_desc_f8(n_eff);
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const bool first = (kb % G) == 0;
+          const int pb = gi & 1;
+          if (first) {
+            mbar_wait(pempty_bar(pb), ((gi >> 1) & 1) ^ 1);
             tc_fence_after();
-            const uint32_t acc = tmem_base + pb * kAccCols;
+          }
+          const int s = it % kStages;
+          mbar_wait(full_bar(s), (it / kStages) & 1);
+          fence_proxy_async();  // routed rows were written by cp.async (generic proxy)
+          tc_fence_after();
+          const uint32_t acc = tmem_base + pb * kAccCols;
+          const bool last = (kb % G) == G - 1 || kb == num_kb - 1;
+          if (elect_one()) {
 #pragma unroll
             for (int sub = 0; sub < 2; ++sub) {
 #pragma unroll
@@ -157,14 +162,12 @@ __global__ void __launch_bounds__(kThreads, 1)
               }
             }
             umma_commit(empty_bar(s));
-            if ((kb % G) == G - 1 || kb == num_kb - 1) {
-              umma_commit(pfull_bar(pb));  // this k block's partial sums are complete
-              ++gi;
-            }
+            if (last) umma_commit(pfull_bar(pb));  // this k block's partial sums are complete
           }
+          __syncwarp();
+          if (last) ++gi;
         }
       }
-      __syncwarp();
     } else {
       // ================= gather producers: hi and lo rows =================
       // 64 threads: thread g owns 16-B chunk c = g & 7 of rows (g >> 3) + 8 j, j = 0..15

@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   if (warp == 0) {
     // ================= TMA producer: weights =================
-    if (lane == 0) {
+    {
       uint32_t it = 0;
       for (int w = blockIdx.x; w < total; w += gridDim.x) {
         const WorkItem wi = get_item(a, w, n_blocks);
@@ -101,30 +101,36 @@ __global__ void __launch_bounds__(kThreads, 1)
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int s = it % kStages;
           mbar_wait(empty_bar(s), ((it / kStages) & 1) ^ 1);
-          mbar_arrive_expect_tx(full_bar(s), 2 * kWTileBytes);
-          tma_load_3d(w_tile(s), &tmap_w, full_bar(s), kb * kRowBytes, wrow0, wi.e);
-          tma_load_3d(w_tile(s) + kWTileBytes, &tmap_w, full_bar(s), kb * kRowBytes, wrow1, wi.e);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(full_bar(s), 2 * kWTileBytes);
+            tma_load_3d(w_tile(s), &tmap_w, full_bar(s), kb * kRowBytes, wrow0, wi.e);
+            tma_load_3d(w_tile(s) + kWTileBytes, &tmap_w, full_bar(s), kb * kRowBytes, wrow1, wi.e);
+          }
+          __syncwarp();
         }
       }
     }
-    __syncwarp();
+      __syncwarp();
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    if (lane == 0) {
-      uint32_t it = 0, li = 0;
-      for (int w = blockIdx.x; w < total; w += gridDim.x, ++li) {
-        const WorkItem wi = get_item(a, w, n_blocks);
-        const int n_eff = (wi.rows + 15) & ~15;
-        const uint32_t idesc = instr_desc<FMT>(n_eff);
-        const int buf = li & 1;
-        mbar_wait(tempty_bar(buf), ((li >> 1) & 1) ^ 1);
+    // The whole warp runs the loop converged and one elected lane issues: under `if (lane == 0)` ptxas
+    // wraps every tcgen05.mma in a per-lane waterfall loop (~65 issue cycles per MMA, ncu r1e), which
+    // made the issuing thread -- not the tensor pipe -- the bottleneck at prefill.
+    uint32_t it = 0, li = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x, ++li) {
+      const WorkItem wi = get_item(a, w, n_blocks);
+      const int n_eff = (wi.rows + 15) & ~15;
+      const uint32_t idesc = instr_desc<FMT>(n_eff);
+      const int buf = li & 1;
+      mbar_wait(tempty_bar(buf), ((li >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t acc = tmem_base + buf * kAccCols;
+      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const int s = it % kStages;
+        mbar_wait(full_bar(s), (it / kStages) & 1);
+        fence_proxy_async();  // routed rows were written by cp.async (generic proxy)
         tc_fence_after();
-        const uint32_t acc = tmem_base + buf * kAccCols;
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
-          const int s = it % kStages;
-          mbar_wait(full_bar(s), (it / kStages) & 1);
-          fence_proxy_async();  // routed rows were written by cp.async (generic proxy)
-          tc_fence_after();
+        if (elect_one()) {
 #pragma unroll
           for (int sub = 0; sub < 2; ++sub) {
 #pragma unroll
@@ -135,11 +141,11 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
           }
           umma_commit(empty_bar(s));  // frees the smem stage once these MMAs have read it
+          if (kb == num_kb - 1) umma_commit(tfull_bar(buf));  // accumulators of this item are complete
         }
-        umma_commit(tfull_bar(buf));  // accumulators of this item are complete
+        __syncwarp();
       }
     }
-    __syncwarp();
   } else if (warp < 6) {
     gather_role<false>(a, total, n_blocks, num_kb, k_bytes, threadIdx.x - 64, x_tile(0), kStageBytes, full_bar(0),
                 empty_bar(0), kStages);
