@@ -435,10 +435,24 @@ extern "C" int sglb_shared_expert(const sglb_shared_problem* p, sglb_stream_t st
              p->workspace_bytes, need);
   MoeWorkspace ws = carve(p->workspace, p->M, 1, 1, p->H, p->I, p->fmt);
   SGLB_CUDA(cudaMemsetAsync(ws.zero_ids, 0, sizeof(int32_t) * p->M, stream));
-  StreamPlan plan = make_plan(p->M, 1, 1, p->I, 1);
-  rc = run_align(ws.zero_ids, p->M, 1, 1, 8 * plan.ng, ws, stream);
+  // same path rule as fused_experts with E = 1 (every token is a routed row of the one expert)
+  int path = p->path;
+  if (path == SGLB_PATH_AUTO) {
+    const bool f8 = p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k);
+    path = ((f8 || (double)p->M >= kUmmaMinRowsPerExpert) && umma_supported(p->fmt, p->M, 1, 1, p->H, p->I))
+               ? SGLB_PATH_UMMA
+               : SGLB_PATH_STREAM;
+  }
+  if (path == SGLB_PATH_UMMA) {
+    SGLB_CHECK(umma_supported(p->fmt, p->M, 1, 1, p->H, p->I),
+               "shared_expert: tcgen05 path does not support fmt=%d H=%d I=%d", p->fmt, p->H, p->I);
+    rc = run_align(ws.zero_ids, p->M, 1, 1, 0, ws, stream);
+  } else {
+    StreamPlan plan = make_plan(p->M, 1, 1, p->I, 1);
+    rc = run_align(ws.zero_ids, p->M, 1, 1, 8 * plan.ng, ws, stream);
+  }
   if (rc) return rc;
-  rc = run_mlp(SGLB_PATH_STREAM, p->fmt, p->M, 1, 1, p->H, p->I, p->hidden, p->w1, p->w2, p->w1_scale,
+  rc = run_mlp(path, p->fmt, p->M, 1, 1, p->H, p->I, p->hidden, p->w1, p->w2, p->w1_scale,
                p->w2_scale, p->block_n, p->block_k, nullptr, ws, ws.ic2, stream);
   if (rc) return rc;
   return launch_shared_axpy(ws.ic2, p->fused_out, p->routed_scaling_factor, p->M * (int64_t)p->H, p->out, stream);

@@ -209,3 +209,33 @@ def test_umma_mxfp4(K, case):
     assert torch.isfinite(outs["umma"]).all(), describe(outs["umma"], ref)
     assert torch.allclose(outs["umma"].float(), ref.float(), **BF16_TOL), "vs oracle: " + describe(outs["umma"], ref)
     assert torch.allclose(outs["umma"].float(), outs["stream"].float(), **BF16_TOL), "vs stream: " + describe(outs["umma"], outs["stream"])
+
+
+@pytest.mark.parametrize("fmt", ["bf16", "int8", "fp8"])
+@pytest.mark.parametrize("shape", [(300, 256, 512), (1024, 512, 1024)])
+def test_shared_expert_umma(K, shape, fmt):
+    """shared_expert with enough rows takes the tcgen05 kernels (E = 1 tile list): dense 2-GEMM MLP +
+    fused_out * routed_scaling_factor epilogue vs the oracle (test_shared_experts.py:34-53)."""
+    M, I, H = shape
+    g = torch.Generator().manual_seed(1111)
+    hs = (torch.randn(M, H, generator=g) / math.sqrt(H)).bfloat16()
+    fo = (torch.randn(M, H, generator=g) / 16).bfloat16()
+    rsf = 2.5
+    if fmt == "bf16":
+        w1 = (torch.randn(2 * I, H, generator=g) / 10).bfloat16()
+        w2 = (torch.randn(H, I, generator=g) / 10).bfloat16()
+        ref = O.shared_expert(hs, w1, w2, fo, rsf, "bf16")
+        out = K.shared_expert(hs.clone(), w1, w2, fo, rsf, False, False, False, None, None, None, False)
+    elif fmt == "int8":
+        w1, s1 = O.per_token_quant_int8((torch.randn(2 * I, H, generator=g) / 10).bfloat16())
+        w2, s2 = O.per_token_quant_int8((torch.randn(H, I, generator=g) / 10).bfloat16())
+        ref = O.shared_expert(hs, w1, w2, fo, rsf, "int8", s1, s2)
+        out = K.shared_expert(hs.clone(), w1, w2, fo, rsf, False, True, False, s1, s2, None, False)
+    else:
+        w1 = (torch.randn(2 * I, H, generator=g) * 100).clamp(-448, 448).to(torch.float8_e4m3fn)
+        w2 = (torch.randn(H, I, generator=g) * 100).clamp(-448, 448).to(torch.float8_e4m3fn)
+        s1 = torch.randn(2 * I // 128, H // 128, generator=g) * 1e-3
+        s2 = torch.randn(H // 128, I // 128, generator=g) * 1e-3
+        ref = O.shared_expert(hs, w1, w2, fo, rsf, "fp8", s1, s2, [128, 128])
+        out = K.shared_expert(hs.clone(), w1, w2, fo, rsf, False, False, True, s1, s2, [128, 128], None, None, False)
+    assert torch.allclose(out.float(), ref.float(), **BF16_TOL), describe(out, ref)
