@@ -42,7 +42,7 @@ def parse():
     ap.add_argument("--sweep", default="1,16,128,1024,4096", help="extra M values reported under 'sweep'")
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--path", default="auto", choices=["auto", "stream", "umma"], help="GEMM path (auto = by rows/expert)")
+    ap.add_argument("--path", default="auto", choices=["auto", "stream", "umma", "umma2"], help="GEMM path (auto = by rows/expert)")
     ap.add_argument("--copies", type=int, default=2, help="weight copies rotated between steps (bench_moe.py:50-58)")
     return ap.parse_args()
 
@@ -157,7 +157,7 @@ def dist_env():
 
 
 FMT_ID = {"bf16": 0, "int8": 1, "fp8": 2, "mxfp4": 4}
-PATHS = {"auto": 0, "stream": 1, "umma": 2}
+PATHS = {"auto": 0, "stream": 1, "umma": 2, "umma2": 3}
 
 
 def path_used(args, fmt, M, topk, E, H, I):
@@ -174,8 +174,9 @@ def path_used(args, fmt, M, topk, E, H, I):
     return "umma" if ok and M * topk / E >= 4.0 else "stream"
 
 
-PATH_DESC = {"stream": "stream (mma.sync weight streaming)", "umma": "umma (tcgen05 + TMEM + TMA)"}
-KERNEL_DESC = {("umma", "bf16"): "umma_moe_kernel", ("umma", "int8"): "umma_moe_kernel", ("umma", "fp8"): "umma_f8_kernel",
+PATH_DESC = {"stream": "stream (mma.sync weight streaming)", "umma": "umma (tcgen05 + TMEM + TMA)",
+             "umma2": "umma2 (tcgen05 cta_group::2, CTA pair per tile)"}
+KERNEL_DESC = {("umma2", "bf16"): "umma2_moe_kernel", ("umma2", "int8"): "umma2_moe_kernel", ("umma", "bf16"): "umma_moe_kernel", ("umma", "int8"): "umma_moe_kernel", ("umma", "fp8"): "umma_f8_kernel",
                ("umma", "mxfp4"): "umma_dq_kernel"}
 
 
@@ -285,7 +286,7 @@ def run_b200(args):
         k_us = stage_us["w13_gemm"]
         achieved = ab["w13"] / (k_us * 1e-6) / 1e9 if k_us > 0 else 0.0
         used = path_used(args, fmt, M, topk, E, H, I)
-        kname = (f"{KERNEL_DESC[(used, fmt)]}<stage 1> (tcgen05 w13 GEMM + silu_and_mul)" if used == "umma"
+        kname = (f"{KERNEL_DESC[(used, fmt)]}<stage 1> (tcgen05 w13 GEMM + silu_and_mul)" if used.startswith("umma")
                  else "stream_gemm_kernel<stage 1> (mma.sync w13 GEMM + silu_and_mul)")
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")

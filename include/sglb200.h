@@ -42,7 +42,12 @@ enum {
 };
 
 /* which GEMM implementation sglb_fused_experts uses */
-enum { SGLB_PATH_AUTO = 0, SGLB_PATH_STREAM = 1, SGLB_PATH_UMMA = 2 };
+enum {
+  SGLB_PATH_AUTO = 0,
+  SGLB_PATH_STREAM = 1, /* mma.sync weight streaming (few rows per expert) */
+  SGLB_PATH_UMMA = 2,   /* tcgen05, one CTA per tile */
+  SGLB_PATH_UMMA2 = 3   /* tcgen05 cta_group::2, a CTA pair per 256 x 256 tile (bf16 / int8, prefill) */
+};
 
 int sglb_version(void);
 const char* sglb_last_error(void);

@@ -18,4 +18,4 @@ from .ops import (CPUQuantMethod, biased_grouped_topk, biased_grouped_topk_out, 
 DROPIN_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "dropin")
 FMT_BF16, FMT_INT8_W8A8, FMT_FP8_W8A16, FMT_MXFP4 = (_lib.FMT_BF16, _lib.FMT_INT8_W8A8,
                                                     _lib.FMT_FP8_W8A16, _lib.FMT_MXFP4)
-PATH_AUTO, PATH_STREAM, PATH_UMMA = _lib.PATH_AUTO, _lib.PATH_STREAM, _lib.PATH_UMMA
+PATH_AUTO, PATH_STREAM, PATH_UMMA, PATH_UMMA2 = _lib.PATH_AUTO, _lib.PATH_STREAM, _lib.PATH_UMMA, _lib.PATH_UMMA2

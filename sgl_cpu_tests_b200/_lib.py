@@ -8,7 +8,7 @@ LIB_PATH = os.path.join(_HERE, "libsglb200.so")
 OK = 0
 DT_BF16, DT_F32, DT_F16 = 0, 1, 2
 FMT_BF16, FMT_INT8_W8A8, FMT_FP8_W8A16, FMT_MXFP4 = 0, 1, 2, 4
-PATH_AUTO, PATH_STREAM, PATH_UMMA = 0, 1, 2
+PATH_AUTO, PATH_STREAM, PATH_UMMA, PATH_UMMA2 = 0, 1, 2, 3
 
 _vp, _i32, _i64, _f32, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t
 

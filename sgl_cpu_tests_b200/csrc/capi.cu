@@ -191,7 +191,7 @@ static int check_format(const char* who, int fmt, int H, int I, const void* s13,
 
 // One GEMM stage on the tcgen05 path over the tile list of an existing alignment.
 static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64_t S, const MoeWorkspace& ws,
-                          cudaStream_t stream, bool f8_native = false) {
+                          cudaStream_t stream, bool f8_native = false, bool pair = false) {
   UmmaArgs u;
   memset(&u, 0, sizeof(u));
   u.W = sa.W;
@@ -209,12 +209,13 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.E = E;
   u.topk = sa.topk;
   u.gather = sa.gather;
-  u.max_tiles = (int)max_items(S, E, kTileRows);
+  u.max_tiles = (int)max_items(S, E, pair ? umma2_tile_rows() : kTileRows);
   u.block_n = sa.block_n;
   u.block_k = sa.block_k;
   u.scale_cols = sa.scale_cols;
   u.X2 = sa.X2;
   if (f8_native) return launch_umma_f8(stage, u, stream);
+  if (pair) return launch_umma2_gemm(fmt, stage, u, stream);
   return launch_umma_gemm(fmt, stage, u, stream);
 }
 
@@ -236,7 +237,7 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
 
   StreamPlan plan = make_plan(M, topk, E, I, 1);
   plan.max_chunks = (int)max_items(S, E, 8 * plan.ng);
-  SGLB_CHECK(path == SGLB_PATH_UMMA || plan.max_chunks <= 65535,
+  SGLB_CHECK(path != SGLB_PATH_STREAM || plan.max_chunks <= 65535,
              "fused_experts(stream path): too many row chunks (%d)", plan.max_chunks);
 
   // stage 1
@@ -251,6 +252,8 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   a.scale_cols = fmt == SGLB_FMT_FP8_W8A16 ? ceil_div(H, bk) : H / 32;
   int rc;
   // fp8 w8a16 on the fp8 tensor cores: activations split into two e4m3 pieces (umma_f8.cu)
+  const bool pair = path == SGLB_PATH_UMMA2;
+  const bool umma = path == SGLB_PATH_UMMA || pair;
   const bool f8 = path == SGLB_PATH_UMMA && fmt == SGLB_FMT_FP8_W8A16 && g_f8_native &&
                   umma_f8_supported(H, I, bn, bk);
   if (fmt == SGLB_FMT_INT8_W8A8) {
@@ -271,7 +274,7 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   }
   {
     StageTimer t(ST_GEMM1, stream);
-    rc = path == SGLB_PATH_UMMA ? run_umma_stage(fmt, 1, a, E, S, ws, stream, f8)
+    rc = umma ? run_umma_stage(fmt, 1, a, E, S, ws, stream, f8, pair)
                                 : dispatch_stream<1>(fmt, a, plan, stream);
   }
   if (rc) return rc;
@@ -306,12 +309,12 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
     a.X = ws.act;
   }
   StageTimer t(ST_GEMM2, stream);
-  return path == SGLB_PATH_UMMA ? run_umma_stage(fmt, 2, a, E, S, ws, stream, f8)
+  return umma ? run_umma_stage(fmt, 2, a, E, S, ws, stream, f8, pair)
                                 : dispatch_stream<2>(fmt, a, plan2, stream);
 }
 
 static int run_align(const int32_t* ids, int64_t M, int topk, int E, int chunk_rows,
-                     const MoeWorkspace& ws, cudaStream_t stream) {
+                     const MoeWorkspace& ws, cudaStream_t stream, int tile_rows = kTileRows) {
   sglb_align_out ao;
   ao.expert_count = ws.expert_count;
   ao.expert_offset = ws.expert_offset;
@@ -321,7 +324,7 @@ static int run_align(const int32_t* ids, int64_t M, int topk, int E, int chunk_r
   ao.tile_list = ws.tile_list;
   ao.counters = ws.counters;
   StageTimer t(ST_ALIGN, stream);
-  int rc = sglb_moe_align(ids, M, topk, E, chunk_rows, kTileRows, &ao, ws.align_scratch, stream);
+  int rc = sglb_moe_align(ids, M, topk, E, chunk_rows, tile_rows, &ao, ws.align_scratch, stream);
   return rc;
 }
 
@@ -401,12 +404,15 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
                ? SGLB_PATH_UMMA
                : SGLB_PATH_STREAM;
   }
-  if (path == SGLB_PATH_UMMA) {
+  if (path == SGLB_PATH_UMMA || path == SGLB_PATH_UMMA2) {
     SGLB_CHECK(umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I),
                "fused_experts: tcgen05 path does not support fmt=%d H=%d I=%d", p->fmt, p->H, p->I);
-    rc = run_align(p->topk_ids, p->M, p->topk, p->E, 0, ws, stream);
+    SGLB_CHECK(path == SGLB_PATH_UMMA || p->fmt == SGLB_FMT_BF16 || p->fmt == SGLB_FMT_INT8_W8A8,
+               "fused_experts: the CTA-pair tcgen05 path takes bf16 and int8 weights only (fmt=%d)", p->fmt);
+    rc = run_align(p->topk_ids, p->M, p->topk, p->E, 0, ws, stream,
+                   path == SGLB_PATH_UMMA2 ? umma2_tile_rows() : kTileRows);
     if (rc) return rc;
-    rc = run_mlp(SGLB_PATH_UMMA, p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2,
+    rc = run_mlp(path, p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2,
                  p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, ws.ic2, stream);
     if (rc) return rc;
   } else {

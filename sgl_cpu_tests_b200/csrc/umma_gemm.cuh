@@ -32,6 +32,9 @@ constexpr int kUmmaTileRows = 128;  // routed rows per tile (tile_rows handed to
 int umma_supported(int fmt, int64_t M, int topk, int E, int H, int I);
 // stage 1: out = silu(X W13_gate^T) * (X W13_up^T);  stage 2: out = (X W2^T) * row_scale
 int launch_umma_gemm(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream);
+// CTA-pair kernels (umma2_gemm.cu): tile_list must hold umma2_tile_rows()-row tiles; bf16 / int8
+int umma2_tile_rows();
+int launch_umma2_gemm(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream);
 // fp8 w8a16 / mxfp4: weights dequantised to bf16 inside the kernel (umma_dq.cu)
 int launch_umma_dq(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream);
 // fp8 w8a16 on the fp8 tensor cores (umma_f8.cu): X/X2 = hi/lo e4m3 pieces, Xscale = per-row 2^e factor

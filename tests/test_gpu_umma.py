@@ -239,3 +239,53 @@ def test_shared_expert_umma(K, shape, fmt):
         ref = O.shared_expert(hs, w1, w2, fo, rsf, "fp8", s1, s2, [128, 128])
         out = K.shared_expert(hs.clone(), w1, w2, fo, rsf, False, False, True, s1, s2, [128, 128], None, None, False)
     assert torch.allclose(out.float(), ref.float(), **BF16_TOL), describe(out, ref)
+
+
+PAIR_CASES = [  # M, I, H, E, topk, style
+    (64, 128, 128, 4, 2, "uniform"),
+    (300, 128, 256, 8, 2, "uniform"),
+    (257, 192, 320, 8, 4, "skewed"),      # partial weight blocks, ragged pair tiles, -1 ids
+    (130, 256, 128, 4, 2, "one"),         # 260 rows on one expert: a full 256-row pair tile + a 4-row one
+    (1, 128, 128, 2, 1, "uniform"),
+    (700, 256, 384, 2, 2, "one"),         # 1400 rows: five full pair tiles + 120 rows
+    (1024, 768, 2048, 128, 8, "uniform"),
+]
+
+
+@pytest.mark.parametrize("case", PAIR_CASES)
+def test_umma2_bf16(K, case):
+    """CTA-pair kernel (tcgen05.mma.cta_group::2, umma2_gemm.cu) vs the oracle and the single-CTA kernel."""
+    M, I, H, E, topk, style = case
+    g = torch.Generator().manual_seed(1111)
+    a = torch.randn(M, H, generator=g).bfloat16() / 10
+    w1 = (torch.randn(E, 2 * I, H, generator=g) / 10).bfloat16()
+    w2 = (torch.randn(E, H, I, generator=g) / 10).bfloat16()
+    ids = make_ids(M, E, topk, style, g)
+    tw = torch.rand(M, topk, generator=g) / (topk if style == "one" else 1)
+    ref = O.native_fused_moe(a, w1, w2, tw, ids)
+    ad, w1d, w2d, twd, idd = a.cuda(), w1.cuda(), w2.cuda(), tw.cuda(), ids.cuda()
+    out_u = K.fused_experts_impl(ad, w1d, w2d, twd, idd, False, K.FMT_BF16, None, None, None, False, path=K.PATH_UMMA)
+    out_p = K.fused_experts_impl(ad, w1d, w2d, twd, idd, False, K.FMT_BF16, None, None, None, False, path=K.PATH_UMMA2)
+    torch.cuda.synchronize()
+    out_u, out_p = out_u.cpu(), out_p.cpu()
+    assert torch.isfinite(out_p).all(), describe(out_p, ref)
+    assert torch.allclose(out_p.float(), ref.float(), **BF16_TOL), "vs oracle: " + describe(out_p, ref)
+    assert torch.allclose(out_p.float(), out_u.float(), **BF16_TOL), "vs single-CTA: " + describe(out_p, out_u)
+
+
+@pytest.mark.parametrize("case", [c for c in PAIR_CASES if c[1] % 128 == 0 and c[2] % 128 == 0])
+def test_umma2_int8(K, case):
+    M, I, H, E, topk, style = case
+    g = torch.Generator().manual_seed(1111)
+    a = (torch.randn(M, H, generator=g) / math.sqrt(H)).bfloat16()
+    w1 = torch.randint(-127, 128, (E, 2 * I, H), generator=g, dtype=torch.int8)
+    w2 = torch.randint(-127, 128, (E, H, I), generator=g, dtype=torch.int8)
+    s1, s2 = torch.rand(E, 2 * I, generator=g) * 1e-2, torch.rand(E, H, generator=g) * 1e-2
+    ids = make_ids(M, E, topk, style, g)
+    tw = torch.rand(M, topk, generator=g)
+    dev = [t.cuda() for t in (a, w1, w2, tw, ids, s1, s2)]
+    out_u = K.fused_experts_impl(*dev[:5], False, K.FMT_INT8_W8A8, dev[5], dev[6], None, False, path=K.PATH_UMMA).cpu()
+    out_p = K.fused_experts_impl(*dev[:5], False, K.FMT_INT8_W8A8, dev[5], dev[6], None, False, path=K.PATH_UMMA2).cpu()
+    assert torch.isfinite(out_p).all(), describe(out_p, out_u)
+    # exact integer accumulation and the same f32 epilogue expressions on both kernels
+    assert torch.equal(out_p, out_u), "vs single-CTA: " + describe(out_p, out_u)
