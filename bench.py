@@ -171,6 +171,8 @@ def path_used(args, fmt, M, topk, E, H, I):
     else:
         eb = {"bf16": 2, "int8": 1}[fmt]
         ok = (H * eb) % 128 == 0 and (I * eb) % 128 == 0
+    if ok and fmt == "bf16" and M * topk / E >= 128.0:
+        return "umma2"
     return "umma" if ok and M * topk / E >= 4.0 else "stream"
 
 

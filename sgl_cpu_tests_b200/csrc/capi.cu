@@ -79,6 +79,7 @@ constexpr int kMinChunkRows = 8;
 // Measured on B200 (Qwen3 shape): the persistent TMA-fed tcgen05 kernel streams weights faster than the
 // mma.sync kernel from about 4 routed rows per expert upwards and ties below.
 constexpr double kUmmaMinRowsPerExpert = 4.0;
+constexpr double kPairMinRowsPerExpert = 128.0;
 constexpr int kTileRows = kUmmaTileRows;
 
 static int64_t max_items(int64_t S, int E, int rows) {
@@ -403,6 +404,10 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     path = ((f8 || rows_per_expert >= kUmmaMinRowsPerExpert) && umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I))
                ? SGLB_PATH_UMMA
                : SGLB_PATH_STREAM;
+    // bf16 prefill: the CTA-pair kernel wins once pair tiles fill up (Qwen3 M = 4096: 793 vs 705 TFLOP/s,
+    // M = 8192: 940 vs 804); int8 stays on the single-CTA kernel (940 vs 805 TOP/s at M = 4096)
+    if (path == SGLB_PATH_UMMA && p->fmt == SGLB_FMT_BF16 && rows_per_expert >= kPairMinRowsPerExpert)
+      path = SGLB_PATH_UMMA2;
   }
   if (path == SGLB_PATH_UMMA || path == SGLB_PATH_UMMA2) {
     SGLB_CHECK(umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I),
