@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--path", default="auto", choices=["auto", "stream", "umma", "umma2"], help="GEMM path (auto = by rows/expert)")
+    ap.add_argument("--block-k", type=int, default=128, help="fp8 scale block along K (experiments; the layer's is 128)")
     ap.add_argument("--copies", type=int, default=2, help="weight copies rotated between steps (bench_moe.py:50-58)")
     return ap.parse_args()
 
@@ -53,6 +54,7 @@ SHAPES = {  # E, topk, H, I
     "gptoss": (128, 4, 2880, 2880),
     "refbench": (256, 8, 7168, 384),   # bench_moe.py:144-145
 }
+BLOCK_K = 128
 WBYTES = {"bf16": 2.0, "int8": 1.0, "fp8": 1.0, "mxfp4": 0.5}
 
 
@@ -78,8 +80,9 @@ def make_weights(fmt, E, H, I, device, gen):
     if fmt == "fp8":
         w1 = (rnd(E, 2 * I, H) * 100).clamp(-400, 400).to(torch.float8_e4m3fn)
         w2 = (rnd(E, H, I) * 100).clamp(-400, 400).to(torch.float8_e4m3fn)
-        return dict(w1=w1, w2=w2, s1=rnd(E, 2 * I // 128, H // 128) * 1e-3, s2=rnd(E, H // 128, I // 128) * 1e-3,
-                    block=[128, 128])
+        bk = BLOCK_K
+        return dict(w1=w1, w2=w2, s1=rnd(E, 2 * I // 128, H // bk) * 1e-3, s2=rnd(E, H // 128, I // bk) * 1e-3,
+                    block=[128, bk])
     w1 = torch.randint(0, 256, (E, 2 * I, H // 2), device=device, generator=gen, dtype=torch.uint8)
     w2 = torch.randint(0, 256, (E, H, I // 2), device=device, generator=gen, dtype=torch.uint8)
     s1 = torch.randint(118, 122, (E, 2 * I, H // 32), device=device, generator=gen, dtype=torch.uint8)
@@ -178,7 +181,7 @@ def path_used(args, fmt, M, topk, E, H, I):
 
 PATH_DESC = {"stream": "stream (mma.sync weight streaming)", "umma": "umma (tcgen05 + TMEM + TMA)",
              "umma2": "umma2 (tcgen05 cta_group::2, CTA pair per tile)"}
-KERNEL_DESC = {("umma2", "bf16"): "umma2_moe_kernel", ("umma2", "int8"): "umma2_moe_kernel", ("umma", "bf16"): "umma_moe_kernel", ("umma", "int8"): "umma_moe_kernel", ("umma", "fp8"): "umma_f8_kernel",
+KERNEL_DESC = {("umma2", "fp8"): "umma2_f8_kernel", ("umma2", "bf16"): "umma2_moe_kernel", ("umma2", "int8"): "umma2_moe_kernel", ("umma", "bf16"): "umma_moe_kernel", ("umma", "int8"): "umma_moe_kernel", ("umma", "fp8"): "umma_f8_kernel",
                ("umma", "mxfp4"): "umma_dq_kernel"}
 
 
@@ -457,6 +460,7 @@ def run_reference(args):
 
 if __name__ == "__main__":
     a = parse()
+    BLOCK_K = a.block_k
     if a.impl == "reference":
         run_reference(a)
     else:

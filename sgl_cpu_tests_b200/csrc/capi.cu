@@ -215,7 +215,7 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.block_k = sa.block_k;
   u.scale_cols = sa.scale_cols;
   u.X2 = sa.X2;
-  if (f8_native) return launch_umma_f8(stage, u, stream);
+  if (f8_native) return pair ? launch_umma2_f8(stage, u, stream) : launch_umma_f8(stage, u, stream);
   if (pair) return launch_umma2_gemm(fmt, stage, u, stream);
   return launch_umma_gemm(fmt, stage, u, stream);
 }
@@ -255,7 +255,7 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   // fp8 w8a16 on the fp8 tensor cores: activations split into two e4m3 pieces (umma_f8.cu)
   const bool pair = path == SGLB_PATH_UMMA2;
   const bool umma = path == SGLB_PATH_UMMA || pair;
-  const bool f8 = path == SGLB_PATH_UMMA && fmt == SGLB_FMT_FP8_W8A16 && g_f8_native &&
+  const bool f8 = umma && fmt == SGLB_FMT_FP8_W8A16 && g_f8_native &&
                   umma_f8_supported(H, I, bn, bk);
   if (fmt == SGLB_FMT_INT8_W8A8) {
     StageTimer t(ST_QUANT_X, stream);
@@ -412,8 +412,9 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
   if (path == SGLB_PATH_UMMA || path == SGLB_PATH_UMMA2) {
     SGLB_CHECK(umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I),
                "fused_experts: tcgen05 path does not support fmt=%d H=%d I=%d", p->fmt, p->H, p->I);
-    SGLB_CHECK(path == SGLB_PATH_UMMA || p->fmt == SGLB_FMT_BF16 || p->fmt == SGLB_FMT_INT8_W8A8,
-               "fused_experts: the CTA-pair tcgen05 path takes bf16 and int8 weights only (fmt=%d)", p->fmt);
+    SGLB_CHECK(path == SGLB_PATH_UMMA || p->fmt == SGLB_FMT_BF16 || p->fmt == SGLB_FMT_INT8_W8A8 ||
+                   (p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k)),
+               "fused_experts: the CTA-pair tcgen05 path takes bf16, int8 and tensor-native fp8 weights only (fmt=%d)", p->fmt);
     rc = run_align(p->topk_ids, p->M, p->topk, p->E, 0, ws, stream,
                    path == SGLB_PATH_UMMA2 ? umma2_tile_rows() : kTileRows);
     if (rc) return rc;

@@ -22,7 +22,7 @@
 //   empty[s]     tcgen05.commit multicast to both CTAs: stage may be refilled
 //   tfull[b]     tcgen05.commit multicast: accumulators complete
 //   tempty[b] L  one arrive per epilogue warp of both CTAs: buffer drained
-#include "umma_common.cuh"
+#include "umma_pair.cuh"
 
 namespace sglb {
 
@@ -36,92 +36,6 @@ constexpr int kFirstEpiWarp2 = 6;
 constexpr int kThreads2 = (kFirstEpiWarp2 + kEpiWarps) * 32;  // 448
 constexpr int kXchgBytes = 4 * 2 * 2048;                      // 4 warp pairs x 2 buffers x (16 tokens x 32 lanes f32)
 constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + kEpiWarps * kEpiBufBytes + kXchgBytes + 1024 + 256;
-constexpr int kPairRows = 256;                                // routed rows per pair tile
-
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-// shared::cluster address of `addr` (a shared::cta address of this CTA) in CTA `rank` of the cluster
-__device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-// Remote arrive on a barrier of another CTA of the pair.  Deliberately without .release.cluster /
-// .acquire.cluster on the waiting side: ptxas turns cluster-scope acquire into CCTL.IVALL (an L1
-// invalidate) and release into a full membar, which serialised every pipeline stage (~1.1 us per
-// stage, ncu r1f).  Nothing crosses the pair through the generic proxy here: the data the barriers
-// guard is read by the tensor core (async proxy, after fence.proxy.async in the writer's CTA) or
-// lives in TMEM (ordered by tcgen05.fence), the same discipline CUTLASS' 2-SM kernels use.
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-// TMA load whose completion bytes are counted on a barrier of the pair's leader CTA
-__device__ __forceinline__ void tma_load_3d_pair(uint32_t dst, const CUtensorMap* map, uint32_t leader_bar,
-                                                 int c0, int c1, int c2) {
-  asm volatile(
-      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, "
-      "%4, %5}], [%2];" ::"r"(dst),
-      "l"(reinterpret_cast<uint64_t>(map)), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2)
-      : "memory");
-}
-template <int FMT>
-__device__ __forceinline__ void umma_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                          uint32_t accumulate) {
-  if constexpr (FMT == SGLB_FMT_INT8_W8A8) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-  } else {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-  }
-}
-// arrives (once all MMAs issued so far have completed) on the barrier at this offset in both CTAs
-__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
-  asm volatile(
-      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
-      "h"((uint16_t)3)
-      : "memory");
-}
-// instruction descriptor for the pair MMA: M = 256, N = n
-template <int FMT>
-__device__ __forceinline__ uint32_t instr_desc_pair(int n) {
-  const uint32_t cfmt = FMT == SGLB_FMT_INT8_W8A8 ? 2u : 1u;
-  return (cfmt << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
-}
-__device__ __forceinline__ void named_bar_sync(int id, int threads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
-}
-__device__ __forceinline__ float sel8(const float (&v)[8], int i) {
-  float r = v[0];
-#pragma unroll
-  for (int k = 1; k < 8; ++k) r = i == k ? v[k] : r;
-  return r;
-}
-
-struct PairItem {
-  int e, row_start, rows, nb;
-};
-__device__ __forceinline__ PairItem get_pair_item(const UmmaArgs& a, int w, int n_blocks) {
-  PairItem it;
-  const int t = w / n_blocks;
-  it.nb = w - t * n_blocks;
-  it.e = a.tile_list[3 * t + 0];
-  it.row_start = a.tile_list[3 * t + 1];
-  it.rows = a.tile_list[3 * t + 2];
-  return it;
-}
 
 template <int FMT, int STAGE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
@@ -286,7 +200,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
     const bool is_up = STAGE == 1 && q >= 2;
     const int pair_idx = (q & 1) + 2 * par;
     float* xbuf = reinterpret_cast<float*>(smem_raw + (xchg_base + pair_idx * 4096 - smem_u32(smem_raw)));
-    const uint32_t tempty_leader[2] = {mapa(tempty_bar(0), 0), mapa(tempty_bar(1), 0)};
+    const uint32_t tempty_l0 = mapa(tempty_bar(0), 0), tempty_l1 = mapa(tempty_bar(1), 0);
     uint32_t li = 0;
     for (int w = cluster_id; w < total; w += num_clusters, ++li) {
       const PairItem wi = get_pair_item(a, w, n_blocks);
@@ -373,7 +287,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(tempty_leader[buf]);
+      if (lane == 0) mbar_arrive_cluster(buf ? tempty_l1 : tempty_l0);
     }
   }
 

@@ -35,6 +35,8 @@ int launch_umma_gemm(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream)
 // CTA-pair kernels (umma2_gemm.cu): tile_list must hold umma2_tile_rows()-row tiles; bf16 / int8
 int umma2_tile_rows();
 int launch_umma2_gemm(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream);
+// fp8 tensor-native kernel on a CTA pair (umma2_f8.cu): same operands as launch_umma_f8, 256-row tiles
+int launch_umma2_f8(int stage, const UmmaArgs& a, cudaStream_t stream);
 // fp8 w8a16 / mxfp4: weights dequantised to bf16 inside the kernel (umma_dq.cu)
 int launch_umma_dq(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream);
 // fp8 w8a16 on the fp8 tensor cores (umma_f8.cu): X/X2 = hi/lo e4m3 pieces, Xscale = per-row 2^e factor

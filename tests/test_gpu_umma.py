@@ -289,3 +289,27 @@ def test_umma2_int8(K, case):
     assert torch.isfinite(out_p).all(), describe(out_p, out_u)
     # exact integer accumulation and the same f32 epilogue expressions on both kernels
     assert torch.equal(out_p, out_u), "vs single-CTA: " + describe(out_p, out_u)
+
+
+@pytest.mark.parametrize("block", [[128, 128], [64, 128], [128, 256]])
+@pytest.mark.parametrize("case", F8_CASES + [(700, 256, 384, 2, 2, "one"), (1024, 512, 1024, 16, 4, "uniform")])
+def test_umma2_fp8(K, case, block):
+    """Tensor-native fp8 kernel on a CTA pair (umma2_f8.cu) vs the oracle and the single-CTA kernel."""
+    M, I, H, E, topk, style = case
+    bn, bk = block
+    g = torch.Generator().manual_seed(1111)
+    a = (torch.randn(M, H, generator=g) / math.sqrt(H)).bfloat16()
+    w1 = (torch.randn(E, 2 * I, H, generator=g) * 400).clamp(-448, 448).to(torch.float8_e4m3fn)
+    w2 = (torch.randn(E, H, I, generator=g) * 400).clamp(-448, 448).to(torch.float8_e4m3fn)
+    cd = lambda x, y: (x + y - 1) // y
+    w1s = torch.randn(E, cd(2 * I, bn), cd(H, bk), generator=g) * 1e-3
+    w2s = torch.randn(E, cd(H, bn), cd(I, bk), generator=g) * 1e-3
+    ids = make_ids(M, E, topk, style, g)
+    tw = torch.rand(M, topk, generator=g) / topk
+    ref = O.fused_experts(a, w1, w2, tw, ids, "fp8", w1s, w2s, block)
+    dev = [t.cuda() for t in (a, w1, w2, tw, ids, w1s, w2s)]
+    out_u = K.fused_experts_impl(*dev[:5], False, K.FMT_FP8_W8A16, dev[5], dev[6], block, False, path=K.PATH_UMMA).cpu()
+    out_p = K.fused_experts_impl(*dev[:5], False, K.FMT_FP8_W8A16, dev[5], dev[6], block, False, path=K.PATH_UMMA2).cpu()
+    assert torch.isfinite(out_p).all(), describe(out_p, ref)
+    assert torch.allclose(out_p.float(), ref.float(), **BF16_TOL), "vs oracle: " + describe(out_p, ref)
+    assert torch.allclose(out_p.float(), out_u.float(), **BF16_TOL), "vs single-CTA: " + describe(out_p, out_u)
