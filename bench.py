@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--path", default="auto", choices=["auto", "stream", "umma", "umma2"], help="GEMM path (auto = by rows/expert)")
+    ap.add_argument("--no-mx4-native", action="store_true", help="mxfp4: dequantising kernels instead of the block-scaled tensor cores")
     ap.add_argument("--block-k", type=int, default=128, help="fp8 scale block along K (experiments; the layer's is 128)")
     ap.add_argument("--copies", type=int, default=2, help="weight copies rotated between steps (bench_moe.py:50-58)")
     return ap.parse_args()
@@ -83,8 +84,13 @@ def make_weights(fmt, E, H, I, device, gen):
         bk = BLOCK_K
         return dict(w1=w1, w2=w2, s1=rnd(E, 2 * I // 128, H // bk) * 1e-3, s2=rnd(E, H // 128, I // bk) * 1e-3,
                     block=[128, bk])
-    w1 = torch.randint(0, 256, (E, 2 * I, H // 2), device=device, generator=gen, dtype=torch.uint8)
-    w2 = torch.randint(0, 256, (E, H, I // 2), device=device, generator=gen, dtype=torch.uint8)
+    def nibbles(*shape):  # 64 spare bytes behind the tensor: the 4-bit TMA boxes of a K % 128 != 0 weight read past it
+        n = math.prod(shape)
+        buf = torch.zeros(n + 64, device=device, dtype=torch.uint8)
+        buf[:n] = torch.randint(0, 256, (n,), device=device, generator=gen, dtype=torch.uint8)
+        return buf[:n].view(*shape)
+    w1 = nibbles(E, 2 * I, H // 2)
+    w2 = nibbles(E, H, I // 2)
     s1 = torch.randint(118, 122, (E, 2 * I, H // 32), device=device, generator=gen, dtype=torch.uint8)
     s2 = torch.randint(118, 122, (E, H, I // 32), device=device, generator=gen, dtype=torch.uint8)
     return dict(w1=w1, w2=w2, s1=s1, s2=s2, block=None)
@@ -169,6 +175,8 @@ def path_used(args, fmt, M, topk, E, H, I):
         return args.path
     if fmt == "fp8" and H % 128 == 0 and I % 128 == 0:
         return "umma"          # tensor-native fp8 kernel at every M (capi.cu AUTO rule)
+    if fmt == "mxfp4" and H % 64 == 0 and I % 64 == 0 and not args.no_mx4_native:
+        return "umma"          # block-scaled tensor-native mxfp4 kernel at every M
     if fmt in ("fp8", "mxfp4"):
         ok = H % 64 == 0 and I % 64 == 0
     else:
@@ -228,6 +236,7 @@ def run_b200(args):
     M = args.tokens
     hbm_peak, tc_peak, peak_src = peaks()
     lib = L.load()
+    lib.sglb_set_mx4_native(0 if args.no_mx4_native else 1)
 
     if world > 1:
         from sgl_cpu_tests_b200 import ep
@@ -291,7 +300,8 @@ def run_b200(args):
         k_us = stage_us["w13_gemm"]
         achieved = ab["w13"] / (k_us * 1e-6) / 1e9 if k_us > 0 else 0.0
         used = path_used(args, fmt, M, topk, E, H, I)
-        kname = (f"{KERNEL_DESC[(used, fmt)]}<stage 1> (tcgen05 w13 GEMM + silu_and_mul)" if used.startswith("umma")
+        kdesc = "umma_mx4_kernel" if (fmt == "mxfp4" and used == "umma" and not args.no_mx4_native) else KERNEL_DESC[(used, fmt)]
+        kname = (f"{kdesc}<stage 1> (tcgen05 w13 GEMM + silu_and_mul)" if used.startswith("umma")
                  else "stream_gemm_kernel<stage 1> (mma.sync w13 GEMM + silu_and_mul)")
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")

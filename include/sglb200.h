@@ -117,6 +117,10 @@ typedef struct sglb_moe_problem {
   void* out;                /* [M,H] bf16 */
   void* workspace;
   size_t workspace_bytes; /* >= sglb_fused_experts_workspace_bytes(...) */
+  /* mxfp4 only, optional (NULL = dequantising kernels): the e8m0 scales re-tiled by sglb_mx4_tile_scales
+   * (split = I for w13, 0 for w2); with them the GEMMs run on the block-scaled fp4 tensor cores */
+  const void* w13_scale_tiles;
+  const void* w2_scale_tiles;
 } sglb_moe_problem;
 
 size_t sglb_fused_experts_workspace_bytes(int64_t M, int topk, int E, int H, int I, int fmt);
@@ -145,6 +149,17 @@ typedef struct sglb_shared_problem {
 } sglb_shared_problem;
 
 int sglb_shared_expert(const sglb_shared_problem* p, sglb_stream_t stream);
+
+/* ---- mxfp4 scale tiles for the block-scaled tensor cores ----------------------------------------------
+ * e8m0 scales [E, rows, K/32] (test_mxfp4.py:69-88 layout) -> 512-byte tiles of 128 rows x 4 k-groups in
+ * the order tcgen05.cp expects, [E, blocks, ceil(K/128), 512].  split > 0 tiles the rows [0, split) and
+ * [split, rows) separately (gate and up halves of w13: split = I); padding entries hold 2^0.
+ * Weights used with the tiles: K % 64 == 0, and when K % 128 != 0 the buffer must stay readable for 32
+ * bytes past its end (the last row's final TMA box). */
+size_t sglb_mx4_scale_tiles_bytes(int64_t E, int rows, int split, int K);
+int sglb_mx4_tile_scales(const void* scales, void* tiles, int64_t E, int rows, int split, int K,
+                         sglb_stream_t stream);
+void sglb_set_mx4_native(int on); /* 0: keep mxfp4 on the dequantising kernels even when tiles are given */
 
 /* ---- K9 mxfp4 linear ------------------------------------------------------------------------------
  * mxfp4_scaled_mm_cpu (test_mxfp4.py:167,196): out[M,N] bf16 = A[M,K] bf16 . dequant(Bq,Bs)^T + bias

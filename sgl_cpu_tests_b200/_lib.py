@@ -24,6 +24,7 @@ class MoeProblem(C.Structure):
         ("hidden", _vp), ("w13", _vp), ("w2", _vp), ("topk_weights", _vp), ("topk_ids", _vp),
         ("w13_scale", _vp), ("w2_scale", _vp), ("block_n", _i32), ("block_k", _i32),
         ("out", _vp), ("workspace", _vp), ("workspace_bytes", _sz),
+        ("w13_scale_tiles", _vp), ("w2_scale_tiles", _vp),
     ]
 
 
@@ -43,6 +44,9 @@ SIGNATURES = {
     "sglb_launch_count": (C.c_uint64, []),
     "sglb_profile_enable": (None, [C.c_int]),
     "sglb_set_fp8_native": (None, [C.c_int]),
+    "sglb_set_mx4_native": (None, [C.c_int]),
+    "sglb_mx4_scale_tiles_bytes": (_sz, [_i64, C.c_int, C.c_int, C.c_int]),
+    "sglb_mx4_tile_scales": (C.c_int, [_vp, _vp, _i64, C.c_int, C.c_int, C.c_int, _vp]),
     "sglb_profile_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_int), C.c_int]),
     "sglb_grouped_topk": (C.c_int, [_vp, C.c_int, _vp, C.c_int, _i64, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.c_int, _f32, _vp, _vp, _vp]),

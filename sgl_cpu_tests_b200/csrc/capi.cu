@@ -31,6 +31,7 @@ struct StageEvents {
   int stage;
 };
 static bool g_profile = false;
+static bool g_mx4_native = true;  // mxfp4: block-scaled tensor-native kernel (umma_mx4.cu) when scale tiles are given
 static bool g_f8_native = true;  // fp8: tensor-native kernel (umma_f8.cu) vs dequantising kernel (umma_dq.cu)
 static std::vector<StageEvents> g_events;
 static size_t g_events_used = 0;
@@ -81,6 +82,7 @@ constexpr int kMinChunkRows = 8;
 constexpr double kUmmaMinRowsPerExpert = 4.0;
 constexpr double kPairMinRowsPerExpert = 128.0;
 constexpr int kTileRows = kUmmaTileRows;
+constexpr int kMinTileRows = 16;  // smallest tile_rows any path hands to moe_align (sizes tile_list)
 
 static int64_t max_items(int64_t S, int E, int rows) {
   return (S < E ? S : E) + S / rows + 1;
@@ -103,7 +105,7 @@ static MoeWorkspace carve(void* base, int64_t M, int topk, int E, int H, int I, 
   w.sorted_slot = (int32_t*)take(sizeof(int32_t) * S);
   w.slot_pos = (int32_t*)take(sizeof(int32_t) * S);
   w.chunk_list = (int32_t*)take(sizeof(int32_t) * 3 * max_items(S, E, kMinChunkRows));
-  w.tile_list = (int32_t*)take(sizeof(int32_t) * 3 * max_items(S, E, kTileRows));
+  w.tile_list = (int32_t*)take(sizeof(int32_t) * 3 * max_items(S, E, kMinTileRows));
   w.align_scratch = (int32_t*)take(sglb_moe_align_scratch_bytes(M, topk, E));
   w.zero_ids = (int32_t*)take(sizeof(int32_t) * M);
   // +kTileRows rows of slack: the tcgen05 path reads whole 128-row tiles past the last expert
@@ -115,7 +117,7 @@ static MoeWorkspace carve(void* base, int64_t M, int topk, int E, int H, int I, 
     w.xs = (float*)take(sizeof(float) * M);
     w.actq = (int8_t*)take((size_t)(S + kTileRows) * I);
     w.acts = (float*)take(sizeof(float) * (S + kTileRows));
-  } else if (fmt == SGLB_FMT_FP8_W8A16) {
+  } else if (fmt == SGLB_FMT_FP8_W8A16 || fmt == SGLB_FMT_MXFP4) {
     w.xq = (int8_t*)take((size_t)M * H);
     w.xq2 = (int8_t*)take((size_t)M * H);
     w.xs = (float*)take(sizeof(float) * M);
@@ -192,7 +194,8 @@ static int check_format(const char* who, int fmt, int H, int I, const void* s13,
 
 // One GEMM stage on the tcgen05 path over the tile list of an existing alignment.
 static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64_t S, const MoeWorkspace& ws,
-                          cudaStream_t stream, bool f8_native = false, bool pair = false) {
+                          cudaStream_t stream, bool f8_native = false, bool pair = false,
+                          const void* mx4_tiles = nullptr, int mx4_cap = 0) {
   UmmaArgs u;
   memset(&u, 0, sizeof(u));
   u.W = sa.W;
@@ -210,11 +213,14 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.E = E;
   u.topk = sa.topk;
   u.gather = sa.gather;
-  u.max_tiles = (int)max_items(S, E, pair ? umma2_tile_rows() : kTileRows);
+  u.max_tiles = (int)max_items(S, E, mx4_tiles ? mx4_cap : (pair ? umma2_tile_rows() : kTileRows));
   u.block_n = sa.block_n;
   u.block_k = sa.block_k;
   u.scale_cols = sa.scale_cols;
   u.X2 = sa.X2;
+  u.Wsf = mx4_tiles;
+  u.tile_cap = mx4_cap;
+  if (mx4_tiles) return launch_umma_mx4(stage, u, stream);
   if (f8_native) return pair ? launch_umma2_f8(stage, u, stream) : launch_umma_f8(stage, u, stream);
   if (pair) return launch_umma2_gemm(fmt, stage, u, stream);
   return launch_umma_gemm(fmt, stage, u, stream);
@@ -225,7 +231,8 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
 static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, const void* hidden,
                           const void* w13, const void* w2, const void* s13, const void* s2, int bn,
                           int bk, const float* row_scale, const MoeWorkspace& ws, void* ic2_out,
-                          cudaStream_t stream) {
+                          cudaStream_t stream, const void* s13_tiles = nullptr, const void* s2_tiles = nullptr,
+                          int mx4_cap = 0) {
   const int64_t S = M * topk;
   StreamArgs a;
   memset(&a, 0, sizeof(a));
@@ -255,8 +262,8 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   // fp8 w8a16 on the fp8 tensor cores: activations split into two e4m3 pieces (umma_f8.cu)
   const bool pair = path == SGLB_PATH_UMMA2;
   const bool umma = path == SGLB_PATH_UMMA || pair;
-  const bool f8 = umma && fmt == SGLB_FMT_FP8_W8A16 && g_f8_native &&
-                  umma_f8_supported(H, I, bn, bk);
+  const bool mx4 = umma && !pair && fmt == SGLB_FMT_MXFP4 && s13_tiles && s2_tiles && mx4_cap > 0;
+  const bool f8 = mx4 || (umma && fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(H, I, bn, bk));
   if (fmt == SGLB_FMT_INT8_W8A8) {
     StageTimer t(ST_QUANT_X, stream);
     rc = sglb_quant_rows_int8(hidden, M, H, ws.xq, ws.xs, stream);
@@ -275,7 +282,7 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   }
   {
     StageTimer t(ST_GEMM1, stream);
-    rc = umma ? run_umma_stage(fmt, 1, a, E, S, ws, stream, f8, pair)
+    rc = umma ? run_umma_stage(fmt, 1, a, E, S, ws, stream, f8, pair, mx4 ? s13_tiles : nullptr, mx4_cap)
                                 : dispatch_stream<1>(fmt, a, plan, stream);
   }
   if (rc) return rc;
@@ -310,7 +317,7 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
     a.X = ws.act;
   }
   StageTimer t(ST_GEMM2, stream);
-  return umma ? run_umma_stage(fmt, 2, a, E, S, ws, stream, f8, pair)
+  return umma ? run_umma_stage(fmt, 2, a, E, S, ws, stream, f8, pair, mx4 ? s2_tiles : nullptr, mx4_cap)
                                 : dispatch_stream<2>(fmt, a, plan2, stream);
 }
 
@@ -361,6 +368,16 @@ extern "C" int sglb_profile_read(float* ms_out, int* calls_out, int n) {
 }
 
 extern "C" void sglb_set_fp8_native(int on) { g_f8_native = on != 0; }
+extern "C" void sglb_set_mx4_native(int on) { g_mx4_native = on != 0; }
+extern "C" size_t sglb_mx4_scale_tiles_bytes(int64_t E, int rows, int split, int K) {
+  if (E <= 0 || rows <= 0 || K <= 0) return 0;
+  return mx4_scale_tiles_bytes(E, rows, split, K);
+}
+extern "C" int sglb_mx4_tile_scales(const void* scales, void* tiles, int64_t E, int rows, int split, int K,
+                                    sglb_stream_t stream) {
+  SGLB_CHECK(E >= 0 && (E == 0 || (scales && tiles)), "mx4_tile_scales: null pointer");
+  return launch_mx4_tile_scales(scales, tiles, E, rows, split, K, (cudaStream_t)stream);
+}
 extern "C" int sglb_split_rows_e4m3(const void* x_bf16, int64_t rows, int K, void* hi, void* lo, float* rexp,
                                     sglb_stream_t stream) {
   SGLB_CHECK(rows >= 0 && K > 0, "split_rows_e4m3: bad shape");
@@ -396,12 +413,16 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
   MoeWorkspace ws = carve(p->workspace, p->M, p->topk, p->E, p->H, p->I, p->fmt);
 
   int path = p->path;
+  const double rows_per_expert = (double)p->M * p->topk / p->E;
+  // mxfp4 on the block-scaled tensor cores needs the re-tiled scales (sglb_mx4_tile_scales)
+  const bool mx4 = p->fmt == SGLB_FMT_MXFP4 && g_mx4_native && p->w13_scale_tiles && p->w2_scale_tiles &&
+                   umma_mx4_supported(p->H, p->I);
+  const int mx4_cap = mx4 ? umma_mx4_tile_rows(rows_per_expert) : 0;
   if (path == SGLB_PATH_AUTO) {
-    const double rows_per_expert = (double)p->M * p->topk / p->E;
     // fp8 on the fp8 tensor cores streams weights faster than the mma.sync kernel at every batch size
     // measured (DSV3 M = 16: 82 % vs 59 % of the HBM roofline): no ALU work per weight byte
     const bool f8 = p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k);
-    path = ((f8 || rows_per_expert >= kUmmaMinRowsPerExpert) && umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I))
+    path = ((f8 || mx4 || rows_per_expert >= kUmmaMinRowsPerExpert) && umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I))
                ? SGLB_PATH_UMMA
                : SGLB_PATH_STREAM;
     // bf16 prefill: the CTA-pair kernel wins once pair tiles fill up (Qwen3 M = 4096: 793 vs 705 TFLOP/s,
@@ -415,11 +436,13 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     SGLB_CHECK(path == SGLB_PATH_UMMA || p->fmt == SGLB_FMT_BF16 || p->fmt == SGLB_FMT_INT8_W8A8 ||
                    (p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k)),
                "fused_experts: the CTA-pair tcgen05 path takes bf16, int8 and tensor-native fp8 weights only (fmt=%d)", p->fmt);
+    const bool use_mx4 = mx4 && path == SGLB_PATH_UMMA;
     rc = run_align(p->topk_ids, p->M, p->topk, p->E, 0, ws, stream,
-                   path == SGLB_PATH_UMMA2 ? umma2_tile_rows() : kTileRows);
+                   use_mx4 ? mx4_cap : (path == SGLB_PATH_UMMA2 ? umma2_tile_rows() : kTileRows));
     if (rc) return rc;
     rc = run_mlp(path, p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2,
-                 p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, ws.ic2, stream);
+                 p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, ws.ic2, stream,
+                 use_mx4 ? p->w13_scale_tiles : nullptr, use_mx4 ? p->w2_scale_tiles : nullptr, mx4_cap);
     if (rc) return rc;
   } else {
     StreamPlan plan = make_plan(p->M, p->topk, p->E, p->I, 1);

@@ -227,7 +227,10 @@ __device__ __forceinline__ void gather_role(const UmmaArgs& a, int total, int n_
 // ---- epilogue warps -------------------------------------------------------------------------------------
 // kEpiWarps warps; `ew` = index among them, `warp` = warp index in the CTA (its TMEM lane quadrant is
 // warp & 3).  INT8: s32 accumulators with activation / weight scales; otherwise f32 accumulators.
-template <bool kInt8, int STAGE, bool kRelaxed>
+// kTokScale: f32 accumulators times a per-routed-row factor a.Xscale (the 2^e of the e4m3 hi/lo split).
+// kAccStride / kSubStride: TMEM columns between the two accumulator buffers / the two sub-tiles.
+template <bool kInt8, int STAGE, bool kRelaxed, bool kTokScale = false, int kAccStride = kAccCols,
+          int kSubStride = kWSub>
 __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int n_blocks, uint8_t* smem_raw,
                                               uint32_t epi_base, uint32_t tfull0, uint32_t tempty0,
                                               uint32_t tmem_base, int warp, int ew, int lane) {
@@ -262,9 +265,9 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
         const int p = wi.row_start + min(lane + 32 * i, wi.rows - 1);
         if (32 * i < n_eff) {
           if constexpr (STAGE == 1) {
-            if (kInt8) xs_r[i] = a.Xscale[a.sorted_slot[p] / a.topk];
+            if (kInt8 || kTokScale) xs_r[i] = a.Xscale[a.sorted_slot[p] / a.topk];
           } else {
-            if (kInt8) xs_r[i] = a.Xscale[p];
+            if (kInt8 || kTokScale) xs_r[i] = a.Xscale[p];
             if (a.row_scale != nullptr) rs_r[i] = a.row_scale[a.sorted_slot[p]];
           }
         }
@@ -272,7 +275,7 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
       if (kRelaxed) mbar_wait_relaxed(tfull_bar(buf), (li >> 1) & 1);
       else mbar_wait(tfull_bar(buf), (li >> 1) & 1);
       tc_fence_after();
-      const uint32_t acc = tmem_base + lane_off + buf * kAccCols;
+      const uint32_t acc = tmem_base + lane_off + buf * kAccStride;
       constexpr int kSubs = STAGE == 1 ? 1 : 2;
 #pragma unroll 1
       for (int sub = 0; sub < kSubs; ++sub) {
@@ -290,7 +293,7 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
           if constexpr (STAGE == 1) {
             uint32_t gv[16], uv[16];
             tmem_ld16(acc + c0, gv);
-            tmem_ld16(acc + kWSub + c0, uv);
+            tmem_ld16(acc + kSubStride + c0, uv);
             tmem_ld_wait(gv);
             tmem_ld_wait(uv);
 #pragma unroll
@@ -301,14 +304,19 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
                 const float up = xs * (float)(int)uv[j] * ws1;
                 *reinterpret_cast<float*>(ebuf + j * ROWB + lane * 4) = silu_f(gate) * up;
               } else {
-                const float gate = __uint_as_float(gv[j]), up = __uint_as_float(uv[j]);
+                float gate = __uint_as_float(gv[j]), up = __uint_as_float(uv[j]);
+                if constexpr (kTokScale) {
+                  const float xs = __shfl_sync(0xffffffffu, xsel, 16 * par + j);
+                  gate *= xs;
+                  up *= xs;
+                }
                 *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) =
                     __float2bfloat16_rn(silu_f(gate) * up);
               }
             }
           } else {
             uint32_t v[16];
-            tmem_ld16(acc + sub * kWSub + c0, v);
+            tmem_ld16(acc + sub * kSubStride + c0, v);
             tmem_ld_wait(v);
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
@@ -319,6 +327,7 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
                 val = xs * (float)(int)v[j] * ws0;
               } else {
                 val = __uint_as_float(v[j]);
+                if constexpr (kTokScale) val *= __shfl_sync(0xffffffffu, xsel, 16 * par + j);
               }
               *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(val * rs);
             }

@@ -23,7 +23,9 @@ struct UmmaArgs {
   int max_tiles;           // host upper bound on counters[2]
   int block_n, block_k;    // fp8 scale block
   int scale_cols;          // fp8: ceil(K/bk); mxfp4: K/32
-  const void* X2;          // fp8 tensor-native path: lo pieces of the routed rows (X = hi pieces, e4m3)
+  const void* X2;          // fp8 / mxfp4 tensor-native paths: lo pieces of the routed rows (X = hi pieces, e4m3)
+  const void* Wsf;         // mxfp4 tensor-native path: e8m0 scales re-tiled for tcgen05.cp (umma_mx4.cu)
+  int tile_cap;            // mxfp4 tensor-native path: row capacity of the tiles in tile_list (16..112)
 };
 
 constexpr int kUmmaTileRows = 128;  // routed rows per tile (tile_rows handed to moe_align)
@@ -42,6 +44,13 @@ int launch_umma_dq(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream);
 // fp8 w8a16 on the fp8 tensor cores (umma_f8.cu): X/X2 = hi/lo e4m3 pieces, Xscale = per-row 2^e factor
 int umma_f8_supported(int H, int I, int block_n, int block_k);
 int launch_umma_f8(int stage, const UmmaArgs& a, cudaStream_t stream);
+// mxfp4 on the block-scaled fp8/fp4 tensor cores (umma_mx4.cu): weights e2m1 via TMA, e8m0 scales in TMEM
+int umma_mx4_supported(int H, int I);
+int umma_mx4_tile_rows(double rows_per_expert);
+int launch_umma_mx4(int stage, const UmmaArgs& a, cudaStream_t stream);
+// e8m0 scales [E, rows, K/32] -> 512-byte tcgen05.cp tiles [E, blocks(rows, split), ceil(K/128)]
+size_t mx4_scale_tiles_bytes(int64_t E, int rows, int split, int K);
+int launch_mx4_tile_scales(const void* src, void* dst, int64_t E, int rows, int split, int K, cudaStream_t stream);
 int launch_split_rows_e4m3(const void* x_bf16, int64_t rows, int K, void* hi, void* lo, float* rexp,
                            cudaStream_t stream);
 

@@ -249,6 +249,45 @@ def _resident_mx_scale(s, is_vnni, dev):
     return sd
 
 
+def _mx4_tiles(s_dev, split):
+    """e8m0 scales [E, rows, K/32] on the device -> the 512-byte tiles the block-scaled tensor-core kernel
+    copies into TMEM (csrc/umma_mx4.cu); built once per scale tensor and cached."""
+    key = _registry_key(s_dev, False, ("mx4tiles", split))
+    hit = _registry.get(key)
+    if hit is not None:
+        return hit[1]
+    E, rows, G = _rows_k(s_dev, False)
+    lib = L.load()
+    tiles = torch.empty(lib.sglb_mx4_scale_tiles_bytes(E, rows, split, 32 * G), dtype=torch.uint8, device=s_dev.device)
+    L.check(lib.sglb_mx4_tile_scales(s_dev.data_ptr(), tiles.data_ptr(), E, rows, split, 32 * G, _stream()))
+    tiles._sglb_src = s_dev  # keeps the keyed pointer alive for as long as the cache entry
+    _registry_put(key, 0, tiles)
+    return tiles
+
+
+def _mx4_weight(w_dev):
+    """The weight itself when the 4-bit TMA boxes may read it (32-byte aligned; 32 readable bytes past
+    the end when K is not a multiple of 128), else a padded device copy (cached); None if unusable."""
+    K = 2 * w_dev.shape[-1]
+    if K % 64 != 0:
+        return None
+    if w_dev.data_ptr() % 32 == 0:
+        st = w_dev.untyped_storage()
+        slack = st.nbytes() - (w_dev.storage_offset() + w_dev.numel())
+        if K % 128 == 0 or slack >= 32:
+            return w_dev
+    key = _registry_key(w_dev, False, "mx4pad")
+    hit = _registry.get(key)
+    if hit is not None:
+        return hit[1]
+    buf = torch.zeros(w_dev.numel() + 64, dtype=torch.uint8, device=w_dev.device)
+    padded = buf[:w_dev.numel()].view(w_dev.shape)
+    padded.copy_(w_dev)
+    padded._sglb_src = w_dev
+    _registry_put(key, 0, padded)
+    return padded
+
+
 # ---- K1: routers -----------------------------------------------------------------------------------------
 def _router(gating_output, correction_bias, topk, renormalize, num_expert_group, topk_group,
             routed_scaling_factor, out_w=None, out_ids=None):
@@ -402,10 +441,16 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
         ids = _to_dev(topk_ids, dev, torch.int32)
         w13 = _resident_weight(w1, is_vnni, dev)
         w2d = _resident_weight(w2, is_vnni, dev)
-        s13 = s2 = None
+        s13 = s2 = t13 = t2 = None
         if fmt == L.FMT_MXFP4:
             s13 = _resident_mx_scale(w1_scale, is_vnni, dev)
             s2 = _resident_mx_scale(w2_scale, is_vnni, dev)
+            if H % 64 == 0 and I % 64 == 0:  # block-scaled tensor-core path (umma_mx4.cu)
+                w13p, w2p = _mx4_weight(w13), _mx4_weight(w2d)
+                if w13p is not None and w2p is not None:
+                    w13, w2d = w13p, w2p
+                    t13 = _mx4_tiles(s13.view(E, 2 * I, H // 32), I)
+                    t2 = _mx4_tiles(s2.view(E, H, I // 32), 0)
         elif fmt != L.FMT_BF16:
             s13 = _resident_aux(w1_scale, dev, torch.float32)
             s2 = _resident_aux(w2_scale, dev, torch.float32)
@@ -420,7 +465,7 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
                              w13=w13.data_ptr(), w2=w2d.data_ptr(), topk_weights=tw.data_ptr(),
                              topk_ids=ids.data_ptr(), w13_scale=_ptr(s13), w2_scale=_ptr(s2), block_n=bn,
                              block_k=bk, out=out.data_ptr(), workspace=ws.data_ptr(),
-                             workspace_bytes=ws.numel())
+                             workspace_bytes=ws.numel(), w13_scale_tiles=_ptr(t13), w2_scale_tiles=_ptr(t2))
             L.check(lib.sglb_fused_experts(p, _stream()))
         if on_cuda:
             if inplace and out is not hidden_states:

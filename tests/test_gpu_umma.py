@@ -190,11 +190,25 @@ def test_split_rows_e4m3_is_exact_near_the_row_maximum(K):
     assert ((rec - xf).abs() <= rowmax * 2.0 ** -17).all()
 
 
-@pytest.mark.parametrize("case", DQ_CASES + [(64, 2880, 2880, 4, 2, "uniform")])
-def test_umma_mxfp4(K, case):
+MX4_CASES = DQ_CASES + [
+    (64, 2880, 2880, 4, 2, "uniform"),    # gpt-oss expert shape: K = 22.5 stages of 128, 22.5 row blocks
+    (1, 128, 128, 2, 1, "uniform"),
+    (5, 64, 192, 2, 2, "uniform"),        # I = 64: half a weight block per sub-tile
+    (700, 256, 384, 2, 2, "one"),         # 1400 rows on one expert: 12 full 112-row tiles + a ragged one
+]
+
+
+@pytest.mark.parametrize("native", [0, 1])
+@pytest.mark.parametrize("case", MX4_CASES)
+def test_umma_mxfp4(K, case, native):
+    """native = 1: e2m1 weights and e8m0 scales straight into tcgen05.mma kind::mxf8f6f4.block_scale
+    (umma_mx4.cu); native = 0: the kernel that dequantises to bf16 in shared memory (umma_dq.cu)."""
     M, I, H, E, topk, style = case
+    if not native and case not in DQ_CASES and case[2] != 2880:
+        pytest.skip("dequantising kernel covered by the shared cases")
     g = torch.Generator().manual_seed(1111)
     a = torch.randn(M, H, generator=g).bfloat16() / 10
+    a[0, :8] *= 2.0 ** -12
     w1q, w1s = O.mxfp4_quantize((torch.rand(E, 2 * I, H, generator=g) - 0.5) * 2e-1)
     w2q, w2s = O.mxfp4_quantize((torch.rand(E, H, I, generator=g) - 0.5) * 2e-1)
     w1s, w2s = w1s.view(E, 2 * I, H // 32).contiguous(), w2s.view(E, H, I // 32).contiguous()
@@ -203,12 +217,51 @@ def test_umma_mxfp4(K, case):
     ref = O.fused_experts(a, w1q, w2q, tw, ids, "mxfp4", w1s, w2s)
     dev = [t.cuda() for t in (a, w1q, w2q, tw, ids, w1s, w2s)]
     outs = {}
-    for name, path in (("stream", K.PATH_STREAM), ("umma", K.PATH_UMMA)):
-        outs[name] = K.fused_experts_impl(dev[0], dev[1], dev[2], dev[3], dev[4], False, K.FMT_MXFP4, dev[5], dev[6],
-                                          None, False, path=path).cpu()
+    lib = K._lib.load()
+    lib.sglb_set_mx4_native(native)
+    try:
+        for name, path in (("stream", K.PATH_STREAM), ("umma", K.PATH_UMMA)):
+            outs[name] = K.fused_experts_impl(dev[0], dev[1], dev[2], dev[3], dev[4], False, K.FMT_MXFP4, dev[5], dev[6],
+                                              None, False, path=path).cpu()
+    finally:
+        lib.sglb_set_mx4_native(1)
     assert torch.isfinite(outs["umma"]).all(), describe(outs["umma"], ref)
     assert torch.allclose(outs["umma"].float(), ref.float(), **BF16_TOL), "vs oracle: " + describe(outs["umma"], ref)
     assert torch.allclose(outs["umma"].float(), outs["stream"].float(), **BF16_TOL), "vs stream: " + describe(outs["umma"], outs["stream"])
+
+
+@pytest.mark.parametrize("shape", [(3, 256, 0, 256), (1, 5760, 2880, 2880), (1, 200, 72, 96)])
+def test_mx4_scale_tiles_layout(K, shape):
+    """sglb_mx4_tile_scales against the layout written out in numpy: tile (e, block, k stage) holds the
+    128 rows x 4 k-groups at byte (r % 32) * 16 + (r // 32) * 4 + g, rows tiled per [0, split) / [split, rows)
+    segment, padding = 127 (2^0)."""
+    E, rows, split, Kdim = shape
+    G = Kdim // 32
+    g = torch.Generator().manual_seed(5)
+    sc = torch.randint(100, 140, (E, rows, G), generator=g, dtype=torch.uint8)
+    lib = K._lib.load()
+    n = lib.sglb_mx4_scale_tiles_bytes(E, rows, split, Kdim)
+    tiles = torch.empty(n, dtype=torch.uint8, device="cuda")
+    K._lib.check(lib.sglb_mx4_tile_scales(sc.cuda().data_ptr(), tiles.data_ptr(), E, rows, split, Kdim, None))
+    torch.cuda.synchronize()
+    cd = lambda x, y: (x + y - 1) // y
+    segs = [(0, split), (split, rows)] if split else [(0, rows)]
+    nkb = cd(Kdim, 128)
+    ref = []
+    for e in range(E):
+        for lo, hi in segs:
+            for b in range(cd(hi - lo, 128)):
+                for kb in range(nkb):
+                    t = torch.full((512,), 127, dtype=torch.uint8)
+                    for r in range(128):
+                        row = lo + b * 128 + r
+                        for q in range(4):
+                            if row < hi and kb * 4 + q < G:
+                                t[(r % 32) * 16 + (r // 32) * 4 + q] = sc[e, row, kb * 4 + q]
+                    ref.append(t)
+    ref = torch.cat(ref)
+    assert ref.numel() == n
+    assert torch.equal(tiles.cpu(), ref)
 
 
 @pytest.mark.parametrize("fmt", ["bf16", "int8", "fp8"])
