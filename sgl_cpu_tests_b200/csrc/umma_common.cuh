@@ -229,8 +229,10 @@ __device__ __forceinline__ void gather_role(const UmmaArgs& a, int total, int n_
 // warp & 3).  INT8: s32 accumulators with activation / weight scales; otherwise f32 accumulators.
 // kTokScale: f32 accumulators times a per-routed-row factor a.Xscale (the 2^e of the e4m3 hi/lo split).
 // kAccStride / kSubStride: TMEM columns between the two accumulator buffers / the two sub-tiles.
+// kConcat: the accumulator of a tile holds the hi-piece products in columns [0, n_eff) and the lo-piece
+// products in [n_eff, 2 n_eff) (one MMA over the concatenated pieces); the epilogue adds them.
 template <bool kInt8, int STAGE, bool kRelaxed, bool kTokScale = false, int kAccStride = kAccCols,
-          int kSubStride = kWSub>
+          int kSubStride = kWSub, bool kConcat = false>
 __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int n_blocks, uint8_t* smem_raw,
                                               uint32_t epi_base, uint32_t tfull0, uint32_t tempty0,
                                               uint32_t tmem_base, int warp, int ew, int lane) {
@@ -296,6 +298,18 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
             tmem_ld16(acc + kSubStride + c0, uv);
             tmem_ld_wait(gv);
             tmem_ld_wait(uv);
+            if constexpr (kConcat) {
+              uint32_t gl[16], ul[16];
+              tmem_ld16(acc + n_eff + c0, gl);
+              tmem_ld16(acc + kSubStride + n_eff + c0, ul);
+              tmem_ld_wait(gl);
+              tmem_ld_wait(ul);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                gv[j] = __float_as_uint(__uint_as_float(gv[j]) + __uint_as_float(gl[j]));
+                uv[j] = __float_as_uint(__uint_as_float(uv[j]) + __uint_as_float(ul[j]));
+              }
+            }
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               if constexpr (kInt8) {
@@ -318,6 +332,13 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
             uint32_t v[16];
             tmem_ld16(acc + sub * kSubStride + c0, v);
             tmem_ld_wait(v);
+            if constexpr (kConcat) {
+              uint32_t vl[16];
+              tmem_ld16(acc + sub * kSubStride + n_eff + c0, vl);
+              tmem_ld_wait(vl);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(vl[j]));
+            }
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               const float rs = __shfl_sync(0xffffffffu, rsel, 16 * par + j);

@@ -100,7 +100,12 @@ __device__ __forceinline__ void umma_mx4(uint32_t d_tmem, uint64_t adesc, uint64
       : "memory");
 }
 
-template <int STAGE>
+// CONCAT (tiles of at most 48 routed rows, the decode regime): the lo pieces sit right behind the hi
+// pieces in shared memory, one MMA of N = 2 n_eff covers both and the epilogue adds the two column
+// ranges.  An MMA costs at least the 4 KB read of its weight operand (32 cycles) whatever N is (ncu:
+// with separate hi / lo MMAs the tensor pipe was busy 57 % of the time at 4 rows per expert and bounded
+// the kernel at 55 % of the HBM roofline), so halving their number matters more than their size.
+template <int STAGE, bool CONCAT>
 __global__ void __launch_bounds__(kThreads, 1)
     umma_mx4_kernel(const __grid_constant__ CUtensorMap tmap_w, const UmmaArgs a, const int nstages,
                     const int w_tx_bytes) {
@@ -194,7 +199,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     for (int w = blockIdx.x; w < total; w += gridDim.x, ++li) {
       const WorkItem wi = get_item(a, w, n_blocks);
       const int n_eff = (wi.rows + 15) & ~15;
-      const uint32_t idesc = instr_desc_mx4(n_eff);
+      const uint32_t idesc = instr_desc_mx4(CONCAT ? 2 * n_eff : n_eff);
       const int buf = li & 1;
       mbar_wait_bounded(tempty_bar(buf), ((li >> 1) & 1) ^ 1);
       tc_fence_after();
@@ -217,7 +222,7 @@ __global__ void __launch_bounds__(kThreads, 1)
               const uint64_t bl = smem_desc_sw128(xl_tile(s) + j * 32);
               const uint32_t id = idesc | ((uint32_t)j << 29);  // weight scale of k group j
               umma_mx4(acc + sub * kTileCapMax, ad, bh, id, tsfa + 4 * sub, tsfb, (kb > 0 || j > 0) ? 1u : 0u);
-              umma_mx4(acc + sub * kTileCapMax, ad, bl, id, tsfa + 4 * sub, tsfb, 1u);
+              if constexpr (!CONCAT) umma_mx4(acc + sub * kTileCapMax, ad, bl, id, tsfa + 4 * sub, tsfb, 1u);
             }
           }
           umma_commit(empty_bar(s));
@@ -249,7 +254,8 @@ __global__ void __launch_bounds__(kThreads, 1)
       for (int kb = 0; kb < num_kb; ++kb, ++it) {
         const int s = it % nstages;
         mbar_wait_bounded(empty_bar(s), ((it / nstages) & 1) ^ 1);
-        const uint32_t dh = xh_tile(s) + dst0, dl = xl_tile(s) + dst0;
+        const uint32_t dh = xh_tile(s) + dst0;
+        const uint32_t dl = (CONCAT ? xh_tile(s) + n_eff * kRowBytes : xl_tile(s)) + dst0;
         const bool valid = kb * kRowBytes + c * 16 < a.K;
         const int koff = valid ? kb * kRowBytes : 0;
 #pragma unroll
@@ -263,7 +269,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       }
     }
   } else {
-    epilogue_role<false, STAGE, true, true, kAccStrideMx, kTileCapMax>(
+    epilogue_role<false, STAGE, true, true, kAccStrideMx, kTileCapMax, CONCAT>(
         a, total, n_blocks, smem_raw, epi_base, tfull_bar(0), tempty_bar(0), tmem_base, warp, warp - kFirstEpiWarp,
         lane);
   }
@@ -329,7 +335,9 @@ int mx4_weight_map(const void* W, int K, int rows, int E, CUtensorMap* out) {
   return SGLB_OK;
 }
 
-template <int STAGE>
+constexpr int kConcatCapMax = 48;  // 2 x 48 columns per sub-tile fit the 112-column accumulator slot
+
+template <int STAGE, bool CONCAT>
 int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   CUtensorMap map;
   int rc = mx4_weight_map(a.W, a.K, a.rows_per_expert, a.E, &map);
@@ -346,7 +354,7 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   const int smem = nstages * stage_bytes(cap) + fixed_bytes();
   static int attr_smem = 0;  // per instantiation
   if (attr_smem < smem) {
-    SGLB_CUDA(cudaFuncSetAttribute(umma_mx4_kernel<STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    SGLB_CUDA(cudaFuncSetAttribute(umma_mx4_kernel<STAGE, CONCAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
     attr_smem = kSmemLimit;
   }
   // bytes one weight box adds to the mbarrier transaction count: the packed nibbles (the 8-byte gaps of
@@ -358,7 +366,7 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   const int n_blocks = STAGE == 1 ? ceil_div(a.N, kWSub) : ceil_div(a.N, 2 * kWSub);
   const int64_t max_items = (int64_t)a.max_tiles * n_blocks;
   const int grid = (int)(max_items < sm_count() ? (max_items > 0 ? max_items : 1) : sm_count());
-  SGLB_CUDA(launch_pdl(umma_mx4_kernel<STAGE>, dim3(grid), dim3(kThreads), (size_t)smem, stream, map, a, nstages, tx));
+  SGLB_CUDA(launch_pdl(umma_mx4_kernel<STAGE, CONCAT>, dim3(grid), dim3(kThreads), (size_t)smem, stream, map, a, nstages, tx));
   return SGLB_OK;
 }
 
@@ -375,12 +383,16 @@ int umma_mx4_tile_rows(double rows_per_expert) {
     return e ? atoi(e) : 0;
   }();
   if (forced >= 16 && forced <= kTileCapMax && forced % 16 == 0) return forced;
-  return rows_per_expert <= 8.0 ? 32 : (rows_per_expert <= 24.0 ? 64 : kTileCapMax);
+  return rows_per_expert <= 8.0 ? 32 : (rows_per_expert <= 40.0 ? kConcatCapMax : kTileCapMax);
 }
 
 int launch_umma_mx4(int stage, const UmmaArgs& a, cudaStream_t stream) {
   SGLB_CHECK(a.Wsf != nullptr && a.X2 != nullptr && a.Xscale != nullptr, "mxfp4 tensor path: missing operand");
-  int rc = stage == 1 ? launch_one<1>(a, stream) : launch_one<2>(a, stream);
+  int rc;
+  if (a.tile_cap <= kConcatCapMax)
+    rc = stage == 1 ? launch_one<1, true>(a, stream) : launch_one<2, true>(a, stream);
+  else
+    rc = stage == 1 ? launch_one<1, false>(a, stream) : launch_one<2, false>(a, stream);
   if (rc == SGLB_OK) count_launch();
   return rc;
 }
