@@ -283,6 +283,12 @@ def run_b200(args):
                    "path": PATH_DESC[path_used(args, fmt, M, topk, E, H, I)]},
         "clocks": clk, "gpu_launches": int(launches),
     }
+    if world > 1:
+        out["config"]["exchange"] = {"p2p": "NVLink peer memory (ep_p2p.cu: stores into the owners' buffers, peer loads back; no NCCL on the data path)",
+                                     "fixed": "NCCL all-to-all, fixed capacity", "exact": "NCCL all-to-all, exact splits"}.get(
+                                         layer_sets[0].last_mode, str(layer_sets[0].last_mode))
+    out["dtype"] = {"fp8": "e4m3 x e4m3(hi+lo) -> f32", "mxfp4": "e2m1 x e4m3(hi+lo) -> f32"}.get(fmt, out["dtype"]) if \
+        path_used(args, fmt, M, topk, E, H, I) == "umma" and not args.no_mx4_native else out["dtype"]
 
     if world == 1:
         # ---- per-stage kernel timing for the roofline (second pass, same steps, CUDA events per stage) ----

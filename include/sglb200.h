@@ -207,6 +207,31 @@ int sglb_ep_pack(const void* hidden, const int32_t* topk_ids, const float* topk_
 int sglb_ep_combine(const void* ret, const int32_t* dest_row, const int32_t* send_count, int64_t M,
                     int world, int H, int cap, void* out, sglb_stream_t stream);
 
+/* ---- K8, decode regime: the same exchange over NVLink peer memory (csrc/ep_p2p.cu) ---------------------
+ * Every rank allocates one region (sglb_p2p_alloc: cudaMalloc + CUDA IPC handle), the 64-byte handles are
+ * exchanged by the host layer and opened with sglb_p2p_open; peer_bases[r] is rank r's region as mapped in
+ * this process (the rank's own allocation for r == rank).  `seq` counts calls (1, 2, ...) and must advance
+ * identically on every rank; `cap` = slots per source rank (>= every rank's token count, equal on all ranks).
+ *   dispatch:      stores rows / local ids / weights of this rank's M tokens into every peer's receive
+ *                  buffers (slot rank*cap + m) and raises the per-source arrival flag on every peer
+ *   wait_dispatch: returns (on the stream) once all `world` sources' rows of call seq have arrived
+ *   (the caller then runs sglb_fused_experts over the world*cap received slots, output into the y buffer)
+ *   combine:       raises the "partial rows ready" flag on every peer, waits for the owners of each token's
+ *                  experts and sums their rows read over NVLink, rank order, f32 -> bf16 */
+int sglb_p2p_alloc(size_t bytes, void** ptr, void* ipc_handle_64);
+int sglb_p2p_open(const void* ipc_handle_64, void** peer_ptr);
+int sglb_p2p_close(void* peer_ptr);
+int sglb_p2p_free(void* ptr);
+/* offsets[0..8) = recv_x[2], recv_ids[2], recv_weights[2], y[2] (index = seq & 1); returns the region size */
+size_t sglb_ep_p2p_region_bytes(int world, int cap, int H, int topk, size_t* offsets);
+int sglb_ep_p2p_dispatch(const void* hidden, const int32_t* topk_ids, const float* topk_weights, int64_t M,
+                         int topk, int E, int world, int rank, int H, int cap, void* const* peer_bases,
+                         uint32_t seq, sglb_stream_t stream);
+int sglb_ep_p2p_wait_dispatch(const void* local_base, int world, int cap, int H, int topk, uint32_t seq,
+                              sglb_stream_t stream);
+int sglb_ep_p2p_combine(const int32_t* topk_ids, int64_t M, int topk, int E, int world, int rank, int H,
+                        int cap, void* const* peer_bases, uint32_t seq, void* out, sglb_stream_t stream);
+
 /* ---- building blocks exposed for tests and for the expert-parallel layer --------------------------
  * per-row dynamic int8 quantisation (test_moe_int8.py:23-31): q = round(x * 127/absmax), scale = absmax/127 */
 int sglb_quant_rows_int8(const void* x_bf16, int64_t rows, int K, int8_t* q, float* scale,

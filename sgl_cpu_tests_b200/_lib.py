@@ -65,6 +65,16 @@ SIGNATURES = {
     "sglb_ep_pack": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _i64, _vp,
                                _vp, _vp]),
     "sglb_ep_combine": (C.c_int, [_vp, _vp, _vp, _i64, C.c_int, C.c_int, C.c_int, _vp, _vp]),
+    "sglb_p2p_alloc": (C.c_int, [_sz, C.POINTER(_vp), _vp]),
+    "sglb_p2p_open": (C.c_int, [_vp, C.POINTER(_vp)]),
+    "sglb_p2p_close": (C.c_int, [_vp]),
+    "sglb_p2p_free": (C.c_int, [_vp]),
+    "sglb_ep_p2p_region_bytes": (_sz, [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(_sz)]),
+    "sglb_ep_p2p_dispatch": (C.c_int, [_vp, _vp, _vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.POINTER(_vp), C.c_uint32, _vp]),
+    "sglb_ep_p2p_wait_dispatch": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, _vp]),
+    "sglb_ep_p2p_combine": (C.c_int, [_vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(_vp),
+                                      C.c_uint32, _vp, _vp]),
     "sglb_topk_reduce": (C.c_int, [_vp, _vp, _i64, C.c_int, C.c_int, _vp, _vp]),
 }
 

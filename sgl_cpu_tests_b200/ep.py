@@ -23,6 +23,8 @@ The device work is behind a small backend object so the host orchestration (spli
 offsets, ordering of the collectives) can be exercised on CPU under ``gloo`` by the tests, which plug
 in the oracle there; the product backend is `CudaBackend` and nothing else ships.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -66,6 +68,12 @@ class CudaBackend:
         return ops.fused_experts_impl(x, w["w1"], w["w2"], tw, ids, False, self.fmt, w.get("s1"), w.get("s2"),
                                       w.get("block"), self.is_vnni)
 
+    def experts_into(self, x, tw, ids, out):
+        """Local experts over received slots with separate ids / weights tensors, result written to `out`."""
+        w = self.w
+        return ops.fused_experts_impl(x, w["w1"], w["w2"], tw, ids, False, self.fmt, w.get("s1"), w.get("s2"),
+                                      w.get("block"), self.is_vnni, out=out)
+
     def combine(self, ret, dest_row, send_count, world, cap):
         M = dest_row.shape[0]
         H = ret.shape[1]
@@ -92,6 +100,100 @@ class DistComm:
         return recv
 
 
+class _DevMem:
+    """Zero-copy torch view of raw device memory through __cuda_array_interface__."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class PeerExchange:
+    """Decode-regime exchange over NVLink peer memory (csrc/ep_p2p.cu): one cudaMalloc'd region per rank,
+    mapped into every peer through CUDA IPC; rows, ids and weights are stored straight into the owners'
+    receive buffers and partial results are read back with peer loads.  No NCCL call on the data path --
+    torch.distributed only carries the 64-byte IPC handles once, at construction."""
+
+    def __init__(self, group, world, rank, cap, H, topk, device):
+        import ctypes as C
+        lib = L.load()
+        self.world, self.rank, self.cap, self.H, self.topk = world, rank, cap, H, topk
+        offs = (C.c_size_t * 8)()
+        self.nbytes = lib.sglb_ep_p2p_region_bytes(world, cap, H, topk, offs)
+        if self.nbytes == 0:
+            raise RuntimeError("PeerExchange: unsupported geometry")
+        self.offs = list(offs)
+        base = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        status = "ok"
+        try:
+            L.check(lib.sglb_p2p_alloc(self.nbytes, C.byref(base), handle))
+        except RuntimeError as e:  # keep going: every rank must reach the collective below
+            status = str(e)
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (status, bytes(handle.raw)), group=group)
+        self.base = base.value
+        self.peers = (C.c_void_p * world)()
+        self._opened = []
+        if all(g[0] == "ok" for g in gathered):
+            for r in range(world):
+                if r == rank:
+                    self.peers[r] = self.base
+                    continue
+                p = C.c_void_p()
+                try:
+                    L.check(lib.sglb_p2p_open(C.create_string_buffer(gathered[r][1], 64), C.byref(p)))
+                    self._opened.append(p.value)
+                    self.peers[r] = p.value
+                except RuntimeError as e:
+                    status = str(e)
+                    break
+        else:
+            status = next(g[0] for g in gathered if g[0] != "ok")
+        # every rank learns whether every rank mapped every peer: all use the path or none does
+        final = [None] * world
+        dist.all_gather_object(final, status, group=group)
+        bad = [f for f in final if f != "ok"]
+        if bad:
+            self.close()
+            raise RuntimeError(f"PeerExchange: peer mapping failed on some rank: {bad[0]}")
+        mem = torch.as_tensor(_DevMem(self.base, self.nbytes), device=device)
+        rows = world * cap
+
+        def view(off, dtype, cols):
+            nb = rows * cols * torch.empty((), dtype=dtype).element_size()
+            return mem[off:off + nb].view(dtype).view(rows, cols)
+        self.recv_x = [view(self.offs[p], torch.bfloat16, H) for p in range(2)]
+        self.recv_ids = [view(self.offs[2 + p], torch.int32, topk) for p in range(2)]
+        self.recv_tw = [view(self.offs[4 + p], torch.float32, topk) for p in range(2)]
+        self.y = [view(self.offs[6 + p], torch.bfloat16, H) for p in range(2)]
+        self.seq = 0
+
+    def close(self):
+        lib = L.load()
+        for p in self._opened:
+            lib.sglb_p2p_close(p)
+        self._opened = []
+        if self.base:
+            lib.sglb_p2p_free(self.base)
+            self.base = None
+
+    def run(self, x, tw, ids, E, experts_fn):
+        """dispatch -> wait -> experts_fn(recv_x, recv_tw, recv_ids, out=y) -> combine; returns [M, H]."""
+        lib = L.load()
+        s = torch.cuda.current_stream().cuda_stream
+        M = x.shape[0]
+        self.seq += 1
+        seq, par = self.seq & 0xFFFFFFFF, self.seq & 1
+        L.check(lib.sglb_ep_p2p_dispatch(x.data_ptr(), ids.data_ptr(), tw.data_ptr(), M, self.topk, E, self.world,
+                                         self.rank, self.H, self.cap, self.peers, seq, s))
+        L.check(lib.sglb_ep_p2p_wait_dispatch(self.base, self.world, self.cap, self.H, self.topk, seq, s))
+        experts_fn(self.recv_x[par], self.recv_tw[par], self.recv_ids[par], self.y[par])
+        out = torch.empty_like(x)
+        L.check(lib.sglb_ep_p2p_combine(ids.data_ptr(), M, self.topk, E, self.world, self.rank, self.H, self.cap,
+                                        self.peers, seq, out.data_ptr(), s))
+        return out
+
+
 class EPMoE:
     """One MoE layer's routed experts, expert-parallel.
 
@@ -109,6 +211,18 @@ class EPMoE:
         self.E, self.topk, self.world = num_experts, topk, world
         self.backend = backend if backend is not None else CudaBackend(weights, fmt, num_experts // world, topk, is_vnni)
         self.last_mode = None
+        self._peer = {}          # (cap, H) -> PeerExchange
+        self._peer_failed = False
+
+    def _peer_exchange(self, cap, H, device):
+        key = (cap, H)
+        if key not in self._peer:
+            try:
+                self._peer[key] = PeerExchange(self.comm.group, self.world, self.comm.rank, cap, H, self.topk, device)
+            except RuntimeError:
+                self._peer_failed = True     # decided identically on every rank (see PeerExchange.__init__)
+                return None
+        return self._peer[key]
 
     def forward(self, x, topk_weights, topk_ids, mode=None, capacity=None):
         """capacity: rows reserved per destination rank in fixed mode; must be the SAME on every rank and
@@ -127,6 +241,17 @@ class EPMoE:
         if mode is None:
             # every rank must take the same branch: decide from static shapes only
             mode = "fixed" if cap * world * H * x.element_size() <= self.FIXED_CAPACITY_BYTES else "exact"
+            if (mode == "fixed" and world > 1 and x.is_cuda and isinstance(B, CudaBackend) and M >= 1 and H % 8 == 0
+                    and not self._peer_failed and os.environ.get("SGLB_EP_P2P", "1") != "0"):
+                mode = "p2p"
+        if mode == "p2p":
+            pcap = max(16, 1 << (cap - 1).bit_length())     # slots per source: next power of two
+            px = self._peer_exchange(pcap, H, x.device)
+            if px is None:
+                mode = "fixed"
+            else:
+                self.last_mode = mode
+                return px.run(x, tw, ids, self.E, B.experts_into)
         self.last_mode = mode
         if mode == "fixed":
             rows, recv_rows, sc, rc = cap * world, cap * world, None, None

@@ -409,8 +409,9 @@ _WDT = {L.FMT_BF16: (torch.bfloat16,), L.FMT_INT8_W8A8: (torch.int8,), L.FMT_FP8
 
 
 def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, fmt, w1_scale, w2_scale,
-                       block_size, is_vnni, path=L.PATH_AUTO):
-    """Format-explicit core behind every fused_experts_cpu signature vintage."""
+                       block_size, is_vnni, path=L.PATH_AUTO, out=None):
+    """Format-explicit core behind every fused_experts_cpu signature vintage.  `out` (CUDA callers only):
+    a [M, H] bf16 device tensor that receives the result instead of a fresh allocation."""
     if hidden_states.dim() != 2 or hidden_states.dtype != torch.bfloat16:
         raise RuntimeError("fused_experts: hidden_states must be a 2-D bfloat16 tensor")
     if w1.dtype not in _WDT[fmt] or w2.dtype != w1.dtype:
@@ -454,7 +455,11 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
         elif fmt != L.FMT_BF16:
             s13 = _resident_aux(w1_scale, dev, torch.float32)
             s2 = _resident_aux(w2_scale, dev, torch.float32)
-        if on_cuda and inplace and x.data_ptr() == hidden_states.data_ptr():
+        if out is not None:
+            if not on_cuda or inplace or out.shape != x.shape or out.dtype != x.dtype or not out.is_contiguous() \
+                    or out.device != x.device:
+                raise RuntimeError("fused_experts: out= needs CUDA inputs, inplace=False and a contiguous tensor like hidden_states")
+        elif on_cuda and inplace and x.data_ptr() == hidden_states.data_ptr():
             out = x
         else:
             out = torch.empty_like(x)

@@ -45,8 +45,20 @@ def main():
             tw, ids = torch.topk(torch.softmax(score, -1), topk)
             ids = ids.to(torch.int32)
             ref = K.fused_experts_impl(x, w["w1"], w["w2"], tw, ids, False, fid, w["s1"], w["s2"], w["block"], False)
-            for mode in ("fixed", "exact"):
+            outs = {}
+            for mode in ("fixed", "exact", "p2p", "p2p", "p2p"):   # p2p thrice: both buffer parities and their reuse
                 out = layer.forward(x, tw, ids, mode=mode)
+                if mode == "p2p" and layer.last_mode != "p2p":
+                    ok = False
+                    print(f"[rank {rank}] peer-memory path unavailable", flush=True)
+                if mode in outs and mode == "p2p":
+                    ok &= torch.equal(out, outs[mode])
+                outs[mode] = out
+                if mode == "p2p":   # same per-rank partial rows, same rank-order f32 sum as the NCCL path
+                    same = torch.equal(out, outs["fixed"])
+                    ok &= same
+                    if not same and rank == 0:
+                        print(f"[rank {rank}] {fmt} M={M}: p2p differs bitwise from the NCCL fixed-capacity path", flush=True)
                 d = (out.float() - ref.float()).abs().max().item()
                 if fmt == "int8":   # the reference's int8 criterion (test_moe_int8.py:134-137): partial sums cancel
                     good = float((out.float() - ref.float()).abs().mean() / ref.float().abs().mean()) < 0.01
