@@ -168,6 +168,35 @@ void sglb_set_mx4_native(int on); /* 0: keep mxfp4 on the dequantising kernels e
 int sglb_mxfp4_mm(const void* A, const void* Bq, const void* Bs, const float* bias, int64_t M, int N,
                   int K, void* out, void* workspace, size_t workspace_bytes, sglb_stream_t stream);
 
+/* ---- K10 dense quantised linears ------------------------------------------------
+ * One entry point behind the reference's dense ops; out[M,N] bf16 = A[M,K] . dequant(W[N,K])^T + bias:
+ *   weight_packed_linear(mat1, mat2, bias?, is_vnni)                      test_gemm.py:22-25      fmt BF16
+ *   int8_scaled_mm_cpu(Aq, Bq, As, Bs, bias?, out_dtype, is_vnni)         test_gemm_int8.py:69    fmt INT8, a_scale set
+ *   int8_scaled_mm_with_quant(A, Bq, Bs, bias?, out_dtype, is_vnni)       test_gemm_int8.py:74    fmt INT8, a_scale NULL
+ *   fp8_scaled_mm_cpu(A, Bq, Bs, block_size, bias?, out_dtype, is_vnni)   test_gemm_fp8.py:54-62  fmt FP8_W8A16
+ * W is row-major [N,K] (the HBM twin registered by convert_weight_packed); w_scale: int8 f32 [N], fp8 f32
+ * [ceil(N/bn), ceil(K/bk)], mxfp4 u8 [N,K/32].  A is bf16 [M,K], or int8 [M,K] with a_scale f32 [M]
+ * (per_token_quant_int8_cpu's outputs).  bias f32 [N] or NULL, added in f32 before the one bf16 rounding.
+ * Same kernels as fused_experts stage 2 with E = 1, topk = 1, no row weights. */
+typedef struct sglb_linear_problem {
+  int64_t M;
+  int32_t N, K;
+  int32_t fmt;
+  int32_t path;         /* SGLB_PATH_AUTO / _STREAM / _UMMA */
+  const void* A;
+  const float* a_scale; /* int8 only; NULL = quantise A (bf16) per token inside the call */
+  const void* W;
+  const void* w_scale;
+  int32_t block_n, block_k;
+  const float* bias;
+  void* out; /* [M,N] bf16 */
+  void* workspace;
+  size_t workspace_bytes; /* >= sglb_linear_workspace_bytes(M, N, K, fmt) */
+} sglb_linear_problem;
+
+size_t sglb_linear_workspace_bytes(int64_t M, int N, int K, int fmt);
+int sglb_linear(const sglb_linear_problem* p, sglb_stream_t stream);
+
 /* ---- K7 prepack ---------------------------------------------------------------------------------
  * convert_weight_packed (test_moe.py:75-76,115-124; test_gemm.py:36-46; test_gemm_int8.py:80-93)
  * and convert_scale_packed (test_mxfp4.py:160,182-185) define a CPU (AMX/VNNI) tile layout.  These

@@ -74,6 +74,54 @@ def scaled_weight(weight, scales, block_n, block_k):
 
 
 # ---------------------------------------------------------------------------------------------------
+# dense quantised linears; pinned by tests/golden/gemm_*.pt (make_golden_gemm.py)
+
+
+def linear_bf16(mat1, mat2, bias=None):
+    """test_gemm.py:12-20: f32 matmul, bias rounded to bf16 before the add, one rounding of the sum."""
+    ref = torch.matmul(mat1.float(), mat2.float().t())
+    if bias is not None:
+        ref.add_(bias.bfloat16())
+    return ref.bfloat16()
+
+
+def per_token_quant_int8_gemm(x):
+    """test_gemm_int8.py:11-20 (as per_token_quant_int8 above, but the clamp is 1e-10)."""
+    x = x.float()
+    absmax = x.abs().max(dim=-1).values
+    absmax = absmax.clamp_min(1e-10).unsqueeze(-1)
+    scale_x = absmax / 127
+    x_q = x.mul(127 / absmax)
+    x_q = torch.round(x_q).to(torch.int8)
+    return x_q, scale_x
+
+
+def linear_int8(Aq, Bq, As, Bs, bias=None, output_dtype=torch.bfloat16):
+    """test_gemm_int8.py:23-47 (native_w8a8_per_token_matmul): C = As * (Aq @ Bq^T) * Bs (+ bias), f32."""
+    C = torch.matmul(Aq.to(torch.float32), Bq.to(torch.float32).t())
+    C = As.reshape(-1, 1) * C * Bs.view(1, -1)
+    if bias is not None:
+        C.add_(bias.view(1, -1))
+    return C.to(output_dtype)
+
+
+def linear_int8_with_quant(A, Bq, Bs, bias=None, output_dtype=torch.bfloat16):
+    """int8_scaled_mm_with_quant (test_gemm_int8.py:74): the quantiser above fused with linear_int8."""
+    Aq, As = per_token_quant_int8_gemm(A)
+    return linear_int8(Aq, Bq, As, Bs, bias, output_dtype)
+
+
+def linear_fp8(A, Wq, scales, block_size, bias=None):
+    """test_gemm_fp8.py:23-52: the weight is dequantised block-wise in f32 and ROUNDED TO bf16, the matmul
+    runs in bf16 (f32 accumulation inside torch), the bias is rounded to bf16 and added in bf16."""
+    w = scaled_weight(Wq, scales, block_size[0], block_size[1]).to(A.dtype)
+    out = torch.matmul(A, w.t())
+    if bias is not None:
+        out = out + bias.to(A.dtype)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------
 # MXFP4 (test_mxfp4.py:15-128)
 
 E2M1_VALUES = [0, 0.5, 1, 1.5, 2, 3, 4, 6]

@@ -37,6 +37,15 @@ class SharedProblem(C.Structure):
     ]
 
 
+class LinearProblem(C.Structure):
+    _fields_ = [
+        ("M", _i64), ("N", _i32), ("K", _i32), ("fmt", _i32), ("path", _i32),
+        ("A", _vp), ("a_scale", _vp), ("W", _vp), ("w_scale", _vp),
+        ("block_n", _i32), ("block_k", _i32), ("bias", _vp), ("out", _vp),
+        ("workspace", _vp), ("workspace_bytes", _sz),
+    ]
+
+
 # name -> (restype, argtypes); also the list tests check against include/sglb200.h
 SIGNATURES = {
     "sglb_version": (C.c_int, []),
@@ -56,6 +65,8 @@ SIGNATURES = {
     "sglb_fused_experts_workspace_bytes": (_sz, [_i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "sglb_fused_experts": (C.c_int, [C.POINTER(MoeProblem), _vp]),
     "sglb_shared_expert": (C.c_int, [C.POINTER(SharedProblem), _vp]),
+    "sglb_linear_workspace_bytes": (_sz, [_i64, C.c_int, C.c_int, C.c_int]),
+    "sglb_linear": (C.c_int, [C.POINTER(LinearProblem), _vp]),
     "sglb_mxfp4_mm": (C.c_int, [_vp, _vp, _vp, _vp, _i64, C.c_int, C.c_int, _vp, _vp, _sz, _vp]),
     "sglb_repack_weight": (C.c_int, [_vp, _vp, C.c_int, C.c_int, _i64, _i64, _i64, C.c_int, C.c_int, _vp]),
     "sglb_repack_scale": (C.c_int, [_vp, _vp, _i64, _i64, _i64, C.c_int, _vp]),

@@ -220,6 +220,7 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.X2 = sa.X2;
   u.Wsf = mx4_tiles;
   u.tile_cap = mx4_cap;
+  u.bias = sa.bias;
   if (mx4_tiles) return launch_umma_mx4(stage, u, stream);
   if (f8_native) return pair ? launch_umma2_f8(stage, u, stream) : launch_umma_f8(stage, u, stream);
   if (pair) return launch_umma2_gemm(fmt, stage, u, stream);
@@ -528,4 +529,111 @@ extern "C" int sglb_mxfp4_mm(const void* A, const void* Bq, const void* Bs, cons
   a.bias = bias;
   a.scale_cols = K / 32;
   return dispatch_stream<2>(SGLB_FMT_MXFP4, a, plan, stream);
+}
+
+// ---- dense quantised linears: stage 2 of the expert kernels with E = 1 ----------
+// Workspace: the MoE carve with H = K and a token intermediate of 16 columns (act / ic2 are unused here).
+extern "C" size_t sglb_linear_workspace_bytes(int64_t M, int N, int K, int fmt) {
+  (void)N;
+  if (M < 0 || K <= 0) return 0;
+  return carve(nullptr, M, 1, 1, K, 16, fmt).bytes;
+}
+
+extern "C" int sglb_linear(const sglb_linear_problem* p, sglb_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  SGLB_CHECK(p != nullptr, "linear: null problem");
+  const int fmt = p->fmt, N = p->N, K = p->K;
+  const int64_t M = p->M;
+  SGLB_CHECK(M >= 0 && N > 0 && K > 0, "linear: bad shape M=%lld N=%d K=%d", (long long)M, N, K);
+  SGLB_CHECK(N % 8 == 0, "linear: N=%d must be a multiple of 8", N);
+  switch (fmt) {
+    case SGLB_FMT_BF16:
+      SGLB_CHECK(K % 8 == 0, "linear: bf16 needs K %% 8 == 0 (K=%d)", K);
+      break;
+    case SGLB_FMT_INT8_W8A8:
+      SGLB_CHECK(K % 16 == 0, "linear: int8 needs K %% 16 == 0 (K=%d)", K);
+      SGLB_CHECK(p->w_scale, "linear: int8 w8a8 needs the per-channel weight scale");
+      break;
+    case SGLB_FMT_FP8_W8A16:
+      SGLB_CHECK(K % 16 == 0, "linear: fp8 needs K %% 16 == 0 (K=%d)", K);
+      SGLB_CHECK(p->w_scale && p->block_n > 0 && p->block_k > 0, "linear: fp8 w8a16 needs block scales and block_size");
+      SGLB_CHECK(p->block_k % 64 == 0, "linear: fp8 block_k=%d must be a multiple of 64", p->block_k);
+      break;
+    case SGLB_FMT_MXFP4:
+      SGLB_CHECK(K % 32 == 0, "linear: mxfp4 needs K %% 32 == 0 (K=%d)", K);
+      SGLB_CHECK(p->w_scale, "linear: mxfp4 needs e8m0 scales");
+      break;
+    default:
+      set_error("linear: unsupported weight format %d", fmt);
+      return SGLB_ERR_INVALID;
+  }
+  SGLB_CHECK(p->a_scale == nullptr || fmt == SGLB_FMT_INT8_W8A8, "linear: a_scale is int8 w8a8 only");
+  SGLB_CHECK(p->W, "linear: null weight pointer");
+  if (M == 0) return SGLB_OK;
+  SGLB_CHECK(p->A && p->out, "linear: null tensor pointer");
+  const size_t need = sglb_linear_workspace_bytes(M, N, K, fmt);
+  SGLB_CHECK(p->workspace && p->workspace_bytes >= need, "linear: workspace too small (%zu < %zu)",
+             p->workspace_bytes, need);
+  MoeWorkspace ws = carve(p->workspace, M, 1, 1, K, 16, fmt);
+  SGLB_CUDA(cudaMemsetAsync(ws.zero_ids, 0, sizeof(int32_t) * M, stream));
+
+  const bool f8 = fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(K, K, p->block_n, p->block_k);
+  const bool umma_ok = umma_supported(fmt, M, 1, 1, K, K) != 0;
+  int path = p->path;
+  if (path == SGLB_PATH_AUTO)
+    path = (umma_ok && (f8 || (double)M >= kUmmaMinRowsPerExpert)) ? SGLB_PATH_UMMA : SGLB_PATH_STREAM;
+  SGLB_CHECK(path == SGLB_PATH_STREAM || path == SGLB_PATH_UMMA, "linear: path %d not available", path);
+  SGLB_CHECK(path != SGLB_PATH_UMMA || umma_ok, "linear: tcgen05 path does not support fmt=%d K=%d", fmt, K);
+
+  StreamArgs a;
+  memset(&a, 0, sizeof(a));
+  a.chunk_list = ws.chunk_list;
+  a.counters = ws.counters;
+  a.sorted_slot = ws.sorted_slot;
+  a.topk = 1;
+  a.block_n = p->block_n;
+  a.block_k = p->block_k;
+  a.W = p->W;
+  a.Wscale = p->w_scale;
+  a.K = K;
+  a.N = N;
+  a.rows_per_expert = N;
+  a.out = p->out;
+  a.bias = p->bias;
+  a.scale_cols = fmt == SGLB_FMT_FP8_W8A16 ? ceil_div(K, p->block_k) : K / 32;
+  a.X = p->A;
+  int rc;
+  if (fmt == SGLB_FMT_INT8_W8A8) {
+    if (p->a_scale) {
+      a.Xscale = p->a_scale;
+    } else {
+      StageTimer t(ST_QUANT_X, stream);
+      rc = sglb_quant_rows_int8(p->A, M, K, ws.xq, ws.xs, stream);
+      if (rc) return rc;
+      a.X = ws.xq;
+      a.Xscale = ws.xs;
+    }
+  } else if (path == SGLB_PATH_UMMA && f8) {
+    StageTimer t(ST_QUANT_X, stream);
+    rc = launch_split_rows_e4m3(p->A, M, K, ws.xq, ws.xq2, ws.xs, stream);
+    if (rc) return rc;
+    a.X = ws.xq;
+    a.X2 = ws.xq2;
+    a.Xscale = ws.xs;
+  }
+  if (path == SGLB_PATH_UMMA) {
+    rc = run_align(ws.zero_ids, M, 1, 1, 0, ws, stream);
+    if (rc) return rc;
+    a.gather = 1;  // identity through sorted_slot (E = 1 keeps token order); rows are clamped to the tile
+    StageTimer t(ST_GEMM2, stream);
+    return run_umma_stage(fmt, 2, a, 1, M, ws, stream, f8);
+  }
+  StreamPlan plan = make_plan(M, 1, 1, N, 2);
+  plan.max_chunks = (int)max_items(M, 1, 8 * plan.ng);
+  SGLB_CHECK(plan.max_chunks <= 65535, "linear: M too large for the streaming path");
+  rc = run_align(ws.zero_ids, M, 1, 1, 8 * plan.ng, ws, stream);
+  if (rc) return rc;
+  a.gather = 0;
+  StageTimer t(ST_GEMM2, stream);
+  return dispatch_stream<2>(fmt, a, plan, stream);
 }

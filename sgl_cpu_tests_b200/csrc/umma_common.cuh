@@ -289,6 +289,8 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
           ws0 = ws[n];
           if (STAGE == 1) ws1 = ws[a.N + n];
         }
+        float bias_n = 0.f;  // dense linears: f32 bias of output n (this lane's TMEM lane)
+        if (STAGE == 2 && a.bias != nullptr && n < a.N) bias_n = a.bias[n];
 #pragma unroll 1
         for (int c0 = 16 * par; c0 < n_eff; c0 += 32) {  // n_eff is warp-uniform
           const float xsel = sel4(xs_r, c0 >> 5), rsel = sel4(rs_r, c0 >> 5);
@@ -350,7 +352,7 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
                 val = __uint_as_float(v[j]);
                 if constexpr (kTokScale) val *= __shfl_sync(0xffffffffu, xsel, 16 * par + j);
               }
-              *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(val * rs);
+              *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(fmaf(val, rs, bias_n));
             }
           }
           __syncwarp();

@@ -292,6 +292,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll
         for (int sub = 0; sub < kSubs; ++sub) {
           const int nbase = STAGE == 1 ? wi.nb * kWSub + q * 32 : wi.nb * 2 * kWSub + sub * kWSub + q * 32;
+          float bias_n = 0.f;
+          if (STAGE == 2 && a.bias != nullptr && nbase + lane < a.N) bias_n = a.bias[nbase + lane];
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const float xs = __shfl_sync(0xffffffffu, xsel, 16 * par + j);
@@ -300,7 +302,7 @@ __global__ void __launch_bounds__(kThreads, 1)
               val = silu_f(acc[0][c][j] * xs) * (acc[1][c][j] * xs);
             } else {
               const float rs = __shfl_sync(0xffffffffu, rsel, 16 * par + j);
-              val = acc[sub][c][j] * xs * rs;
+              val = fmaf(acc[sub][c][j] * xs, rs, bias_n);
             }
             *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(val);
           }

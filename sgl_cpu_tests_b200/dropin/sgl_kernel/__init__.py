@@ -67,6 +67,17 @@ _def("shared_expert_cpu.v12(Tensor hidden_states, Tensor w1, Tensor w2, Tensor f
 _def("mxfp4_scaled_mm_cpu(Tensor mat1, Tensor mat2, Tensor scales2, Tensor? bias, bool is_vnni) -> Tensor",
      _ops.mxfp4_scaled_mm)
 
+# dense quantised linears: test_gemm.py:22-25, test_gemm_int8.py:68-74, test_gemm_fp8.py:54-62
+_def("weight_packed_linear(Tensor mat1, Tensor mat2, Tensor? bias, bool is_vnni) -> Tensor",
+     _ops.weight_packed_linear)
+_def("per_token_quant_int8_cpu(Tensor A) -> (Tensor, Tensor)", _ops.per_token_quant_int8)
+_def("int8_scaled_mm_cpu(Tensor mat1, Tensor mat2, Tensor scales1, Tensor scales2, Tensor? bias, "
+     "ScalarType out_dtype, bool is_vnni) -> Tensor", _ops.int8_scaled_mm)
+_def("int8_scaled_mm_with_quant(Tensor mat1, Tensor mat2, Tensor scales2, Tensor? bias, ScalarType out_dtype, "
+     "bool is_vnni) -> Tensor", _ops.int8_scaled_mm_with_quant)
+_def("fp8_scaled_mm_cpu(Tensor mat1, Tensor mat2, Tensor scales2, int[] block_size, Tensor? bias, "
+     "ScalarType out_dtype, bool is_vnni) -> Tensor", _ops.fp8_scaled_mm)
+
 from . import common_ops  # noqa: E402,F401
 
 __all__ = ["common_ops"]

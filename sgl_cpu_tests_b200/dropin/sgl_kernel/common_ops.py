@@ -10,6 +10,11 @@ convert_scale_packed = _ops.convert_scale_packed
 fused_experts_cpu = _ops.fused_experts
 shared_expert_cpu = _ops.shared_expert
 mxfp4_scaled_mm_cpu = _ops.mxfp4_scaled_mm
+weight_packed_linear = _ops.weight_packed_linear
+per_token_quant_int8_cpu = _ops.per_token_quant_int8
+int8_scaled_mm_cpu = _ops.int8_scaled_mm
+int8_scaled_mm_with_quant = _ops.int8_scaled_mm_with_quant
+fp8_scaled_mm_cpu = _ops.fp8_scaled_mm
 
 
 def grouped_topk_cpu(*args):

@@ -622,6 +622,98 @@ def mxfp4_scaled_mm(mat1, mat2, scales2, bias, is_vnni):
     return out if on_cuda else out.cpu()
 
 
+# ---- K10: dense quantised linears ---------------------------------------------------
+def _linear(A, W, fmt, is_vnni, w_scale=None, a_scale=None, block_size=None, bias=None, out_dtype=None,
+            path=L.PATH_AUTO, who="linear"):
+    """out[M,N] bf16 = A[M,K] . dequant(W[N,K])^T + bias through sglb_linear (stage 2 of the expert kernels
+    with E = 1).  W may be the packed tensor convert_weight_packed returned (is_vnni=True)."""
+    if out_dtype not in (None, torch.bfloat16):
+        raise RuntimeError(f"{who}: only bfloat16 outputs are supported (got {out_dtype})")
+    if A.dim() != 2 or W.dim() != 2:
+        raise RuntimeError(f"{who}: mat1 and mat2 must be 2-D")
+    M, K = A.shape
+    comp = fmt == L.FMT_INT8_W8A8 and bool(is_vnni)
+    _, N, Kw = _rows_k(W, comp)
+    if Kw != K:
+        raise RuntimeError(f"{who}: inner dimensions differ (mat1 K={K}, mat2 K={Kw})")
+    bn = bk = 0
+    if fmt == L.FMT_FP8_W8A16:
+        if block_size is None or len(block_size) != 2:
+            raise RuntimeError(f"{who}: fp8 needs block_size=[block_n, block_k]")
+        bn, bk = int(block_size[0]), int(block_size[1])
+        if w_scale is None or w_scale.numel() != -(-N // bn) * -(-K // bk):
+            raise RuntimeError(f"{who}: fp8 scales must be [ceil(N/{bn}), ceil(K/{bk})]")
+    if fmt == L.FMT_INT8_W8A8 and (w_scale is None or w_scale.numel() != N):
+        raise RuntimeError(f"{who}: int8 needs a per-channel scale of {N} elements")
+    if a_scale is not None and a_scale.numel() != M:
+        raise RuntimeError(f"{who}: activation scale must hold one value per row ({M})")
+    on_cuda = A.is_cuda
+    dev = A.device if on_cuda else _device()
+    lib = L.load()
+    with torch.cuda.device(dev):
+        a = _to_dev(A, dev)
+        wd = _resident_weight(W, bool(is_vnni), dev)
+        sd = _resident_aux(w_scale, dev, torch.float32)
+        asd = _to_dev(a_scale.reshape(-1), dev, torch.float32) if a_scale is not None else None
+        bd = _resident_aux(bias, dev, torch.float32, "b")
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+        nws = lib.sglb_linear_workspace_bytes(M, N, K, fmt)
+        with _launch_lock:
+            ws = _workspace(nws, dev)
+            p = L.LinearProblem(M=M, N=N, K=K, fmt=fmt, path=path, A=_ptr(a), a_scale=_ptr(asd), W=_ptr(wd),
+                                w_scale=_ptr(sd), block_n=bn, block_k=bk, bias=_ptr(bd), out=_ptr(out),
+                                workspace=ws.data_ptr(), workspace_bytes=ws.numel())
+            L.check(lib.sglb_linear(p, _stream()))
+    return out if on_cuda else out.cpu()
+
+
+def weight_packed_linear(mat1, mat2, bias, is_vnni):
+    """weight_packed_linear(mat1, mat2, bias?, is_vnni) -> Tensor   (test_gemm.py:22-25)."""
+    if mat1.dtype != torch.bfloat16 or mat2.dtype != torch.bfloat16:
+        raise RuntimeError("weight_packed_linear: mat1 / mat2 must be bfloat16")
+    return _linear(mat1, mat2, L.FMT_BF16, is_vnni, bias=bias, who="weight_packed_linear")
+
+
+def per_token_quant_int8(A):
+    """per_token_quant_int8_cpu(A) -> (Aq int8 [M,K], As f32 [M,1])   (test_gemm_int8.py:68, oracle :11-20)."""
+    if A.dim() != 2 or A.dtype != torch.bfloat16:
+        raise RuntimeError("per_token_quant_int8: A must be a 2-D bfloat16 tensor")
+    on_cuda = A.is_cuda
+    dev = A.device if on_cuda else _device()
+    M, K = A.shape
+    with torch.cuda.device(dev):
+        a = _to_dev(A, dev)
+        q = torch.empty(M, K, dtype=torch.int8, device=dev)
+        sc = torch.empty(M, 1, dtype=torch.float32, device=dev)
+        L.check(L.load().sglb_quant_rows_int8(_ptr(a), M, K, _ptr(q), _ptr(sc), _stream()))
+    return (q, sc) if on_cuda else (q.cpu(), sc.cpu())
+
+
+def int8_scaled_mm(mat1, mat2, scales1, scales2, bias, out_dtype, is_vnni):
+    """int8_scaled_mm_cpu(Aq, Bq, As, Bs, bias?, out_dtype, is_vnni) -> Tensor   (test_gemm_int8.py:69)."""
+    if mat1.dtype != torch.int8 or mat2.dtype != torch.int8:
+        raise RuntimeError("int8_scaled_mm: mat1 / mat2 must be int8")
+    return _linear(mat1, mat2, L.FMT_INT8_W8A8, is_vnni, w_scale=scales2, a_scale=scales1, bias=bias,
+                   out_dtype=out_dtype, who="int8_scaled_mm")
+
+
+def int8_scaled_mm_with_quant(mat1, mat2, scales2, bias, out_dtype, is_vnni):
+    """int8_scaled_mm_with_quant(A, Bq, Bs, bias?, out_dtype, is_vnni) -> Tensor   (test_gemm_int8.py:74):
+    per-token quantisation of A fused into the call."""
+    if mat1.dtype != torch.bfloat16 or mat2.dtype != torch.int8:
+        raise RuntimeError("int8_scaled_mm_with_quant: mat1 must be bfloat16 and mat2 int8")
+    return _linear(mat1, mat2, L.FMT_INT8_W8A8, is_vnni, w_scale=scales2, bias=bias, out_dtype=out_dtype,
+                   who="int8_scaled_mm_with_quant")
+
+
+def fp8_scaled_mm(mat1, mat2, scales2, block_size, bias, out_dtype, is_vnni):
+    """fp8_scaled_mm_cpu(A, Bq, Bs, block_size, bias?, out_dtype, is_vnni) -> Tensor   (test_gemm_fp8.py:54-62)."""
+    if mat1.dtype != torch.bfloat16 or mat2.dtype != torch.float8_e4m3fn:
+        raise RuntimeError("fp8_scaled_mm: mat1 must be bfloat16 and mat2 float8_e4m3fn")
+    return _linear(mat1, mat2, L.FMT_FP8_W8A16, is_vnni, w_scale=scales2, block_size=block_size, bias=bias,
+                   out_dtype=out_dtype, who="fp8_scaled_mm")
+
+
 def split_rows_e4m3(x):
     """bf16 rows -> (hi, lo, rexp): two e4m3 pieces (uint8 storage) and the per-row power-of-two factor with
     x ~= (hi + lo) * rexp -- the activation format of the tensor-native fp8 path (csrc/umma_f8.cu)."""
