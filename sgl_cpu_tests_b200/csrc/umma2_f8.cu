@@ -13,6 +13,8 @@
 //   warp 1      leader: MMA issuer; peer: relay (routed rows landed -> leader's full barrier)
 //   warps 2-3   gather producers, hi and lo pieces of this CTA's half of the routed rows
 //   warps 4-11  epilogue: acc += scale * partial per k block (128 f32 registers per thread), fused output
+#include <type_traits>
+
 #include "umma_pair.cuh"
 
 namespace sglb {
@@ -246,39 +248,45 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
           }
         }
       }
-      float acc[8][16];
+      // acc[c][j/2]: two tokens per register pair, accumulated with the packed f32x2 FMA
+      float2 acc[8][8];
 #pragma unroll
       for (int c = 0; c < 8; ++c)
 #pragma unroll
-        for (int j = 0; j < 16; ++j) acc[c][j] = 0.f;
+        for (int j = 0; j < 8; ++j) acc[c][j] = make_float2(0.f, 0.f);
+      auto accv = [&](int c, int j) { return (j & 1) ? acc[c][j >> 1].y : acc[c][j >> 1].x; };
 
       const int ngroups = ceil_div(num_kb, G);
       float sn = __ldg(srow);
       for (int g = 0; g < ngroups; ++g, ++gi) {
-        const float sc = sn;
+        const float2 sc = make_float2(sn, sn);
         if (g + 1 < ngroups) sn = __ldg(srow + g + 1);
         const int pb = gi & 1;
         mbar_wait(pfull_bar(pb), (gi >> 1) & 1);
         tc_fence_after();
-        const uint32_t part = tmem_base + lane_off + pb * kAccCols;
+        const uint32_t part = tmem_base + lane_off + pb * kAccCols + 16 * par;
+        // Software pipeline over the eight 16-token chunks (same scheme as umma_f8.cu): the load of chunk
+        // c + 1 is in flight under the 8 packed FMAs of chunk c; full tiles take a branch-free copy.
+        uint32_t v[2][16];
+        auto promote = [&](auto full_tag) {
+          constexpr bool kFull = decltype(full_tag)::value;
+          if (kFull || 16 * par < n_eff) tmem_ld16(part, v[0]);
 #pragma unroll
-        for (int c = 0; c < 8; c += 2) {
-          const int c0 = 32 * c + 16 * par;
-          if (c0 < n_eff) {  // warp-uniform
-            uint32_t v0[16], v1[16];
-            tmem_ld16(part + c0, v0);
-            const bool two = c0 + 32 < n_eff;
-            if (two) tmem_ld16(part + c0 + 32, v1);
-            tmem_ld_wait(v0);
+          for (int c = 0; c < 8; ++c) {
+            if (kFull || 32 * c + 16 * par < n_eff) {  // warp-uniform, monotone in c
+              tmem_ld_wait(v[c & 1]);
+              if (c + 1 < 8 && (kFull || 32 * (c + 1) + 16 * par < n_eff))
+                tmem_ld16(part + 32 * (c + 1), v[(c + 1) & 1]);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) acc[c][j] = fmaf(sc, __uint_as_float(v0[j]), acc[c][j]);
-            if (two) {
-              tmem_ld_wait(v1);
-#pragma unroll
-              for (int j = 0; j < 16; ++j) acc[c + 1][j] = fmaf(sc, __uint_as_float(v1[j]), acc[c + 1][j]);
+              for (int j = 0; j < 8; ++j)
+                acc[c][j] = __ffma2_rn(
+                    sc, make_float2(__uint_as_float(v[c & 1][2 * j]), __uint_as_float(v[c & 1][2 * j + 1])),
+                    acc[c][j]);
             }
           }
-        }
+        };
+        if (n_eff == 256) promote(std::true_type{});
+        else promote(std::false_type{});
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(pb ? pempty_l1 : pempty_l0);
@@ -296,7 +304,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               const float xs = __shfl_sync(0xffffffffu, xsel, 16 * par + j);
-              xb[j * 32 + lane] = acc[c][j] * xs;
+              xb[j * 32 + lane] = accv(c, j) * xs;
             }
             named_bar_sync(1 + pair_idx, 64);
             continue;
@@ -305,7 +313,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const float xs = __shfl_sync(0xffffffffu, xsel, 16 * par + j);
-            const float r = silu_f(acc[c][j] * xs) * xb[j * 32 + lane];
+            const float r = silu_f(accv(c, j) * xs) * xb[j * 32 + lane];
             *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(r);
           }
         } else {
@@ -313,7 +321,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
           for (int j = 0; j < 16; ++j) {
             const float xs = __shfl_sync(0xffffffffu, xsel, 16 * par + j);
             const float rs = __shfl_sync(0xffffffffu, rsel, 16 * par + j);
-            *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(acc[c][j] * xs * rs);
+            *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(accv(c, j) * xs * rs);
           }
         }
         __syncwarp();

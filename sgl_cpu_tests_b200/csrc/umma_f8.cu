@@ -28,6 +28,8 @@
 //                 silu_and_mul (stage 1) / topk-weight (stage 2) epilogue
 #include <cuda_fp8.h>
 
+#include <type_traits>
+
 #include "umma_common.cuh"
 
 namespace sglb {
@@ -242,18 +244,19 @@ __global__ void __launch_bounds__(kThreads, 1)
           }
         }
       }
-      float acc[2][4][16];
+      // acc[sub][c][j/2]: two tokens per register pair, accumulated with the packed f32x2 FMA
+      float2 acc[2][4][8];
 #pragma unroll
       for (int s = 0; s < 2; ++s)
 #pragma unroll
         for (int c = 0; c < 4; ++c)
 #pragma unroll
-          for (int j = 0; j < 16; ++j) acc[s][c][j] = 0.f;
+          for (int j = 0; j < 8; ++j) acc[s][c][j] = make_float2(0.f, 0.f);
 
       const int ngroups = ceil_div(num_kb, G);
       float s0n = __ldg(srow0), s1n = __ldg(srow1);
       for (int g = 0; g < ngroups; ++g, ++gi) {
-        const float s0 = s0n, s1 = s1n;
+        const float2 s0 = make_float2(s0n, s0n), s1 = make_float2(s1n, s1n);
         if (g + 1 < ngroups) {
           s0n = __ldg(srow0 + g + 1);
           s1n = __ldg(srow1 + g + 1);
@@ -261,23 +264,37 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int pb = gi & 1;
         mbar_wait(pfull_bar(pb), (gi >> 1) & 1);
         tc_fence_after();
-        const uint32_t part = tmem_base + lane_off + pb * kAccCols;
+        const uint32_t part = tmem_base + lane_off + pb * kAccCols + 16 * par;
+        // Software pipeline over the four 16-token chunks: the TMEM loads of chunk c + 1 are in flight
+        // while chunk c is accumulated (ncu r1f: with load -> wait -> FMA per chunk the promotion took
+        // ~750 clk per k block against ~900 clk of MMAs, and the two serialised on the two partial buffers).
+        // Eight half-steps h = (chunk c, sub-tile): v[sub] is reloaded for step h + 1 as soon as the wait of
+        // step h has returned, so one 16-column load is always in flight under the 8 packed FMAs of a step.
+        // Full tiles (the prefill case) take a branch-free copy so the loads keep one uniform base register.
+        uint32_t v[2][16];
+        auto promote = [&](auto full_tag) {
+          constexpr bool kFull = decltype(full_tag)::value;
+          if (kFull || 16 * par < n_eff) tmem_ld16(part, v[0]);
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          const int c0 = 32 * c + 16 * par;
-          if (c0 < n_eff) {  // warp-uniform
-            uint32_t v0[16], v1[16];
-            tmem_ld16(part + c0, v0);
-            tmem_ld16(part + kWSub + c0, v1);
-            tmem_ld_wait(v0);
-            tmem_ld_wait(v1);
+          for (int h = 0; h < 8; ++h) {
+            const int c = h >> 1, sub = h & 1;
+            if (kFull || 32 * c + 16 * par < n_eff) {  // warp-uniform, monotone in c
+              tmem_ld_wait(v[sub]);
+              if (h + 1 < 8) {
+                const int c2 = (h + 1) >> 1, sub2 = (h + 1) & 1;
+                if (kFull || 32 * c2 + 16 * par < n_eff) tmem_ld16(part + sub2 * kWSub + 32 * c2, v[sub2]);
+              }
+              const float2 sc = sub ? s1 : s0;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              acc[0][c][j] = fmaf(s0, __uint_as_float(v0[j]), acc[0][c][j]);
-              acc[1][c][j] = fmaf(s1, __uint_as_float(v1[j]), acc[1][c][j]);
+              for (int j = 0; j < 8; ++j)
+                acc[sub][c][j] = __ffma2_rn(
+                    sc, make_float2(__uint_as_float(v[sub][2 * j]), __uint_as_float(v[sub][2 * j + 1])),
+                    acc[sub][c][j]);
             }
           }
-        }
+        };
+        if (n_eff == kUmmaTileRows) promote(std::true_type{});
+        else promote(std::false_type{});
         tc_fence_before();
         mbar_arrive(pempty_bar(pb));
       }
@@ -299,10 +316,13 @@ __global__ void __launch_bounds__(kThreads, 1)
             const float xs = __shfl_sync(0xffffffffu, xsel, 16 * par + j);
             float val;
             if constexpr (STAGE == 1) {
-              val = silu_f(acc[0][c][j] * xs) * (acc[1][c][j] * xs);
+              const float g_ = (j & 1) ? acc[0][c][j >> 1].y : acc[0][c][j >> 1].x;
+              const float u_ = (j & 1) ? acc[1][c][j >> 1].y : acc[1][c][j >> 1].x;
+              val = silu_f(g_ * xs) * (u_ * xs);
             } else {
               const float rs = __shfl_sync(0xffffffffu, rsel, 16 * par + j);
-              val = fmaf(acc[sub][c][j] * xs, rs, bias_n);
+              const float a_ = (j & 1) ? acc[sub][c][j >> 1].y : acc[sub][c][j >> 1].x;
+              val = fmaf(a_ * xs, rs, bias_n);
             }
             *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(val);
           }
