@@ -45,6 +45,9 @@ def parse():
     ap.add_argument("--path", default="auto", choices=["auto", "stream", "umma", "umma2"], help="GEMM path (auto = by rows/expert)")
     ap.add_argument("--no-mx4-native", action="store_true", help="mxfp4: dequantising kernels instead of the block-scaled tensor cores")
     ap.add_argument("--block-k", type=int, default=128, help="fp8 scale block along K (experiments; the layer's is 128)")
+    ap.add_argument("--launch", default="auto", choices=["auto", "eager", "graph"],
+                    help="how the value leg launches a step: eager C-ABI calls, or one CUDA-graph replay per step "
+                         "(auto = graph on one GPU up to 1024 tokens, where the step is launch bound)")
     ap.add_argument("--copies", type=int, default=2, help="weight copies rotated between steps (bench_moe.py:50-58)")
     return ap.parse_args()
 
@@ -244,6 +247,26 @@ def run_b200(args):
     else:
         layer_sets = [make_weights(fmt, E, H, I, dev, gen) for _ in range(args.copies)]
 
+    def use_graph(m):
+        return world == 1 and (args.launch == "graph" or (args.launch == "auto" and m <= 1024))
+
+    def make_graph_step(x, tw, ids):
+        """One captured call per weight copy; a step is a single graph replay (K.GraphedExperts)."""
+        graphs = []
+        for w in layer_sets:
+            g = K.GraphedExperts(x.shape[0], w["w1"], w["w2"], tw.shape[1], FMT_ID[fmt], w["s1"], w["s2"], w["block"],
+                                 False, path=PATHS[args.path])
+            g.hidden.copy_(x), g.topk_weights.copy_(tw), g.topk_ids.copy_(ids)
+            graphs.append(g)
+        torch.cuda.synchronize()
+
+        def step(i):
+            g = graphs[i % len(graphs)]
+            g.graph.replay()
+            return g.out
+        step.kernels_per_step = graphs[0].kernels_per_replay
+        return step
+
     def make_step(x, tw, ids):
         outs = [torch.empty_like(x) for _ in range(2)]
 
@@ -256,7 +279,9 @@ def run_b200(args):
         return step
 
     x, tw, ids = make_batch(M, E, topk, H, dev, gen)
-    step = make_step(x, tw, ids)
+    eager_step = make_step(x, tw, ids)
+    graphed = use_graph(M)
+    step = make_graph_step(x, tw, ids) if graphed else eager_step
 
     # ---- headline: device-resident inputs ----
     clocks = ClockSampler(local)
@@ -268,6 +293,8 @@ def run_b200(args):
     clocks.start()
     ms = time_steps(step, args.steps, 0, world)
     launches = K.launch_count() - l_w
+    if graphed:  # kernels inside the replayed graphs (counted once, at capture, by the C ABI)
+        launches = step.kernels_per_step * args.steps
     # The timed region lasts a few ms, less than nvidia-smi needs to report once: keep the same steps running
     # (untimed, same count on every rank) until the sampler has seen about half a second of this load.
     extra = int(min(20000, max(0.0, 0.6 - ms * 1e-3) / max(ms * 1e-3 / args.steps, 1e-6)))
@@ -287,7 +314,8 @@ def run_b200(args):
         "config": {"workload": f"{args.shape} MoE layer {fmt}: E={E} topk={topk} H={H} I={I}, M={M} tokens/step/GPU",
                    "tokens_per_step_per_gpu": M, "parallelism": "single GPU" if world == 1 else f"ep{world}",
                    "l2_policy": f"inputs larger than L2: {args.copies} weight copies rotated between steps",
-                   "path": PATH_DESC[path_used(args, fmt, M, topk, E, H, I)]},
+                   "path": PATH_DESC[path_used(args, fmt, M, topk, E, H, I)],
+                   "launch": "one CUDA-graph replay per step (K.GraphedExperts)" if graphed else "eager C-ABI calls"},
         "clocks": clk, "gpu_launches": int(launches),
     }
     if world > 1:
@@ -302,7 +330,7 @@ def run_b200(args):
         ab = algorithmic_bytes(fmt, E, H, I, M, topk, ids)
         lib.sglb_profile_enable(1)
         for i in range(args.steps):
-            step(i)
+            eager_step(i)
         torch.cuda.synchronize()
         import ctypes
         msv = (ctypes.c_float * 6)()
@@ -313,7 +341,7 @@ def run_b200(args):
         k_us = stage_us["w13_gemm"]
         achieved = ab["w13"] / (k_us * 1e-6) / 1e9 if k_us > 0 else 0.0
         used = path_used(args, fmt, M, topk, E, H, I)
-        kdesc = "umma_mx4_kernel" if (fmt == "mxfp4" and used == "umma" and not args.no_mx4_native) else KERNEL_DESC[(used, fmt)]
+        kdesc = "umma_mx4_kernel" if (fmt == "mxfp4" and used == "umma" and not args.no_mx4_native) else KERNEL_DESC.get((used, fmt), "stream_gemm_kernel")
         kname = (f"{kdesc}<stage 1> (tcgen05 w13 GEMM + silu_and_mul)" if used.startswith("umma")
                  else "stream_gemm_kernel<stage 1> (mma.sync w13 GEMM + silu_and_mul)")
         traffic = None
@@ -335,13 +363,15 @@ def run_b200(args):
             sweep = []
             for m in [int(v) for v in args.sweep.split(",") if v]:
                 xs, tws, idss = make_batch(m, E, topk, H, dev, gen)
-                st = make_step(xs, tws, idss)
+                st = make_graph_step(xs, tws, idss) if use_graph(m) else make_step(xs, tws, idss)
                 t = time_steps(st, 20, 3, 1) / 20
+                t_eager = time_steps(make_step(xs, tws, idss), 20, 3, 1) / 20 if use_graph(m) else t
                 abm = algorithmic_bytes(fmt, E, H, I, m, topk, idss)
                 flops = 6.0 * m * topk * H * I
                 sweep.append({"M": m, "ms": t, "tokens_per_s": m / (t * 1e-3), "hbm_frac": abm["total"] / (t * 1e-3) / 1e9 / hbm_peak,
                               "tflops": flops / (t * 1e-3) / 1e12, "tc_frac_bf16_peak": flops / (t * 1e-3) / 1e12 / tc_peak,
-                              "active_experts": abm["e_act"]})
+                              "active_experts": abm["e_act"], "launch": "graph" if use_graph(m) else "eager",
+                              "ms_eager": t_eager})
             out["sweep"] = sweep
 
     # ---- e2e: the drop-in op with HOST buffers ----

@@ -11,7 +11,7 @@ import os
 
 from . import _lib, ops
 from . import _lib as L  # noqa: F401  (K.L.PATH_*, K.L.FMT_*)
-from .ops import (CPUQuantMethod, biased_grouped_topk, biased_grouped_topk_out, clear_weight_cache,
+from .ops import (CPUQuantMethod, GraphedExperts, biased_grouped_topk, biased_grouped_topk_out, clear_weight_cache,
                   convert_scale_packed, convert_weight_packed, fused_experts, fused_experts_impl,
                   grouped_topk, grouped_topk_out, launch_count, moe_align, mxfp4_scaled_mm,
                   shared_expert, split_rows_e4m3, weight_packed_linear, per_token_quant_int8,

@@ -483,6 +483,63 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
         return out.cpu()
 
 
+class GraphedExperts:
+    """One fused_experts call captured in a CUDA graph over static device buffers and replayed per step.
+
+    At decode batch sizes the six kernels of a call run for a few microseconds each, less than it takes the
+    host to launch them (ctypes + cudaLaunchKernelEx per kernel); a replay is one launch.  Fill `hidden`,
+    `topk_weights` and `topk_ids` in place (or pass tensors to __call__, which copies them on the current
+    stream), then read `out`.  Weights must be device tensors: their addresses are baked into the graph
+    (kernel arguments and TMA descriptors)."""
+
+    def __init__(self, num_tokens, w1, w2, topk, fmt, w1_scale=None, w2_scale=None, block_size=None,
+                 is_vnni=False, path=L.PATH_AUTO):
+        if not (w1.is_cuda and w2.is_cuda):
+            raise RuntimeError("GraphedExperts: weights must be CUDA tensors")
+        dev = w1.device
+        E, H, I = _weight_geometry(w1, w2, fmt, is_vnni)
+        self.hidden = torch.zeros(num_tokens, H, dtype=torch.bfloat16, device=dev)
+        self.topk_weights = torch.zeros(num_tokens, topk, dtype=torch.float32, device=dev)
+        self.topk_ids = torch.zeros(num_tokens, topk, dtype=torch.int32, device=dev)
+        self.out = torch.empty_like(self.hidden)
+        self._keep = (w1, w2, w1_scale, w2_scale)
+        nws = L.load().sglb_fused_experts_workspace_bytes(num_tokens, topk, E, H, I, fmt)
+        self._ws = torch.empty(max(nws, 1 << 20), dtype=torch.uint8, device=dev)
+        side = torch.cuda.Stream(device=dev)
+        key = (dev.index, side.cuda_stream)
+
+        def call():
+            fused_experts_impl(self.hidden, w1, w2, self.topk_weights, self.topk_ids, False, fmt, w1_scale,
+                               w2_scale, block_size, is_vnni, path=path, out=self.out)
+
+        with torch.cuda.device(dev):
+            side.wait_stream(torch.cuda.current_stream())
+            with _launch_lock:
+                _workspaces[key] = self._ws
+                try:
+                    with torch.cuda.stream(side):  # lazy one-off work (function attributes, scale tiles) outside the capture
+                        n0 = launch_count()
+                        call()
+                        self.kernels_per_replay = launch_count() - n0
+                    side.synchronize()
+                    self.graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(self.graph, stream=side):
+                        call()
+                finally:
+                    _workspaces.pop(key, None)
+            torch.cuda.current_stream().wait_stream(side)
+
+    def __call__(self, hidden_states=None, topk_weights=None, topk_ids=None):
+        if hidden_states is not None:
+            self.hidden.copy_(hidden_states, non_blocking=True)
+        if topk_weights is not None:
+            self.topk_weights.copy_(topk_weights, non_blocking=True)
+        if topk_ids is not None:
+            self.topk_ids.copy_(topk_ids, non_blocking=True)
+        self.graph.replay()
+        return self.out
+
+
 def fused_experts(*args):
     """fused_experts_cpu with the reference's three positional signature vintages:
       14 args (bench_moe.py:65-82, test_moe_int8.py:129, test_moe_fp8_ext.py:118):

@@ -358,3 +358,33 @@ def test_errors_surface_as_runtime_error(K):
         K.grouped_topk(a, torch.randn(5, 8), 2, False, 1, 1, 0, None, None)  # token count mismatch
     with pytest.raises(RuntimeError):
         K.grouped_topk(a, torch.randn(4, 8), 2, False, 3, 1, 0, None, None)  # G does not divide E
+
+
+# ------------------------------------------------------------------------------------------ CUDA graph replay
+@pytest.mark.parametrize("fmt", ["bf16", "int8"])
+def test_graphed_experts_matches_eager(K, fmt):
+    """K.GraphedExperts (one captured call, replayed) is bit-identical to the eager call, also after the
+    static input buffers are refilled."""
+    torch.manual_seed(7)
+    M, E, topk, H, I = 33, 16, 4, 256, 128
+    dev = torch.device("cuda")
+    if fmt == "bf16":
+        w1 = (torch.randn(E, 2 * I, H) / 10).bfloat16().to(dev)
+        w2 = (torch.randn(E, H, I) / 10).bfloat16().to(dev)
+        s1 = s2 = None
+        f = K.FMT_BF16
+    else:
+        w1 = torch.randint(-127, 128, (E, 2 * I, H), dtype=torch.int8).to(dev)
+        w2 = torch.randint(-127, 128, (E, H, I), dtype=torch.int8).to(dev)
+        s1, s2 = (torch.rand(E, 2 * I) * 1e-2).to(dev), (torch.rand(E, H) * 1e-2).to(dev)
+        f = K.FMT_INT8_W8A8
+    g = K.GraphedExperts(M, w1, w2, topk, f, s1, s2)
+    assert g.kernels_per_replay >= 4
+    for seed in (1, 2):
+        torch.manual_seed(seed)
+        x = (torch.randn(M, H) / 4).bfloat16().to(dev)
+        tw, ids = routing(M, E, topk)
+        out = g(x, tw.to(dev), ids.to(dev)).clone()
+        ref = K.fused_experts_impl(x, w1, w2, tw.to(dev), ids.to(dev), False, f, s1, s2, None, False)
+        torch.cuda.synchronize()
+        assert torch.equal(out, ref)
