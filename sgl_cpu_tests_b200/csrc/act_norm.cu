@@ -1,0 +1,218 @@
+// The two ops either side of the MoE block in a decoder layer, HBM-bound row kernels:
+//   silu_and_mul_cpu      test_activation.py:10-28 (out variant), bench_silu_and_mul.py:31 (functional)
+//   rmsnorm_cpu           test_norm.py:10,43-48        out = to_dtype(x * rsqrt(mean(x^2) + eps)) * weight
+//   fused_add_rmsnorm_cpu test_norm.py:11,50-63        x += residual (f32); residual = to_dtype(x); x = rmsnorm(x)
+// Rounding follows the reference's torch oracles: silu is rounded to the tensor dtype before the product
+// (F.silu(gate) * up on bf16 / f16 tensors), the normalised value is rounded before the weight product
+// (test_norm.py:28), the residual sum feeds the variance in f32 before it is rounded (:22-23).
+//
+// One CTA per row, 16-byte vector accesses when the row length and the pointers allow it, a scalar path
+// otherwise (test_norm.py:66 uses hidden = 4096 + 13).  Bytes per row: silu 3 d e, rmsnorm 2 h e (+ weight from
+// L2), fused add 4 h e; the row stays in registers between the reduction and the scaling pass.
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+
+namespace sglb {
+namespace {
+
+constexpr int kRowThreads = 256;
+constexpr int kMaxVec = 4;  // 16-byte vectors per thread kept in registers: rows up to 256*4*8 = 8192 elements
+
+template <typename T>
+__device__ __forceinline__ T from_float(float v);
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_float<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <>
+__device__ __forceinline__ __half from_float<__half>(float v) { return __float2half_rn(v); }
+
+template <typename T>
+struct alignas(16) Vec8 {
+  T v[8];
+};
+
+template <typename T>
+__device__ __forceinline__ float tof(T v);
+template <>
+__device__ __forceinline__ float tof<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <>
+__device__ __forceinline__ float tof<__half>(__half v) { return __half2float(v); }
+
+__device__ __forceinline__ float block_sum(float v, float* red) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = 0.f;
+#pragma unroll
+  for (int w = 0; w < kRowThreads / 32; ++w) t += red[w];  // same order in every thread
+  __syncthreads();
+  return t;
+}
+
+// ---- silu_and_mul: out[r, j] = T(silu(x[r, j])) * x[r, d + j] ------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(kRowThreads) silu_and_mul_kernel(const T* __restrict__ x, T* __restrict__ out,
+                                                                   int64_t rows, int d, int vec) {
+  pdl_wait();
+  pdl_trigger();
+  const int64_t per_row = vec ? d / 8 : d;
+  const int64_t total = rows * per_row;
+  for (int64_t i = blockIdx.x * (int64_t)kRowThreads + threadIdx.x; i < total; i += (int64_t)gridDim.x * kRowThreads) {
+    const int64_t r = i / per_row;
+    const int64_t j = i - r * per_row;
+    if (vec) {
+      const Vec8<T> g = *reinterpret_cast<const Vec8<T>*>(x + r * 2 * d + j * 8);
+      const Vec8<T> u = *reinterpret_cast<const Vec8<T>*>(x + r * 2 * d + d + j * 8);
+      Vec8<T> o;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float gf = tof<T>(g.v[k]);
+        const float s = tof<T>(from_float<T>(gf / (1.0f + __expf(-gf))));
+        o.v[k] = from_float<T>(s * tof<T>(u.v[k]));
+      }
+      *reinterpret_cast<Vec8<T>*>(out + r * d + j * 8) = o;
+    } else {
+      const float gf = tof<T>(x[r * 2 * d + j]);
+      const float s = tof<T>(from_float<T>(gf / (1.0f + __expf(-gf))));
+      out[r * d + j] = from_float<T>(s * tof<T>(x[r * 2 * d + d + j]));
+    }
+  }
+}
+
+// ---- rmsnorm / fused_add_rmsnorm: one CTA per row -----------------------------------------------------
+// kAdd: x <- x + residual in f32, residual <- T(sum), the f32 sum feeds the variance (test_norm.py:20-24).
+// kVec: the row sits in registers as 16-byte vectors between the reduction and the scaling pass.
+template <typename T, bool kAdd, bool kVec>
+__global__ void __launch_bounds__(kRowThreads) rmsnorm_kernel(const T* x_in, T* residual, const T* __restrict__ weight, T* out,
+                                                              int hidden, float eps) {
+  __shared__ float red[kRowThreads / 32];
+  pdl_wait();
+  pdl_trigger();
+  const int64_t r = blockIdx.x;
+  const T* xr = x_in + r * hidden;
+  T* rr = kAdd ? residual + r * hidden : nullptr;
+  T* orow = out + r * hidden;
+  float ss = 0.f;
+  if constexpr (kVec) {
+    const int nvec = hidden / 8;
+    float f[kMaxVec][8];
+#pragma unroll
+    for (int i = 0; i < kMaxVec; ++i) {
+      const int v = threadIdx.x + i * kRowThreads;
+      if (v < nvec) {
+        const Vec8<T> a = *reinterpret_cast<const Vec8<T>*>(xr + v * 8);
+        Vec8<T> b;
+        if constexpr (kAdd) b = *reinterpret_cast<const Vec8<T>*>(rr + v * 8);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          float t = tof<T>(a.v[k]);
+          if constexpr (kAdd) {
+            t += tof<T>(b.v[k]);
+            b.v[k] = from_float<T>(t);
+          }
+          f[i][k] = t;
+          ss += t * t;
+        }
+        if constexpr (kAdd) *reinterpret_cast<Vec8<T>*>(rr + v * 8) = b;
+      }
+    }
+    const float inv = rsqrtf(block_sum(ss, red) / (float)hidden + eps);
+#pragma unroll
+    for (int i = 0; i < kMaxVec; ++i) {
+      const int v = threadIdx.x + i * kRowThreads;
+      if (v < nvec) {
+        const Vec8<T> w = *reinterpret_cast<const Vec8<T>*>(weight + v * 8);
+        Vec8<T> o;
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          o.v[k] = from_float<T>(tof<T>(from_float<T>(f[i][k] * inv)) * tof<T>(w.v[k]));
+        *reinterpret_cast<Vec8<T>*>(orow + v * 8) = o;
+      }
+    }
+  } else {
+    // scalar path (row length or alignment rules the vectors out): two passes over the row; the residual
+    // is rewritten only in the second one so that the f32 sum can be rebuilt from the original operands
+    // (each thread touches the same elements in both passes; out may alias x)
+    for (int j = threadIdx.x; j < hidden; j += kRowThreads) {
+      float t = tof<T>(xr[j]);
+      if constexpr (kAdd) t += tof<T>(rr[j]);
+      ss += t * t;
+    }
+    const float inv = rsqrtf(block_sum(ss, red) / (float)hidden + eps);
+    for (int j = threadIdx.x; j < hidden; j += kRowThreads) {
+      float t = tof<T>(xr[j]);
+      if constexpr (kAdd) {
+        t += tof<T>(rr[j]);
+        rr[j] = from_float<T>(t);
+      }
+      orow[j] = from_float<T>(tof<T>(from_float<T>(t * inv)) * tof<T>(weight[j]));
+    }
+  }
+}
+
+template <typename T>
+int launch_silu(const void* x, void* out, int64_t rows, int d, cudaStream_t stream) {
+  const int vec = (d % 8 == 0) && (((uintptr_t)x | (uintptr_t)out) & 15) == 0;
+  const int64_t work = rows * (vec ? d / 8 : d);
+  int64_t blocks = ceil_div64(work, kRowThreads);
+  if (blocks > 148 * 16) blocks = 148 * 16;  // grid-stride beyond 16 CTAs per SM
+  SGLB_CUDA(launch_pdl(silu_and_mul_kernel<T>, dim3((unsigned)blocks), dim3(kRowThreads), 0, stream, (const T*)x,
+                       (T*)out, rows, d, vec));
+  count_launch();
+  return SGLB_OK;
+}
+
+template <typename T, bool kAdd>
+int launch_norm(const void* x, void* residual, const void* weight, void* out, int64_t rows, int hidden, float eps,
+                cudaStream_t stream) {
+  const bool vec = hidden % 8 == 0 && hidden <= kRowThreads * kMaxVec * 8 &&
+                   (((uintptr_t)x | (uintptr_t)out | (uintptr_t)weight | (uintptr_t)residual) & 15) == 0;
+  auto kern = vec ? rmsnorm_kernel<T, kAdd, true> : rmsnorm_kernel<T, kAdd, false>;
+  SGLB_CUDA(launch_pdl(kern, dim3((unsigned)rows), dim3(kRowThreads), 0, stream, (const T*)x, (T*)residual,
+                       (const T*)weight, (T*)out, hidden, eps));
+  count_launch();
+  return SGLB_OK;
+}
+
+}  // namespace
+}  // namespace sglb
+
+using namespace sglb;
+
+extern "C" int sglb_silu_and_mul(const void* x, void* out, int64_t rows, int d, int dtype, sglb_stream_t stream) {
+  SGLB_CHECK(rows >= 0 && d > 0, "silu_and_mul: bad shape rows=%lld d=%d", (long long)rows, d);
+  if (rows == 0) return SGLB_OK;
+  SGLB_CHECK(x && out, "silu_and_mul: null pointer");
+  if (dtype == SGLB_DT_BF16) return launch_silu<__nv_bfloat16>(x, out, rows, d, (cudaStream_t)stream);
+  if (dtype == SGLB_DT_F16) return launch_silu<__half>(x, out, rows, d, (cudaStream_t)stream);
+  set_error("silu_and_mul: unsupported dtype %d (bf16 / f16)", dtype);
+  return SGLB_ERR_INVALID;
+}
+
+extern "C" int sglb_rmsnorm(const void* x, const void* weight, float eps, void* out, int64_t rows, int hidden,
+                            int dtype, sglb_stream_t stream) {
+  SGLB_CHECK(rows >= 0 && hidden > 0 && rows < (1ll << 31), "rmsnorm: bad shape rows=%lld hidden=%d", (long long)rows, hidden);
+  if (rows == 0) return SGLB_OK;
+  SGLB_CHECK(x && weight && out, "rmsnorm: null pointer");
+  if (dtype == SGLB_DT_BF16)
+    return launch_norm<__nv_bfloat16, false>(x, nullptr, weight, out, rows, hidden, eps, (cudaStream_t)stream);
+  if (dtype == SGLB_DT_F16)
+    return launch_norm<__half, false>(x, nullptr, weight, out, rows, hidden, eps, (cudaStream_t)stream);
+  set_error("rmsnorm: unsupported dtype %d (bf16 / f16)", dtype);
+  return SGLB_ERR_INVALID;
+}
+
+extern "C" int sglb_fused_add_rmsnorm(void* x, void* residual, const void* weight, float eps, int64_t rows,
+                                      int hidden, int dtype, sglb_stream_t stream) {
+  SGLB_CHECK(rows >= 0 && hidden > 0 && rows < (1ll << 31), "fused_add_rmsnorm: bad shape rows=%lld hidden=%d",
+             (long long)rows, hidden);
+  if (rows == 0) return SGLB_OK;
+  SGLB_CHECK(x && residual && weight, "fused_add_rmsnorm: null pointer");
+  if (dtype == SGLB_DT_BF16)
+    return launch_norm<__nv_bfloat16, true>(x, residual, weight, x, rows, hidden, eps, (cudaStream_t)stream);
+  if (dtype == SGLB_DT_F16)
+    return launch_norm<__half, true>(x, residual, weight, x, rows, hidden, eps, (cudaStream_t)stream);
+  set_error("fused_add_rmsnorm: unsupported dtype %d (bf16 / f16)", dtype);
+  return SGLB_ERR_INVALID;
+}

@@ -200,17 +200,31 @@ __device__ __forceinline__ void gather_role(const UmmaArgs& a, int total, int n_
     const int c = g & 7, rbase = g >> 3;  // 16-B chunk of the 128-B row; rows rbase + 16*j
     const uint32_t dst0 = rbase * kRowBytes + ((c ^ (rbase & 7)) << 4);
     uint32_t it = 0;
-    for (int w = blockIdx.x; w < total; w += gridDim.x) {
-      const WorkItem wi = get_item(a, w, n_blocks);
+    // Two-level lookahead over the dependent loads tile_list -> sorted_slot: the descriptor of item i + 2 and
+    // the row indices of item i + 1 are fetched while item i is copied.
+    const int step = gridDim.x;
+    auto rows_of = [&](const WorkItem& wi, int (&xr)[8]) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int p = wi.row_start + min(rbase + 16 * j, wi.rows - 1);
+        xr[j] = a.gather ? a.sorted_slot[p] : p;  // raw slot: the division waits until the value is used
+      }
+    };
+    const int w0 = blockIdx.x;
+    WorkItem cur = get_item(a, w0 < total ? w0 : 0, n_blocks);
+    WorkItem nxt = get_item(a, w0 + step < total ? w0 + step : 0, n_blocks);
+    int xr_cur[8];
+    rows_of(cur, xr_cur);
+    for (int w = w0; w < total; w += step) {
+      const WorkItem wi = cur;
       const int n_eff = (wi.rows + 15) & ~15;
       const char* src[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int r = rbase + 16 * j;
-        const int p = wi.row_start + min(r, wi.rows - 1);
-        const int xr = a.gather ? (a.sorted_slot[p] / a.topk) : p;
-        src[j] = (const char*)a.X + (size_t)xr * k_bytes + c * 16;
-      }
+      for (int j = 0; j < 8; ++j)
+        src[j] = (const char*)a.X + (size_t)(a.gather ? xr_cur[j] / a.topk : xr_cur[j]) * k_bytes + c * 16;
+      cur = nxt;
+      if (w + step < total) rows_of(cur, xr_cur);  // consumed by the next iteration
+      if (w + 2 * step < total) nxt = get_item(a, w + 2 * step, n_blocks);
       for (int kb = 0; kb < num_kb; ++kb, ++it) {
         const int s = it % kStages;
         if (kRelaxed) mbar_wait_relaxed(empty_bar(s), ((it / kStages) & 1) ^ 1);

@@ -25,6 +25,8 @@
 #include <mutex>
 #include <unordered_map>
 
+#include <stdlib.h>
+
 #include "umma_common.cuh"
 
 namespace sglb {
@@ -94,8 +96,13 @@ __global__ void __launch_bounds__(kThreads, 1)
     // ================= TMA producer: weights =================
     {
       uint32_t it = 0;
+      // The descriptor of the next item is fetched while this item streams: a dependent tile_list load at
+      // every item start leaves the ring's freed slots unissued for its latency (one item is only ~11 us of
+      // HBM time per SM for int8 at decode).
+      WorkItem nxt = get_item(a, blockIdx.x < total ? blockIdx.x : 0, n_blocks);
       for (int w = blockIdx.x; w < total; w += gridDim.x) {
-        const WorkItem wi = get_item(a, w, n_blocks);
+        const WorkItem wi = nxt;
+        if (w + (int)gridDim.x < total) nxt = get_item(a, w + gridDim.x, n_blocks);
         const int wrow0 = STAGE == 1 ? wi.nb * kWSub : wi.nb * 2 * kWSub;
         const int wrow1 = STAGE == 1 ? a.N + wi.nb * kWSub : wrow0 + kWSub;
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
@@ -259,7 +266,12 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   }
   const int n_blocks = STAGE == 1 ? ceil_div(a.N, kWSub) : ceil_div(a.N, 2 * kWSub);
   const int64_t max_items = (int64_t)a.max_tiles * n_blocks;
-  const int grid = (int)(max_items < sm_count() ? (max_items > 0 ? max_items : 1) : sm_count());
+  int grid = (int)(max_items < sm_count() ? (max_items > 0 ? max_items : 1) : sm_count());
+  static const int forced_grid = [] {
+    const char* e = getenv("SGLB_GRID");  // experiments: persistent grid size
+    return e ? atoi(e) : 0;
+  }();
+  if (forced_grid > 0 && forced_grid < grid) grid = forced_grid;
   SGLB_CUDA(launch_pdl(umma_moe_kernel<FMT, STAGE>, dim3(grid), dim3(kThreads), kSmemBytes, stream, map, a));
   return SGLB_OK;
 }
