@@ -197,6 +197,18 @@ typedef struct sglb_linear_problem {
 size_t sglb_linear_workspace_bytes(int64_t M, int N, int K, int fmt);
 int sglb_linear(const sglb_linear_problem* p, sglb_stream_t stream);
 
+/* ---- K11 the ops either side of the MoE block ----------------------------------------
+ * silu_and_mul_cpu       test_activation.py:10-28 (out, x), bench_silu_and_mul.py:31 (functional):
+ *                        out[r, j] = T(silu(x[r, j])) * x[r, d + j], x [rows, 2d], out [rows, d]
+ * rmsnorm_cpu            test_norm.py:43-48: out = T(x * rsqrt(mean(x^2) + eps)) * weight, rows of `hidden`
+ * fused_add_rmsnorm_cpu  test_norm.py:50-63: x += residual in f32; residual = T(x); x = rmsnorm(x), in place
+ * dtype = SGLB_DT_BF16 or SGLB_DT_F16 for every tensor of a call; rows are contiguous. */
+int sglb_silu_and_mul(const void* x, void* out, int64_t rows, int d, int dtype, sglb_stream_t stream);
+int sglb_rmsnorm(const void* x, const void* weight, float eps, void* out, int64_t rows, int hidden, int dtype,
+                 sglb_stream_t stream);
+int sglb_fused_add_rmsnorm(void* x, void* residual, const void* weight, float eps, int64_t rows, int hidden,
+                           int dtype, sglb_stream_t stream);
+
 /* ---- K7 prepack ---------------------------------------------------------------------------------
  * convert_weight_packed (test_moe.py:75-76,115-124; test_gemm.py:36-46; test_gemm_int8.py:80-93)
  * and convert_scale_packed (test_mxfp4.py:160,182-185) define a CPU (AMX/VNNI) tile layout.  These

@@ -121,6 +121,20 @@ def linear_fp8(A, Wq, scales, block_size, bias=None):
     return out
 
 
+def rmsnorm(x, weight, eps=1e-6, residual=None):
+    """test_norm.py:13-33 (forward_native): f32 statistics, the normalised value is rounded to the input dtype
+    before the weight product; with a residual the f32 sum feeds the variance and is returned rounded."""
+    orig_dtype = x.dtype
+    x = x.to(torch.float32)
+    if residual is not None:
+        x = x + residual.to(torch.float32)
+        residual = x.to(orig_dtype)
+    variance = x.pow(2).mean(dim=-1, keepdim=True)
+    x = x * torch.rsqrt(variance + eps)
+    x = x.to(orig_dtype) * weight
+    return x if residual is None else (x, residual)
+
+
 # ---------------------------------------------------------------------------------------------------
 # MXFP4 (test_mxfp4.py:15-128)
 

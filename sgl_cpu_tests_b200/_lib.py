@@ -67,6 +67,9 @@ SIGNATURES = {
     "sglb_shared_expert": (C.c_int, [C.POINTER(SharedProblem), _vp]),
     "sglb_linear_workspace_bytes": (_sz, [_i64, C.c_int, C.c_int, C.c_int]),
     "sglb_linear": (C.c_int, [C.POINTER(LinearProblem), _vp]),
+    "sglb_silu_and_mul": (C.c_int, [_vp, _vp, _i64, C.c_int, C.c_int, _vp]),
+    "sglb_rmsnorm": (C.c_int, [_vp, _vp, _f32, _vp, _i64, C.c_int, C.c_int, _vp]),
+    "sglb_fused_add_rmsnorm": (C.c_int, [_vp, _vp, _vp, _f32, _i64, C.c_int, C.c_int, _vp]),
     "sglb_mxfp4_mm": (C.c_int, [_vp, _vp, _vp, _vp, _i64, C.c_int, C.c_int, _vp, _vp, _sz, _vp]),
     "sglb_repack_weight": (C.c_int, [_vp, _vp, C.c_int, C.c_int, _i64, _i64, _i64, C.c_int, C.c_int, _vp]),
     "sglb_repack_scale": (C.c_int, [_vp, _vp, _i64, _i64, _i64, C.c_int, _vp]),

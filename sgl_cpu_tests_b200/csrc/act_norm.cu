@@ -56,11 +56,11 @@ __global__ void __launch_bounds__(kRowThreads) silu_and_mul_kernel(const T* __re
                                                                    int64_t rows, int d, int vec) {
   pdl_wait();
   pdl_trigger();
-  const int64_t per_row = vec ? d / 8 : d;
-  const int64_t total = rows * per_row;
-  for (int64_t i = blockIdx.x * (int64_t)kRowThreads + threadIdx.x; i < total; i += (int64_t)gridDim.x * kRowThreads) {
-    const int64_t r = i / per_row;
-    const int64_t j = i - r * per_row;
+  // grid.x covers one row (16-byte vectors or scalars), grid.y strides over the rows: no index division
+  const int per_row = vec ? d / 8 : d;
+  const int j = blockIdx.x * kRowThreads + threadIdx.x;
+  if (j >= per_row) return;
+  for (int64_t r = blockIdx.y; r < rows; r += gridDim.y) {
     if (vec) {
       const Vec8<T> g = *reinterpret_cast<const Vec8<T>*>(x + r * 2 * d + j * 8);
       const Vec8<T> u = *reinterpret_cast<const Vec8<T>*>(x + r * 2 * d + d + j * 8);
@@ -154,11 +154,13 @@ __global__ void __launch_bounds__(kRowThreads) rmsnorm_kernel(const T* x_in, T* 
 template <typename T>
 int launch_silu(const void* x, void* out, int64_t rows, int d, cudaStream_t stream) {
   const int vec = (d % 8 == 0) && (((uintptr_t)x | (uintptr_t)out) & 15) == 0;
-  const int64_t work = rows * (vec ? d / 8 : d);
-  int64_t blocks = ceil_div64(work, kRowThreads);
-  if (blocks > 148 * 16) blocks = 148 * 16;  // grid-stride beyond 16 CTAs per SM
-  SGLB_CUDA(launch_pdl(silu_and_mul_kernel<T>, dim3((unsigned)blocks), dim3(kRowThreads), 0, stream, (const T*)x,
-                       (T*)out, rows, d, vec));
+  const int bx = ceil_div(vec ? d / 8 : d, kRowThreads);
+  int64_t by = rows;
+  const int64_t cap = (148 * 32 + bx - 1) / bx;  // about 32 CTAs per SM in flight, the rest by striding
+  if (by > cap) by = cap;
+  if (by > 65535) by = 65535;
+  SGLB_CUDA(launch_pdl(silu_and_mul_kernel<T>, dim3((unsigned)bx, (unsigned)by), dim3(kRowThreads), 0, stream,
+                       (const T*)x, (T*)out, rows, d, vec));
   count_launch();
   return SGLB_OK;
 }

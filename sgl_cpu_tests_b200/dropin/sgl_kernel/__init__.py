@@ -78,6 +78,13 @@ _def("int8_scaled_mm_with_quant(Tensor mat1, Tensor mat2, Tensor scales2, Tensor
 _def("fp8_scaled_mm_cpu(Tensor mat1, Tensor mat2, Tensor scales2, int[] block_size, Tensor? bias, "
      "ScalarType out_dtype, bool is_vnni) -> Tensor", _ops.fp8_scaled_mm)
 
+# bench_silu_and_mul.py:31 (functional); the (out, x) form of test_activation.py:26 and the
+# norm out-variants of test_norm.py:43-56 are module attributes of common_ops / ops._kernels
+_def("silu_and_mul_cpu(Tensor input) -> Tensor", _ops.silu_and_mul)
+_def("rmsnorm_cpu(Tensor(a!) output, Tensor input, Tensor weight, float eps) -> ()", _ops.rmsnorm)
+_def("fused_add_rmsnorm_cpu(Tensor(a!) input, Tensor(b!) residual, Tensor weight, float eps) -> ()",
+     _ops.fused_add_rmsnorm)
+
 from . import common_ops  # noqa: E402,F401
 
 __all__ = ["common_ops"]

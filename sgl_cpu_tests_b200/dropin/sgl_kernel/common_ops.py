@@ -15,6 +15,9 @@ per_token_quant_int8_cpu = _ops.per_token_quant_int8
 int8_scaled_mm_cpu = _ops.int8_scaled_mm
 int8_scaled_mm_with_quant = _ops.int8_scaled_mm_with_quant
 fp8_scaled_mm_cpu = _ops.fp8_scaled_mm
+silu_and_mul_cpu = _ops.silu_and_mul
+rmsnorm_cpu = _ops.rmsnorm
+fused_add_rmsnorm_cpu = _ops.fused_add_rmsnorm
 
 
 def grouped_topk_cpu(*args):

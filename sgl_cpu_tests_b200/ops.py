@@ -768,6 +768,81 @@ def fp8_scaled_mm(mat1, mat2, scales2, block_size, bias, out_dtype, is_vnni):
                    out_dtype=out_dtype, who="fp8_scaled_mm")
 
 
+# ---- K11: silu_and_mul / rmsnorm / fused_add_rmsnorm -------------------------------
+def _act_dtype(t, who):
+    if t.dtype not in (torch.bfloat16, torch.float16):
+        raise RuntimeError(f"{who}: bfloat16 or float16 tensors only (got {t.dtype})")
+    return _DT[t.dtype]
+
+
+def silu_and_mul(*args):
+    """silu_and_mul_cpu(x) -> Tensor (bench_silu_and_mul.py:31) or silu_and_mul_cpu(out, x) -> None
+    (test_activation.py:26)."""
+    if len(args) == 1:
+        out, x = None, args[0]
+    elif len(args) == 2:
+        out, x = args
+    else:
+        raise RuntimeError("silu_and_mul: expected (x) or (out, x)")
+    dt = _act_dtype(x, "silu_and_mul")
+    if x.shape[-1] % 2:
+        raise RuntimeError("silu_and_mul: the last dimension must be even")
+    d = x.shape[-1] // 2
+    oshape = tuple(x.shape[:-1]) + (d,)
+    if out is not None and (tuple(out.shape) != oshape or out.dtype != x.dtype):
+        raise RuntimeError("silu_and_mul: out must be [..., d] of the input dtype")
+    on_cuda = x.is_cuda
+    dev = x.device if on_cuda else _device()
+    with torch.cuda.device(dev):
+        xd = _to_dev(x, dev)
+        od = out if (out is not None and out.is_cuda and out.is_contiguous()) else torch.empty(oshape, dtype=x.dtype, device=dev)
+        rows = xd.numel() // (2 * d) if d else 0
+        L.check(L.load().sglb_silu_and_mul(_ptr(xd), _ptr(od), rows, d, dt, _stream()))
+    if out is None:
+        return od if on_cuda else od.cpu()
+    if od is not out:
+        out.copy_(od)
+    return None
+
+
+def rmsnorm(out, x, weight, eps):
+    """rmsnorm_cpu(out, x, weight, eps) -> None   (test_norm.py:43-45)."""
+    dt = _act_dtype(x, "rmsnorm")
+    if weight.dtype != x.dtype or out.dtype != x.dtype or out.shape != x.shape or weight.numel() != x.shape[-1]:
+        raise RuntimeError("rmsnorm: out / weight must match the input's dtype, shape and hidden size")
+    dev = x.device if x.is_cuda else _device()
+    hidden = x.shape[-1]
+    with torch.cuda.device(dev):
+        xd, wd = _to_dev(x, dev), _to_dev(weight, dev)
+        od = out if (out.is_cuda and out.is_contiguous()) else torch.empty_like(xd)
+        L.check(L.load().sglb_rmsnorm(_ptr(xd), _ptr(wd), float(eps), _ptr(od), xd.numel() // hidden, hidden, dt,
+                                      _stream()))
+    if od is not out:
+        out.copy_(od)
+    return None
+
+
+def fused_add_rmsnorm(x, residual, weight, eps):
+    """fused_add_rmsnorm_cpu(x, residual, weight, eps) -> None, both updated in place   (test_norm.py:56)."""
+    dt = _act_dtype(x, "fused_add_rmsnorm")
+    if residual.dtype != x.dtype or residual.shape != x.shape or weight.dtype != x.dtype or \
+            weight.numel() != x.shape[-1]:
+        raise RuntimeError("fused_add_rmsnorm: residual / weight must match the input's dtype, shape and hidden size")
+    dev = x.device if x.is_cuda else _device()
+    hidden = x.shape[-1]
+    with torch.cuda.device(dev):
+        inplace = x.is_cuda and x.is_contiguous() and residual.is_cuda and residual.is_contiguous()
+        xd = x if inplace else _to_dev(x, dev).clone()
+        rd = residual if inplace else _to_dev(residual, dev).clone()
+        wd = _to_dev(weight, dev)
+        L.check(L.load().sglb_fused_add_rmsnorm(_ptr(xd), _ptr(rd), _ptr(wd), float(eps), xd.numel() // hidden,
+                                                hidden, dt, _stream()))
+    if not inplace:
+        x.copy_(xd)
+        residual.copy_(rd)
+    return None
+
+
 def split_rows_e4m3(x):
     """bf16 rows -> (hi, lo, rexp): two e4m3 pieces (uint8 storage) and the per-row power-of-two factor with
     x ~= (hi + lo) * rexp -- the activation format of the tensor-native fp8 path (csrc/umma_f8.cu)."""

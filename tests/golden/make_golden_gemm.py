@@ -59,7 +59,9 @@ def install():
     torch.ops.__dict__["sgl_kernel"] = _NS()
 
 
-def collect(fn, shapes):
+def collect(fn, shapes, ref_second=False):
+    """ref_second: the script calls compare(ours, reference) (test_activation.py / test_norm.py) instead of
+    compare(reference, ours)."""
     cases = []
     for args in shapes:
         del G.CALLS[:], G.COMPARES[:]
@@ -70,7 +72,7 @@ def collect(fn, shapes):
                 seen.add(n)
                 calls.append((n, a))
         cases.append({"args": list(args), "calls": calls,
-                      "refs": [G._clone(r) for r, _ in G.COMPARES]})
+                      "refs": [G._clone(b if ref_second else a) for a, b in G.COMPARES]})
     return cases
 
 
@@ -91,6 +93,25 @@ def main():
               for b in (False, True)][:12]
     shapes += [(260, 512, 1024, True, False)]
     G.save("gemm_fp8", collect(g["run_single_test"], shapes))
+
+    # silu_and_mul (test_activation.py) and the rmsnorm pair (test_norm.py)
+    install()
+    none = lambda *a: None  # noqa: E731
+    extra = {"silu_and_mul_cpu": G._record("silu_and_mul_cpu", none), "rmsnorm_cpu": G._record("rmsnorm_cpu", none),
+             "fused_add_rmsnorm_cpu": G._record("fused_add_rmsnorm_cpu", none)}
+    for k, v in extra.items():
+        setattr(sys.modules["sgl_kernel.common_ops"], k, v)
+    import types
+    opsmod, kern = types.ModuleType("sgl_kernel.ops"), types.ModuleType("sgl_kernel.ops._kernels")
+    kern.silu_and_mul_cpu = extra["silu_and_mul_cpu"]
+    sys.modules["sgl_kernel.ops"], sys.modules["sgl_kernel.ops._kernels"] = opsmod, kern
+    g = load_defs("test_activation.py")
+    cases = collect(g["run_single_test"], [([17, 1024], torch.bfloat16, "cpu"), ([5, 2, 344], torch.float16, "cpu"),
+                                           ([3, 22016], torch.bfloat16, "cpu"), ([9, 30], torch.float16, "cpu")], True)
+    g = load_defs("test_norm.py")
+    cases += collect(g["run_single_test"], [([33, 1024], torch.bfloat16, "cpu"), ([9, 4096 + 13], torch.float16, "cpu"),
+                                            ([2, 5120], torch.float16, "cpu"), ([4, 8200], torch.bfloat16, "cpu")], True)
+    G.save("act_norm", cases)
 
 
 if __name__ == "__main__":
