@@ -281,7 +281,14 @@ def run_b200(args):
     x, tw, ids = make_batch(M, E, topk, H, dev, gen)
     eager_step = make_step(x, tw, ids)
     graphed = use_graph(M)
-    step = make_graph_step(x, tw, ids) if graphed else eager_step
+    step = eager_step
+    if graphed:
+        try:
+            step = make_graph_step(x, tw, ids)
+        except Exception as e:  # capture refused (driver / allocator state): measure the eager launches instead
+            sys.stderr.write(f"[bench] CUDA graph capture failed ({e}); falling back to eager launches\n")
+            torch.cuda.synchronize()
+            graphed = False
 
     # ---- headline: device-resident inputs ----
     clocks = ClockSampler(local)
@@ -363,14 +370,14 @@ def run_b200(args):
             sweep = []
             for m in [int(v) for v in args.sweep.split(",") if v]:
                 xs, tws, idss = make_batch(m, E, topk, H, dev, gen)
-                st = make_graph_step(xs, tws, idss) if use_graph(m) else make_step(xs, tws, idss)
+                st = make_graph_step(xs, tws, idss) if (graphed and use_graph(m)) else make_step(xs, tws, idss)
                 t = time_steps(st, 20, 3, 1) / 20
-                t_eager = time_steps(make_step(xs, tws, idss), 20, 3, 1) / 20 if use_graph(m) else t
+                t_eager = time_steps(make_step(xs, tws, idss), 20, 3, 1) / 20 if (graphed and use_graph(m)) else t
                 abm = algorithmic_bytes(fmt, E, H, I, m, topk, idss)
                 flops = 6.0 * m * topk * H * I
                 sweep.append({"M": m, "ms": t, "tokens_per_s": m / (t * 1e-3), "hbm_frac": abm["total"] / (t * 1e-3) / 1e9 / hbm_peak,
                               "tflops": flops / (t * 1e-3) / 1e12, "tc_frac_bf16_peak": flops / (t * 1e-3) / 1e12 / tc_peak,
-                              "active_experts": abm["e_act"], "launch": "graph" if use_graph(m) else "eager",
+                              "active_experts": abm["e_act"], "launch": "graph" if (graphed and use_graph(m)) else "eager",
                               "ms_eager": t_eager})
             out["sweep"] = sweep
 

@@ -224,6 +224,13 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   if (mx4_tiles) return launch_umma_mx4(stage, u, stream);
   if (f8_native) return pair ? launch_umma2_f8(stage, u, stream) : launch_umma_f8(stage, u, stream);
   if (pair) return launch_umma2_gemm(fmt, stage, u, stream);
+  if (fmt == SGLB_FMT_BF16 || fmt == SGLB_FMT_INT8_W8A8) {
+    // expected number of tiles when the call is weight-streaming bound (few rows per active expert)
+    const double M = (double)S / sa.topk;
+    double active = E == 1 ? 1.0 : E * (1.0 - pow(1.0 - (double)(sa.topk < E ? sa.topk : E) / E, M));
+    if (active < 1) active = 1;
+    if ((double)S / active <= 32.0) u.est_tiles = (int)(active + 0.5);
+  }
   return launch_umma_gemm(fmt, stage, u, stream);
 }
 

@@ -27,6 +27,7 @@ struct UmmaArgs {
   const void* Wsf;         // mxfp4 tensor-native path: e8m0 scales re-tiled for tcgen05.cp (umma_mx4.cu)
   int tile_cap;            // mxfp4 tensor-native path: row capacity of the tiles in tile_list (16..112)
   const float* bias;       // stage 2 optional f32 [N] added after row_scale (dense linears, E = 1)
+  int est_tiles;           // umma_gemm.cu, decode regime: expected tile count (0 = unknown), sizes the persistent grid
 };
 
 constexpr int kUmmaTileRows = 128;  // routed rows per tile (tile_rows handed to moe_align)
