@@ -85,6 +85,28 @@ _def("rmsnorm_cpu(Tensor(a!) output, Tensor input, Tensor weight, float eps) -> 
 _def("fused_add_rmsnorm_cpu(Tensor(a!) input, Tensor(b!) residual, Tensor weight, float eps) -> ()",
      _ops.fused_add_rmsnorm)
 
+class _ArityPacket:
+    """Front of an op that exists in several positional vintages.  torch resolves overloads by trying each schema
+    in turn and formats an error message -- including the repr of every tensor argument, about 1 ms -- for each
+    one that does not match; the 13-argument fused_experts_cpu call paid that on every call.  This object sits on
+    the torch.ops.sgl_kernel namespace under the op's name, dispatches on the argument count in Python, and
+    forwards everything else (.default, .quant_method, overloads(), ...) to the registered OpOverloadPacket."""
+
+    def __init__(self, name, fn):
+        self._packet = getattr(torch.ops.sgl_kernel, name)
+        self._fn = fn
+
+    def __call__(self, *args):
+        return self._fn(*args)
+
+    def __getattr__(self, item):
+        return getattr(self._packet, item)
+
+
+for _name, _fn in (("fused_experts_cpu", _ops.fused_experts), ("shared_expert_cpu", _ops.shared_expert)):
+    setattr(torch.ops.sgl_kernel, _name, _ArityPacket(_name, _fn))
+
+
 from . import common_ops  # noqa: E402,F401
 
 __all__ = ["common_ops"]
