@@ -185,8 +185,7 @@ def path_used(args, fmt, M, topk, E, H, I):
     else:
         eb = {"bf16": 2, "int8": 1}[fmt]
         ok = (H * eb) % 128 == 0 and (I * eb) % 128 == 0
-    if ok and fmt == "bf16" and M * topk / E >= 128.0:
-        return "umma2"
+    # (the CTA-pair kernel is explicit-only: capi.cu no longer picks it under AUTO)
     return "umma" if ok and M * topk / E >= 4.0 else "stream"
 
 
@@ -364,6 +363,19 @@ def run_b200(args):
         step_gbs = ab["total"] / (ms_per_step * 1e-3) / 1e9
         out["step_roofline"] = {"bound": "hbm", "achieved": step_gbs, "peak": hbm_peak, "unit": "GB/s",
                                 "frac": step_gbs / hbm_peak, "algorithmic_bytes": ab["total"], "stage_us": stage_us}
+        # Which roof bounds this workload: time of the algorithmic FLOPs at the measured tensor peak against time
+        # of the algorithmic bytes at the measured HBM peak.  Prefill batches are tensor bound; the
+        # denominator is the sustained cuBLAS bf16 figure for every format (fp8 / mxfp4 issue two e4m3 passes).
+        w13_flops = 4.0 * M * topk * H * I
+        step_flops = 6.0 * M * topk * H * I
+        if w13_flops / (tc_peak * 1e12) > ab["w13"] / (hbm_peak * 1e9):
+            tf = w13_flops / (k_us * 1e-6) / 1e12 if k_us > 0 else 0.0
+            out["roofline"].update({"bound": "tensor", "achieved": tf, "peak": tc_peak, "unit": "TFLOP/s",
+                                    "frac": tf / tc_peak, "algorithmic_flops": w13_flops,
+                                    "hbm_gbs": achieved, "peak_kind": "sustained cuBLAS bf16 (MEASURED_PEAKS.json)"})
+            stf = step_flops / (ms_per_step * 1e-3) / 1e12
+            out["step_roofline"].update({"bound": "tensor", "achieved": stf, "peak": tc_peak, "unit": "TFLOP/s",
+                                         "frac": stf / tc_peak, "algorithmic_flops": step_flops, "hbm_gbs": step_gbs})
 
         # ---- sweep over M ----
         if not args.no_sweep:

@@ -435,7 +435,11 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
                : SGLB_PATH_STREAM;
     // bf16 prefill: the CTA-pair kernel wins once pair tiles fill up (Qwen3 M = 4096: 793 vs 705 TFLOP/s,
     // M = 8192: 940 vs 804); int8 stays on the single-CTA kernel (940 vs 805 TOP/s at M = 4096)
-    if (path == SGLB_PATH_UMMA && p->fmt == SGLB_FMT_BF16 && rows_per_expert >= kPairMinRowsPerExpert)
+    // The pair kernel is NOT taken automatically any more: tests/test_gpu_fullsize.py (tools/dbg_perm.py) found
+    // it not bit-reproducible from run to run at 256 rows per expert (a few rows per call off by up to 6e-2,
+    // inside the reference tolerance but a race: the relay / remote-arrive chain of umma_pair.cuh orders the
+    // peer CTA's cp.async rows at CTA scope only).  It stays available as SGLB_PATH_UMMA2 until that is fixed.
+    if (false && path == SGLB_PATH_UMMA && p->fmt == SGLB_FMT_BF16 && rows_per_expert >= kPairMinRowsPerExpert)
       path = SGLB_PATH_UMMA2;
   }
   if (path == SGLB_PATH_UMMA || path == SGLB_PATH_UMMA2) {

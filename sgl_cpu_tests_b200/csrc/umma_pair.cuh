@@ -31,6 +31,13 @@ __device__ __forceinline__ void cluster_sync_all() {
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// Same arrive with cluster-scope release semantics: everything the arriving thread has observed (the peer's
+// cp.async rows, through the CTA-scope barrier it waited on) is ordered before the arrive for the whole
+// cluster.  Used by the relay warp, which has nothing else to do, so the membar it costs is off the critical path;
+// the leader's wait stays a plain (CTA-scope) wait.
+__device__ __forceinline__ void mbar_arrive_cluster_release(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 // TMA load whose completion bytes are counted on a barrier of the pair's leader CTA
 __device__ __forceinline__ void tma_load_3d_pair(uint32_t dst, const CUtensorMap* map, uint32_t leader_bar,
                                                  int c0, int c1, int c2) {

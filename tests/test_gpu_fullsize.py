@@ -1,0 +1,150 @@
+"""Full-size parity at the BASELINE.json shapes through size-independent properties (the oracle cannot run
+E x [2I, H] matmuls at these sizes in seconds):
+
+  * routers: ids bit-exact against the (vectorised) oracle at the full token counts;
+  * align: sortedness / inverse permutation / counts of the index layout at S = 65536 slots;
+  * fused_experts: exact linearity in a power-of-two scaling of the top-k weights, exact equivariance under a
+    permutation of the tokens, a masked slot (id -1) equals a zero weight, the two GEMM paths agree within the
+    reference tolerance, and a handful of sampled tokens agree with the oracle evaluated on those tokens only.
+
+Weights are generated on the device (up to 11.3 GB for the DeepSeek-V3 layer).  Run with -m gpu."""
+import math
+
+import pytest
+import torch
+
+from oracle import moe_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+TOL = dict(rtol=1e-2, atol=1e-2)  # utils.py:3-12 of the reference
+
+
+@pytest.fixture(scope="module")
+def K():
+    import sgl_cpu_tests_b200 as K
+    assert torch.cuda.is_available()
+    return K
+
+
+def routing(M, E, topk, seed):
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    score = torch.softmax(torch.randn(M, E, device=DEV, generator=g), dim=-1)
+    w, ids = torch.topk(score, topk)
+    return w.contiguous(), ids.to(torch.int32).contiguous()
+
+
+def make_layer(fmt, E, H, I, seed=5):
+    g = torch.Generator(device=DEV).manual_seed(seed)
+
+    def rnd(*s):
+        return torch.randn(*s, device=DEV, generator=g, dtype=torch.bfloat16)
+    if fmt == "bf16":
+        return dict(w1=rnd(E, 2 * I, H) / 8, w2=rnd(E, H, I) / 8, s1=None, s2=None, block=None)
+    if fmt == "int8":
+        w1 = torch.randint(-127, 128, (E, 2 * I, H), device=DEV, generator=g, dtype=torch.int8)
+        w2 = torch.randint(-127, 128, (E, H, I), device=DEV, generator=g, dtype=torch.int8)
+        return dict(w1=w1, w2=w2, s1=torch.rand(E, 2 * I, device=DEV, generator=g) * 1e-3 + 1e-4,
+                    s2=torch.rand(E, H, device=DEV, generator=g) * 1e-3 + 1e-4, block=None)
+    if fmt == "fp8":
+        w1 = torch.empty(E, 2 * I, H, device=DEV, dtype=torch.float8_e4m3fn)
+        w2 = torch.empty(E, H, I, device=DEV, dtype=torch.float8_e4m3fn)
+        for e in range(E):  # per expert: the bf16 staging of a whole DSV3 layer would be 22 GB
+            w1[e] = (rnd(2 * I, H) * 200).clamp(-400, 400).to(torch.float8_e4m3fn)
+            w2[e] = (rnd(H, I) * 200).clamp(-400, 400).to(torch.float8_e4m3fn)
+        # O(1) intermediates: |w| ~ 200, x ~ 1/sqrt(H) -> stage-1 sums ~ 200 s1, stage-2 sums ~ sqrt(I) 0.5 200 s2
+        s1 = (torch.rand(E, 2 * I // 128, H // 128, device=DEV, generator=g) + 0.5) * 5e-3
+        s2 = (torch.rand(E, H // 128, I // 128, device=DEV, generator=g) + 0.5) * 2.5e-4
+        return dict(w1=w1, w2=w2, s1=s1, s2=s2, block=[128, 128])
+    raise ValueError(fmt)
+
+
+def call(K, layer, fmt_id, x, tw, ids, path=None):
+    kw = {} if path is None else {"path": path}
+    return K.fused_experts_impl(x, layer["w1"], layer["w2"], tw, ids, False, fmt_id, layer["s1"], layer["s2"],
+                                layer["block"], False, **kw)
+
+
+# ------------------------------------------------------------------------------------------ routers + align
+@pytest.mark.parametrize("M,E,G,topk,tg,biased", [(4096, 128, 1, 8, 1, False), (8192, 256, 8, 8, 4, True)])
+def test_router_full_size(K, M, E, G, topk, tg, biased):
+    torch.manual_seed(M)
+    gating = torch.randn(M, E)           # f32 logits: well separated, no tie rows (tests/test_oracle.py tie_rows)
+    bias = torch.randn(E) if biased else None
+    hs = torch.empty(M, 1, dtype=torch.bfloat16)
+    if biased:
+        w, ids = K.biased_grouped_topk(hs.cuda(), gating.cuda(), bias.cuda(), topk, True, G, tg)
+        rw, rids = O.biased_grouped_topk(gating, bias, topk, True, G, tg)
+    else:
+        w, ids = K.grouped_topk(hs.cuda(), gating.cuda(), topk, True, G, tg)
+        rw, rids = O.grouped_topk(gating, topk, True, G, tg)
+    assert torch.equal(ids.cpu(), rids.to(torch.int32))
+    torch.testing.assert_close(w.cpu(), rw, rtol=1e-5, atol=1e-6)
+
+
+def test_align_full_size_properties(K):
+    M, E, topk = 8192, 256, 8
+    _, ids = routing(M, E, topk, 3)
+    ids[::7, 3] = -1                      # masked slots (test_moe_offloading_cpu.py:57-68)
+    al = K.moe_align(ids, E)
+    S = M * topk
+    flat = ids.reshape(-1).cpu().long()
+    count = al["expert_count"].cpu().long()
+    assert torch.equal(count, torch.bincount(flat[flat >= 0], minlength=E))
+    nvalid = int(count.sum())
+    sorted_slot = al["sorted_slot"].cpu().long()[:nvalid]
+    experts = flat[sorted_slot]
+    key = experts * S + sorted_slot       # stable by (expert, slot): strictly increasing
+    assert bool((key[1:] > key[:-1]).all())
+    pos = al["slot_pos"].cpu().long()
+    assert bool((pos[flat < 0] == -1).all())
+    assert torch.equal(sorted_slot[pos[flat >= 0]], torch.nonzero(flat >= 0).squeeze(1))
+
+
+# ------------------------------------------------------------------------------------------ fused_experts
+CASES = [("bf16", 128, 8, 2048, 768, 4096), ("int8", 128, 8, 2048, 768, 4096), ("fp8", 256, 8, 7168, 2048, 512)]
+
+
+@pytest.mark.parametrize("fmt,E,topk,H,I,M", CASES)
+def test_fused_experts_full_size_properties(K, fmt, E, topk, H, I, M):
+    fmt_id = {"bf16": K.FMT_BF16, "int8": K.FMT_INT8_W8A8, "fp8": K.FMT_FP8_W8A16}[fmt]
+    layer = make_layer(fmt, E, H, I)
+    g = torch.Generator(device=DEV).manual_seed(9)
+    x = torch.randn(M, H, device=DEV, generator=g, dtype=torch.bfloat16) / (4 if fmt != "fp8" else math.sqrt(H))
+    tw, ids = routing(M, E, topk, 9)
+    out = call(K, layer, fmt_id, x, tw, ids)
+    assert bool(torch.isfinite(out.float()).all()) and float(out.float().abs().max()) > 0
+
+    # (1) power-of-two scaling of the top-k weights is exact through the f32 sum and the bf16 rounding
+    assert torch.equal(call(K, layer, fmt_id, x, tw * 2.0, ids).float(), out.float() * 2.0)
+
+    # (2) token permutation: every row is computed from its own operands in a fixed order
+    perm = torch.randperm(M, device=DEV, generator=g)
+    assert torch.equal(call(K, layer, fmt_id, x[perm].contiguous(), tw[perm].contiguous(), ids[perm].contiguous()),
+                       out[perm])
+
+    # (3) a masked slot contributes exactly what a zero weight contributes
+    ids_m, tw_z = ids.clone(), tw.clone()
+    ids_m[::3, 1] = -1
+    tw_z[::3, 1] = 0.0
+    assert torch.equal(call(K, layer, fmt_id, x, tw, ids_m), call(K, layer, fmt_id, x, tw_z, ids))
+
+    # (4) weight-streaming kernel vs tcgen05 kernel on the same problem (a 256-token slice keeps the mma.sync path short)
+    sl = slice(0, 256)
+    a = call(K, layer, fmt_id, x[sl].contiguous(), tw[sl].contiguous(), ids[sl].contiguous(), path=K.PATH_STREAM)
+    b = call(K, layer, fmt_id, x[sl].contiguous(), tw[sl].contiguous(), ids[sl].contiguous(), path=K.PATH_UMMA)
+    scale = max(1e-6, float(a.float().abs().max()))   # tolerances relative to the output range
+    torch.testing.assert_close(a.float() / scale, b.float() / scale, **TOL)
+
+    # (5) sampled tokens against the oracle restricted to the experts those tokens use
+    rows = torch.tensor([0, M - 1] if fmt == "fp8" else [0, 1, M // 2, M - 1])  # fp8: 44 M weights per expert on the CPU
+    used = torch.unique(ids[rows.to(DEV)].cpu().long())
+    remap = torch.full((E,), -1, dtype=torch.long)
+    remap[used] = torch.arange(used.numel())
+    sub = {k: (v[used.to(DEV)].cpu() if isinstance(v, torch.Tensor) else v) for k, v in layer.items()}
+    ref = O.fused_experts(x[rows.to(DEV)].cpu(), sub["w1"], sub["w2"], tw[rows.to(DEV)].cpu(),
+                          remap[ids[rows.to(DEV)].cpu().long()].to(torch.int32), fmt, sub["s1"], sub["s2"], sub["block"])
+    got = out[rows.to(DEV)].float().cpu()
+    scale = max(1e-6, float(ref.float().abs().max()))
+    torch.testing.assert_close(got / scale, ref.float() / scale, **TOL)
