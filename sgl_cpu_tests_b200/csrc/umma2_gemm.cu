@@ -153,7 +153,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
           const int s = it % kStages2;
           mbar_wait(xfull_bar(s), (it / kStages2) & 1);
           fence_proxy_async();
-          if (elect_one()) mbar_arrive_cluster(mapa(full_bar(s), 0));
+          if (elect_one()) mbar_arrive_cluster_release(mapa(full_bar(s), 0));
           __syncwarp();
         }
       }

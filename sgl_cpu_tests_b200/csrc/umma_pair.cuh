@@ -22,7 +22,10 @@ __device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-// Remote arrive on a barrier of another CTA of the pair.  Deliberately without .release.cluster /
+// Remote arrive on a barrier of another CTA of the pair (TMEM hand-back by the epilogue warps: ordered by
+// tcgen05.wait::ld + tcgen05.fence).  NOT sufficient for the relay of the peer's cp.async rows -- see
+// mbar_arrive_cluster_release below; the text that follows records why the plain form was tried there.
+// Deliberately without .release.cluster /
 // .acquire.cluster on the waiting side: ptxas turns cluster-scope acquire into CCTL.IVALL (an L1
 // invalidate) and release into a full membar, which serialised every pipeline stage (~1.1 us per
 // stage, ncu r1f).  Nothing crosses the pair through the generic proxy here: the data the barriers
@@ -33,8 +36,12 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
 }
 // Same arrive with cluster-scope release semantics: everything the arriving thread has observed (the peer's
 // cp.async rows, through the CTA-scope barrier it waited on) is ordered before the arrive for the whole
-// cluster.  Used by the relay warp, which has nothing else to do, so the membar it costs is off the critical path;
-// the leader's wait stays a plain (CTA-scope) wait.
+// cluster; the leader's wait stays a plain (CTA-scope) wait.  Used by the relay warp.  Measured
+// (tools/dbg_pair_determinism.py, Qwen3 bf16 / int8, 256 rows per expert): with the plain arrive 1-20 rows per
+// 4096 differed from run to run; with this one 12 of 12 runs are bit-identical to the single-CTA kernel -- but
+// the membar serialises the relay at ~1 us per stage (bf16 M = 8192: 965 -> 440 TFLOP/s), so the pair kernels are
+// explicit-only until the peer's rows arrive through the async proxy (TMA gather4 with the completion counted on
+// the leader's barrier).
 __device__ __forceinline__ void mbar_arrive_cluster_release(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
