@@ -69,10 +69,19 @@ void sglb_set_fp8_native(int on);
  * grouped_topk_cpu          (test_grouped_topk.py:61-69, test_moe.py:61-70)  : bias == NULL
  * biased_grouped_topk_cpu   (test_biased_grouped_topk.py:71-80)              : bias != NULL
  * gating [M,E] (gating_dtype), bias [E] (bias_dtype); out topk_weights [M,topk] f32,
- * topk_ids [M,topk] i32, picks in descending score order, ties to the lowest expert index. */
+ * topk_ids [M,topk] i32, picks in descending score order, ties to the lowest expert index.
+ * The biased variant's sigmoid is the correctly rounded one, (float)(1/(1+exp(-(double)x))), so ids and
+ * weights are bit-reproducible by the CPU oracle (csrc/router.cu header).
+ * Serving arguments of the 9-argument form (test_moe.py:61-70; the reference always passes 0, None, None):
+ *   num_fused_shared_experts n > 0: the last of the topk slots becomes the fused shared expert,
+ *     id = E + (token % n), weight = (sum of routed weights) / routed_scaling_factor; renormalisation
+ *     divides by the routed sum only.  routed_scaling_factor is used for that slot only.
+ *   num_token_non_padded: device scalar (int32, or int64 when non_padded_is_i64) or NULL; rows at and past
+ *     it get ids = -1 and weights = 0. */
 int sglb_grouped_topk(const void* gating, int gating_dtype, const void* bias, int bias_dtype,
                       int64_t M, int E, int topk, int num_expert_group, int topk_group,
-                      int renormalize, float routed_scaling_factor, float* topk_weights,
+                      int renormalize, int num_fused_shared_experts, float routed_scaling_factor,
+                      const void* num_token_non_padded, int non_padded_is_i64, float* topk_weights,
                       int32_t* topk_ids, sglb_stream_t stream);
 
 /* ---- K2 moe_align -----------------------------------------------------------------------------

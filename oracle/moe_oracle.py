@@ -196,7 +196,51 @@ def _topk_lowest_index(scores, k):
     return torch.gather(scores, -1, ids), ids
 
 
-def grouped_topk(gating_output, topk, renormalize, num_expert_group, topk_group):
+def sigmoid_cr(x):
+    """The build's sigmoid contract: the correctly rounded f32 sigmoid, evaluated in f64 and rounded once,
+    (float)(1 / (1 + exp(-(double)x))) -- the same expression csrc/router.cu evaluates.  The reference's oracle
+    calls `gating_output.sigmoid()` (test_biased_grouped_topk.py:22); torch's f32 CPU sigmoid is a ~1-ulp
+    approximation that differs from this value on ~30 % of inputs by one ulp, which no other implementation can
+    reproduce bit for bit.  tests/test_oracle.py counts the rows whose ids differ between the two definitions."""
+    return (1.0 / (1.0 + torch.exp(-x.double()))).float()
+
+
+def _seq_sum(w):
+    """f32 sum over the last dim in index order (the router kernel adds its picks one by one)."""
+    acc = w[..., 0].clone()
+    for j in range(1, w.shape[-1]):
+        acc = acc + w[..., j]
+    return acc.unsqueeze(-1)
+
+
+def _serving_args(w, ids, E, renormalize, num_fused_shared_experts, routed_scaling_factor, num_token_non_padded):
+    """Last three arguments of the 9-argument router call (test_moe.py:61-70 passes 0, None, None).  Semantics of
+    sglang's python router ([UPSTREAM-MEMORY] sglang/srt/layers/moe/topk.py) -- PARITY UNPINNED, the reference
+    never exercises them: with n fused shared experts the last slot becomes id E + (token % n) (sglang draws the
+    replica at random; a fixed rule here) with weight sum(routed) / routed_scaling_factor, renormalisation divides
+    by the routed sum only; rows >= num_token_non_padded get ids -1 (and weight 0 here)."""
+    n = int(num_fused_shared_experts or 0)
+    rsf = 1.0 if routed_scaling_factor is None else float(routed_scaling_factor)
+    w = w.to(torch.float32)
+    ids = ids.to(torch.int32)
+    routed = w[:, :-1] if n > 0 else w
+    wsum = _seq_sum(routed)
+    if n > 0:
+        w = w.clone()
+        ids = ids.clone()
+        w[:, -1:] = wsum / torch.tensor(rsf, dtype=torch.float32)
+        ids[:, -1] = (E + torch.arange(ids.shape[0]) % n).to(torch.int32)
+    if renormalize:
+        w = w / wsum
+    if num_token_non_padded is not None:
+        pad = torch.arange(ids.shape[0]) >= int(num_token_non_padded)
+        ids = ids.masked_fill(pad.unsqueeze(-1), -1)
+        w = w.masked_fill(pad.unsqueeze(-1), 0.0)
+    return w, ids
+
+
+def grouped_topk(gating_output, topk, renormalize, num_expert_group, topk_group, num_fused_shared_experts=0,
+                 routed_scaling_factor=None, num_token_non_padded=None):
     """test_grouped_topk.py:9-39 with the tie-break made explicit.  gating_output: any float dtype,
     math in f32 (the script feeds .float() inputs, :49-50)."""
     scores = torch.softmax(gating_output.float(), dim=-1)
@@ -209,14 +253,15 @@ def grouped_topk(gating_output, topk, renormalize, num_expert_group, topk_group)
     score_mask = group_mask.unsqueeze(-1).expand(n, G, E // G).reshape(n, -1)
     tmp = scores.masked_fill(~score_mask.bool(), 0.0)
     w, ids = _topk_lowest_index(tmp, topk)
-    if renormalize:
-        w = w / w.sum(dim=-1, keepdim=True)
-    return w.to(torch.float32), ids.to(torch.int32)
+    return _serving_args(w, ids, E, renormalize, num_fused_shared_experts, routed_scaling_factor, num_token_non_padded)
 
 
-def biased_grouped_topk(gating_output, correction_bias, topk, renormalize, num_expert_group, topk_group):
-    """test_biased_grouped_topk.py:9-47 with the tie-break made explicit."""
-    scores = gating_output.float().sigmoid()
+def biased_grouped_topk(gating_output, correction_bias, topk, renormalize, num_expert_group, topk_group,
+                        num_fused_shared_experts=0, routed_scaling_factor=None, num_token_non_padded=None,
+                        sigmoid=sigmoid_cr):
+    """test_biased_grouped_topk.py:9-47 with the tie-break made explicit and the sigmoid pinned to sigmoid_cr
+    (pass sigmoid=torch.sigmoid for the reference's literal expression)."""
+    scores = sigmoid(gating_output.float())
     n, E = scores.shape
     G = max(1, num_expert_group)
     choice = scores + correction_bias.float().unsqueeze(0)
@@ -232,9 +277,7 @@ def biased_grouped_topk(gating_output, correction_bias, topk, renormalize, num_e
     tmp = choice.masked_fill(~score_mask.bool(), float("-inf"))
     _, ids = _topk_lowest_index(tmp, topk)
     w = scores.gather(1, ids)
-    if renormalize:
-        w = w / w.sum(dim=-1, keepdim=True)
-    return w.to(torch.float32), ids.to(torch.int32)
+    return _serving_args(w, ids, E, renormalize, num_fused_shared_experts, routed_scaling_factor, num_token_non_padded)
 
 
 # ---------------------------------------------------------------------------------------------------

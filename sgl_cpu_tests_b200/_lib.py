@@ -58,7 +58,7 @@ SIGNATURES = {
     "sglb_mx4_tile_scales": (C.c_int, [_vp, _vp, _i64, C.c_int, C.c_int, C.c_int, _vp]),
     "sglb_profile_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_int), C.c_int]),
     "sglb_grouped_topk": (C.c_int, [_vp, C.c_int, _vp, C.c_int, _i64, C.c_int, C.c_int, C.c_int, C.c_int,
-                                    C.c_int, _f32, _vp, _vp, _vp]),
+                                    C.c_int, C.c_int, _f32, _vp, C.c_int, _vp, _vp, _vp]),
     "sglb_moe_align_scratch_bytes": (_sz, [_i64, C.c_int, C.c_int]),
     "sglb_moe_align_max_items": (_i64, [_i64, C.c_int, C.c_int, C.c_int]),
     "sglb_moe_align": (C.c_int, [_vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(AlignOut), _vp, _vp]),

@@ -6,6 +6,20 @@
 // Tie-break rule (the reference leaves it open): among equal scores the lowest
 // index wins; picks are emitted in descending score order.  oracle/moe_oracle.py states the
 // same rule and the tests hold this kernel bit-exact on ids to it.
+//
+// Sigmoid contract (biased variant): s = (float)(1.0 / (1.0 + exp(-(double)x))), the correctly rounded f32
+// sigmoid, evaluated in f64 and rounded once.  The reference's oracle calls torch's f32 sigmoid, whose CPU
+// implementation is only ~1 ulp accurate (it differs from the correctly rounded value on ~30 % of inputs), so
+// no second implementation can reproduce it bit for bit; the f64 definition can be evaluated identically on
+// both sides (oracle/moe_oracle.py:sigmoid_cr) and makes ids AND weights of the biased router bit-exact.
+//
+// Serving arguments of the 9-argument call (test_moe.py:61-70; semantics from sglang's python router, not
+// pinned by the reference): num_fused_shared_experts n > 0 makes the LAST of the topk slots the fused shared
+// expert: id = E + (token % n), weight = (sum of the routed weights) / routed_scaling_factor, and the
+// renormalisation divides by the routed sum only; num_token_non_padded (device scalar) masks rows at and
+// past it: ids = -1, weights = 0.  routed_scaling_factor is used for that slot only -- the op never
+// scales the routed weights (sglang asserts apply_routed_scaling_factor_on_output == False on this path;
+// shared_expert_cpu applies the factor).
 #include "common.cuh"
 
 namespace sglb {
@@ -51,11 +65,24 @@ template <int PER, typename TG, typename TB, bool BIASED>
 __global__ void __launch_bounds__(128) router_kernel(const TG* __restrict__ gating,
                                                     const TB* __restrict__ bias, int64_t M, int E,
                                                     int topk, int G, int topk_group, int renorm,
-                                                    float routed_scale, float* __restrict__ out_w,
+                                                    int n_shared, float routed_scale,
+                                                    const void* __restrict__ non_padded, int non_padded_i64,
+                                                    float* __restrict__ out_w,
                                                     int32_t* __restrict__ out_id) {
   const int lane = threadIdx.x & 31;
   const int64_t tok = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (tok >= M) return;
+  if (non_padded != nullptr) {
+    const int64_t n_valid = non_padded_i64 ? *reinterpret_cast<const int64_t*>(non_padded)
+                                           : (int64_t) * reinterpret_cast<const int32_t*>(non_padded);
+    if (tok >= n_valid) {  // padded row: every slot masked
+      if (lane < topk) {
+        out_w[tok * topk + lane] = 0.f;
+        out_id[tok * topk + lane] = -1;
+      }
+      return;
+    }
+  }
   const TG* row = gating + tok * E;
   const float NEG = -INFINITY;
 
@@ -89,7 +116,7 @@ __global__ void __launch_bounds__(128) router_kernel(const TG* __restrict__ gati
     for (int k = 0; k < PER; ++k) {
       int e = lane + 32 * k;
       if (e < E) {
-        s[k] = 1.0f / (1.0f + expf(-s[k]));
+        s[k] = (float)(1.0 / (1.0 + exp(-(double)s[k])));  // correctly rounded: see the file header
         c[k] = s[k] + load_as_float<TB>(bias + e);
       } else {
         s[k] = 0.f;
@@ -156,7 +183,8 @@ __global__ void __launch_bounds__(128) router_kernel(const TG* __restrict__ gati
   float wsum = 0.f;
   float my_w = 0.f;
   int my_id = 0;
-  for (int r = 0; r < topk; ++r) {
+  const int routed = n_shared > 0 ? topk - 1 : topk;
+  for (int r = 0; r < routed; ++r) {
     float bv = NEG;
     int bi = 0x7fffffff;
 #pragma unroll
@@ -187,8 +215,11 @@ __global__ void __launch_bounds__(128) router_kernel(const TG* __restrict__ gati
   }
   if (lane < topk) {
     float w = my_w;
+    if (n_shared > 0 && lane == topk - 1) {
+      w = wsum / routed_scale;
+      my_id = E + (int)(tok % n_shared);
+    }
     if (renorm) w = w / wsum;
-    w *= routed_scale;
     out_w[tok * topk + lane] = w;
     out_id[tok * topk + lane] = my_id;
   }
@@ -196,15 +227,16 @@ __global__ void __launch_bounds__(128) router_kernel(const TG* __restrict__ gati
 
 template <typename TG, typename TB, bool BIASED>
 static int launch_router(const void* gating, const void* bias, int64_t M, int E, int topk, int G,
-                         int topk_group, int renorm, float routed_scale, float* out_w,
+                         int topk_group, int renorm, int n_shared, float routed_scale,
+                         const void* non_padded, int non_padded_i64, float* out_w,
                          int32_t* out_id, cudaStream_t stream) {
   const int warps = 4;
   dim3 grid((unsigned)ceil_div64(M, warps)), block(warps * 32);
   const int per = ceil_div(E, 32);
 #define SGLB_ROUTER_CASE(P)                                                                      \
   router_kernel<P, TG, TB, BIASED><<<grid, block, 0, stream>>>(                                  \
-      (const TG*)gating, (const TB*)bias, M, E, topk, G, topk_group, renorm, routed_scale, out_w, \
-      out_id)
+      (const TG*)gating, (const TB*)bias, M, E, topk, G, topk_group, renorm, n_shared, routed_scale, \
+      non_padded, non_padded_i64, out_w, out_id)
   if (per <= 1) SGLB_ROUTER_CASE(1);
   else if (per <= 2) SGLB_ROUTER_CASE(2);
   else if (per <= 4) SGLB_ROUTER_CASE(4);
@@ -219,18 +251,19 @@ static int launch_router(const void* gating, const void* bias, int64_t M, int E,
 
 template <typename TG, bool BIASED>
 static int dispatch_bias(int bias_dtype, const void* gating, const void* bias, int64_t M, int E,
-                         int topk, int G, int topk_group, int renorm, float routed_scale,
-                         float* out_w, int32_t* out_id, cudaStream_t stream) {
+                         int topk, int G, int topk_group, int renorm, int n_shared, float routed_scale,
+                         const void* non_padded, int non_padded_i64, float* out_w, int32_t* out_id,
+                         cudaStream_t stream) {
   switch (bias_dtype) {
     case SGLB_DT_BF16:
-      return launch_router<TG, __nv_bfloat16, BIASED>(gating, bias, M, E, topk, G, topk_group,
-                                                      renorm, routed_scale, out_w, out_id, stream);
+      return launch_router<TG, __nv_bfloat16, BIASED>(gating, bias, M, E, topk, G, topk_group, renorm, n_shared,
+                                                      routed_scale, non_padded, non_padded_i64, out_w, out_id, stream);
     case SGLB_DT_F32:
-      return launch_router<TG, float, BIASED>(gating, bias, M, E, topk, G, topk_group, renorm,
-                                              routed_scale, out_w, out_id, stream);
+      return launch_router<TG, float, BIASED>(gating, bias, M, E, topk, G, topk_group, renorm, n_shared,
+                                              routed_scale, non_padded, non_padded_i64, out_w, out_id, stream);
     case SGLB_DT_F16:
-      return launch_router<TG, __half, BIASED>(gating, bias, M, E, topk, G, topk_group, renorm,
-                                               routed_scale, out_w, out_id, stream);
+      return launch_router<TG, __half, BIASED>(gating, bias, M, E, topk, G, topk_group, renorm, n_shared,
+                                               routed_scale, non_padded, non_padded_i64, out_w, out_id, stream);
   }
   set_error("router: unsupported bias dtype %d", bias_dtype);
   return SGLB_ERR_INVALID;
@@ -242,12 +275,18 @@ using namespace sglb;
 
 extern "C" int sglb_grouped_topk(const void* gating, int gating_dtype, const void* bias,
                                  int bias_dtype, int64_t M, int E, int topk, int num_expert_group,
-                                 int topk_group, int renormalize, float routed_scaling_factor,
-                                 float* topk_weights, int32_t* topk_ids, sglb_stream_t stream_) {
+                                 int topk_group, int renormalize, int num_fused_shared_experts,
+                                 float routed_scaling_factor, const void* num_token_non_padded,
+                                 int non_padded_is_i64, float* topk_weights, int32_t* topk_ids,
+                                 sglb_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   SGLB_CHECK(M >= 0 && E > 0, "router: bad shape M=%lld E=%d", (long long)M, E);
   SGLB_CHECK(E <= 32 * kMaxPerLane, "router: E=%d exceeds %d", E, 32 * kMaxPerLane);
-  SGLB_CHECK(topk >= 1 && topk <= 32 && topk <= E, "router: topk=%d must be in [1, min(32,E)]", topk);
+  const int n_shared = num_fused_shared_experts;
+  SGLB_CHECK(n_shared >= 0, "router: num_fused_shared_experts=%d must be >= 0", n_shared);
+  SGLB_CHECK(topk >= 1 && topk <= 32 && topk - (n_shared > 0) <= E && topk - (n_shared > 0) >= 1,
+             "router: topk=%d must be in [1, min(32,E)] (one more slot with fused shared experts)", topk);
+  SGLB_CHECK(n_shared == 0 || routed_scaling_factor != 0.f, "router: routed_scaling_factor must not be 0");
   if (num_expert_group <= 0) num_expert_group = 1;
   if (topk_group <= 0) topk_group = num_expert_group;
   SGLB_CHECK(num_expert_group <= 32 && E % num_expert_group == 0,
@@ -259,11 +298,13 @@ extern "C" int sglb_grouped_topk(const void* gating, int gating_dtype, const voi
   const bool biased = bias != nullptr;
 #define SGLB_R(TG)                                                                                 \
   (biased ? dispatch_bias<TG, true>(bias_dtype, gating, bias, M, E, topk, num_expert_group,        \
-                                    topk_group, renormalize, routed_scaling_factor, topk_weights,  \
+                                    topk_group, renormalize, n_shared, routed_scaling_factor,      \
+                                    num_token_non_padded, non_padded_is_i64, topk_weights,         \
                                     topk_ids, stream)                                              \
           : launch_router<TG, float, false>(gating, nullptr, M, E, topk, num_expert_group,         \
-                                            topk_group, renormalize, routed_scaling_factor,        \
-                                            topk_weights, topk_ids, stream))
+                                            topk_group, renormalize, n_shared,                     \
+                                            routed_scaling_factor, num_token_non_padded,           \
+                                            non_padded_is_i64, topk_weights, topk_ids, stream))
   switch (gating_dtype) {
     case SGLB_DT_BF16: return SGLB_R(__nv_bfloat16);
     case SGLB_DT_F32: return SGLB_R(float);

@@ -288,24 +288,35 @@ def _mx4_weight(w_dev):
 
 # ---- K1: routers -----------------------------------------------------------------------------------------
 def _router(gating_output, correction_bias, topk, renormalize, num_expert_group, topk_group,
-            routed_scaling_factor, out_w=None, out_ids=None):
+            num_fused_shared_experts=0, routed_scaling_factor=None, num_token_non_padded=None,
+            out_w=None, out_ids=None):
     if gating_output.dim() != 2:
         raise RuntimeError("grouped_topk: gating_output must be [num_tokens, num_experts]")
     if gating_output.dtype not in _DT:
         raise RuntimeError(f"grouped_topk: unsupported gating dtype {gating_output.dtype}")
     M, E = gating_output.shape
+    n_shared = int(num_fused_shared_experts or 0)
     dev = gating_output.device if gating_output.is_cuda else _device()
     with torch.cuda.device(dev):
         g = _to_dev(gating_output, dev)
         b = _to_dev(correction_bias, dev) if correction_bias is not None else None
         if b is not None and (b.dim() != 1 or b.numel() != E or b.dtype not in _DT):
             raise RuntimeError("biased_grouped_topk: correction_bias must be [num_experts] bf16/f16/f32")
+        npad, npad64 = None, 0
+        if num_token_non_padded is not None:
+            npad = num_token_non_padded
+            if not torch.is_tensor(npad):
+                npad = torch.tensor([int(npad)], dtype=torch.int32)
+            if npad.numel() != 1 or npad.dtype not in (torch.int32, torch.int64):
+                raise RuntimeError("grouped_topk: num_token_non_padded must hold one int32 / int64 value")
+            npad = _to_dev(npad, dev)
+            npad64 = int(npad.dtype == torch.int64)
         w = torch.empty(M, topk, dtype=torch.float32, device=dev)
         ids = torch.empty(M, topk, dtype=torch.int32, device=dev)
         L.check(L.load().sglb_grouped_topk(
             g.data_ptr(), _DT[g.dtype], _ptr(b), _DT[b.dtype] if b is not None else 0, M, E, int(topk),
-            int(num_expert_group), int(topk_group), int(bool(renormalize)),
-            float(1.0 if routed_scaling_factor is None else routed_scaling_factor),
+            int(num_expert_group), int(topk_group), int(bool(renormalize)), n_shared,
+            float(1.0 if routed_scaling_factor is None else routed_scaling_factor), _ptr(npad), npad64,
             w.data_ptr(), ids.data_ptr(), _stream()))
     if out_w is not None:
         out_w.copy_(w)
@@ -323,22 +334,20 @@ def _check_tokens(hidden_states, gating_output):
 
 def grouped_topk(hidden_states, gating_output, topk, renormalize, num_expert_group, topk_group,
                  num_fused_shared_experts=0, routed_scaling_factor=None, num_token_non_padded=None):
-    """grouped_topk_cpu, 9-arg functional form (test_moe.py:61-70) -> (topk_weights f32, topk_ids i32)."""
+    """grouped_topk_cpu, 9-arg functional form (test_moe.py:61-70) -> (topk_weights f32, topk_ids i32).
+    The last three arguments follow sglang's python router (csrc/router.cu header); the reference passes
+    0, None, None."""
     _check_tokens(hidden_states, gating_output)
-    if num_fused_shared_experts not in (0, None):
-        raise RuntimeError("grouped_topk: num_fused_shared_experts != 0 is not supported")
-    if num_token_non_padded is not None:
-        raise RuntimeError("grouped_topk: num_token_non_padded is not supported")
     return _router(gating_output, None, topk, renormalize, num_expert_group, topk_group,
-                   routed_scaling_factor)
+                   num_fused_shared_experts, routed_scaling_factor, num_token_non_padded)
 
 
 def grouped_topk_out(topk_weights, topk_ids, hidden_states, gating_output, topk, renormalize,
                      num_expert_group, topk_group):
     """grouped_topk_cpu, 8-arg out-variant (test_grouped_topk.py:57-69) -> None."""
     _check_tokens(hidden_states, gating_output)
-    return _router(gating_output, None, topk, renormalize, num_expert_group, topk_group, None,
-                   topk_weights, topk_ids)
+    return _router(gating_output, None, topk, renormalize, num_expert_group, topk_group,
+                   out_w=topk_weights, out_ids=topk_ids)
 
 
 def biased_grouped_topk(hidden_states, gating_output, correction_bias, topk, renormalize,
@@ -346,18 +355,16 @@ def biased_grouped_topk(hidden_states, gating_output, correction_bias, topk, ren
                         routed_scaling_factor=None, num_token_non_padded=None):
     """biased_grouped_topk_cpu, functional form (by analogy with grouped_topk_cpu)."""
     _check_tokens(hidden_states, gating_output)
-    if num_fused_shared_experts not in (0, None) or num_token_non_padded is not None:
-        raise RuntimeError("biased_grouped_topk: fused shared experts / token padding are not supported")
     return _router(gating_output, correction_bias, topk, renormalize, num_expert_group, topk_group,
-                   routed_scaling_factor)
+                   num_fused_shared_experts, routed_scaling_factor, num_token_non_padded)
 
 
 def biased_grouped_topk_out(topk_weights, topk_ids, hidden_states, gating_output, correction_bias, topk,
                             renormalize, num_expert_group, topk_group):
     """biased_grouped_topk_cpu, 9-arg out-variant (test_biased_grouped_topk.py:67-80) -> None."""
     _check_tokens(hidden_states, gating_output)
-    return _router(gating_output, correction_bias, topk, renormalize, num_expert_group, topk_group, None,
-                   topk_weights, topk_ids)
+    return _router(gating_output, correction_bias, topk, renormalize, num_expert_group, topk_group,
+                   out_w=topk_weights, out_ids=topk_ids)
 
 
 # ---- K2: moe_align (exposed for tests and the expert-parallel layer) -------------------------------------

@@ -69,31 +69,77 @@ def test_grouped_topk_out_variant_and_golden(K):
             assert torch.equal(ids, id_o)
             assert torch.allclose(w, w_o, rtol=1e-5, atol=1e-7)
             assert torch.allclose(dense(ids, w, c["E"]), dense(c["ref_ids"], c["ref_weights"], c["E"]), rtol=1e-5, atol=1e-6)
+        else:
+            # bf16 logits x 2M (test_grouped_topk.py:44-46) saturate the softmax: picks with a live probability are
+            # bit-exact; picks whose probability underflowed are ties at zero, which both sides break identically
+            # unless expf underflows one element earlier on one side.  The weights must agree either way.
+            live = (w_o > 1e-30) & (w > 1e-30)
+            assert torch.equal(ids[live], id_o[live])
+            assert torch.allclose(dense(ids, w, c["E"]), dense(id_o, w_o, c["E"]), rtol=1e-4, atol=1e-6)
+
+
+BIASED_SHAPES = [(122, 256, 8, 8, 2), (33, 64, 4, 4, 2), (7, 32, 8, 3, 3), (2048, 256, 8, 8, 4), (8192, 256, 8, 8, 4),
+                 (100, 384, 1, 8, 1)]
 
 
 @pytest.mark.parametrize("renorm", [True, False])
-def test_biased_grouped_topk(K, renorm):
+def test_biased_grouped_topk_bit_exact(K, renorm):
+    """ids, their order AND the weights are bit-exact: both sides evaluate the correctly rounded sigmoid
+    (csrc/router.cu header, O.sigmoid_cr), one f32 add for the bias, the same tie-break and the same f32 sum order."""
     torch.manual_seed(1111)
-    for (M, E, G, topk, tg) in [(122, 256, 8, 8, 2), (33, 64, 4, 4, 2), (7, 32, 8, 3, 3), (2048, 256, 8, 8, 4)]:
-        for dt in (torch.float32, torch.bfloat16):
-            gating = torch.randn(M, E, dtype=dt)
+    for (M, E, G, topk, tg) in BIASED_SHAPES:
+        for dt, scale in ((torch.float32, 1.0), (torch.bfloat16, 1.0), (torch.bfloat16, 2.0 * M)):
+            gating = torch.randn(M, E, dtype=dt) * scale       # last style: test_biased_grouped_topk.py:53-55
             bias = torch.randn(E, dtype=dt)
             w_ref, id_ref = O.biased_grouped_topk(gating, bias, topk, renorm, G, tg)
             w = torch.empty(M, topk, dtype=torch.float32)
             ids = torch.empty(M, topk, dtype=torch.int32)
             K.biased_grouped_topk_out(w, ids, torch.zeros(M, 4), gating, bias, topk, renorm, G, tg)
-            # sigmoid + bias is not monotone-safe across two exp implementations: a 1-ulp difference can
-            # flip a near-tie.  f32 logits: at most a stray row; bf16 logits collide far more often.
-            mism = (ids != id_ref).any(dim=1).float().mean()
-            assert mism <= (0.01 if dt == torch.float32 else 0.25), float(mism)
-            ok = (ids == id_ref).all(dim=1)
-            assert torch.allclose(w[ok], w_ref[ok], rtol=1e-5, atol=1e-7)
+            assert torch.equal(ids, id_ref), (M, E, dt, scale, int((ids != id_ref).any(dim=1).sum()))
+            assert torch.equal(w, w_ref), (M, E, dt, scale, float((w - w_ref).abs().max()))
+
+
+def test_biased_grouped_topk_golden(K):
+    """The reference's own case (bf16 logits x 2M, bf16 bias, E 256 G 8 k 8 tg 2, M 122) and criterion
+    (dense scatter allclose, test_biased_grouped_topk.py:87-91), plus bit-equality with the oracle."""
     for c in load_golden("router_biased"):
-        if c["gating"].dtype != torch.float32:
-            continue
         w, ids = K.biased_grouped_topk(torch.zeros(c["M"], 4), c["gating"].cuda(), c["bias"].cuda(), c["topk"],
                                        c["renormalize"], c["G"], c["topk_group"])
-        assert torch.allclose(dense(ids, w, c["E"]), dense(c["ref_ids"], c["ref_weights"], c["E"]), rtol=1e-5, atol=1e-6)
+        w, ids = w.cpu(), ids.cpu()
+        w_o, id_o = O.biased_grouped_topk(c["gating"], c["bias"], c["topk"], c["renormalize"], c["G"], c["topk_group"])
+        assert torch.equal(ids, id_o) and torch.equal(w, w_o)
+        if c["gating"].dtype == torch.float32:
+            assert torch.allclose(dense(ids, w, c["E"]), dense(c["ref_ids"], c["ref_weights"], c["E"]), rtol=1e-5, atol=1e-6)
+
+
+def test_sigmoid_every_bf16_input(K):
+    """All 2^16 bf16 bit patterns (finite ones) through the biased router with zero bias, topk = E = 32, no
+    renormalisation: the returned weights are the kernel's sigmoid of each logit; bit-equal to O.sigmoid_cr."""
+    bits = torch.arange(0, 65536, dtype=torch.int32).to(torch.int16).view(torch.bfloat16)
+    gating = bits[torch.isfinite(bits.float())]
+    gating = gating[: gating.numel() // 32 * 32].view(-1, 32)
+    w, ids = K.biased_grouped_topk(torch.zeros(gating.shape[0], 4), gating.cuda(), torch.zeros(32).cuda(), 32, False, 1, 1)
+    got = torch.zeros(gating.shape, dtype=torch.float32).scatter_(1, ids.long().cpu(), w.cpu())
+    assert torch.equal(got, O.sigmoid_cr(gating.float()))
+
+
+def test_router_serving_args(K):
+    """num_fused_shared_experts / routed_scaling_factor / num_token_non_padded of the 9-argument call
+    (test_moe.py:61-70); parity unpinned, oracle = O._serving_args."""
+    torch.manual_seed(5)
+    M, E = 37, 64
+    g, b = torch.randn(M, E, dtype=torch.bfloat16), torch.randn(E, dtype=torch.bfloat16)
+    hs = torch.zeros(M, 4)
+    for renorm in (True, False):
+        for nfs, rsf, npad in ((0, 2.5, None), (1, 2.5, None), (2, None, torch.tensor([30])), (0, None, torch.tensor(5, dtype=torch.int64)),
+                               (1, 16.0, 11)):
+            topk = 4 + (nfs > 0)
+            w, ids = K.biased_grouped_topk(hs, g.cuda(), b.cuda(), topk, renorm, 4, 2, nfs, rsf, npad if npad is None or isinstance(npad, int) else npad.cuda())
+            w_o, id_o = O.biased_grouped_topk(g, b, topk, renorm, 4, 2, nfs, rsf, npad)
+            assert torch.equal(ids.cpu(), id_o) and torch.equal(w.cpu(), w_o), (renorm, nfs, rsf)
+            w, ids = K.grouped_topk(hs, g, topk, renorm, 4, 2, nfs, rsf, npad)
+            w_o, id_o = O.grouped_topk(g, topk, renorm, 4, 2, nfs, rsf, npad)
+            assert torch.equal(ids, id_o) and torch.allclose(w, w_o, rtol=1e-5, atol=1e-7), (renorm, nfs, rsf)
 
 
 # ------------------------------------------------------------------------------------------ moe_align

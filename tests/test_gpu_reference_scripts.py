@@ -1,0 +1,23 @@
+"""The reference's own scripts, unmodified, against the drop-in package (tools/run_reference_scripts.py).
+Needs the reference checkout: $SGLB_REFERENCE, ./baseline/_ref (git-ignored scratch that travels to the GPU box) or
+/root/reference; skipped when none of them holds the scripts."""
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+import run_reference_scripts as R  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+REF = R.find_reference(None)
+
+
+@pytest.mark.skipif(REF is None, reason="reference scripts not available (set SGLB_REFERENCE)")
+@pytest.mark.parametrize("script", [t[0] for t in R.TESTS])
+def test_reference_script_passes_unmodified(script):
+    rc, out, err, verdicts, _ = R.run_script(REF, script, 900)
+    assert rc == 0, err[-2000:]
+    assert verdicts, f"{script} printed no verdict:\n{out[-2000:]}"
+    assert all(verdicts), f"{script}: {verdicts.count(False)} of {len(verdicts)} comparisons printed False:\n{out[-3000:]}"
