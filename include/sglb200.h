@@ -130,6 +130,22 @@ typedef struct sglb_moe_problem {
    * (split = I for w13, 0 for w2); with them the GEMMs run on the block-scaled fp4 tensor cores */
   const void* w13_scale_tiles;
   const void* w2_scale_tiles;
+  /* 17-argument vintage (on-box vllm cpu_moe.py:308-326; gpt-oss): optional per-expert f32 biases added to the
+   * dequantised GEMM results -- w13_bias [E,2I] before the activation, w2_bias [E,H] before the topk weight --
+   * and the activation: act 0 = silu(gate)*up, act 1 = clamped swiglu g*sigmoid(alpha*g)*(u+1) with
+   * g = min(gate,limit), u = clamp(up,-limit,limit) (limit <= 0: no clamp).  Gate = rows [0,I), up = rows [I,2I). */
+  const float* w13_bias;
+  const float* w2_bias;
+  int32_t act;
+  float alpha, limit;
+  /* Slot-addressed output (expert-parallel return path): when slot_out != NULL stage 2 writes the bf16 row of
+   * routed slot s = token*topk + j to row s of slot_out (row slot_map[s] when slot_map != NULL) and the top-k
+   * reduce is skipped; rows of masked slots are not written; `out` may be NULL.  The caller reduces a token's
+   * rows in slot order (sglb_topk_reduce's arithmetic), which makes n-GPU results identical to one GPU's. */
+  void* slot_out;
+  const int32_t* slot_map;
+  /* > 0: expected routed rows per expert for the AUTO path rule (default M*topk/E) */
+  float rows_per_expert_hint;
 } sglb_moe_problem;
 
 size_t sglb_fused_experts_workspace_bytes(int64_t M, int topk, int E, int H, int I, int fmt);
@@ -150,7 +166,8 @@ typedef struct sglb_shared_problem {
   const void* w1_scale;
   const void* w2_scale;
   int32_t block_n, block_k;
-  const void* fused_out; /* [M,H] bf16 */
+  const void* fused_out; /* [M,H] bf16; NULL: out receives the MLP result alone (the caller applies
+                          * sglb_shared_axpy later, e.g. after an expert-parallel combine) */
   float routed_scaling_factor;
   void* out; /* [M,H] bf16, may alias hidden */
   void* workspace;
@@ -158,6 +175,9 @@ typedef struct sglb_shared_problem {
 } sglb_shared_problem;
 
 int sglb_shared_expert(const sglb_shared_problem* p, sglb_stream_t stream);
+/* the epilogue alone: out[i] = bf16(y[i] + fused[i] * routed_scaling_factor), n bf16 elements */
+int sglb_shared_axpy(const void* y, const void* fused, float routed_scaling_factor, int64_t n, void* out,
+                     sglb_stream_t stream);
 
 /* ---- mxfp4 scale tiles for the block-scaled tensor cores ----------------------------------------------
  * e8m0 scales [E, rows, K/32] (test_mxfp4.py:69-88 layout) -> 512-byte tiles of 128 rows x 4 k-groups in
@@ -239,48 +259,66 @@ int sglb_repack_scale(const void* src, void* dst, int64_t E, int64_t N, int64_t 
 /* ---- K8 expert-parallel dispatch / combine ---------------------------------------------------------
  * Nothing in the reference shards experts; its hook is that fused_experts_cpu ignores ids == -1
  * (test_moe_offloading_cpu.py:57-68), which is what a rank sees for experts it does not own.
- * Rank r owns experts [r*E/world, (r+1)*E/world).  These three kernels are the device side of the
- * exchange; the collective itself (NCCL all-to-all) is issued by the host layer (ep.py).
- *   plan:    dest_row[m*world + r] = row of token m in the segment sent to rank r (token order) or -1;
- *            send_count[r] = rows in that segment
- *   pack:    send_x[seg(r) + dest_row] = hidden[m];  send_meta[row] = {topk local ids (-1 if not owned
- *            by r), topk weights as f32 bits};  seg(r) = r*cap if cap > 0 (fixed-capacity exchange,
- *            padding rows read as all -1) else exclusive scan of send_count;  send_rows = total rows
- *            of the send buffers (cap*world, or sum of send_count)
- *   combine: out[m] = bf16( sum over r of ret[seg(r) + dest_row[m,r]] ), f32, rank order */
+ * Rank r owns experts [r*E/world, (r+1)*E/world).  These kernels are the device side of the exchange; the
+ * collective itself (NCCL all-to-all) is issued by the host layer (ep.py).  Token rows travel once per
+ * (token, owner rank); what comes back is one bf16 row per routed SLOT (the owner runs sglb_fused_experts with
+ * slot_out / slot_map), and the source adds a token's rows in slot order in f32 with one rounding, so the
+ * n-GPU result is bit-identical to the one-GPU result.
+ *   plan:      dest_row[m*world + r] = row of token m in the segment sent to rank r (token order) or -1;
+ *              send_count[r] = rows in that segment;  slot_index[m*topk + j] = index of slot (m, j) inside the
+ *              slot segment returned by its owner (slots of one owner numbered in (token, j) order) or -1;
+ *              send_slots[r] = slots owned by rank r
+ *   pack:      send_x[row_seg(r) + dest_row] = hidden[m];  send_meta[row] = {topk local ids (-1 if not owned
+ *              by r), topk weights as f32 bits};  send_rows = total rows of the send buffers
+ *   ret_index: (owner) ret_index[i*topk + j] = position of received slot (row i, j) in the return buffer, the
+ *              numbering the source computed in plan (-1 for masked slots); recv_ids rows are id_stride ints
+ *              apart (2*topk for the packed meta rows); recv_count / recv_slots [world]: rows / slots received
+ *              from each source (device arrays; NULL with a fixed capacity)
+ *   combine:   out[m] = bf16( sum_j ret[slot_seg(owner(m,j)) + slot_index[m,j]] ), f32, slot order; with
+ *              shared_y != NULL additionally out = bf16(shared_y[m] + that * routed_scaling_factor)
+ *   row_seg(r) = r*cap, slot_seg(r) = r*cap*topk when cap > 0 (fixed-capacity exchange, padding rows read as
+ *   all -1), else the exclusive scans of the row / slot counts (exact splits). */
 int sglb_ep_plan(const int32_t* topk_ids, int64_t M, int topk, int E, int world, int32_t* dest_row,
-                 int32_t* send_count, sglb_stream_t stream);
+                 int32_t* send_count, int32_t* slot_index, int32_t* send_slots, sglb_stream_t stream);
 int sglb_ep_pack(const void* hidden, const int32_t* topk_ids, const float* topk_weights,
                  const int32_t* dest_row, const int32_t* send_count, int64_t M, int topk, int E,
                  int world, int H, int cap, int64_t send_rows, void* send_x, int32_t* send_meta,
                  sglb_stream_t stream);
-int sglb_ep_combine(const void* ret, const int32_t* dest_row, const int32_t* send_count, int64_t M,
-                    int world, int H, int cap, void* out, sglb_stream_t stream);
+int sglb_ep_ret_index(const int32_t* recv_ids, int id_stride, int64_t recv_rows, int topk, int world, int cap,
+                      const int32_t* recv_count, const int32_t* recv_slots, int32_t* ret_index,
+                      sglb_stream_t stream);
+int sglb_ep_combine(const void* ret, const int32_t* topk_ids, const int32_t* slot_index,
+                    const int32_t* send_slots, int64_t M, int topk, int E, int world, int H, int cap,
+                    const void* shared_y, float routed_scaling_factor, void* out, sglb_stream_t stream);
 
 /* ---- K8, decode regime: the same exchange over NVLink peer memory (csrc/ep_p2p.cu) ---------------------
  * Every rank allocates one region (sglb_p2p_alloc: cudaMalloc + CUDA IPC handle), the 64-byte handles are
  * exchanged by the host layer and opened with sglb_p2p_open; peer_bases[r] is rank r's region as mapped in
- * this process (the rank's own allocation for r == rank).  `seq` counts calls (1, 2, ...) and must advance
- * identically on every rank; `cap` = slots per source rank (>= every rank's token count, equal on all ranks).
- *   dispatch:      stores rows / local ids / weights of this rank's M tokens into every peer's receive
- *                  buffers (slot rank*cap + m) and raises the per-source arrival flag on every peer
- *   wait_dispatch: returns (on the stream) once all `world` sources' rows of call seq have arrived
- *   (the caller then runs sglb_fused_experts over the world*cap received slots, output into the y buffer)
- *   combine:       raises the "partial rows ready" flag on every peer, waits for the owners of each token's
- *                  experts and sums their rows read over NVLink, rank order, f32 -> bf16 */
+ * this process (the rank's own allocation for r == rank).  Calls are counted on the device (the region holds
+ * the counter, advanced by dispatch), so the three kernels can sit in a CUDA graph; `parity` (0 / 1) selects
+ * the buffer set and must alternate call by call, identically on every rank; `cap` = slots per source rank
+ * (>= every rank's token count, equal on all ranks).
+ *   dispatch:      stores rows / local ids / weights of this rank's M tokens (M may be 0) into every peer's
+ *                  receive buffers (row rank*cap + m) and raises the per-source arrival flag on every peer
+ *   wait_dispatch: returns (on the stream) once all `world` sources' rows of this call have arrived
+ *   (the caller then runs sglb_fused_experts over the world*cap received rows with slot_out = the y buffer)
+ *   combine:       raises the "rows ready" flag on every peer, waits for the owners of each token's experts
+ *                  and adds the token's topk slot rows, read over NVLink, in slot order, f32 -> bf16
+ *                  (+ the shared expert epilogue as in sglb_ep_combine) */
 int sglb_p2p_alloc(size_t bytes, void** ptr, void* ipc_handle_64);
 int sglb_p2p_open(const void* ipc_handle_64, void** peer_ptr);
 int sglb_p2p_close(void* peer_ptr);
 int sglb_p2p_free(void* ptr);
-/* offsets[0..8) = recv_x[2], recv_ids[2], recv_weights[2], y[2] (index = seq & 1); returns the region size */
+/* offsets[0..8) = recv_x[2], recv_ids[2], recv_weights[2], y[2] (index = parity); y holds world*cap*topk rows;
+ * returns the region size */
 size_t sglb_ep_p2p_region_bytes(int world, int cap, int H, int topk, size_t* offsets);
 int sglb_ep_p2p_dispatch(const void* hidden, const int32_t* topk_ids, const float* topk_weights, int64_t M,
                          int topk, int E, int world, int rank, int H, int cap, void* const* peer_bases,
-                         uint32_t seq, sglb_stream_t stream);
-int sglb_ep_p2p_wait_dispatch(const void* local_base, int world, int cap, int H, int topk, uint32_t seq,
-                              sglb_stream_t stream);
+                         int parity, sglb_stream_t stream);
+int sglb_ep_p2p_wait_dispatch(const void* local_base, int world, int cap, int H, int topk, sglb_stream_t stream);
 int sglb_ep_p2p_combine(const int32_t* topk_ids, int64_t M, int topk, int E, int world, int rank, int H,
-                        int cap, void* const* peer_bases, uint32_t seq, void* out, sglb_stream_t stream);
+                        int cap, void* const* peer_bases, int parity, const void* shared_y,
+                        float routed_scaling_factor, void* out, sglb_stream_t stream);
 
 /* ---- building blocks exposed for tests and for the expert-parallel layer --------------------------
  * per-row dynamic int8 quantisation (test_moe_int8.py:23-31): q = round(x * 127/absmax), scale = absmax/127 */

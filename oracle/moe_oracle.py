@@ -336,19 +336,39 @@ def torch_naive_moe(a, w1, w2, topk_weight, topk_ids):
     return (out.view(B, -1, w2.shape[1]) * topk_weight.view(B, -1, 1).to(out.dtype)).sum(dim=1)
 
 
-def native_fused_moe(a, w1, w2, topk_weight, topk_ids):
+def swiglu_oai(x, alpha, limit):
+    """gpt-oss clamped swiglu (on-box vllm SwigluOAIAndMul.forward_native, activation.py:388-395) with the gate / up
+    halves laid out like every other format of this op (gate = first half, up = second half; the interleaved
+    checkpoint layout is a loader concern).  PARITY UNPINNED: no reference call site passes alpha / limit."""
+    d = x.shape[-1] // 2
+    gate, up = x[..., :d], x[..., d:]
+    if limit is not None and limit > 0:
+        gate = gate.clamp(min=None, max=limit)
+        up = up.clamp(min=-limit, max=limit)
+    return gate * torch.sigmoid(gate * (1.702 if alpha is None else alpha)) * (up + 1)
+
+
+def native_fused_moe(a, w1, w2, topk_weight, topk_ids, w1_bias=None, w2_bias=None, alpha=None, limit=None):
     """test_moe_fp8_ext.py:70-91 / test_moe_offloading_cpu.py:28-52: f32 everywhere, ids == -1 (or any
-    id without an expert) contribute zero rows; result cast to a.dtype."""
+    id without an expert) contribute zero rows; result cast to a.dtype.  The optional arguments are the
+    17-argument vintage (per-expert biases, clamped swiglu) -- parity unpinned, see swiglu_oai."""
     B, D = a.shape
     topk = topk_ids.shape[1]
     old = a.dtype
     a_rep = a.view(B, -1, D).repeat(1, topk, 1).reshape(-1, D).float()
     out = torch.zeros(B * topk, w2.shape[1], dtype=torch.float32)
+    oai = alpha is not None or limit is not None
     for i in range(w1.shape[0]):
         mask = _masked_rows(topk_ids, i)
         if mask.sum():
-            ic1 = silu_and_mul(torch.matmul(a_rep[mask], w1[i].float().transpose(0, 1)))
-            out[mask] = torch.matmul(ic1, w2[i].float().transpose(0, 1))
+            ic0 = torch.matmul(a_rep[mask], w1[i].float().transpose(0, 1))
+            if w1_bias is not None:
+                ic0 = ic0 + w1_bias[i].float()
+            ic1 = swiglu_oai(ic0, alpha, limit) if oai else silu_and_mul(ic0)
+            o = torch.matmul(ic1, w2[i].float().transpose(0, 1))
+            if w2_bias is not None:
+                o = o + w2_bias[i].float()
+            out[mask] = o
     return (out.view(B, -1, w2.shape[1]) * topk_weight.view(B, -1, 1).to(out.dtype)).sum(dim=1).to(old)
 
 
@@ -370,22 +390,47 @@ def torch_w8a8_per_column_moe(a, w1, w2, w1_s, w2_s, topk_weight, topk_ids):
     return (out.view(B, -1, w2.shape[1]) * topk_weight.view(B, -1, 1).to(out.dtype)).sum(dim=1).to(a.dtype)
 
 
-def fused_experts(a, w1, w2, topk_weight, topk_ids, fmt, w1_scale=None, w2_scale=None, block_size=None):
+def fused_experts(a, w1, w2, topk_weight, topk_ids, fmt, w1_scale=None, w2_scale=None, block_size=None, **extra):
     """One entry point per weight format; fmt in {"bf16", "int8", "fp8", "mxfp4"}.
-    Weights are row-major (unpacked)."""
+    Weights are row-major (unpacked).  extra: w1_bias, w2_bias, alpha, limit (17-argument vintage; not int8)."""
+    if extra and fmt == "int8":
+        raise ValueError("the int8 oracle has no bias / clamped-swiglu form")
     if fmt == "bf16":
-        return native_fused_moe(a, w1, w2, topk_weight, topk_ids)
+        return native_fused_moe(a, w1, w2, topk_weight, topk_ids, **extra)
     if fmt == "int8":
         return torch_w8a8_per_column_moe(a, w1, w2, w1_scale, w2_scale, topk_weight, topk_ids)
     if fmt == "fp8":
         bn, bk = block_size
         return native_fused_moe(a, scaled_weight(w1, w1_scale, bn, bk), scaled_weight(w2, w2_scale, bn, bk),
-                                topk_weight, topk_ids)
+                                topk_weight, topk_ids, **extra)
     if fmt == "mxfp4":
         w1d = mxfp4_dequantize(w1, torch.float32, w1_scale)
         w2d = mxfp4_dequantize(w2, torch.float32, w2_scale)
-        return native_fused_moe(a, w1d, w2d, topk_weight, topk_ids)
+        return native_fused_moe(a, w1d, w2d, topk_weight, topk_ids, **extra)
     raise ValueError(fmt)
+
+
+def fused_experts_lean(a, w1, w2, topk_weight, topk_ids, fmt, w1_scale=None, w2_scale=None, block_size=None):
+    """fused_experts with the weight-only formats dequantised PER ACTIVE EXPERT inside the loop instead of for the
+    whole [E, ...] tensor up front (a DeepSeek-V3 layer is 11 GB of e4m3: 45 GB as f32).  Same arithmetic, same
+    results bit for bit (tests/test_oracle.py); used by bench.py's CPU legs."""
+    if fmt in ("bf16", "int8"):
+        return fused_experts(a, w1, w2, topk_weight, topk_ids, fmt, w1_scale, w2_scale, block_size)
+    B, D = a.shape
+    topk = topk_ids.shape[1]
+    a_rep = a.view(B, -1, D).repeat(1, topk, 1).reshape(-1, D).float()
+    out = torch.zeros(B * topk, w2.shape[1], dtype=torch.float32)
+
+    def deq(w, s, i):
+        if fmt == "fp8":
+            return scaled_weight(w[i], s[i], block_size[0], block_size[1])
+        return mxfp4_dequantize(w[i], torch.float32, s[i])
+    for i in range(w1.shape[0]):
+        mask = _masked_rows(topk_ids, i)
+        if mask.sum():
+            ic1 = silu_and_mul(torch.matmul(a_rep[mask], deq(w1, w1_scale, i).transpose(0, 1)))
+            out[mask] = torch.matmul(ic1, deq(w2, w2_scale, i).transpose(0, 1))
+    return (out.view(B, -1, w2.shape[1]) * topk_weight.view(B, -1, 1).to(out.dtype)).sum(dim=1).to(a.dtype)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -454,26 +499,61 @@ def pack_scale(s):
 # fused_experts_cpu ignores ids == -1, test_moe_offloading_cpu.py:57-68.)
 
 
+def slot_rows(a, w1, w2, topk_weight, topk_ids):
+    """One bf16 row per routed slot, [B * topk, H]: bf16(f32(W2[e] . silu_and_mul(W1[e] . x)) * weight) -- what a
+    single GPU holds in its ic2 buffer before the top-k reduce.  Rows of masked slots are zero.  f32 weights."""
+    B, D = a.shape
+    topk = topk_ids.shape[1]
+    a_rep = a.view(B, -1, D).repeat(1, topk, 1).reshape(-1, D).float()
+    out = torch.zeros(B * topk, w2.shape[1], dtype=torch.float32)
+    for i in range(w1.shape[0]):
+        mask = _masked_rows(topk_ids, i)
+        if mask.sum():
+            ic1 = silu_and_mul(torch.matmul(a_rep[mask], w1[i].float().transpose(0, 1)))
+            out[mask] = torch.matmul(ic1, w2[i].float().transpose(0, 1))
+    return (out * topk_weight.reshape(-1, 1).float()).to(a.dtype)
+
+
+def reduce_slots(rows, topk_ids, num_experts):
+    """csrc/misc.cu topk_reduce: out[m] = bf16(sum_j f32(rows[m, j])) over valid slots, j ascending."""
+    B, topk = topk_ids.shape
+    acc = torch.zeros(B, rows.shape[-1], dtype=torch.float32)
+    r = rows.view(B, topk, rows.shape[-1])
+    for j in range(topk):
+        ok = (topk_ids[:, j] >= 0) & (topk_ids[:, j] < num_experts)
+        acc[ok] += r[ok, j].float()
+    return acc.to(rows.dtype)
+
+
 def ep_plan(topk_ids, num_experts, world):
-    """dest_row[m, r] = index of token m in the segment sent to rank r (token order) or -1;
-    send_count[r] = rows in that segment.  Rank r owns experts [r*E/world, (r+1)*E/world)."""
-    M = topk_ids.shape[0]
+    """dest_row[m, r] = index of token m in the row segment sent to rank r (token order) or -1;
+    send_count[r] = rows in that segment;  slot_index[m, j] = index of slot (m, j) among the slots owned by its
+    owner rank, numbered in (token, j) order, -1 for ids outside [0, E);  send_slots[r] = slots owned by r.
+    Rank r owns experts [r*E/world, (r+1)*E/world)."""
+    M, topk = topk_ids.shape
     e_local = num_experts // world
     dest_row = torch.full((M, world), -1, dtype=torch.int32)
     send_count = torch.zeros(world, dtype=torch.int32)
+    slot_index = torch.full((M, topk), -1, dtype=torch.int32)
+    send_slots = torch.zeros(world, dtype=torch.int32)
     ids = topk_ids.long()
     for r in range(world):
-        flag = ((ids >= r * e_local) & (ids < (r + 1) * e_local)).any(dim=1)
+        mine = (ids >= r * e_local) & (ids < (r + 1) * e_local)
+        flag = mine.any(dim=1)
         n = int(flag.sum())
         dest_row[flag, r] = torch.arange(n, dtype=torch.int32)
         send_count[r] = n
-    return dest_row, send_count
+        flat = mine.reshape(-1)
+        k = int(flat.sum())
+        slot_index.view(-1)[flat] = torch.arange(k, dtype=torch.int32)
+        send_slots[r] = k
+    return dest_row, send_count, slot_index, send_slots
 
 
-def ep_seg_start(send_count, world, cap):
+def ep_seg_start(count, world, cap):
     if cap > 0:
         return [r * cap for r in range(world)]
-    c = [int(v) for v in send_count]
+    c = [int(v) for v in count]
     return [sum(c[:r]) for r in range(world)]
 
 
@@ -497,12 +577,39 @@ def ep_pack(x, topk_ids, topk_weights, dest_row, send_count, num_experts, world,
     return send_x, meta
 
 
-def ep_combine(ret, dest_row, send_count, world, cap):
-    """out[m] = bf16(sum_r ret[seg(r) + dest_row[m, r]]) in f32, rank order."""
-    M = dest_row.shape[0]
-    seg = ep_seg_start(send_count, world, cap)
+def ep_ret_index(recv_meta, topk, world, cap, recv_count=None, recv_slots=None):
+    """Owner side: position of received slot (row i, j) in the return buffer, -1 for masked slots.  Valid slots
+    of the rows received from source s are numbered in row order from slot_seg(s) = s*cap*topk (fixed capacity)
+    or the exclusive scan of recv_slots (exact splits) -- the numbering the source computed in ep_plan."""
+    rows = recv_meta.shape[0]
+    ids = recv_meta[:, :topk]
+    out = torch.full((rows, topk), -1, dtype=torch.int32)
+    row_seg = ep_seg_start(recv_count, world, cap) if cap == 0 else [s * cap for s in range(world)]
+    slot_seg = ep_seg_start(recv_slots, world, 0) if cap == 0 else [s * cap * topk for s in range(world)]
+    for s in range(world):
+        n = cap if cap > 0 else int(recv_count[s])
+        blk = ids[row_seg[s]:row_seg[s] + n]
+        valid = (blk >= 0).reshape(-1)
+        o = out[row_seg[s]:row_seg[s] + n].view(-1)
+        o[valid] = slot_seg[s] + torch.arange(int(valid.sum()), dtype=torch.int32)
+    return out
+
+
+def ep_combine(ret, topk_ids, slot_index, send_slots, num_experts, world, cap, shared_y=None, rsf=1.0):
+    """out[m] = bf16(sum_j f32(ret[slot_seg(owner(m, j)) + slot_index[m, j]])), j ascending over valid slots (the
+    single-GPU reduce_slots order); with shared_y: bf16(f32(shared_y) + f32(that bf16) * rsf), fused multiply-add
+    (csrc/misc.cu shared_axpy_kernel)."""
+    M, topk = topk_ids.shape
+    e_local = num_experts // world
+    seg = torch.tensor(ep_seg_start(send_slots, world, cap * topk if cap > 0 else 0), dtype=torch.long)
     acc = torch.zeros(M, ret.shape[1], dtype=torch.float32)
-    for r in range(world):
-        sel = dest_row[:, r] >= 0
-        acc[sel] += ret[seg[r] + dest_row[sel, r].long()].float()
-    return acc.to(ret.dtype)
+    for j in range(topk):
+        e = topk_ids[:, j].long()
+        ok = (e >= 0) & (e < num_experts)
+        pos = seg[(e[ok] // e_local)] + slot_index[ok, j].long()
+        acc[ok] += ret[pos].float()
+    out = acc.to(ret.dtype)
+    if shared_y is not None:
+        rsf32 = float(torch.tensor(rsf, dtype=torch.float32))
+        out = (shared_y.double() + out.double() * rsf32).float().to(ret.dtype)   # fmaf in f32, then the bf16 rounding
+    return out

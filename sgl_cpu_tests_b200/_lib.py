@@ -9,6 +9,7 @@ OK = 0
 DT_BF16, DT_F32, DT_F16 = 0, 1, 2
 FMT_BF16, FMT_INT8_W8A8, FMT_FP8_W8A16, FMT_MXFP4 = 0, 1, 2, 4
 PATH_AUTO, PATH_STREAM, PATH_UMMA, PATH_UMMA2 = 0, 1, 2, 3
+ACT_SILU, ACT_SWIGLU_OAI = 0, 1
 
 _vp, _i32, _i64, _f32, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t
 
@@ -25,6 +26,8 @@ class MoeProblem(C.Structure):
         ("w13_scale", _vp), ("w2_scale", _vp), ("block_n", _i32), ("block_k", _i32),
         ("out", _vp), ("workspace", _vp), ("workspace_bytes", _sz),
         ("w13_scale_tiles", _vp), ("w2_scale_tiles", _vp),
+        ("w13_bias", _vp), ("w2_bias", _vp), ("act", _i32), ("alpha", _f32), ("limit", _f32),
+        ("slot_out", _vp), ("slot_map", _vp), ("rows_per_expert_hint", _f32),
     ]
 
 
@@ -75,20 +78,23 @@ SIGNATURES = {
     "sglb_repack_scale": (C.c_int, [_vp, _vp, _i64, _i64, _i64, C.c_int, _vp]),
     "sglb_quant_rows_int8": (C.c_int, [_vp, _i64, C.c_int, _vp, _vp, _vp]),
     "sglb_split_rows_e4m3": (C.c_int, [_vp, _i64, C.c_int, _vp, _vp, _vp, _vp]),
-    "sglb_ep_plan": (C.c_int, [_vp, _i64, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp]),
+    "sglb_ep_plan": (C.c_int, [_vp, _i64, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp]),
+    "sglb_ep_ret_index": (C.c_int, [_vp, C.c_int, _i64, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp]),
+    "sglb_shared_axpy": (C.c_int, [_vp, _vp, _f32, _i64, _vp, _vp]),
     "sglb_ep_pack": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _i64, _vp,
                                _vp, _vp]),
-    "sglb_ep_combine": (C.c_int, [_vp, _vp, _vp, _i64, C.c_int, C.c_int, C.c_int, _vp, _vp]),
+    "sglb_ep_combine": (C.c_int, [_vp, _vp, _vp, _vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _f32,
+                                  _vp, _vp]),
     "sglb_p2p_alloc": (C.c_int, [_sz, C.POINTER(_vp), _vp]),
     "sglb_p2p_open": (C.c_int, [_vp, C.POINTER(_vp)]),
     "sglb_p2p_close": (C.c_int, [_vp]),
     "sglb_p2p_free": (C.c_int, [_vp]),
     "sglb_ep_p2p_region_bytes": (_sz, [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(_sz)]),
     "sglb_ep_p2p_dispatch": (C.c_int, [_vp, _vp, _vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
-                                       C.POINTER(_vp), C.c_uint32, _vp]),
-    "sglb_ep_p2p_wait_dispatch": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, _vp]),
+                                       C.POINTER(_vp), C.c_int, _vp]),
+    "sglb_ep_p2p_wait_dispatch": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp]),
     "sglb_ep_p2p_combine": (C.c_int, [_vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(_vp),
-                                      C.c_uint32, _vp, _vp]),
+                                      C.c_int, _vp, _f32, _vp, _vp]),
     "sglb_topk_reduce": (C.c_int, [_vp, _vp, _i64, C.c_int, C.c_int, _vp, _vp]),
 }
 

@@ -192,6 +192,17 @@ static int check_format(const char* who, int fmt, int H, int I, const void* s13,
   return SGLB_OK;
 }
 
+// Optional pieces of the two epilogues (gpt-oss expert bias + clamped swiglu; slot-addressed stage-2 output).
+struct MlpExtra {
+  const float* w13_bias = nullptr;  // [E, 2I] f32
+  const float* w2_bias = nullptr;   // [E, H] f32
+  int act = SGLB_ACT_SILU;
+  float alpha = 1.f, limit = 0.f;
+  int out_by_slot = 0;              // stage 2 writes row sorted_slot[p] (through out_map) of ic2_out
+  const int32_t* out_map = nullptr;
+  bool any() const { return w13_bias || w2_bias || act != SGLB_ACT_SILU || out_by_slot; }
+};
+
 // One GEMM stage on the tcgen05 path over the tile list of an existing alignment.
 static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64_t S, const MoeWorkspace& ws,
                           cudaStream_t stream, bool f8_native = false, bool pair = false,
@@ -221,6 +232,12 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.Wsf = mx4_tiles;
   u.tile_cap = mx4_cap;
   u.bias = sa.bias;
+  u.ebias = sa.ebias;
+  u.act = sa.act;
+  u.act_alpha = sa.act_alpha;
+  u.act_limit = sa.act_limit;
+  u.out_by_slot = sa.out_by_slot;
+  u.out_map = sa.out_map;
   if (mx4_tiles) return launch_umma_mx4(stage, u, stream);
   if (f8_native) return pair ? launch_umma2_f8(stage, u, stream) : launch_umma_f8(stage, u, stream);
   if (pair) return launch_umma2_gemm(fmt, stage, u, stream);
@@ -240,7 +257,7 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
                           const void* w13, const void* w2, const void* s13, const void* s2, int bn,
                           int bk, const float* row_scale, const MoeWorkspace& ws, void* ic2_out,
                           cudaStream_t stream, const void* s13_tiles = nullptr, const void* s2_tiles = nullptr,
-                          int mx4_cap = 0) {
+                          int mx4_cap = 0, const MlpExtra& ex = MlpExtra()) {
   const int64_t S = M * topk;
   StreamArgs a;
   memset(&a, 0, sizeof(a));
@@ -266,6 +283,10 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   a.out = ws.act;
   a.row_scale = nullptr;
   a.scale_cols = fmt == SGLB_FMT_FP8_W8A16 ? ceil_div(H, bk) : H / 32;
+  a.ebias = ex.w13_bias;
+  a.act = ex.act;
+  a.act_alpha = ex.alpha;
+  a.act_limit = ex.limit;
   int rc;
   // fp8 w8a16 on the fp8 tensor cores: activations split into two e4m3 pieces (umma_f8.cu)
   const bool pair = path == SGLB_PATH_UMMA2;
@@ -308,6 +329,9 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   a.out = ic2_out;
   a.row_scale = row_scale;
   a.scale_cols = fmt == SGLB_FMT_FP8_W8A16 ? ceil_div(I, bk) : I / 32;
+  a.ebias = ex.w2_bias;
+  a.out_by_slot = ex.out_by_slot;
+  a.out_map = ex.out_map;
   if (fmt == SGLB_FMT_INT8_W8A8) {
     StageTimer t(ST_QUANT_ACT, stream);
     rc = launch_quant_rows_f32((const float*)ws.act, S, I, ws.actq, ws.acts, stream);
@@ -413,15 +437,29 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
   if (rc) return rc;
   SGLB_CHECK(p->w13 && p->w2, "fused_experts: null weight pointer");
   if (p->M == 0) return SGLB_OK;  // empty batch: activation pointers may legitimately be null
-  SGLB_CHECK(p->hidden && p->topk_weights && p->topk_ids && p->out, "fused_experts: null tensor pointer");
+  SGLB_CHECK(p->hidden && p->topk_weights && p->topk_ids && (p->out || p->slot_out), "fused_experts: null tensor pointer");
+  SGLB_CHECK(p->act == SGLB_ACT_SILU || p->act == SGLB_ACT_SWIGLU_OAI, "fused_experts: unknown activation %d", p->act);
+  SGLB_CHECK(p->slot_map == nullptr || p->slot_out != nullptr, "fused_experts: slot_map needs slot_out");
+  MlpExtra ex;
+  ex.w13_bias = p->w13_bias;
+  ex.w2_bias = p->w2_bias;
+  ex.act = p->act;
+  ex.alpha = p->alpha;
+  ex.limit = p->limit;
+  ex.out_by_slot = p->slot_out != nullptr;
+  ex.out_map = p->slot_map;
+  void* stage2_out = nullptr;  // set below: ws.ic2 (expert-sorted rows, reduced by K5) or the caller's slot rows
   const size_t need = sglb_fused_experts_workspace_bytes(p->M, p->topk, p->E, p->H, p->I, p->fmt);
   SGLB_CHECK(p->workspace && p->workspace_bytes >= need, "fused_experts: workspace too small (%zu < %zu)",
              p->workspace_bytes, need);
   SGLB_CHECK(((uintptr_t)p->workspace & 255) == 0, "fused_experts: workspace must be 256-byte aligned");
   MoeWorkspace ws = carve(p->workspace, p->M, p->topk, p->E, p->H, p->I, p->fmt);
+  stage2_out = p->slot_out ? p->slot_out : (void*)ws.ic2;
 
   int path = p->path;
-  const double rows_per_expert = (double)p->M * p->topk / p->E;
+  // expected routed rows per expert decide the path; a caller whose ids are mostly masked (an expert-parallel
+  // rank sees world x cap slots of which ~1/world are its own) passes its own estimate
+  const double rows_per_expert = p->rows_per_expert_hint > 0.f ? (double)p->rows_per_expert_hint : (double)p->M * p->topk / p->E;
   // mxfp4 on the block-scaled tensor cores needs the re-tiled scales (sglb_mx4_tile_scales)
   const bool mx4 = p->fmt == SGLB_FMT_MXFP4 && g_mx4_native && p->w13_scale_tiles && p->w2_scale_tiles &&
                    umma_mx4_supported(p->H, p->I);
@@ -448,22 +486,26 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     SGLB_CHECK(path == SGLB_PATH_UMMA || p->fmt == SGLB_FMT_BF16 || p->fmt == SGLB_FMT_INT8_W8A8 ||
                    (p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k)),
                "fused_experts: the CTA-pair tcgen05 path takes bf16, int8 and tensor-native fp8 weights only (fmt=%d)", p->fmt);
+    SGLB_CHECK(path == SGLB_PATH_UMMA || !ex.any(),
+               "fused_experts: the CTA-pair tcgen05 path has no expert bias / clamped swiglu / slot-addressed output");
     const bool use_mx4 = mx4 && path == SGLB_PATH_UMMA;
     rc = run_align(p->topk_ids, p->M, p->topk, p->E, 0, ws, stream,
                    use_mx4 ? mx4_cap : (path == SGLB_PATH_UMMA2 ? umma2_tile_rows() : kTileRows));
     if (rc) return rc;
     rc = run_mlp(path, p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2,
-                 p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, ws.ic2, stream,
-                 use_mx4 ? p->w13_scale_tiles : nullptr, use_mx4 ? p->w2_scale_tiles : nullptr, mx4_cap);
+                 p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, stage2_out, stream,
+                 use_mx4 ? p->w13_scale_tiles : nullptr, use_mx4 ? p->w2_scale_tiles : nullptr, mx4_cap, ex);
     if (rc) return rc;
   } else {
     StreamPlan plan = make_plan(p->M, p->topk, p->E, p->I, 1);
     rc = run_align(p->topk_ids, p->M, p->topk, p->E, 8 * plan.ng, ws, stream);
     if (rc) return rc;
     rc = run_mlp(SGLB_PATH_STREAM, p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2,
-                 p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, ws.ic2, stream);
+                 p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, stage2_out, stream, nullptr,
+                 nullptr, 0, ex);
     if (rc) return rc;
   }
+  if (p->slot_out) return SGLB_OK;  // the caller reduces the slot rows (expert-parallel combine)
   StageTimer t(ST_REDUCE, stream);
   return sglb_topk_reduce(ws.ic2, ws.slot_pos, p->M, p->topk, p->H, p->out, stream);
 }
@@ -476,7 +518,7 @@ extern "C" int sglb_shared_expert(const sglb_shared_problem* p, sglb_stream_t st
   if (rc) return rc;
   SGLB_CHECK(p->w1 && p->w2, "shared_expert: null weight pointer");
   if (p->M == 0) return SGLB_OK;
-  SGLB_CHECK(p->hidden && p->fused_out && p->out, "shared_expert: null tensor pointer");
+  SGLB_CHECK(p->hidden && p->out, "shared_expert: null tensor pointer");
   const size_t need = sglb_fused_experts_workspace_bytes(p->M, 1, 1, p->H, p->I, p->fmt);
   SGLB_CHECK(p->workspace && p->workspace_bytes >= need, "shared_expert: workspace too small (%zu < %zu)",
              p->workspace_bytes, need);
@@ -499,10 +541,17 @@ extern "C" int sglb_shared_expert(const sglb_shared_problem* p, sglb_stream_t st
     rc = run_align(ws.zero_ids, p->M, 1, 1, 8 * plan.ng, ws, stream);
   }
   if (rc) return rc;
+  // without fused_out the MLP result goes straight to `out` (E = 1 keeps token order: sorted position = token)
   rc = run_mlp(path, p->fmt, p->M, 1, 1, p->H, p->I, p->hidden, p->w1, p->w2, p->w1_scale,
-               p->w2_scale, p->block_n, p->block_k, nullptr, ws, ws.ic2, stream);
-  if (rc) return rc;
+               p->w2_scale, p->block_n, p->block_k, nullptr, ws, p->fused_out ? (void*)ws.ic2 : p->out, stream);
+  if (rc || !p->fused_out) return rc;
   return launch_shared_axpy(ws.ic2, p->fused_out, p->routed_scaling_factor, p->M * (int64_t)p->H, p->out, stream);
+}
+
+extern "C" int sglb_shared_axpy(const void* y, const void* fused, float routed_scaling_factor, int64_t n, void* out,
+                                sglb_stream_t stream) {
+  SGLB_CHECK(n >= 0 && (n == 0 || (y && fused && out)), "shared_axpy: bad arguments");
+  return launch_shared_axpy(y, fused, routed_scaling_factor, n, out, (cudaStream_t)stream);
 }
 
 extern "C" int sglb_mxfp4_mm(const void* A, const void* Bq, const void* Bs, const float* bias, int64_t M,

@@ -115,6 +115,26 @@ template <>
 __device__ __forceinline__ float load_as_float<__half>(const __half* p) { return __half2float(*p); }
 
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
+// Stage-1 activation.  act 0: silu(gate) * up (test_moe.py:17-19).  act 1: gpt-oss clamped swiglu of the 17-argument
+// fused_experts_cpu vintage (alpha, limit): g = min(gate, limit), u = clamp(up, -limit, limit),
+// out = g * sigmoid(alpha * g) * (u + 1); limit <= 0 means "no clamp".
+enum { SGLB_ACT_SILU = 0, SGLB_ACT_SWIGLU_OAI = 1 };
+__device__ __forceinline__ float glu_f(float gate, float up, int act, float alpha, float limit) {
+  if (act == SGLB_ACT_SILU) return silu_f(gate) * up;
+  if (limit > 0.f) {
+    gate = fminf(gate, limit);
+    up = fminf(fmaxf(up, -limit), limit);
+  }
+  return gate / (1.0f + __expf(-alpha * gate)) * (up + 1.0f);
+}
+// Where stage 2 writes routed row p (position in expert-sorted order): row p of `out`, or -- when the caller
+// asked for slot-addressed output (expert-parallel return path) -- row sorted_slot[p] (= token * topk + slot),
+// optionally sent through one more table (the compact return buffer of the NCCL exchange).
+__device__ __forceinline__ int64_t out_row_of(int p, const int32_t* sorted_slot, int by_slot, const int32_t* out_map) {
+  if (!by_slot) return p;
+  const int s = sorted_slot[p];
+  return out_map != nullptr ? out_map[s] : s;
+}
 
 // ---- legacy warp MMA (decode / weight-streaming path) ----------------------------------------
 // D(16x8,f32) += A(16x16,bf16,row) * B(16x8,bf16,col)

@@ -1,23 +1,31 @@
 // K8, decode regime: expert-parallel dispatch / combine over NVLink peer memory, no collective library
-// on the data path.  At decode batch sizes the NCCL exchange of ep.py (three all-to-alls per layer) costs
+// on the data path.  At decode batch sizes the NCCL exchange of ep.py (all-to-alls of a few hundred KB) costs
 // more than the experts themselves (2 GPUs, Qwen3 int8, 128 tokens per rank: 250 us per step against 120 us
-// on one GPU); the payload is a few hundred KB, so the exchange is pure latency.  Here every rank owns
-// one cudaMalloc'd region that all peers map through CUDA IPC, and two kernels do the exchange:
+// on one GPU): the exchange is pure latency.  Here every rank owns one cudaMalloc'd region that all peers map
+// through CUDA IPC, and two kernels do the exchange:
 //
 //   dispatch  block (m, r) stores token m's row straight into rank r's receive buffer (slot [src, m]:
 //             fixed capacity, no counts to agree on) together with its topk ids in r's local numbering
 //             (-1 where r does not own the expert, and for the unused slots m >= M); the last block to
 //             finish raises flag[src] = seq on every peer (system-scope release)
-//   experts   the ordinary local fused_experts over the world*cap received slots, after a one-block
-//             kernel has seen every source's flag (system-scope acquire); output rows go to `y`
+//   experts   the ordinary local fused_experts over the world*cap received rows, after a one-block
+//             kernel has seen every source's flag (system-scope acquire), with SLOT-ADDRESSED output: the
+//             stage-2 epilogue writes the bf16 row of slot (row i, j) to y[i*topk + j] -- exactly the row a
+//             single GPU holds in its ic2 buffer for that (token, expert) pair
 //   combine   raises the "y ready" flag on every peer, waits for the peers that own experts of its
-//             token, then reads their partial rows over NVLink (L1-bypassing loads) and sums them in
-//             rank order in f32 -- the same order as ep_combine_kernel, so outputs are bit-identical to
-//             the NCCL path and to one GPU's reduction order.
+//             token, then reads the token's topk rows over NVLink (L1-bypassing loads) and adds them in
+//             slot order j = 0..topk-1 in f32 with one rounding -- sglb_topk_reduce's arithmetic, so the
+//             result is bit-identical to the single-GPU fused_experts (and to the NCCL path of ep.cu);
+//             optionally fuses shared_expert_cpu's epilogue, out = bf16(y_shared + bf16(sum) * rsf)
 //
-// Buffers are double-buffered on the parity of `seq`.  Reuse is safe without further handshakes: a rank
-// can only start dispatch(i+2) after its combine(i+1), which waited for every peer's experts(i+1) to
-// finish, i.e. after every reader of the buffers of call i is done (same argument for `y`).
+// Call counting lives on the device: every rank's region holds `seq`, advanced by the dispatch kernel, and
+// the three kernels read it from there, so a captured CUDA graph can be replayed (no per-call kernel
+// argument).  Buffers are double-buffered on `par`, a kernel argument: callers alternate par = 0, 1, 0, ...
+// (two captured graphs).  Reuse is safe without further handshakes: a rank can only start dispatch(i+2)
+// after its combine(i+1), which waited for every peer's experts(i+1) to finish, i.e. after every reader of
+// the buffers of call i is done (same argument for `y`).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace sglb {
@@ -27,7 +35,7 @@ namespace {
 constexpr int kMaxWorld = 16;
 
 struct P2PLayout {
-  size_t x[2], ids[2], tw[2], y[2], flags, counter, total;
+  size_t x[2], ids[2], tw[2], y[2], flags, counter, seq, total;
 };
 
 __host__ __device__ inline P2PLayout p2p_layout(int world, int cap, int H, int topk) {
@@ -43,10 +51,11 @@ __host__ __device__ inline P2PLayout p2p_layout(int world, int cap, int H, int t
     L.x[p] = take(rows * H * 2);
     L.ids[p] = take(rows * topk * 4);
     L.tw[p] = take(rows * topk * 4);
-    L.y[p] = take(rows * H * 2);
+    L.y[p] = take(rows * topk * H * 2);  // one row per routed slot
   }
   L.flags = take(sizeof(uint32_t) * 2 * kMaxWorld);
   L.counter = take(256);
+  L.seq = take(256);
   L.total = off;
   return L;
 }
@@ -76,13 +85,14 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
-// Spins until *flag has reached seq (wrap-safe); a peer that never arrives ends in a trap after 20 s
-// rather than in a hung GPU.
-__device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t seq) {
+// Spins until *flag has reached seq (wrap-safe).  A peer that never arrives (a crashed rank) ends in a trap
+// after `timeout_ns` rather than in a hung GPU; 0 waits for ever (SGLB_EP_TIMEOUT_S, default 60 s: long
+// enough for a peer held up by a prefill batch, a GC pause or checkpoint I/O).
+__device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t seq, uint64_t timeout_ns) {
   const uint64_t t0 = globaltimer_ns();
   while ((int32_t)(ld_acquire_sys(flag) - seq) < 0) {
     __nanosleep(64);
-    if (globaltimer_ns() - t0 > 20000000000ull) __trap();
+    if (timeout_ns != 0 && globaltimer_ns() - t0 > timeout_ns) __trap();
   }
 }
 
@@ -90,10 +100,11 @@ __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t seq) {
 __global__ void __launch_bounds__(128)
     ep_p2p_dispatch_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ ids,
                            const float* __restrict__ tw, int M, int topk, int E_local, int world, int rank, int H,
-                           int cap, PeerPtrs peers, uint32_t seq) {
+                           int cap, PeerPtrs peers, int par) {
   const int m = blockIdx.x, r = blockIdx.y;
   const P2PLayout L = p2p_layout(world, cap, H, topk);
-  const int par = seq & 1;
+  // this call's number: the local counter + 1 (the last block stores it back, after every block has read it)
+  const uint32_t seq = *reinterpret_cast<const volatile uint32_t*>(peers.base[rank] + L.seq) + 1u;
   const size_t slot = (size_t)rank * cap + m;
   char* pb = peers.base[r];
   int32_t* pid = reinterpret_cast<int32_t*>(pb + L.ids[par]) + slot * topk;
@@ -127,6 +138,7 @@ __global__ void __launch_bounds__(128)
     const uint32_t total = gridDim.x * gridDim.y;
     if (atomicAdd(counter, 1u) == total - 1) {
       *counter = 0;
+      *reinterpret_cast<volatile uint32_t*>(peers.base[rank] + L.seq) = seq;
       __threadfence_system();
       for (int q = 0; q < world; ++q)
         st_release_sys(reinterpret_cast<uint32_t*>(peers.base[q] + L.flags) + rank, seq);
@@ -135,25 +147,29 @@ __global__ void __launch_bounds__(128)
 }
 
 // one block: every source's rows of call `seq` have landed in this rank's receive buffers
-__global__ void ep_p2p_wait_kernel(const char* base, size_t flags_off, int world, uint32_t seq) {
-  if ((int)threadIdx.x < world) wait_flag(reinterpret_cast<const uint32_t*>(base + flags_off) + threadIdx.x, seq);
+__global__ void ep_p2p_wait_kernel(const char* base, size_t flags_off, size_t seq_off, int world, uint64_t timeout_ns) {
+  const uint32_t seq = *reinterpret_cast<const volatile uint32_t*>(base + seq_off);
+  if ((int)threadIdx.x < world)
+    wait_flag(reinterpret_cast<const uint32_t*>(base + flags_off) + threadIdx.x, seq, timeout_ns);
 }
 
-// grid (M, ceil(H/8/256)), 256 threads
+// grid (max(M, 1), ceil(H/8/256)), 256 threads
 __global__ void __launch_bounds__(256)
-    ep_p2p_combine_kernel(const int32_t* __restrict__ ids, int topk, int E_local, int world, int rank, int H, int cap,
-                          PeerPtrs peers, uint32_t seq, __nv_bfloat16* __restrict__ out) {
+    ep_p2p_combine_kernel(const int32_t* __restrict__ ids, int M, int topk, int E_local, int world, int rank, int H,
+                          int cap, PeerPtrs peers, int par, uint64_t timeout_ns,
+                          const __nv_bfloat16* __restrict__ shared_y, float rsf, __nv_bfloat16* __restrict__ out) {
   const int64_t m = blockIdx.x;
   const P2PLayout L = p2p_layout(world, cap, H, topk);
-  const int par = seq & 1;
-  __shared__ uint32_t need;  // bit r: rank r owns at least one expert of token m
-  if (threadIdx.x == 0) need = 0;
-  __syncthreads();
-  // this rank's partial rows are complete (previous kernels of the stream): tell every peer
-  if ((int)threadIdx.x < world) {
+  const uint32_t seq = *reinterpret_cast<const volatile uint32_t*>(peers.base[rank] + L.seq);
+  // this rank's slot rows are complete (previous kernels of the stream): block (0, 0) tells every peer
+  if (blockIdx.x == 0 && blockIdx.y == 0 && (int)threadIdx.x < world) {
     __threadfence_system();
     st_release_sys(reinterpret_cast<uint32_t*>(peers.base[threadIdx.x] + L.flags) + kMaxWorld + rank, seq);
   }
+  if (m >= M) return;  // a rank without tokens only announces its rows
+  __shared__ uint32_t need;  // bit r: rank r owns at least one expert of token m
+  if (threadIdx.x == 0) need = 0;
+  __syncthreads();
   for (int j = threadIdx.x; j < topk; j += 256) {
     const int e = ids[m * topk + j];
     if (e >= 0 && e < E_local * world) atomicOr(&need, 1u << (e / E_local));
@@ -161,14 +177,15 @@ __global__ void __launch_bounds__(256)
   __syncthreads();
   const uint32_t nd = need;
   if ((int)threadIdx.x < world && ((nd >> threadIdx.x) & 1u))
-    wait_flag(reinterpret_cast<const uint32_t*>(peers.base[rank] + L.flags) + kMaxWorld + threadIdx.x, seq);
+    wait_flag(reinterpret_cast<const uint32_t*>(peers.base[rank] + L.flags) + kMaxWorld + threadIdx.x, seq, timeout_ns);
   __syncthreads();
   const int h0 = (blockIdx.y * 256 + threadIdx.x) * 8;
   if (h0 >= H) return;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  for (int r = 0; r < world; ++r) {
-    if (!((nd >> r) & 1u)) continue;
-    const char* src = peers.base[r] + L.y[par] + (((size_t)rank * cap + m) * H + h0) * 2;
+  for (int j = 0; j < topk; ++j) {  // slot order: the single-GPU reduction order
+    const int e = ids[m * topk + j];
+    if (e < 0 || e >= E_local * world) continue;
+    const char* src = peers.base[e / E_local] + L.y[par] + ((((size_t)rank * cap + m) * topk + j) * H + h0) * 2;
     const int4 v = ld_peer16(src);
     const uint32_t* wv = reinterpret_cast<const uint32_t*>(&v);
 #pragma unroll
@@ -177,10 +194,28 @@ __global__ void __launch_bounds__(256)
       acc[2 * i + 1] += bf16_bits_to_float(wv[i] >> 16);
     }
   }
+  if (shared_y != nullptr) {  // shared_expert_cpu's epilogue on the rounded sum (misc.cu shared_axpy_kernel)
+    const int4 yv = *reinterpret_cast<const int4*>(shared_y + (size_t)m * H + h0);
+    const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      acc[2 * i] = fmaf(bf16_round(acc[2 * i]), rsf, bf16_bits_to_float(yw[i] & 0xffffu));
+      acc[2 * i + 1] = fmaf(bf16_round(acc[2 * i + 1]), rsf, bf16_bits_to_float(yw[i] >> 16));
+    }
+  }
   uint32_t o[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) o[i] = pack_bf16x2(acc[2 * i], acc[2 * i + 1]);
   *reinterpret_cast<int4*>(out + (size_t)m * H + h0) = make_int4(o[0], o[1], o[2], o[3]);
+}
+
+uint64_t timeout_ns() {
+  static const uint64_t v = [] {
+    const char* e = getenv("SGLB_EP_TIMEOUT_S");
+    const double s = e ? atof(e) : 60.0;
+    return s <= 0 ? (uint64_t)0 : (uint64_t)(s * 1e9);
+  }();
+  return v;
 }
 
 int fill_peers(void* const* peer_bases, int world, PeerPtrs* p) {
@@ -247,7 +282,7 @@ extern "C" size_t sglb_ep_p2p_region_bytes(int world, int cap, int H, int topk, 
 
 extern "C" int sglb_ep_p2p_dispatch(const void* hidden, const int32_t* topk_ids, const float* topk_weights, int64_t M,
                                     int topk, int E, int world, int rank, int H, int cap, void* const* peer_bases,
-                                    uint32_t seq, sglb_stream_t stream) {
+                                    int parity, sglb_stream_t stream) {
   SGLB_CHECK(E % world == 0 && rank >= 0 && rank < world && H % 8 == 0 && topk >= 1, "ep_p2p_dispatch: bad shape");
   SGLB_CHECK(M >= 0 && M <= cap, "ep_p2p_dispatch: %lld tokens exceed the capacity %d", (long long)M, cap);
   SGLB_CHECK(M == 0 || (hidden && topk_ids && topk_weights), "ep_p2p_dispatch: null pointer");
@@ -255,35 +290,36 @@ extern "C" int sglb_ep_p2p_dispatch(const void* hidden, const int32_t* topk_ids,
   int rc = fill_peers(peer_bases, world, &peers);
   if (rc) return rc;
   ep_p2p_dispatch_kernel<<<dim3((unsigned)cap, (unsigned)world), 128, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)hidden, topk_ids, topk_weights, (int)M, topk, E / world, world, rank, H, cap, peers, seq);
+      (const __nv_bfloat16*)hidden, topk_ids, topk_weights, (int)M, topk, E / world, world, rank, H, cap, peers, parity & 1);
   SGLB_LAUNCH_CHECK();
   count_launch();
   return SGLB_OK;
 }
 
-extern "C" int sglb_ep_p2p_wait_dispatch(const void* local_base, int world, int cap, int H, int topk, uint32_t seq,
+extern "C" int sglb_ep_p2p_wait_dispatch(const void* local_base, int world, int cap, int H, int topk,
                                          sglb_stream_t stream) {
   SGLB_CHECK(local_base && world >= 1 && world <= kMaxWorld, "ep_p2p_wait_dispatch: bad arguments");
   const P2PLayout L = p2p_layout(world, cap, H, topk);
-  ep_p2p_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>((const char*)local_base, L.flags, world, seq);
+  ep_p2p_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>((const char*)local_base, L.flags, L.seq, world, timeout_ns());
   SGLB_LAUNCH_CHECK();
   count_launch();
   return SGLB_OK;
 }
 
 extern "C" int sglb_ep_p2p_combine(const int32_t* topk_ids, int64_t M, int topk, int E, int world, int rank, int H,
-                                   int cap, void* const* peer_bases, uint32_t seq, void* out, sglb_stream_t stream) {
-  SGLB_CHECK(E % world == 0 && rank >= 0 && rank < world && H % 8 == 0 && topk >= 1 && M <= cap,
+                                   int cap, void* const* peer_bases, int parity, const void* shared_y,
+                                   float routed_scaling_factor, void* out, sglb_stream_t stream) {
+  SGLB_CHECK(E % world == 0 && rank >= 0 && rank < world && H % 8 == 0 && topk >= 1 && M >= 0 && M <= cap,
              "ep_p2p_combine: bad shape");
   PeerPtrs peers;
   int rc = fill_peers(peer_bases, world, &peers);
   if (rc) return rc;
-  // every rank has to run this kernel (it tells the peers that this rank's partial rows are ready), so the
-  // peer-memory path takes ranks with at least one token only; ep.py keeps empty batches on the NCCL path
-  SGLB_CHECK(M >= 1 && topk_ids && out, "ep_p2p_combine: needs at least one local token and non-null pointers");
-  const unsigned gx = (unsigned)M;
+  // every rank runs this kernel, tokens or not: it tells the peers that this rank's slot rows are ready
+  SGLB_CHECK(M == 0 || (topk_ids && out), "ep_p2p_combine: null pointer");
+  const unsigned gx = (unsigned)(M > 0 ? M : 1);
   ep_p2p_combine_kernel<<<dim3(gx, (unsigned)ceil_div(ceil_div(H, 8), 256)), 256, 0, (cudaStream_t)stream>>>(
-      topk_ids, topk, E / world, world, rank, H, cap, peers, seq, (__nv_bfloat16*)out);
+      topk_ids, (int)M, topk, E / world, world, rank, H, cap, peers, parity & 1, timeout_ns(),
+      (const __nv_bfloat16*)shared_y, routed_scaling_factor, (__nv_bfloat16*)out);
   SGLB_LAUNCH_CHECK();
   count_launch();
   return SGLB_OK;

@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(256)
   pdl_wait();
   pdl_trigger();
   int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (i < n) out[i] = __float2bfloat16_rn(__bfloat162float(y[i]) + __bfloat162float(fused[i]) * rsf);
+  if (i < n) out[i] = __float2bfloat16_rn(fmaf(__bfloat162float(fused[i]), rsf, __bfloat162float(y[i])));
 }
 
 // ---- K7 prepack: row-major [N,K] <-> [N/32, K/V, 32, V] (element size EB bytes) -------------------

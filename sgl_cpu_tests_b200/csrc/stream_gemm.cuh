@@ -38,6 +38,12 @@ struct StreamArgs {
   int block_n, block_k;    // fp8 scale block
   int scale_cols;          // fp8: ceil(K/bk); mxfp4: K/32
   const void* X2;          // tcgen05 fp8 path only (see UmmaArgs)
+  const float* ebias;      // per-expert f32 bias [E, rows_per_expert] or nullptr (gpt-oss w1_bias / w2_bias): added to
+                           // the dequantised accumulator before the activation (stage 1) / before row_scale (stage 2)
+  int act;                 // stage 1: SGLB_ACT_SILU or SGLB_ACT_SWIGLU_OAI (common.cuh glu_f)
+  float act_alpha, act_limit;
+  int out_by_slot;         // stage 2: write routed row p to row sorted_slot[p] (through out_map if set) instead of p
+  const int32_t* out_map;
 };
 
 template <int FMT>
@@ -330,13 +336,20 @@ __global__ void __launch_bounds__(WN* WK * 32)
           gate = xs * gate * ws[n];
           up = xs * up * ws[a.N + n];
         }
+        if (a.ebias != nullptr) {
+          const float* eb = a.ebias + (size_t)e * a.rows_per_expert;
+          gate += eb[n];
+          up += eb[a.N + n];
+        }
+        const float actv = glu_f(gate, up, a.act, a.act_alpha, a.act_limit);
         if (FMT == SGLB_FMT_INT8_W8A8)
-          reinterpret_cast<float*>(a.out)[(size_t)p * a.N + n] = silu_f(gate) * up;
+          reinterpret_cast<float*>(a.out)[(size_t)p * a.N + n] = actv;
         else
-          out[(size_t)p * a.N + n] = __float2bfloat16_rn(silu_f(gate) * up);
+          out[(size_t)p * a.N + n] = __float2bfloat16_rn(actv);
       } else {
         float rs = 1.f;
         if (a.row_scale != nullptr) rs = a.row_scale[a.sorted_slot[p]];
+        const int64_t orow = out_row_of(p, a.sorted_slot, a.out_by_slot, a.out_map);
 #pragma unroll
         for (int b = 0; b < 2; ++b) {
           const int n = nbase[b] + rofs;
@@ -347,7 +360,8 @@ __global__ void __launch_bounds__(WN* WK * 32)
             v = xs * v * ws[n];
           }
           if (a.bias != nullptr) v += a.bias[n];
-          out[(size_t)p * a.N + n] = __float2bfloat16_rn(v * rs);
+          if (a.ebias != nullptr) v += a.ebias[(size_t)e * a.rows_per_expert + n];
+          out[(size_t)orow * a.N + n] = __float2bfloat16_rn(v * rs);
         }
       }
     }

@@ -305,6 +305,12 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
         }
         float bias_n = 0.f;  // dense linears: f32 bias of output n (this lane's TMEM lane)
         if (STAGE == 2 && a.bias != nullptr && n < a.N) bias_n = a.bias[n];
+        float eb0 = 0.f, eb1 = 0.f;  // per-expert bias of this lane's output(s)
+        if (a.ebias != nullptr && n < a.N) {
+          const float* eb = a.ebias + (size_t)wi.e * a.rows_per_expert;
+          eb0 = eb[n];
+          if (STAGE == 1) eb1 = eb[a.N + n];
+        }
 #pragma unroll 1
         for (int c0 = 16 * par; c0 < n_eff; c0 += 32) {  // n_eff is warp-uniform
           const float xsel = sel4(xs_r, c0 >> 5), rsel = sel4(rs_r, c0 >> 5);
@@ -330,9 +336,9 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
             for (int j = 0; j < 16; ++j) {
               if constexpr (kInt8) {
                 const float xs = __shfl_sync(0xffffffffu, xsel, 16 * par + j);
-                const float gate = xs * (float)(int)gv[j] * ws0;
-                const float up = xs * (float)(int)uv[j] * ws1;
-                *reinterpret_cast<float*>(ebuf + j * ROWB + lane * 4) = silu_f(gate) * up;
+                const float gate = xs * (float)(int)gv[j] * ws0 + eb0;
+                const float up = xs * (float)(int)uv[j] * ws1 + eb1;
+                *reinterpret_cast<float*>(ebuf + j * ROWB + lane * 4) = glu_f(gate, up, a.act, a.act_alpha, a.act_limit);
               } else {
                 float gate = __uint_as_float(gv[j]), up = __uint_as_float(uv[j]);
                 if constexpr (kTokScale) {
@@ -341,7 +347,7 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
                   up *= xs;
                 }
                 *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) =
-                    __float2bfloat16_rn(silu_f(gate) * up);
+                    __float2bfloat16_rn(glu_f(gate + eb0, up + eb1, a.act, a.act_alpha, a.act_limit));
               }
             }
           } else {
@@ -366,7 +372,7 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
                 val = __uint_as_float(v[j]);
                 if constexpr (kTokScale) val *= __shfl_sync(0xffffffffu, xsel, 16 * par + j);
               }
-              *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(fmaf(val, rs, bias_n));
+              *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(fmaf(val + eb0, rs, bias_n));
             }
           }
           __syncwarp();
@@ -375,9 +381,11 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
           for (int i = 0; i < NRD; ++i) {
             const int tok = rd_tok + TPI * i;
             const int4 piece = *reinterpret_cast<const int4*>(ebuf + tok * ROWB + rd_seg * 16);
-            if (c0 + tok < wi.rows && nn < a.N)
-              *reinterpret_cast<int4*>((char*)a.out +
-                                       ((size_t)(wi.row_start + c0 + tok) * a.N + nn) * OB) = piece;
+            if (c0 + tok < wi.rows && nn < a.N) {
+              const int64_t orow = STAGE == 2 ? out_row_of(wi.row_start + c0 + tok, a.sorted_slot, a.out_by_slot, a.out_map)
+                                              : (int64_t)(wi.row_start + c0 + tok);
+              *reinterpret_cast<int4*>((char*)a.out + ((size_t)orow * a.N + nn) * OB) = piece;
+            }
           }
           __syncwarp();
         }

@@ -311,6 +311,12 @@ __global__ void __launch_bounds__(kThreads, 1)
           const int nbase = STAGE == 1 ? wi.nb * kWSub + q * 32 : wi.nb * 2 * kWSub + sub * kWSub + q * 32;
           float bias_n = 0.f;
           if (STAGE == 2 && a.bias != nullptr && nbase + lane < a.N) bias_n = a.bias[nbase + lane];
+          float eb0 = 0.f, eb1 = 0.f;  // per-expert bias of this lane's output(s)
+          if (a.ebias != nullptr && nbase + lane < a.N) {
+            const float* eb = a.ebias + (size_t)wi.e * a.rows_per_expert;
+            eb0 = eb[nbase + lane];
+            if (STAGE == 1) eb1 = eb[a.N + nbase + lane];
+          }
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const float xs = __shfl_sync(0xffffffffu, xsel, 16 * par + j);
@@ -318,11 +324,11 @@ __global__ void __launch_bounds__(kThreads, 1)
             if constexpr (STAGE == 1) {
               const float g_ = (j & 1) ? acc[0][c][j >> 1].y : acc[0][c][j >> 1].x;
               const float u_ = (j & 1) ? acc[1][c][j >> 1].y : acc[1][c][j >> 1].x;
-              val = silu_f(g_ * xs) * (u_ * xs);
+              val = glu_f(g_ * xs + eb0, u_ * xs + eb1, a.act, a.act_alpha, a.act_limit);
             } else {
               const float rs = __shfl_sync(0xffffffffu, rsel, 16 * par + j);
               const float a_ = (j & 1) ? acc[sub][c][j >> 1].y : acc[sub][c][j >> 1].x;
-              val = fmaf(a_ * xs, rs, bias_n);
+              val = fmaf(a_ * xs + eb0, rs, bias_n);
             }
             *reinterpret_cast<__nv_bfloat16*>(ebuf + j * ROWB + lane * 2) = __float2bfloat16_rn(val);
           }
@@ -332,8 +338,11 @@ __global__ void __launch_bounds__(kThreads, 1)
           for (int i = 0; i < NRD; ++i) {
             const int tok = rd_tok + TPI * i;
             const int4 piece = *reinterpret_cast<const int4*>(ebuf + tok * ROWB + rd_seg * 16);
-            if (c0 + tok < wi.rows && nn < a.N)
-              *reinterpret_cast<int4*>((char*)a.out + ((size_t)(wi.row_start + c0 + tok) * a.N + nn) * 2) = piece;
+            if (c0 + tok < wi.rows && nn < a.N) {
+              const int64_t orow = STAGE == 2 ? out_row_of(wi.row_start + c0 + tok, a.sorted_slot, a.out_by_slot, a.out_map)
+                                              : (int64_t)(wi.row_start + c0 + tok);
+              *reinterpret_cast<int4*>((char*)a.out + ((size_t)orow * a.N + nn) * 2) = piece;
+            }
           }
           __syncwarp();
         }

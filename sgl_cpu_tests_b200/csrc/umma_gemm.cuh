@@ -28,6 +28,12 @@ struct UmmaArgs {
   int tile_cap;            // mxfp4 tensor-native path: row capacity of the tiles in tile_list (16..112)
   const float* bias;       // stage 2 optional f32 [N] added after row_scale (dense linears, E = 1)
   int est_tiles;           // umma_gemm.cu, decode regime: expected tile count (0 = unknown), sizes the persistent grid
+  const float* ebias;      // per-expert f32 bias [E, rows_per_expert] or nullptr (gpt-oss w1_bias / w2_bias): added to
+                           // the dequantised accumulator before the activation (stage 1) / before row_scale (stage 2)
+  int act;                 // stage 1: SGLB_ACT_SILU or SGLB_ACT_SWIGLU_OAI (common.cuh glu_f)
+  float act_alpha, act_limit;
+  int out_by_slot;         // stage 2: write routed row p to row sorted_slot[p] (through out_map if set) instead of p
+  const int32_t* out_map;
 };
 
 constexpr int kUmmaTileRows = 128;  // routed rows per tile (tile_rows handed to moe_align)

@@ -1,5 +1,5 @@
 """Expert-parallel fused MoE: experts sharded over the ranks of one NVLink/NVSwitch box, tokens
-data-parallel, one all-to-all each side of the local fused_experts.
+data-parallel, one exchange each side of the local fused_experts.
 
 Nothing in the reference shards experts.  The hook it offers is that ``fused_experts_cpu`` ignores
 ``topk_ids == -1`` (test_moe_offloading_cpu.py:57-68) -- exactly what a rank sees for experts it does
@@ -7,17 +7,25 @@ not own -- so the local compute is the unchanged single-GPU path.
 
 Per layer call, on every rank (M local tokens, rank r owns experts [r*E/n, (r+1)*E/n)):
 
-  plan     (CUDA, csrc/ep.cu)  which ranks own at least one of each token's experts; stable row numbering
-  pack     (CUDA)              token rows + (local ids | weights) gathered per destination rank
-  dispatch (NCCL all-to-all)   rows travel once per (token, destination rank), not once per expert
-  experts  (CUDA)              ordinary fused_experts over the received rows, ids already local / -1
-  return   (NCCL all-to-all)   one partial row per received row
-  combine  (CUDA)              out[m] = sum over ranks in rank order, f32 accumulate -> bf16
+  plan      (CUDA, csrc/ep.cu)  which ranks own at least one of each token's experts; stable numbering of the
+                                rows that travel out and of the slot rows that come back
+  pack      (CUDA)              token rows + (local ids | weights) gathered per destination rank
+  dispatch  (NCCL all-to-all)   rows travel once per (token, destination rank), not once per expert
+  experts   (CUDA)              ordinary fused_experts over the received rows, ids already local / -1, with
+                                slot-addressed output: one bf16 row per routed slot, written by the stage-2
+                                epilogue straight into the return buffer
+  return    (NCCL all-to-all)   one row per routed slot
+  combine   (CUDA)              out[m] = sum of the token's slot rows in slot order, f32, one rounding:
+                                the single-GPU reduction, so n-GPU results are BIT-IDENTICAL to one GPU's
+                                (optionally + the shared expert's epilogue, whose MLP ran on a side stream
+                                while the exchange was in flight)
 
-Two exchange modes, chosen per call from M:
-  * fixed capacity (small M / decode): every segment is padded to M rows and padding carries
-    ids = -1, so the split sizes are static -- no count exchange, no host sync, graph-capturable;
-  * exact splits (large M / prefill): counts are exchanged first and read on the host once.
+Three exchange modes, chosen from the group-agreed capacity (never from a rank-local value):
+  * p2p   (decode): no collective at all -- stores into / loads from the peers' memory over NVLink
+    (csrc/ep_p2p.cu), call counter on the device, CUDA-graph capturable (EPMoE.graphed);
+  * fixed (decode without peer access): every segment is padded to `capacity` rows and padding carries
+    ids = -1, so the split sizes are static -- no count exchange, no host sync;
+  * exact (prefill): row and slot counts are exchanged first and read on the host once.
 
 The device work is behind a small backend object so the host orchestration (split sizes, buffer
 offsets, ordering of the collectives) can be exercised on CPU under ``gloo`` by the tests, which plug
@@ -35,8 +43,9 @@ from . import ops
 class CudaBackend:
     """The product backend: every method ends in libsglb200.so kernels."""
 
-    def __init__(self, weights, fmt, e_local, topk, is_vnni=False):
-        self.w, self.fmt, self.e_local, self.topk, self.is_vnni = weights, fmt, e_local, topk, is_vnni
+    def __init__(self, weights, fmt, e_local, topk, is_vnni=False, path=L.PATH_AUTO, shared=None):
+        self.w, self.fmt, self.e_local, self.topk, self.is_vnni, self.path = weights, fmt, e_local, topk, is_vnni, path
+        self.shared = shared   # dict(w1, w2, s1, s2, block, fmt) of the replicated shared expert, or None
 
     @staticmethod
     def _s():
@@ -44,11 +53,12 @@ class CudaBackend:
 
     def plan(self, ids, E, world):
         M, topk = ids.shape
-        dest_row = torch.empty(M, world, dtype=torch.int32, device=ids.device)
-        send_count = torch.empty(world, dtype=torch.int32, device=ids.device)
-        L.check(L.load().sglb_ep_plan(ids.data_ptr(), M, topk, E, world, dest_row.data_ptr(),
-                                      send_count.data_ptr(), self._s()))
-        return dest_row, send_count
+        i32 = dict(dtype=torch.int32, device=ids.device)
+        dest_row, send_count = torch.empty(M, world, **i32), torch.empty(world, **i32)
+        slot_index, send_slots = torch.empty(M, topk, **i32), torch.empty(world, **i32)
+        L.check(L.load().sglb_ep_plan(ids.data_ptr(), M, topk, E, world, dest_row.data_ptr(), send_count.data_ptr(),
+                                      slot_index.data_ptr(), send_slots.data_ptr(), self._s()))
+        return dest_row, send_count, slot_index, send_slots
 
     def pack(self, x, ids, tw, dest_row, send_count, E, world, cap, rows):
         M, H = x.shape
@@ -60,26 +70,48 @@ class CudaBackend:
                                       send_meta.data_ptr(), self._s()))
         return send_x, send_meta
 
-    def experts(self, x, meta):
+    def ret_index(self, recv_meta, world, cap, recv_count=None, recv_slots=None):
+        rows, topk = recv_meta.shape[0], self.topk
+        out = torch.empty(rows, topk, dtype=torch.int32, device=recv_meta.device)
+        L.check(L.load().sglb_ep_ret_index(recv_meta.data_ptr(), 2 * topk, rows, topk, world, cap, ops._ptr(recv_count),
+                                           ops._ptr(recv_slots), out.data_ptr(), self._s()))
+        return out
+
+    def experts_slots(self, x, meta, ret_index, ret_rows, hint=0.0):
+        """Local experts over the received rows; the stage-2 epilogue writes slot (i, j) to ret[ret_index[i, j]]."""
         topk = self.topk
         ids = meta[:, :topk].contiguous()
         tw = meta[:, topk:].contiguous().view(torch.float32)
+        ret = torch.empty(ret_rows, x.shape[1], dtype=x.dtype, device=x.device)
+        if x.shape[0] == 0 or ret_rows == 0:
+            return ret
         w = self.w
         return ops.fused_experts_impl(x, w["w1"], w["w2"], tw, ids, False, self.fmt, w.get("s1"), w.get("s2"),
-                                      w.get("block"), self.is_vnni)
+                                      w.get("block"), self.is_vnni, path=self.path, slot_out=ret, slot_map=ret_index,
+                                      rows_per_expert_hint=hint)
 
-    def experts_into(self, x, tw, ids, out):
-        """Local experts over received slots with separate ids / weights tensors, result written to `out`."""
+    def experts_into(self, x, tw, ids, y, hint=0.0):
+        """Local experts over received rows with separate ids / weights tensors, slot rows written to `y`."""
         w = self.w
         return ops.fused_experts_impl(x, w["w1"], w["w2"], tw, ids, False, self.fmt, w.get("s1"), w.get("s2"),
-                                      w.get("block"), self.is_vnni, out=out)
+                                      w.get("block"), self.is_vnni, path=self.path, slot_out=y,
+                                      rows_per_expert_hint=hint)
 
-    def combine(self, ret, dest_row, send_count, world, cap):
-        M = dest_row.shape[0]
+    def shared_mlp(self, x):
+        """silu_and_mul(x W1^T) W2^T of the replicated shared expert on the local tokens (bf16), or None."""
+        if self.shared is None or x.shape[0] == 0:
+            return None
+        s = self.shared
+        return ops.shared_expert_impl(x, s["w1"], s["w2"], None, 1.0, False, s.get("fmt", self.fmt), s.get("s1"),
+                                      s.get("s2"), s.get("block"), self.is_vnni)
+
+    def combine(self, ret, ids, slot_index, send_slots, E, world, cap, shared_y=None, rsf=1.0):
+        M, topk = ids.shape
         H = ret.shape[1]
         out = torch.empty(M, H, dtype=ret.dtype, device=ret.device)
-        L.check(L.load().sglb_ep_combine(ret.data_ptr(), dest_row.data_ptr(), send_count.data_ptr(), M, world, H,
-                                         cap, out.data_ptr(), self._s()))
+        L.check(L.load().sglb_ep_combine(ret.data_ptr(), ids.data_ptr(), slot_index.data_ptr(), send_slots.data_ptr(),
+                                         M, topk, E, world, H, cap, ops._ptr(shared_y), float(rsf), out.data_ptr(),
+                                         self._s()))
         return out
 
 
@@ -94,10 +126,21 @@ class DistComm:
     def all_to_all(self, out, inp, out_splits=None, in_splits=None):
         dist.all_to_all_single(out, inp, out_splits, in_splits, group=self.group)
 
-    def exchange_counts(self, send_count):
-        recv = torch.empty_like(send_count)
-        dist.all_to_all_single(recv, send_count, group=self.group)
+    def exchange_counts(self, send_counts):
+        """send_counts [world, c] -> what every peer sends to this rank, same shape."""
+        recv = torch.empty_like(send_counts)
+        dist.all_to_all_single(recv.view(-1), send_counts.contiguous().view(-1), group=self.group)
         return recv
+
+    def max_int(self, value, device):
+        t = torch.tensor([int(value)], dtype=torch.int64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return int(t.item())
+
+    def all_gather_object(self, obj):
+        out = [None] * self.world
+        dist.all_gather_object(out, obj, group=self.group)
+        return out
 
 
 class _DevMem:
@@ -110,13 +153,18 @@ class _DevMem:
 class PeerExchange:
     """Decode-regime exchange over NVLink peer memory (csrc/ep_p2p.cu): one cudaMalloc'd region per rank,
     mapped into every peer through CUDA IPC; rows, ids and weights are stored straight into the owners'
-    receive buffers and partial results are read back with peer loads.  No NCCL call on the data path --
-    torch.distributed only carries the 64-byte IPC handles once, at construction."""
+    receive buffers and the per-slot result rows are read back with peer loads.  No NCCL call on the data
+    path -- torch.distributed only carries the geometry check and the 64-byte IPC handles once, at construction."""
 
-    def __init__(self, group, world, rank, cap, H, topk, device):
+    def __init__(self, comm, cap, H, topk, device):
         import ctypes as C
         lib = L.load()
+        world, rank = comm.world, comm.rank
         self.world, self.rank, self.cap, self.H, self.topk = world, rank, cap, H, topk
+        # every rank must have built the same geometry: offsets into a peer's region are computed locally
+        geo = comm.all_gather_object((world, cap, H, topk))
+        if any(g != geo[0] for g in geo):
+            raise RuntimeError(f"PeerExchange: ranks disagree on (world, capacity, H, topk): {geo}")
         offs = (C.c_size_t * 8)()
         self.nbytes = lib.sglb_ep_p2p_region_bytes(world, cap, H, topk, offs)
         if self.nbytes == 0:
@@ -129,8 +177,7 @@ class PeerExchange:
             L.check(lib.sglb_p2p_alloc(self.nbytes, C.byref(base), handle))
         except RuntimeError as e:  # keep going: every rank must reach the collective below
             status = str(e)
-        gathered = [None] * world
-        dist.all_gather_object(gathered, (status, bytes(handle.raw)), group=group)
+        gathered = comm.all_gather_object((status, bytes(handle.raw)))
         self.base = base.value
         self.peers = (C.c_void_p * world)()
         self._opened = []
@@ -150,83 +197,228 @@ class PeerExchange:
         else:
             status = next(g[0] for g in gathered if g[0] != "ok")
         # every rank learns whether every rank mapped every peer: all use the path or none does
-        final = [None] * world
-        dist.all_gather_object(final, status, group=group)
-        bad = [f for f in final if f != "ok"]
+        bad = [f for f in comm.all_gather_object(status) if f != "ok"]
         if bad:
             self.close()
             raise RuntimeError(f"PeerExchange: peer mapping failed on some rank: {bad[0]}")
         mem = torch.as_tensor(_DevMem(self.base, self.nbytes), device=device)
         rows = world * cap
 
-        def view(off, dtype, cols):
-            nb = rows * cols * torch.empty((), dtype=dtype).element_size()
-            return mem[off:off + nb].view(dtype).view(rows, cols)
-        self.recv_x = [view(self.offs[p], torch.bfloat16, H) for p in range(2)]
-        self.recv_ids = [view(self.offs[2 + p], torch.int32, topk) for p in range(2)]
-        self.recv_tw = [view(self.offs[4 + p], torch.float32, topk) for p in range(2)]
-        self.y = [view(self.offs[6 + p], torch.bfloat16, H) for p in range(2)]
-        self.seq = 0
+        def view(off, dtype, nrows, cols):
+            nb = nrows * cols * torch.empty((), dtype=dtype).element_size()
+            return mem[off:off + nb].view(dtype).view(nrows, cols)
+        self.recv_x = [view(self.offs[p], torch.bfloat16, rows, H) for p in range(2)]
+        self.recv_ids = [view(self.offs[2 + p], torch.int32, rows, topk) for p in range(2)]
+        self.recv_tw = [view(self.offs[4 + p], torch.float32, rows, topk) for p in range(2)]
+        self.y = [view(self.offs[6 + p], torch.bfloat16, rows * topk, H) for p in range(2)]
+        self.calls = 0
+        self.side = torch.cuda.Stream(device=device)
 
     def close(self):
         lib = L.load()
         for p in self._opened:
             lib.sglb_p2p_close(p)
         self._opened = []
-        if self.base:
+        if getattr(self, "base", None):
             lib.sglb_p2p_free(self.base)
             self.base = None
 
-    def run(self, x, tw, ids, E, experts_fn):
-        """dispatch -> wait -> experts_fn(recv_x, recv_tw, recv_ids, out=y) -> combine; returns [M, H]."""
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # interpreter shutdown
+            pass
+
+    def enqueue(self, x, tw, ids, E, backend, par, rsf=1.0, out=None, hint=0.0):
+        """dispatch -> (shared expert on a side stream) -> wait -> local experts into y -> combine, all
+        asynchronous on the current stream; `par` selects the buffer set."""
         lib = L.load()
-        s = torch.cuda.current_stream().cuda_stream
+        main = torch.cuda.current_stream()
+        s = main.cuda_stream
         M = x.shape[0]
-        self.seq += 1
-        seq, par = self.seq & 0xFFFFFFFF, self.seq & 1
-        L.check(lib.sglb_ep_p2p_dispatch(x.data_ptr(), ids.data_ptr(), tw.data_ptr(), M, self.topk, E, self.world,
-                                         self.rank, self.H, self.cap, self.peers, seq, s))
-        L.check(lib.sglb_ep_p2p_wait_dispatch(self.base, self.world, self.cap, self.H, self.topk, seq, s))
-        experts_fn(self.recv_x[par], self.recv_tw[par], self.recv_ids[par], self.y[par])
-        out = torch.empty_like(x)
-        L.check(lib.sglb_ep_p2p_combine(ids.data_ptr(), M, self.topk, E, self.world, self.rank, self.H, self.cap,
-                                        self.peers, seq, out.data_ptr(), s))
+        L.check(lib.sglb_ep_p2p_dispatch(ops._ptr(x), ops._ptr(ids), ops._ptr(tw), M, self.topk, E, self.world,
+                                         self.rank, self.H, self.cap, self.peers, par, s))
+        shared_y = None
+        if backend.shared is not None and M > 0:   # overlaps the exchange and the routed experts
+            self.side.wait_stream(main)
+            with torch.cuda.stream(self.side):
+                shared_y = backend.shared_mlp(x)
+        L.check(lib.sglb_ep_p2p_wait_dispatch(self.base, self.world, self.cap, self.H, self.topk, s))
+        backend.experts_into(self.recv_x[par], self.recv_tw[par], self.recv_ids[par], self.y[par], hint)
+        if out is None:
+            out = torch.empty_like(x)
+        if shared_y is not None:
+            main.wait_stream(self.side)
+        L.check(lib.sglb_ep_p2p_combine(ops._ptr(ids), M, self.topk, E, self.world, self.rank, self.H, self.cap,
+                                        self.peers, par, ops._ptr(shared_y), float(rsf), ops._ptr(out), s))
         return out
+
+    def run(self, x, tw, ids, E, backend, rsf=1.0, hint=0.0):
+        self.calls += 1
+        return self.enqueue(x, tw, ids, E, backend, self.calls & 1, rsf, None, hint)
+
+
+class GraphedEP:
+    """The peer-memory layer call captured in CUDA graphs over static buffers (one graph per buffer parity,
+    replayed alternately): at decode sizes the ~14 launches of a call cost more host time than the kernels
+    run.  Fill `hidden`, `topk_weights`, `topk_ids` -- or, when the layer was given a `router` (layer.Router),
+    `hidden` and `gating`: the router kernel then runs inside the graph -- and read `out`.  Every rank must
+    replay in lockstep, like any collective."""
+
+    def __init__(self, layer, px, num_tokens, H, device, router=None):
+        self.layer, self.px, self.router = layer, px, router
+        topk = layer.topk
+        self.hidden = torch.zeros(num_tokens, H, dtype=torch.bfloat16, device=device)
+        self.gating = torch.zeros(num_tokens, layer.E, dtype=torch.bfloat16, device=device) if router is not None else None
+        self.topk_weights = torch.zeros(num_tokens, topk, dtype=torch.float32, device=device)
+        self.topk_ids = torch.full((num_tokens, topk), -1, dtype=torch.int32, device=device)
+        self.out = torch.empty_like(self.hidden)
+        hint = layer._hint(px.cap)
+        B = layer.backend
+        lib = L.load()
+        e_local, _, I = ops._weight_geometry(B.w["w1"], B.w["w2"], B.fmt, B.is_vnni)
+        nws = lib.sglb_fused_experts_workspace_bytes(layer.world * px.cap, topk, e_local, H, I, B.fmt)
+        self._ws = torch.empty(max(nws, 1 << 20), dtype=torch.uint8, device=device)
+        nside = 1 << 20
+        if B.shared is not None:
+            nside = max(nside, lib.sglb_fused_experts_workspace_bytes(num_tokens, 1, 1, H, B.shared["w2"].shape[-1],
+                                                                      B.shared.get("fmt", B.fmt)))
+        self._ws_side = torch.empty(nside, dtype=torch.uint8, device=device)
+        cap_stream = torch.cuda.Stream(device=device)
+        self.graphs = [None, None]
+
+        def enqueue(par):
+            if router is not None:
+                router(self.gating, self.topk_weights, self.topk_ids)
+            px.enqueue(self.hidden, self.topk_weights, self.topk_ids, layer.E, B, par, layer.rsf, self.out, hint)
+
+        with torch.cuda.device(device):
+            key = (device.index, cap_stream.cuda_stream)
+            skey = (device.index, px.side.cuda_stream)
+            cap_stream.wait_stream(torch.cuda.current_stream())
+            with ops._launch_lock:
+                saved = {k: ops._workspaces.get(k) for k in (key, skey)}
+                ops._workspaces[key], ops._workspaces[skey] = self._ws, self._ws_side
+                try:
+                    with torch.cuda.stream(cap_stream):
+                        # two eager calls (both parities): lazy one-off work (function attributes, tensor maps) stays
+                        # out of the capture, and every rank's device-side call counter advances identically
+                        for _ in range(2):
+                            px.calls += 1
+                            n0 = ops.launch_count()
+                            enqueue(px.calls & 1)
+                            self.kernels_per_replay = ops.launch_count() - n0
+                    cap_stream.synchronize()
+                    for par in (0, 1):
+                        g = torch.cuda.CUDAGraph()
+                        with torch.cuda.graph(g, stream=cap_stream):
+                            enqueue(par)
+                        self.graphs[par] = g
+                finally:
+                    for k, v in saved.items():
+                        if v is None:
+                            ops._workspaces.pop(k, None)
+                        else:
+                            ops._workspaces[k] = v
+            torch.cuda.current_stream().wait_stream(cap_stream)
+
+    def __call__(self, hidden_states=None, topk_weights=None, topk_ids=None, gating=None):
+        if hidden_states is not None:
+            self.hidden.copy_(hidden_states, non_blocking=True)
+        if gating is not None:
+            self.gating.copy_(gating, non_blocking=True)
+        if topk_weights is not None:
+            self.topk_weights.copy_(topk_weights, non_blocking=True)
+        if topk_ids is not None:
+            self.topk_ids.copy_(topk_ids, non_blocking=True)
+        self.px.calls += 1
+        self.graphs[self.px.calls & 1].replay()
+        return self.out
 
 
 class EPMoE:
-    """One MoE layer's routed experts, expert-parallel.
+    """One MoE layer's routed experts (and optionally its shared expert), expert-parallel.
 
     weights: dict(w1=[E/n, 2I, H], w2=[E/n, H, I], s1, s2, block) -- this rank's experts only.
-    forward(x[M,H] bf16, topk_weights[M,k] f32, topk_ids[M,k] i32 with GLOBAL expert ids) -> [M,H] bf16.
+    shared:  dict(w1=[2Is, H], w2=[H, Is], s1, s2, block[, fmt]) -- the replicated shared expert; with it
+             forward returns shared_expert(x) + routed(x) * routed_scaling_factor (shared_expert_cpu's contract).
+    capacity: rows reserved per (source, destination) pair.  A GROUP-WIDE constant >= every rank's token count;
+             if omitted it is agreed once, at the first call, as the next power of two of the maximum token count
+             over the ranks (one all-reduce).  Ranks may hold different -- also zero -- token counts.
+    forward(x[M,H] bf16, topk_weights[M,k] f32, topk_ids[M,k] i32 with GLOBAL expert ids) -> [M,H] bf16,
+    bit-identical to the single-GPU fused_experts (+ shared_expert) on the same tokens when both sides run the
+    same GEMM kernel variant (pass `path`; SGLB_PATH_AUTO picks the kernel from the batch size).
     """
 
     FIXED_CAPACITY_BYTES = 32 << 20   # per-rank dispatch payload up to which padding beats a host sync
 
-    def __init__(self, weights, fmt, num_experts, topk, comm=None, backend=None, is_vnni=False):
+    def __init__(self, weights, fmt, num_experts, topk, comm=None, backend=None, is_vnni=False, capacity=None,
+                 shared=None, routed_scaling_factor=1.0, path=L.PATH_AUTO):
         self.comm = comm if comm is not None else DistComm()
         world = self.comm.world
         if num_experts % world != 0:
             raise RuntimeError(f"EPMoE: {num_experts} experts do not split evenly over {world} ranks")
         self.E, self.topk, self.world = num_experts, topk, world
-        self.backend = backend if backend is not None else CudaBackend(weights, fmt, num_experts // world, topk, is_vnni)
+        self.backend = backend if backend is not None else CudaBackend(weights, fmt, num_experts // world, topk, is_vnni,
+                                                                       path, shared)
+        self.rsf = float(routed_scaling_factor)
+        self.capacity = None if capacity is None else int(capacity)
         self.last_mode = None
         self._peer = {}          # (cap, H) -> PeerExchange
         self._peer_failed = False
+
+    def close(self):
+        for px in self._peer.values():
+            px.close()
+        self._peer = {}
+
+    def _hint(self, cap):
+        """Expected routed rows per local expert: the received rows are mostly masked (a rank owns ~1/world of
+        the slots), so the kernel-path rule of fused_experts gets this estimate instead of rows*topk/E_local."""
+        return float(self.world * cap * self.topk) / float(self.E)
+
+    def _agreed_capacity(self, M, device, capacity):
+        if capacity is not None:
+            return int(capacity)
+        if self.capacity is None:
+            mx = self.comm.max_int(M, device)
+            self.capacity = max(16, 1 << max(0, mx - 1).bit_length())
+        return self.capacity
 
     def _peer_exchange(self, cap, H, device):
         key = (cap, H)
         if key not in self._peer:
             try:
-                self._peer[key] = PeerExchange(self.comm.group, self.world, self.comm.rank, cap, H, self.topk, device)
+                while len(self._peer) >= 2:     # bounded: each entry pins an IPC-mapped region on every rank
+                    self._peer.pop(next(iter(self._peer))).close()
+                self._peer[key] = PeerExchange(self.comm, cap, H, self.topk, device)
             except RuntimeError:
                 self._peer_failed = True     # decided identically on every rank (see PeerExchange.__init__)
                 return None
         return self._peer[key]
 
+    def _mode(self, cap, H, x, mode):
+        if mode is not None:
+            return mode
+        # every rank must take the same branch: decide from group-wide constants only
+        mode = "fixed" if cap * self.world * H * 2 <= self.FIXED_CAPACITY_BYTES else "exact"
+        if (mode == "fixed" and self.world > 1 and x.is_cuda and isinstance(self.backend, CudaBackend) and H % 8 == 0
+                and not self._peer_failed and os.environ.get("SGLB_EP_P2P", "1") != "0"):
+            mode = "p2p"
+        return mode
+
+    def graphed(self, num_tokens, H, device, capacity=None, router=None):
+        """CUDA-graph form of the peer-memory path for a fixed token count (decode); None if peer memory is not
+        available.  `router` (layer.Router): run the router kernel inside the graph, on a static `gating` buffer.
+        Collective: every rank must call it, and replay in lockstep."""
+        cap = self._agreed_capacity(num_tokens, device, capacity)
+        px = self._peer_exchange(cap, H, device)
+        if px is None:
+            return None
+        self.last_mode = "p2p"
+        return GraphedEP(self, px, num_tokens, H, device, router)
+
     def forward(self, x, topk_weights, topk_ids, mode=None, capacity=None):
-        """capacity: rows reserved per destination rank in fixed mode; must be the SAME on every rank and
-        >= every rank's token count (default: this rank's M, i.e. all ranks hold the same M)."""
         B, comm, world = self.backend, self.comm, self.world
         M, H = x.shape
         if topk_ids.shape != (M, self.topk) or topk_weights.shape != (M, self.topk):
@@ -234,41 +426,68 @@ class EPMoE:
         ids = topk_ids.to(torch.int32).contiguous()
         tw = topk_weights.to(torch.float32).contiguous()
         x = x.contiguous()
-        dest_row, send_count = B.plan(ids, self.E, world)
-        cap = M if capacity is None else int(capacity)
+        cap = self._agreed_capacity(M, x.device, capacity)
         if cap < M:
-            raise RuntimeError(f"EPMoE: capacity {cap} is smaller than the {M} local tokens")
-        if mode is None:
-            # every rank must take the same branch: decide from static shapes only
-            mode = "fixed" if cap * world * H * x.element_size() <= self.FIXED_CAPACITY_BYTES else "exact"
-            if (mode == "fixed" and world > 1 and x.is_cuda and isinstance(B, CudaBackend) and M >= 1 and H % 8 == 0
-                    and not self._peer_failed and os.environ.get("SGLB_EP_P2P", "1") != "0"):
-                mode = "p2p"
+            raise RuntimeError(f"EPMoE: the group capacity {cap} is smaller than this rank's {M} tokens; construct the "
+                               "layer with capacity >= the largest batch any rank will bring")
+        mode = self._mode(cap, H, x, mode)
         if mode == "p2p":
-            pcap = max(16, 1 << (cap - 1).bit_length())     # slots per source: next power of two
-            px = self._peer_exchange(pcap, H, x.device)
+            px = self._peer_exchange(cap, H, x.device)
             if px is None:
                 mode = "fixed"
             else:
                 self.last_mode = mode
-                return px.run(x, tw, ids, self.E, B.experts_into)
+                return px.run(x, tw, ids, self.E, B, self.rsf, self._hint(cap))
         self.last_mode = mode
+        shared_y = None
+        if getattr(B, "shared", None) is not None and M > 0:
+            shared_y = self._shared_async(B, x)
+        dest_row, send_count, slot_index, send_slots = B.plan(ids, self.E, world)
+        topk = self.topk
         if mode == "fixed":
-            rows, recv_rows, sc, rc = cap * world, cap * world, None, None
+            rows = recv_rows = cap * world
+            ret_rows = send_ret_rows = cap * world * topk
+            sc = rc = ss = rs = None
+            rcount_dev = rslots_dev = None
+            hint = self._hint(cap)
         else:
-            recv_count = comm.exchange_counts(send_count)
-            both = torch.stack([send_count, recv_count]).cpu()      # the one host sync of this mode
-            sc, rc = both[0].tolist(), both[1].tolist()
-            cap, rows, recv_rows = 0, sum(sc), sum(rc)
+            counts = torch.stack([send_count, send_slots], dim=1).contiguous()
+            recv_counts = comm.exchange_counts(counts)
+            both = torch.cat([counts, recv_counts], dim=1).cpu()      # the one host sync of this mode
+            sc, ss, rc, rs = (both[:, i].tolist() for i in range(4))
+            cap = 0
+            rows, recv_rows, ret_rows, send_ret_rows = sum(sc), sum(rc), sum(ss), sum(rs)
+            rcount_dev, rslots_dev = recv_counts[:, 0].contiguous(), recv_counts[:, 1].contiguous()
+            hint = float(send_ret_rows) / float(self.E // world)
         send_x, send_meta = B.pack(x, ids, tw, dest_row, send_count, self.E, world, cap, rows)
         recv_x = torch.empty(recv_rows, H, dtype=x.dtype, device=x.device)
-        recv_meta = torch.empty(recv_rows, 2 * self.topk, dtype=torch.int32, device=x.device)
+        recv_meta = torch.empty(recv_rows, 2 * topk, dtype=torch.int32, device=x.device)
         comm.all_to_all(recv_x, send_x, rc, sc)
         comm.all_to_all(recv_meta, send_meta, rc, sc)
-        y = B.experts(recv_x, recv_meta)
-        ret = torch.empty(rows, H, dtype=x.dtype, device=x.device)
-        comm.all_to_all(ret, y, sc, rc)
-        return B.combine(ret, dest_row, send_count, world, cap)
+        ret_index = B.ret_index(recv_meta, world, cap, rcount_dev, rslots_dev)
+        y = B.experts_slots(recv_x, recv_meta, ret_index, send_ret_rows, hint)
+        ret = torch.empty(ret_rows, H, dtype=x.dtype, device=x.device)
+        comm.all_to_all(ret, y, ss, rs)
+        if shared_y is not None:
+            shared_y = shared_y()
+        return B.combine(ret, ids, slot_index, send_slots, self.E, world, cap, shared_y, self.rsf)
+
+    def _shared_async(self, B, x):
+        """Shared expert MLP on a side stream (CUDA) while the exchange runs; returns a join function."""
+        if not x.is_cuda:
+            y = B.shared_mlp(x)
+            return lambda: y
+        if not hasattr(self, "_side"):
+            self._side = torch.cuda.Stream(device=x.device)
+        main = torch.cuda.current_stream()
+        self._side.wait_stream(main)
+        with torch.cuda.stream(self._side):
+            y = B.shared_mlp(x)
+
+        def join():
+            main.wait_stream(self._side)
+            return y
+        return join
 
     def forward_host(self, x_host, tw_host, ids_host, out_host=None):
         """End-to-end form used by bench.py's e2e leg: pinned host buffers in, host result out."""

@@ -311,16 +311,21 @@ def _router(gating_output, correction_bias, topk, renormalize, num_expert_group,
                 raise RuntimeError("grouped_topk: num_token_non_padded must hold one int32 / int64 value")
             npad = _to_dev(npad, dev)
             npad64 = int(npad.dtype == torch.int64)
-        w = torch.empty(M, topk, dtype=torch.float32, device=dev)
-        ids = torch.empty(M, topk, dtype=torch.int32, device=dev)
+        def _direct(t, dtype):   # an out tensor the kernel can write in place
+            return (t is not None and t.is_cuda and t.device == dev and t.dtype == dtype and t.is_contiguous()
+                    and tuple(t.shape) == (M, topk))
+        direct = _direct(out_w, torch.float32) and _direct(out_ids, torch.int32)
+        w = out_w if direct else torch.empty(M, topk, dtype=torch.float32, device=dev)
+        ids = out_ids if direct else torch.empty(M, topk, dtype=torch.int32, device=dev)
         L.check(L.load().sglb_grouped_topk(
             g.data_ptr(), _DT[g.dtype], _ptr(b), _DT[b.dtype] if b is not None else 0, M, E, int(topk),
             int(num_expert_group), int(topk_group), int(bool(renormalize)), n_shared,
             float(1.0 if routed_scaling_factor is None else routed_scaling_factor), _ptr(npad), npad64,
             w.data_ptr(), ids.data_ptr(), _stream()))
     if out_w is not None:
-        out_w.copy_(w)
-        out_ids.copy_(ids)
+        if not direct:
+            out_w.copy_(w)
+            out_ids.copy_(ids)
         return None
     if not gating_output.is_cuda:
         return w.cpu(), ids.cpu()
@@ -442,9 +447,13 @@ def _host_graph(M, topk, fmt, w13, w2d, s13, s2, block_size, path):
 
 
 def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, fmt, w1_scale, w2_scale,
-                       block_size, is_vnni, path=L.PATH_AUTO, out=None):
+                       block_size, is_vnni, path=L.PATH_AUTO, out=None, w1_bias=None, w2_bias=None, alpha=None,
+                       limit=None, slot_out=None, slot_map=None, rows_per_expert_hint=0.0):
     """Format-explicit core behind every fused_experts_cpu signature vintage.  `out` (CUDA callers only):
-    a [M, H] bf16 device tensor that receives the result instead of a fresh allocation."""
+    a [M, H] bf16 device tensor that receives the result instead of a fresh allocation.
+    w1_bias [E, 2I] / w2_bias [E, H] / alpha / limit: the 17-argument vintage (gpt-oss expert biases and clamped
+    swiglu; include/sglb200.h).  slot_out (CUDA callers): bf16 rows addressed by routed slot (through slot_map if
+    given) instead of the reduced [M, H] result -- the expert-parallel return path; returns slot_out."""
     if hidden_states.dim() != 2 or hidden_states.dtype != torch.bfloat16:
         raise RuntimeError("fused_experts: hidden_states must be a 2-D bfloat16 tensor")
     if w1.dtype not in _WDT[fmt] or w2.dtype != w1.dtype:
@@ -472,7 +481,8 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
     with torch.cuda.device(dev):
         w13 = _resident_weight(w1, is_vnni, dev)
         w2d = _resident_weight(w2, is_vnni, dev)
-        if not on_cuda and _HOST_GRAPH and M <= _HOST_GRAPH_MAX_TOKENS and out is None:
+        extras = w1_bias is not None or w2_bias is not None or alpha is not None or limit is not None or slot_out is not None
+        if not on_cuda and _HOST_GRAPH and M <= _HOST_GRAPH_MAX_TOKENS and out is None and not extras:
             if fmt == L.FMT_MXFP4:
                 gs13, gs2 = _resident_mx_scale(w1_scale, is_vnni, dev), _resident_mx_scale(w2_scale, is_vnni, dev)
             elif fmt != L.FMT_BF16:
@@ -506,7 +516,24 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
         elif fmt != L.FMT_BF16:
             s13 = _resident_aux(w1_scale, dev, torch.float32)
             s2 = _resident_aux(w2_scale, dev, torch.float32)
-        if out is not None:
+        b13 = b2 = None
+        if w1_bias is not None or w2_bias is not None:
+            if w1_bias is None or w2_bias is None or tuple(w1_bias.shape) != (E, 2 * I) or tuple(w2_bias.shape) != (E, H):
+                raise RuntimeError("fused_experts: w1_bias / w2_bias must be [E, 2I] and [E, H]")
+            b13 = _resident_aux(w1_bias, dev, torch.float32, "b")
+            b2 = _resident_aux(w2_bias, dev, torch.float32, "b")
+        act = L.ACT_SILU
+        if alpha is not None or limit is not None:
+            act = L.ACT_SWIGLU_OAI
+        if slot_out is not None:
+            if not on_cuda or not slot_out.is_cuda or slot_out.dtype != torch.bfloat16 or not slot_out.is_contiguous() \
+                    or slot_out.shape[-1] != H:
+                raise RuntimeError("fused_experts: slot_out needs CUDA inputs and a contiguous bf16 [rows, H] CUDA tensor")
+            if slot_map is None and slot_out.numel() < M * topk * H:
+                raise RuntimeError("fused_experts: slot_out must hold M * topk rows")
+            if slot_map is not None and (slot_map.dtype != torch.int32 or slot_map.numel() != M * topk or not slot_map.is_cuda):
+                raise RuntimeError("fused_experts: slot_map must be an int32 CUDA tensor of M * topk entries")
+        elif out is not None:
             if not on_cuda or inplace or out.shape != x.shape or out.dtype != x.dtype or not out.is_contiguous() \
                     or out.device != x.device:
                 raise RuntimeError("fused_experts: out= needs CUDA inputs, inplace=False and a contiguous tensor like hidden_states")
@@ -520,9 +547,15 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
             p = L.MoeProblem(M=M, topk=topk, E=E, H=H, I=I, fmt=fmt, path=path, hidden=x.data_ptr(),
                              w13=w13.data_ptr(), w2=w2d.data_ptr(), topk_weights=tw.data_ptr(),
                              topk_ids=ids.data_ptr(), w13_scale=_ptr(s13), w2_scale=_ptr(s2), block_n=bn,
-                             block_k=bk, out=out.data_ptr(), workspace=ws.data_ptr(),
-                             workspace_bytes=ws.numel(), w13_scale_tiles=_ptr(t13), w2_scale_tiles=_ptr(t2))
+                             block_k=bk, out=_ptr(out), workspace=ws.data_ptr(),
+                             workspace_bytes=ws.numel(), w13_scale_tiles=_ptr(t13), w2_scale_tiles=_ptr(t2),
+                             w13_bias=_ptr(b13), w2_bias=_ptr(b2), act=act,
+                             alpha=float(1.702 if alpha is None else alpha), limit=float(0.0 if limit is None else limit),
+                             slot_out=_ptr(slot_out), slot_map=_ptr(slot_map),
+                             rows_per_expert_hint=float(rows_per_expert_hint))
             L.check(lib.sglb_fused_experts(p, _stream()))
+        if slot_out is not None:
+            return slot_out
         if on_cuda:
             if inplace and out is not hidden_states:
                 hidden_states.copy_(out)
@@ -619,8 +652,8 @@ def fused_experts(*args):
             raise RuntimeError(f"fused_experts: unknown quant method {fmt}")
         if n == 17:
             b1, b2, alpha, limit = args[12:16]
-            if b1 is not None or b2 is not None or alpha is not None or limit is not None:
-                raise RuntimeError("fused_experts: expert bias / clamped swiglu (alpha, limit) are not supported yet")
+            return fused_experts_impl(hs, w1, w2, tw, ids, bool(inplace), fmt, s1, s2, block, bool(is_vnni),
+                                      w1_bias=b1, w2_bias=b2, alpha=alpha, limit=limit)
     else:
         raise RuntimeError(f"fused_experts_cpu: expected 13, 14 or 17 positional arguments, got {n}")
     return fused_experts_impl(hs, w1, w2, tw, ids, bool(inplace), fmt, s1, s2, block, bool(is_vnni))
@@ -644,11 +677,20 @@ def shared_expert(*args):
     if use_int8 and use_fp8:
         raise RuntimeError("shared_expert: use_int8_w8a8 and use_fp8_w8a16 are mutually exclusive")
     fmt = L.FMT_INT8_W8A8 if use_int8 else (L.FMT_FP8_W8A16 if use_fp8 else L.FMT_BF16)
+    if fused_out is None:
+        raise RuntimeError("shared_expert: fused_experts_out must be a tensor")
+    return shared_expert_impl(hs, w1, w2, fused_out, rsf, bool(inplace), fmt, s1, s2, block, bool(is_vnni))
+
+
+def shared_expert_impl(hs, w1, w2, fused_out, rsf, inplace, fmt, s1, s2, block, is_vnni, out=None):
+    """Format-explicit core of shared_expert_cpu.  fused_out=None (CUDA callers): the MLP result alone,
+    silu_and_mul(x W1^T) W2^T in bf16 -- the expert-parallel layer adds `combined * rsf` in its combine kernel
+    (the same arithmetic as the fused epilogue).  `out`: CUDA tensor that receives the result."""
     if hs.dim() != 2 or hs.dtype != torch.bfloat16:
         raise RuntimeError("shared_expert: hidden_states must be a 2-D bfloat16 tensor")
     if w1.dim() != 2 or w2.dim() != 2 or w1.dtype not in _WDT[fmt] or w2.dtype != w1.dtype:
         raise RuntimeError("shared_expert: w1/w2 must be 2-D and match the quantization method")
-    if fused_out.shape != hs.shape or fused_out.dtype != torch.bfloat16:
+    if fused_out is not None and (fused_out.shape != hs.shape or fused_out.dtype != torch.bfloat16):
         raise RuntimeError("shared_expert: fused_experts_out must match hidden_states")
     M, H = hs.shape
     packed8 = bool(is_vnni) and fmt == L.FMT_INT8_W8A8
@@ -673,13 +715,17 @@ def shared_expert(*args):
         w2d = _resident_weight(w2, bool(is_vnni), dev)
         s1d = _resident_aux(s1, dev, torch.float32)
         s2d = _resident_aux(s2, dev, torch.float32)
-        out = x if (on_cuda and inplace and x.data_ptr() == hs.data_ptr()) else torch.empty_like(x)
+        if out is not None:
+            if not on_cuda or inplace or out.shape != x.shape or out.dtype != x.dtype or not out.is_contiguous():
+                raise RuntimeError("shared_expert: out= needs CUDA inputs, inplace=False and a contiguous tensor like hidden_states")
+        else:
+            out = x if (on_cuda and inplace and x.data_ptr() == hs.data_ptr()) else torch.empty_like(x)
         nws = lib.sglb_fused_experts_workspace_bytes(M, 1, 1, H, I, fmt)
         with _launch_lock:
             ws = _workspace(nws, dev)
             p = L.SharedProblem(M=M, H=H, I=I, fmt=fmt, path=L.PATH_AUTO, hidden=x.data_ptr(), w1=w1d.data_ptr(),
                                 w2=w2d.data_ptr(), w1_scale=_ptr(s1d), w2_scale=_ptr(s2d), block_n=bn, block_k=bk,
-                                fused_out=fo.data_ptr(), routed_scaling_factor=float(rsf), out=out.data_ptr(),
+                                fused_out=_ptr(fo), routed_scaling_factor=float(rsf), out=out.data_ptr(),
                                 workspace=ws.data_ptr(), workspace_bytes=ws.numel())
             L.check(lib.sglb_shared_expert(p, _stream()))
         if on_cuda:

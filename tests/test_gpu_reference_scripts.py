@@ -20,4 +20,10 @@ def test_reference_script_passes_unmodified(script):
     rc, out, err, verdicts, _ = R.run_script(REF, script, 900)
     assert rc == 0, err[-2000:]
     assert verdicts, f"{script} printed no verdict:\n{out[-2000:]}"
+    if not all(verdicts) and script == "test_biased_grouped_topk.py":
+        # the script's bf16 biases collide and torch.topk(sorted=False) breaks exact ties either way: every row that
+        # differs from the script's oracle must be such a tie (tools/run_reference_scripts.py: adjudicate_router)
+        ties_only, note = R.adjudicate_router(REF, script)
+        assert ties_only, note
+        return
     assert all(verdicts), f"{script}: {verdicts.count(False)} of {len(verdicts)} comparisons printed False:\n{out[-3000:]}"

@@ -201,3 +201,23 @@ def test_moe_align_properties():
         assert torch.equal(al["slot_pos"][ss], torch.arange(nv, dtype=torch.int32))
         assert int(al["chunk_list"][:, 2].sum()) == nv and int(al["tile_list"][:, 2].sum()) == nv
         assert (al["chunk_list"][:, 2] <= 8).all()
+
+
+def test_fused_experts_lean_is_fused_experts():
+    """bench.py's CPU legs call the per-expert-dequantising form; it must be the same function bit for bit."""
+    torch.manual_seed(9)
+    M, E, topk, H, I = 19, 6, 3, 256, 128
+    x = (torch.randn(M, H) / 10).bfloat16()
+    tw, ids = torch.topk(torch.softmax(torch.randn(M, E), dim=-1), topk)
+    ids = ids.to(torch.int32)
+    ids[2, 1] = -1
+    w1 = (torch.randn(E, 2 * I, H) * 50).to(torch.float8_e4m3fn)
+    w2 = (torch.randn(E, H, I) * 50).to(torch.float8_e4m3fn)
+    s1, s2 = torch.randn(E, 2 * I // 64, H // 128) * 1e-2, torch.randn(E, H // 64, I // 128) * 1e-2
+    assert torch.equal(O.fused_experts_lean(x, w1, w2, tw, ids, "fp8", s1, s2, [64, 128]),
+                       O.fused_experts(x, w1, w2, tw, ids, "fp8", s1, s2, [64, 128]))
+    q1 = torch.randint(0, 256, (E, 2 * I, H // 2), dtype=torch.uint8)
+    q2 = torch.randint(0, 256, (E, H, I // 2), dtype=torch.uint8)
+    e1 = torch.randint(120, 124, (E, 2 * I, H // 32), dtype=torch.uint8)
+    e2 = torch.randint(120, 124, (E, H, I // 32), dtype=torch.uint8)
+    assert torch.equal(O.fused_experts_lean(x, q1, q2, tw, ids, "mxfp4", e1, e2), O.fused_experts(x, q1, q2, tw, ids, "mxfp4", e1, e2))

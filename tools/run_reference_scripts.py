@@ -12,7 +12,10 @@ else ./baseline/_ref (git-ignored scratch that travels to the GPU box), else /ro
 
   python tools/run_reference_scripts.py [--ref DIR] [--out profiles/r2_reference_scripts.txt] [--bench]
 
-Exit status 1 if any verdict is False, a script crashes, or a script prints no verdict at all.
+Exit status 1 if any verdict is False, a script crashes, or a script prints no verdict at all.  One exception,
+spelled out in the report: test_biased_grouped_topk.py's inputs contain exact ties of the choice score (colliding
+bf16 biases under a saturated sigmoid) on which its oracle, torch.topk(sorted=False), picks either index; its False
+verdicts are re-examined row by row (adjudicate_router) and accepted only if every differing row is such a tie.
 """
 import argparse
 import os
@@ -69,6 +72,57 @@ def run_script(ref, name, timeout):
     return rc, out, err, verdicts, dt
 
 
+# ---- adjudication of router verdicts that depend on exact ties ----------------------------------------------
+# The router scripts compare a dense scatter of (ids, weights) with their own torch oracle, whose picks come from
+# torch.topk(sorted=False): on EXACT ties of the choice score at the top-k boundary torch's CPU kernel
+# (std::nth_element) picks either index, about 50/50 (measured), so no fixed tie-break can reproduce it
+# ("ids attached to [equal scores] are not pinned").  The reference's own biased case has such rows:
+# bf16 biases collide and the x 2M logits saturate the sigmoid.  A False verdict of a router script is therefore
+# re-examined: the script is run once more, still unmodified, with a recording wrapper around the op, and every
+# row whose id set differs from the script's oracle must select the same multiset of choice scores and weights.
+ADJUDICATE = r"""
+import runpy, sys, torch
+import sgl_kernel.common_ops as co
+calls = []
+real = co.biased_grouped_topk_cpu
+def rec(tw, ids, hs, gating, bias, topk, renorm, G, tg):
+    real(tw, ids, hs, gating, bias, topk, renorm, G, tg)
+    calls.append((hs.clone(), gating.clone(), bias.clone(), topk, renorm, G, tg, tw.clone(), ids.clone()))
+co.biased_grouped_topk_cpu = rec
+g = runpy.run_path(sys.argv[1], run_name="__main__")
+oracle = g["biased_grouped_topk"]
+rows = diff = tie_only = 0
+for hs, gating, bias, topk, renorm, G, tg, tw, ids in calls:
+    rw, ri = oracle(hs, gating.float(), bias.float(), topk, renorm, G, tg)
+    s = gating.float().sigmoid()
+    c = s + bias.float().unsqueeze(0)
+    for m in range(ids.shape[0]):
+        a, b = sorted(ri[m].tolist()), sorted(ids[m].tolist())
+        rows += 1
+        if a == b:
+            continue
+        diff += 1
+        ca, cb = sorted(c[m, a].tolist()), sorted(c[m, b].tolist())
+        wa, wb = sorted(rw[m].tolist()), sorted(tw[m].tolist())
+        if ca == cb and all(abs(x - y) <= 1e-6 + 1e-5 * abs(x) for x, y in zip(wa, wb)):
+            tie_only += 1
+print(f"ADJUDICATION rows={rows} differing={diff} exact_tie_only={tie_only}")
+"""
+
+
+def adjudicate_router(ref, name):
+    env = dict(os.environ)
+    env["PYTHONPATH"] = DROPIN + os.pathsep + ref + os.pathsep + env.get("PYTHONPATH", "")
+    p = subprocess.run([sys.executable, "-c", ADJUDICATE, os.path.join(ref, name)], cwd=ref, env=env,
+                       capture_output=True, text=True, timeout=600)
+    m = re.search(r"ADJUDICATION rows=(\d+) differing=(\d+) exact_tie_only=(\d+)", p.stdout)
+    if p.returncode != 0 or not m:
+        return None, (p.stderr.strip().splitlines() or ["no output"])[-1]
+    rows, diff, ties = (int(v) for v in m.groups())
+    return diff == ties, (f"{diff} of {rows} rows select different ids than torch.topk(sorted=False); {ties} of them are exact ties "
+                          f"of the choice score at the top-k boundary (same score multiset, same weights), {diff - ties} are real")
+
+
 def own_timing(shape_lines):
     """The build's own device-resident timing of the bench_moe.py shapes (bench_moe.py:144-145) next to the
     script's host-tensor loop: CUDA events over 20 calls after 3 warm-ups, weights rotated over 2 copies."""
@@ -121,8 +175,15 @@ def main():
         is_bench = name.startswith("bench_")
         n_true, n_false = sum(verdicts), len(verdicts) - sum(verdicts)
         ok = rc == 0 and n_false == 0 and (is_bench or n_true > 0)
+        note = None
+        if rc == 0 and n_false > 0 and name == "test_biased_grouped_topk.py":
+            ties_only, note = adjudicate_router(ref, name)
+            ok = bool(ties_only)
         failed |= not ok
-        lines.append(f"{'PASS' if ok else 'FAIL'}  {name:32s} rc={rc} verdicts: {n_true} True / {n_false} False  ({dt:.1f} s)  -- {what}")
+        status = "PASS" if ok and note is None else ("PASS (exact ties only)" if ok else "FAIL")
+        lines.append(f"{status}  {name:32s} rc={rc} verdicts: {n_true} True / {n_false} False  ({dt:.1f} s)  -- {what}")
+        if note:
+            lines.append("        > " + note)
         for l in out.splitlines():
             if VERDICT_RE.search(l) or l.startswith("### fused_experts"):
                 lines.append("        | " + l.strip())
