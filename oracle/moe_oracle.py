@@ -196,13 +196,34 @@ def _topk_lowest_index(scores, k):
     return torch.gather(scores, -1, ids), ids
 
 
-def sigmoid_cr(x):
-    """The build's sigmoid contract: the correctly rounded f32 sigmoid, evaluated in f64 and rounded once,
-    (float)(1 / (1 + exp(-(double)x))) -- the same expression csrc/router.cu evaluates.  The reference's oracle
-    calls `gating_output.sigmoid()` (test_biased_grouped_topk.py:22); torch's f32 CPU sigmoid is a ~1-ulp
-    approximation that differs from this value on ~30 % of inputs by one ulp, which no other implementation can
-    reproduce bit for bit.  tests/test_oracle.py counts the rows whose ids differ between the two definitions."""
-    return (1.0 / (1.0 + torch.exp(-x.double()))).float()
+_EXP_C = [float.fromhex(h) for h in (
+    "0x1.0000000000000p+0", "0x1.0000000000000p+0", "0x1.0000000000000p-1", "0x1.5555555555555p-3", "0x1.5555555555555p-5",
+    "0x1.1111111111111p-7", "0x1.6c16c16c16c17p-10", "0x1.a01a01a01a01ap-13", "0x1.a01a01a01a01ap-16",
+    "0x1.71de3a556c734p-19", "0x1.27e4fb7789f5cp-22", "0x1.ae64567f544e4p-26", "0x1.1eed8eff8d898p-29",
+    "0x1.6124613a86d09p-33")]                      # 1 / n!, n = 0..13
+
+
+def sigmoid_f64(x):
+    """The build's sigmoid contract (csrc/router.cu:sigmoid_f64, the same sequence operation for operation):
+    1 / (1 + exp(-x)) in f64 from correctly rounded IEEE-754 basic operations only -- exp(t) = 2^k P(r) with
+    k = rint(t / ln 2), r = t - k ln2_hi - k ln2_lo, P the degree-13 Taylor polynomial in Horner form with separate
+    multiplies and adds -- rounded once to f32.  Being a fixed sequence of basic operations it yields the same bits
+    on any IEEE machine, which neither the reference's expression (`gating_output.sigmoid()`,
+    test_biased_grouped_topk.py:22: torch's f32 CPU sigmoid is a ~1-ulp approximation, 30 % of inputs differ from
+    the correctly rounded value) nor a libm exp() (ulp-level differences between libraries flip the f32 rounding
+    where sigmoid sits on a half-ulp) can offer.  tests/test_oracle.py counts the rows whose ids differ from the
+    reference's expression; tests/test_oracle.py also holds it within one f32 ulp of the exact value."""
+    t = (-x.double()).clamp(-50.0, 120.0)
+    k = torch.round(t * float.fromhex("0x1.71547652b82fep+0"))            # half to even, like rint()
+    r = (t - k * float.fromhex("0x1.62e42fee00000p-1")) - k * float.fromhex("0x1.a39ef35793c76p-33")
+    p = torch.full_like(r, _EXP_C[13])
+    for n in range(12, -1, -1):
+        p = p * r + _EXP_C[n]                                            # two roundings: no fused multiply-add
+    e = p * ((k.to(torch.int64) + 1023) << 52).view(torch.float64)       # exact power of two
+    return (1.0 / (1.0 + e)).float()
+
+
+sigmoid_cr = sigmoid_f64   # earlier name
 
 
 def _seq_sum(w):
@@ -258,8 +279,8 @@ def grouped_topk(gating_output, topk, renormalize, num_expert_group, topk_group,
 
 def biased_grouped_topk(gating_output, correction_bias, topk, renormalize, num_expert_group, topk_group,
                         num_fused_shared_experts=0, routed_scaling_factor=None, num_token_non_padded=None,
-                        sigmoid=sigmoid_cr):
-    """test_biased_grouped_topk.py:9-47 with the tie-break made explicit and the sigmoid pinned to sigmoid_cr
+                        sigmoid=sigmoid_f64):
+    """test_biased_grouped_topk.py:9-47 with the tie-break made explicit and the sigmoid pinned to sigmoid_f64
     (pass sigmoid=torch.sigmoid for the reference's literal expression)."""
     scores = sigmoid(gating_output.float())
     n, E = scores.shape

@@ -13,7 +13,7 @@ from . import _lib, ops
 from . import _lib as L  # noqa: F401  (K.L.PATH_*, K.L.FMT_*)
 from .ops import (CPUQuantMethod, GraphedExperts, biased_grouped_topk, biased_grouped_topk_out, clear_weight_cache,
                   convert_scale_packed, convert_weight_packed, fused_experts, fused_experts_impl,
-                  grouped_topk, grouped_topk_out, launch_count, moe_align, mxfp4_scaled_mm,
+                  grouped_topk, grouped_topk_out, invalidate, launch_count, moe_align, mxfp4_scaled_mm,
                   shared_expert, shared_expert_impl, split_rows_e4m3, weight_packed_linear, per_token_quant_int8,
                   int8_scaled_mm, int8_scaled_mm_with_quant, fp8_scaled_mm, silu_and_mul, rmsnorm,
                   fused_add_rmsnorm)

@@ -7,11 +7,15 @@
 // index wins; picks are emitted in descending score order.  oracle/moe_oracle.py states the
 // same rule and the tests hold this kernel bit-exact on ids to it.
 //
-// Sigmoid contract (biased variant): s = (float)(1.0 / (1.0 + exp(-(double)x))), the correctly rounded f32
-// sigmoid, evaluated in f64 and rounded once.  The reference's oracle calls torch's f32 sigmoid, whose CPU
-// implementation is only ~1 ulp accurate (it differs from the correctly rounded value on ~30 % of inputs), so
-// no second implementation can reproduce it bit for bit; the f64 definition can be evaluated identically on
-// both sides (oracle/moe_oracle.py:sigmoid_cr) and makes ids AND weights of the biased router bit-exact.
+// Sigmoid contract (biased variant): sigmoid_f64() below -- evaluated in f64 by a FIXED SEQUENCE OF IEEE-754
+// OPERATIONS (Cody-Waite reduction, degree-13 Taylor polynomial in Horner form, separate multiplies and adds, one
+// division) and rounded once to f32.  Every step is a correctly rounded basic operation, so the CPU oracle
+// (oracle/moe_oracle.py:sigmoid_f64, the same sequence with torch f64 tensor ops) reproduces it bit for bit: ids,
+// their order AND the weights of the biased router are bit-exact.  Two things that do not work: the reference's own
+// expression, torch's f32 sigmoid, is a ~1-ulp approximation (it differs from the correctly rounded value on ~30 % of
+// inputs) that no second implementation can reproduce; and exp() of two math libraries agrees only to an ulp of
+// f64, which is enough to flip the f32 rounding where sigmoid(x) = 0.5 + x/4 - ... sits on a half-ulp of f32
+// (bf16 x = 9.894e-6 did, on the B200 box).
 //
 // Serving arguments of the 9-argument call (test_moe.py:61-70; semantics from sglang's python router, not
 // pinned by the reference): num_fused_shared_experts n > 0 makes the LAST of the topk slots the fused shared
@@ -58,6 +62,27 @@ __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
   return v;
+}
+
+// 1 / (1 + exp(-x)) in f64, every operation an explicitly rounded IEEE-754 one (no contraction into fma), then one
+// rounding to f32.  exp(t) = 2^k * P(r), k = rint(t / ln 2), r = t - k ln2_hi - k ln2_lo, P = sum_{n<=13} r^n / n!
+// (|r| <= 0.347: truncation 4e-18).  t is clamped to [-50, 120]: below, 1 + e = 1 exactly; above, the quotient is
+// far under the smallest f32 subnormal.  oracle/moe_oracle.py:sigmoid_f64 is the same sequence.
+__device__ __forceinline__ float sigmoid_f64(float x) {
+  double t = -(double)x;
+  if (!(t == t)) return x;  // NaN stays NaN (never wins a comparison in the selection below)
+  t = t < -50.0 ? -50.0 : (t > 120.0 ? 120.0 : t);
+  const double k = rint(__dmul_rn(t, 0x1.71547652b82fep+0));
+  const double r = __dsub_rn(__dsub_rn(t, __dmul_rn(k, 0x1.62e42fee00000p-1)), __dmul_rn(k, 0x1.a39ef35793c76p-33));
+  const double c[14] = {0x1.0000000000000p+0,  0x1.0000000000000p+0,  0x1.0000000000000p-1,  0x1.5555555555555p-3,
+                        0x1.5555555555555p-5,  0x1.1111111111111p-7,  0x1.6c16c16c16c17p-10, 0x1.a01a01a01a01ap-13,
+                        0x1.a01a01a01a01ap-16, 0x1.71de3a556c734p-19, 0x1.27e4fb7789f5cp-22, 0x1.ae64567f544e4p-26,
+                        0x1.1eed8eff8d898p-29, 0x1.6124613a86d09p-33};
+  double p = c[13];
+#pragma unroll
+  for (int n = 12; n >= 0; --n) p = __dadd_rn(__dmul_rn(p, r), c[n]);
+  const double e = __dmul_rn(p, __longlong_as_double(((long long)k + 1023ll) << 52));
+  return (float)__ddiv_rn(1.0, __dadd_rn(1.0, e));
 }
 
 // PER = ceil(E/32) rounded up to a compiled size.  Lane l owns experts l, l+32, ...
@@ -116,7 +141,7 @@ __global__ void __launch_bounds__(128) router_kernel(const TG* __restrict__ gati
     for (int k = 0; k < PER; ++k) {
       int e = lane + 32 * k;
       if (e < E) {
-        s[k] = (float)(1.0 / (1.0 + exp(-(double)s[k])));  // correctly rounded: see the file header
+        s[k] = sigmoid_f64(s[k]);  // bit-reproducible on the CPU: see the file header
         c[k] = s[k] + load_as_float<TB>(bias + e);
       } else {
         s[k] = 0.f;

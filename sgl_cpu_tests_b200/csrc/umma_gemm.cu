@@ -22,8 +22,11 @@
 // All operand tiles are [rows x 128 bytes]: 64 bf16 or 128 s8 of K per stage, four UMMA K-steps
 // (32 B each) per stage for either type, so the kernel is written in bytes and only the instruction
 // descriptor (kind::f16 / kind::i8) and the epilogue differ per format.
+#include <algorithm>
+#include <iterator>
 #include <mutex>
 #include <unordered_map>
+#include <vector>
 
 #include <stdlib.h>
 
@@ -211,13 +214,22 @@ struct MapKeyHash {
 // The expert dimension is separate so that a box reaching past an expert's last row is zero-filled.
 int weight_tensor_map(const void* W, uint64_t kbytes, uint64_t rows, uint64_t E, uint32_t box_bytes,
                       uint32_t box_rows, int swizzle128, CUtensorMap* out) {
+  // descriptor cache with least-recently-used eviction: every entry carries the tick of its last use and, when the
+  // table is full, the older half is dropped (a descriptor is 128 bytes and ~1 us to rebuild, so this is cheap)
+  struct Entry {
+    CUtensorMap map;
+    uint64_t tick;
+  };
+  constexpr size_t kMaxEntries = 4096;
   static std::mutex mu;
-  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  static std::unordered_map<MapKey, Entry, MapKeyHash> cache;
+  static uint64_t tick = 0;
   const MapKey key{W, kbytes, rows, E, box_bytes, box_rows, (uint32_t)swizzle128};
   std::lock_guard<std::mutex> lock(mu);
   auto it = cache.find(key);
   if (it != cache.end()) {
-    *out = it->second;
+    it->second.tick = ++tick;
+    *out = it->second.map;
     return SGLB_OK;
   }
   EncodeTiledFn enc = encode_tiled_fn();
@@ -233,8 +245,15 @@ int weight_tensor_map(const void* W, uint64_t kbytes, uint64_t rows, uint64_t E,
                    swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   SGLB_CHECK(r == CUDA_SUCCESS, "tcgen05 path: cuTensorMapEncodeTiled failed (CUresult %d)", (int)r);
-  if (cache.size() > 4096) cache.clear();
-  cache.emplace(key, m);
+  if (cache.size() >= kMaxEntries) {
+    std::vector<uint64_t> ticks;
+    ticks.reserve(cache.size());
+    for (const auto& kv : cache) ticks.push_back(kv.second.tick);
+    std::nth_element(ticks.begin(), ticks.begin() + ticks.size() / 2, ticks.end());
+    const uint64_t cut = ticks[ticks.size() / 2];
+    for (auto i = cache.begin(); i != cache.end();) i = i->second.tick < cut ? cache.erase(i) : std::next(i);
+  }
+  cache.emplace(key, Entry{m, ++tick});
   *out = m;
   return SGLB_OK;
 }

@@ -14,7 +14,9 @@ Tensors may live on the CPU (what the reference scripts allocate) or on a CUDA d
 """
 import math
 import os
+import sys
 import threading
+import weakref
 from enum import IntEnum
 
 import torch
@@ -65,54 +67,118 @@ def _to_dev(t, dev, dtype=None):
 # provided the launches of one call are not interleaved with another thread's.  _launch_lock is held
 # from taking the workspace until the (asynchronous) C call has enqueued everything.
 _workspaces = {}
+_WORKSPACE_ENTRIES = 16   # streams come and go (side streams, captures): keep the most recently used ones
 _launch_lock = threading.RLock()
 
 
 def _workspace(nbytes, dev):
     key = (dev.index, _stream())
-    buf = _workspaces.get(key)
+    buf = _workspaces.pop(key, None)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=dev)
-        _workspaces[key] = buf
+    _workspaces[key] = buf            # most recently used last
+    while len(_workspaces) > _WORKSPACE_ENTRIES:
+        _workspaces.pop(next(iter(_workspaces)))   # stream-ordered frees: torch keeps the memory alive until the stream drains
     return buf
 
 
 # ---- weight registry ------------------------------------------------------------------------------------
+# Host weights (what the reference scripts pass) are uploaded once and served from HBM afterwards.  An entry is
+# keyed on (device, pointer, shape, strides, dtype, packing, kind, torch version counter):
+#   * host tensors: the entry keeps a reference to the tensor, so the address cannot be recycled under another weight
+#     while the entry lives; in-place updates through torch bump the version counter and miss;
+#   * CUDA tensors (packed weights returned by convert_weight_packed, scale tiles): nothing is pinned -- a weakref
+#     finaliser drops the entry when the keyed tensor dies, so a reallocated address cannot hit a stale entry.
+# What the key cannot see: writes that bypass torch's version counter -- `w.data.copy_(...)` (the usual weight-loader /
+# weight-sync idiom), numpy views, torch.from_numpy buffers.  For those callers: sgl_cpu_tests_b200.invalidate(w) after
+# the update, or SGLB_VERIFY_WEIGHTS=1, which fingerprints 64 sampled cache lines of the host tensor at every lookup
+# (~20 us per tensor) and re-uploads on a mismatch.  LRU eviction under two caps: device bytes (SGLB_WEIGHT_CACHE_GB,
+# default 140) and the host bytes the entries keep alive (SGLB_WEIGHT_CACHE_HOST_GB, default 160).
 _WEIGHT_CACHE_BYTES = int(float(os.environ.get("SGLB_WEIGHT_CACHE_GB", "140")) * (1 << 30))
-_registry = {}
+_WEIGHT_CACHE_HOST_BYTES = int(float(os.environ.get("SGLB_WEIGHT_CACHE_HOST_GB", "160")) * (1 << 30))
+_VERIFY_WEIGHTS = os.environ.get("SGLB_VERIFY_WEIGHTS", "0") != "0"
+_registry = {}          # key -> (keep-alive / fingerprint info, device tensor, host bytes)
 _registry_bytes = 0
+_registry_host_bytes = 0
+
+
+def _nbytes(t):
+    return t.numel() * t.element_size()
+
+
+def _sample_hash(t):
+    """64 cache lines spread over a contiguous host tensor's bytes."""
+    b = t.detach().contiguous().view(torch.uint8).reshape(-1)
+    n = b.numel()
+    if n <= 64 * 64:
+        return hash(b.numpy().tobytes())
+    idx = (torch.arange(64, dtype=torch.int64) * ((n - 64) // 63)).unsqueeze(1) + torch.arange(64, dtype=torch.int64)
+    return hash(b[idx.reshape(-1)].numpy().tobytes())
 
 
 def _fingerprint(t):
-    """What a registry entry keeps of its host tensor: the tensor itself.  While the entry exists the host
-    buffer cannot be freed, so its address cannot come back under a different weight, and the key
-    (pointer, shape, dtype, torch version counter) identifies the contents without touching the data.
-    (An earlier revision hashed sampled bytes on every call: ~20 us per tensor, four tensors per call, on
-    the critical path of the host-buffer API.)  clear_weight_cache() / the LRU cap release the references."""
-    return None if t.is_cuda else t
+    """What a registry entry keeps of its key tensor: (the host tensor itself | None for CUDA, sampled hash | None)."""
+    if t.is_cuda:
+        return (None, None)
+    return (t, _sample_hash(t) if _VERIFY_WEIGHTS else None)
 
 
 def _registry_key(t, is_vnni, kind):
-    return (t.device.type, t.device.index, t.data_ptr(), tuple(t.shape), t.dtype, bool(is_vnni), kind,
+    return (t.device.type, t.device.index, t.data_ptr(), tuple(t.shape), tuple(t.stride()), t.dtype, bool(is_vnni), kind,
             t._version)
 
 
-def _registry_put(key, fp, dev_tensor):
-    global _registry_bytes
-    nbytes = dev_tensor.numel() * dev_tensor.element_size()
-    while _registry and _registry_bytes + nbytes > _WEIGHT_CACHE_BYTES:
-        oldest = next(iter(_registry))  # dicts keep insertion order: evict the oldest entry
-        _, old = _registry.pop(oldest)
-        _registry_bytes -= old.numel() * old.element_size()
-    _registry[key] = (fp, dev_tensor)
+def _registry_drop(key):
+    global _registry_bytes, _registry_host_bytes
+    ent = _registry.pop(key, None)
+    if ent is not None:
+        _registry_bytes -= _nbytes(ent[1])
+        _registry_host_bytes -= ent[2]
+
+
+def _registry_get(key, t=None):
+    ent = _registry.get(key)
+    if ent is None:
+        return None
+    if _VERIFY_WEIGHTS and t is not None and ent[0][1] is not None and _sample_hash(t) != ent[0][1]:
+        _registry_drop(key)       # rewritten behind torch's version counter
+        return None
+    _registry[key] = _registry.pop(key)   # most recently used last
+    return ent[1]
+
+
+def _registry_put(key, fp, dev_tensor, key_tensor=None):
+    global _registry_bytes, _registry_host_bytes
+    _registry_drop(key)           # overwriting: the old entry's bytes must not be counted twice
+    nbytes = _nbytes(dev_tensor)
+    host = _nbytes(fp[0]) if (isinstance(fp, tuple) and fp[0] is not None) else 0
+    while _registry and (_registry_bytes + nbytes > _WEIGHT_CACHE_BYTES or
+                         _registry_host_bytes + host > _WEIGHT_CACHE_HOST_BYTES):
+        _registry_drop(next(iter(_registry)))   # least recently used first
+    _registry[key] = (fp if isinstance(fp, tuple) else (None, None), dev_tensor, host)
     _registry_bytes += nbytes
+    _registry_host_bytes += host
+    if key_tensor is not None and key_tensor.is_cuda:
+        weakref.finalize(key_tensor, _registry_drop, key)   # never serve a freed CUDA buffer's address again
+
+
+def invalidate(tensor=None):
+    """Forget the HBM-resident copies made for `tensor` (a host weight / scale that was rewritten in place through
+    `.data`, numpy or another path torch's version counter does not see); None forgets everything."""
+    if tensor is None:
+        return clear_weight_cache()
+    for key in [k for k in _registry if k[0] == tensor.device.type and k[2] == tensor.data_ptr()]:
+        _registry_drop(key)
+    _host_graphs.clear()
 
 
 def clear_weight_cache():
-    global _registry_bytes
+    global _registry_bytes, _registry_host_bytes
     _host_graphs.clear()
+    _host_graph_seen.clear()
     _registry.clear()
     _registry_bytes = 0
+    _registry_host_bytes = 0
 
 
 def _rows_k(w, is_int8_packed):
@@ -147,10 +213,10 @@ def _resident_weight(w, is_vnni, dev):
     if w.is_cuda and not is_vnni:
         return w if w.is_contiguous() else w.contiguous()
     key = _registry_key(w, is_vnni, "w")
-    hit = _registry.get(key)
-    fp = _fingerprint(w)
+    hit = _registry_get(key, w)
     if hit is not None:
-        return hit[1]
+        return hit
+    fp = _fingerprint(w)
     wd = _to_dev(w, dev)
     if is_vnni:
         eb, vnni, comp = _layout_of(w.dtype)
@@ -160,7 +226,7 @@ def _resident_weight(w, is_vnni, dev):
         rm = torch.empty(out_shape, dtype=w.dtype, device=dev)
         _repack(wd, rm, eb, vnni, E, N, K, comp, False)
         wd = rm
-    _registry_put(key, fp, wd)
+    _registry_put(key, fp, wd, w)
     return wd
 
 
@@ -171,12 +237,11 @@ def _resident_aux(t, dev, dtype, kind="s"):
     if t.is_cuda:
         return _to_dev(t, dev, dtype)
     key = _registry_key(t, False, kind)
-    hit = _registry.get(key)
-    fp = _fingerprint(t)
+    hit = _registry_get(key, t)
     if hit is not None:
-        return hit[1]
+        return hit
     td = _to_dev(t, dev, dtype)
-    _registry_put(key, fp, td)
+    _registry_put(key, _fingerprint(t), td, t)
     return td
 
 
@@ -206,7 +271,7 @@ def convert_weight_packed(weight):
         packed = torch.empty(out_shape, dtype=weight.dtype, device=dev)
         _repack(wd, packed, eb, vnni, E, N, K, comp, True)
         result = packed if weight.is_cuda else packed.cpu()
-        _registry_put(_registry_key(result, True, "w"), _fingerprint(result), wd)
+        _registry_put(_registry_key(result, True, "w"), _fingerprint(result), wd, result)
     return result
 
 
@@ -224,7 +289,7 @@ def convert_scale_packed(scale):
         packed = torch.empty_like(sd)
         L.check(L.load().sglb_repack_scale(sd.data_ptr(), packed.data_ptr(), E, N, G, 1, _stream()))
         result = packed if scale.is_cuda else packed.cpu()
-        _registry_put(_registry_key(result, True, "ms"), _fingerprint(result), sd)
+        _registry_put(_registry_key(result, True, "ms"), _fingerprint(result), sd, result)
     return result
 
 
@@ -233,17 +298,17 @@ def _resident_mx_scale(s, is_vnni, dev):
     if s.is_cuda and not is_vnni:
         return s.contiguous()
     key = _registry_key(s, is_vnni, "ms")
-    hit = _registry.get(key)
-    fp = _fingerprint(s)
+    hit = _registry_get(key, s)
     if hit is not None:
-        return hit[1]
+        return hit
+    fp = _fingerprint(s)
     sd = _to_dev(s, dev)
     if is_vnni:
         E, N, G = _rows_k(s, False)
         rm = torch.empty_like(sd)
         L.check(L.load().sglb_repack_scale(sd.data_ptr(), rm.data_ptr(), E, N, G, 0, _stream()))
         sd = rm
-    _registry_put(key, fp, sd)
+    _registry_put(key, fp, sd, s)
     return sd
 
 
@@ -251,15 +316,14 @@ def _mx4_tiles(s_dev, split):
     """e8m0 scales [E, rows, K/32] on the device -> the 512-byte tiles the block-scaled tensor-core kernel
     copies into TMEM (csrc/umma_mx4.cu); built once per scale tensor and cached."""
     key = _registry_key(s_dev, False, ("mx4tiles", split))
-    hit = _registry.get(key)
+    hit = _registry_get(key)
     if hit is not None:
-        return hit[1]
+        return hit
     E, rows, G = _rows_k(s_dev, False)
     lib = L.load()
     tiles = torch.empty(lib.sglb_mx4_scale_tiles_bytes(E, rows, split, 32 * G), dtype=torch.uint8, device=s_dev.device)
     L.check(lib.sglb_mx4_tile_scales(s_dev.data_ptr(), tiles.data_ptr(), E, rows, split, 32 * G, _stream()))
-    tiles._sglb_src = s_dev  # keeps the keyed pointer alive for as long as the cache entry
-    _registry_put(key, 0, tiles)
+    _registry_put(key, (None, None), tiles, s_dev)   # dropped when the keyed scale tensor dies
     return tiles
 
 
@@ -275,14 +339,13 @@ def _mx4_weight(w_dev):
         if K % 128 == 0 or slack >= 32:
             return w_dev
     key = _registry_key(w_dev, False, "mx4pad")
-    hit = _registry.get(key)
+    hit = _registry_get(key)
     if hit is not None:
-        return hit[1]
+        return hit
     buf = torch.zeros(w_dev.numel() + 64, dtype=torch.uint8, device=w_dev.device)
     padded = buf[:w_dev.numel()].view(w_dev.shape)
     padded.copy_(w_dev)
-    padded._sglb_src = w_dev
-    _registry_put(key, 0, padded)
+    _registry_put(key, (None, None), padded, w_dev)
     return padded
 
 
@@ -426,6 +489,8 @@ _HOST_GRAPH = os.environ.get("SGLB_HOST_GRAPH", "1") != "0"
 _HOST_GRAPH_MAX_TOKENS = 1024
 _HOST_GRAPH_ENTRIES = 4
 _host_graphs = {}  # key -> GraphedExperts (insertion order = LRU order), or None after a failed capture
+_host_graph_seen = {}   # key -> calls seen before a capture: a caller whose batch size changes every call never captures
+_host_graph_warned = [False]
 
 
 def _host_graph(M, topk, fmt, w13, w2d, s13, s2, block_size, path):
@@ -435,10 +500,22 @@ def _host_graph(M, topk, fmt, w13, w2d, s13, s2, block_size, path):
         g = _host_graphs.pop(key)
         _host_graphs[key] = g  # most recently used last
         return g
+    # a capture costs two extra calls and two synchronisations: only for a key that comes back
+    seen = _host_graph_seen.get(key, 0) + 1
+    if seen < 2:
+        if len(_host_graph_seen) > 64:
+            _host_graph_seen.clear()
+        _host_graph_seen[key] = seen
+        return None
+    _host_graph_seen.pop(key, None)
     try:
         g = GraphedExperts(M, w13, w2d, topk, fmt, s13, s2, block_size, False, path)
-    except Exception:  # capture refused: this key stays on the eager path
+    except Exception as e:  # capture refused: this key stays on the eager path
         torch.cuda.synchronize()
+        if not _host_graph_warned[0]:
+            _host_graph_warned[0] = True
+            sys.stderr.write(f"[sgl_cpu_tests_b200] CUDA-graph capture of a host-tensor fused_experts call failed "
+                             f"({type(e).__name__}: {e}); such calls stay on eager launches\n")
         g = None
     _host_graphs[key] = g
     while len(_host_graphs) > _HOST_GRAPH_ENTRIES:

@@ -102,3 +102,36 @@ def test_dropin_package_registers_ops(lib):
     env = dict(os.environ, PYTHONPATH=os.path.join(PKG, "dropin"))
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
     assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-2000:]
+
+
+def test_weight_registry_accounting():
+    """Host-side registry logic (no GPU): strides are part of the key, overwriting an entry does not double-count
+    its bytes, eviction is least-recently-used under both caps, invalidate() drops the entries of one tensor."""
+    import torch
+    from sgl_cpu_tests_b200 import ops
+    ops.clear_weight_cache()
+    w = torch.zeros(8, 8)
+    assert ops._registry_key(w, False, "w") != ops._registry_key(w.t(), False, "w")   # same pointer and shape
+    dev_copy = torch.zeros(1024, dtype=torch.uint8)
+    k1 = ops._registry_key(w, False, "w")
+    ops._registry_put(k1, ops._fingerprint(w), dev_copy, w)
+    ops._registry_put(k1, ops._fingerprint(w), dev_copy, w)
+    assert ops._registry_bytes == 1024 and ops._registry_host_bytes == w.numel() * 4
+    old_cap = ops._WEIGHT_CACHE_BYTES
+    try:
+        ops._WEIGHT_CACHE_BYTES = 3 * 1024
+        others = [torch.zeros(4, 4) + i for i in range(3)]
+        keys = [ops._registry_key(o, False, "w") for o in others]
+        ops._registry_put(keys[0], ops._fingerprint(others[0]), dev_copy.clone(), others[0])
+        ops._registry_put(keys[1], ops._fingerprint(others[1]), dev_copy.clone(), others[1])
+        assert ops._registry_get(k1, w) is not None            # touch: k1 becomes the most recently used
+        ops._registry_put(keys[2], ops._fingerprint(others[2]), dev_copy.clone(), others[2])
+        assert k1 in ops._registry and keys[0] not in ops._registry and ops._registry_bytes == 3 * 1024
+    finally:
+        ops._WEIGHT_CACHE_BYTES = old_cap
+    ops.invalidate(w)
+    assert k1 not in ops._registry and ops._registry_bytes == 2 * 1024
+    w.add_(1)                                                  # in-place through torch: new version, new key
+    assert ops._registry_key(w, False, "w") != k1
+    ops.clear_weight_cache()
+    assert ops._registry_bytes == 0 and ops._registry_host_bytes == 0

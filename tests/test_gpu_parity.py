@@ -85,7 +85,7 @@ BIASED_SHAPES = [(122, 256, 8, 8, 2), (33, 64, 4, 4, 2), (7, 32, 8, 3, 3), (2048
 @pytest.mark.parametrize("renorm", [True, False])
 def test_biased_grouped_topk_bit_exact(K, renorm):
     """ids, their order AND the weights are bit-exact: both sides evaluate the correctly rounded sigmoid
-    (csrc/router.cu header, O.sigmoid_cr), one f32 add for the bias, the same tie-break and the same f32 sum order."""
+    (csrc/router.cu header, O.sigmoid_f64), one f32 add for the bias, the same tie-break and the same f32 sum order."""
     torch.manual_seed(1111)
     for (M, E, G, topk, tg) in BIASED_SHAPES:
         for dt, scale in ((torch.float32, 1.0), (torch.bfloat16, 1.0), (torch.bfloat16, 2.0 * M)):
@@ -114,13 +114,13 @@ def test_biased_grouped_topk_golden(K):
 
 def test_sigmoid_every_bf16_input(K):
     """All 2^16 bf16 bit patterns (finite ones) through the biased router with zero bias, topk = E = 32, no
-    renormalisation: the returned weights are the kernel's sigmoid of each logit; bit-equal to O.sigmoid_cr."""
+    renormalisation: the returned weights are the kernel's sigmoid of each logit; bit-equal to O.sigmoid_f64."""
     bits = torch.arange(0, 65536, dtype=torch.int32).to(torch.int16).view(torch.bfloat16)
     gating = bits[torch.isfinite(bits.float())]
     gating = gating[: gating.numel() // 32 * 32].view(-1, 32)
     w, ids = K.biased_grouped_topk(torch.zeros(gating.shape[0], 4), gating.cuda(), torch.zeros(32).cuda(), 32, False, 1, 1)
     got = torch.zeros(gating.shape, dtype=torch.float32).scatter_(1, ids.long().cpu(), w.cpu())
-    want = O.sigmoid_cr(gating.float())
+    want = O.sigmoid_f64(gating.float())
     bad = (got.view(torch.int32) != want.view(torch.int32)).nonzero()
     assert bad.numel() == 0, (bad.shape[0], [(float(gating[i, j]), float(got[i, j]), float(want[i, j])) for i, j in bad[:8].tolist()])
 
@@ -304,6 +304,64 @@ def test_fused_experts_mxfp4(K, shape):
         out = K.fused_experts(a, args[0], args[1], tw, ids, False, K.CPUQuantMethod.MXFP4, args[2], args[3], None, None,
                               None, vnni)
         check_close(out, ref, f"mxfp4 {shape} vnni={vnni}")
+
+
+# gpt-oss: the 17-argument vintage (on-box vllm cpu_moe.py:308-326) -- per-expert biases and the clamped swiglu.
+# PARITY UNPINNED: the reference holds no call site with these arguments; the oracle is O.native_fused_moe's
+# bias / swiglu_oai form (gate = rows [0, I), up = rows [I, 2I)).
+@pytest.mark.parametrize("shape", [(5, 64, 64, 4, 2), (37, 96, 352, 8, 4), (128, 2880, 2880, 8, 4), (600, 256, 512, 4, 2)])
+@pytest.mark.parametrize("act", [(None, None), (1.702, 7.0), (1.702, None)])
+def test_fused_experts_mxfp4_bias_swiglu_oai(K, shape, act):
+    M, N, Kd, E, topk = shape
+    alpha, limit = act
+    torch.manual_seed(77)
+    a = torch.randn(M, Kd, dtype=torch.bfloat16)
+    w1q, w1s = O.mxfp4_quantize((torch.rand(E, 2 * N, Kd) - 0.5) * 2e-1)
+    w2q, w2s = O.mxfp4_quantize((torch.rand(E, Kd, N) - 0.5) * 2e-1)
+    w1s, w2s = w1s.view(E, 2 * N, Kd // 32), w2s.view(E, Kd, N // 32)
+    b1, b2 = torch.randn(E, 2 * N) * 0.5, torch.randn(E, Kd) * 0.5
+    tw, ids = routing(M, E, topk)
+    ids[0, 0] = -1
+    ref = O.fused_experts(a, w1q, w2q, tw, ids, "mxfp4", w1s, w2s, w1_bias=b1, w2_bias=b2, alpha=alpha, limit=limit)
+    out = K.fused_experts(a, w1q, w2q, tw, ids, False, K.CPUQuantMethod.MXFP4, w1s, w2s, None, None, None, b1, b2, alpha,
+                          limit, False)
+    check_close(out, ref, f"mxfp4 bias/act {shape} {act}")
+    if Kd % 64 == 0 and N % 64 == 0:      # the dequantising tcgen05 kernel and the streaming kernel take the same epilogue
+        import sgl_cpu_tests_b200._lib as L
+        L.load().sglb_set_mx4_native(0)
+        try:
+            for path in (K.PATH_STREAM, K.PATH_UMMA):
+                o2 = K.fused_experts_impl(a.cuda(), w1q.cuda(), w2q.cuda(), tw.cuda(), ids.cuda(), False, K.FMT_MXFP4, w1s.cuda(),
+                                          w2s.cuda(), None, False, path=path, w1_bias=b1.cuda(), w2_bias=b2.cuda(), alpha=alpha,
+                                          limit=limit)
+                check_close(o2, ref, f"mxfp4 bias/act {shape} {act} path={path}")
+        finally:
+            L.load().sglb_set_mx4_native(1)
+
+
+@pytest.mark.parametrize("fmt", ["bf16", "fp8"])
+def test_fused_experts_bias_swiglu_oai_other_formats(K, fmt):
+    """The same epilogue arguments through the bf16 (stream + tcgen05) and fp8 tensor-native kernels."""
+    torch.manual_seed(78)
+    M, I, H, E, topk = 90, 256, 512, 8, 3
+    a = torch.randn(M, H, dtype=torch.bfloat16) / 4
+    b1, b2 = torch.randn(E, 2 * I) * 0.3, torch.randn(E, H) * 0.3
+    tw, ids = routing(M, E, topk)
+    if fmt == "bf16":
+        w1, w2 = (torch.randn(E, 2 * I, H) / 10).bfloat16(), (torch.randn(E, H, I) / 10).bfloat16()
+        s1 = s2 = block = None
+        fid = K.FMT_BF16
+    else:
+        w1 = (torch.randn(E, 2 * I, H) * 30).to(torch.float8_e4m3fn)
+        w2 = (torch.randn(E, H, I) * 30).to(torch.float8_e4m3fn)
+        s1, s2, block = torch.rand(E, 2 * I // 128, H // 128) * 4e-3, torch.rand(E, H // 128, I // 128) * 4e-3, [128, 128]
+        fid = K.FMT_FP8_W8A16
+    ref = O.fused_experts(a, w1, w2, tw, ids, fmt, s1, s2, block, w1_bias=b1, w2_bias=b2, alpha=1.702, limit=7.0)
+    dev = lambda t: None if t is None else t.cuda()  # noqa: E731
+    for path in (K.PATH_STREAM, K.PATH_UMMA):
+        out = K.fused_experts_impl(dev(a), dev(w1), dev(w2), dev(tw), dev(ids), False, fid, dev(s1), dev(s2), block, False, path=path,
+                                   w1_bias=dev(b1), w2_bias=dev(b2), alpha=1.702, limit=7.0)
+        check_close(out, ref, f"{fmt} bias/act path={path}")
 
 
 # ------------------------------------------------------------------------------------------ shared expert

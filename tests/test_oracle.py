@@ -53,7 +53,7 @@ def test_router_softmax_matches_reference():
 
 
 def test_router_biased_matches_reference(capsys):
-    """The oracle's sigmoid is the correctly rounded one (O.sigmoid_cr); the reference's own oracle calls torch's
+    """The oracle's sigmoid is the fixed-sequence f64 one (O.sigmoid_f64); the reference's own oracle calls torch's
     f32 sigmoid (~1 ulp).  Rows whose ids differ between the two definitions form the near-tie class: it is computed
     explicitly, its size printed, and equality with the reference fixture is asserted outside it."""
     n_rows = n_near = n_open = 0
@@ -63,7 +63,7 @@ def test_router_biased_matches_reference(capsys):
         w_t, ids_t = O.biased_grouped_topk(*args, sigmoid=torch.sigmoid)      # the reference's literal expression
         near = (ids != ids_t).any(dim=1)
         open_rows = near.clone()
-        for sig in (torch.sigmoid, O.sigmoid_cr):
+        for sig in (torch.sigmoid, O.sigmoid_f64):
             ch = sig(c["gating"].float()) + c["bias"].float()
             gsc = ch.view(ch.shape[0], c["G"], -1).topk(2, dim=-1)[0].sum(dim=-1)
             open_rows |= tie_rows(ch, gsc, c["topk"], c["topk_group"], float("-inf"))
@@ -77,12 +77,12 @@ def test_router_biased_matches_reference(capsys):
         if c["gating"].dtype == torch.float32:
             assert torch.equal(ids.sort(dim=1).values, c["ref_ids"].sort(dim=1).values)
     with capsys.disabled():
-        print(f"\n[biased router] fixture rows {n_rows}: ids differ between sigmoid_cr and torch.sigmoid on {n_near} "
+        print(f"\n[biased router] fixture rows {n_rows}: ids differ between sigmoid_f64 and torch.sigmoid on {n_near} "
               f"rows; exact-tie rows (either definition) {n_open - n_near}")
     assert n_near <= max(1, n_rows // 100)
 
 
-def test_sigmoid_cr_vs_torch_sigmoid_ids():
+def test_sigmoid_f64_vs_torch_sigmoid_ids():
     """Well-conditioned logits at the DeepSeek-V3 router shape: the two sigmoid definitions pick the same ids."""
     torch.manual_seed(7)
     for dt in (torch.float32, torch.bfloat16):
@@ -221,3 +221,27 @@ def test_fused_experts_lean_is_fused_experts():
     e1 = torch.randint(120, 124, (E, 2 * I, H // 32), dtype=torch.uint8)
     e2 = torch.randint(120, 124, (E, H, I // 32), dtype=torch.uint8)
     assert torch.equal(O.fused_experts_lean(x, q1, q2, tw, ids, "mxfp4", e1, e2), O.fused_experts(x, q1, q2, tw, ids, "mxfp4", e1, e2))
+
+
+def test_sigmoid_f64_c_restatement_bit_equal(tmp_path):
+    """oracle/sigmoid_f64.c (plain C, gcc -ffp-contract=off) and the torch restatement of the same operation sequence
+    return the same bits for every finite bf16 input and for a million random f32 inputs, and both are within one f32
+    ulp of the f64 sigmoid."""
+    import ctypes
+    import os
+    import subprocess
+    src = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle", "sigmoid_f64.c")
+    lib = str(tmp_path / "libsigmoid_f64.so")
+    subprocess.run(["gcc", "-O2", "-ffp-contract=off", "-shared", "-fPIC", "-o", lib, src, "-lm"], check=True)
+    fn = ctypes.CDLL(lib).sglb_sigmoid_f64_array
+    fn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long]
+    bits = torch.arange(0, 65536, dtype=torch.int32).to(torch.int16).view(torch.bfloat16).float()
+    torch.manual_seed(0)
+    x = torch.cat([bits[torch.isfinite(bits)], torch.randn(1 << 20) * 8, torch.randn(1 << 18) * 1e-4]).contiguous()
+    out = torch.empty_like(x)
+    fn(x.data_ptr(), out.data_ptr(), x.numel())
+    got = O.sigmoid_f64(x)
+    assert torch.equal(got.view(torch.int32), out.view(torch.int32))
+    exact = torch.sigmoid(x.double())
+    ulp = torch.maximum(exact.float().abs(), torch.tensor(2.0 ** -126)) * 2.0 ** -23
+    assert ((got.double() - exact).abs() <= ulp.double()).all()
