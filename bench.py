@@ -267,16 +267,16 @@ def time_window(fn, steps, world, start=0):
     return float(ms.item()), [float(ms.item())]
 
 
-def time_steps(fn, steps, warmup, world=1, windows=1):
+def time_steps(fn, steps, warmup, world=1, windows=None):
     """W warm-up steps, then `windows` windows of exactly K steps each; returns (median window ms, all windows,
-    per-rank ms of the median window)."""
+    per-rank ms of the median window), or just the one window's ms when `windows` is not given."""
     for i in range(warmup):
         fn(i)
+    if windows is None:
+        return time_window(fn, steps, world, warmup)[0]
     res = [time_window(fn, steps, world, warmup + w * steps) for w in range(windows)]
     order = sorted(range(windows), key=lambda i: res[i][0])
     mid = order[len(order) // 2]
-    if windows == 1:
-        return res[0][0]
     return res[mid][0], [r[0] for r in res], res[mid][1]
 
 
@@ -391,15 +391,16 @@ class Workload:
         from sgl_cpu_tests_b200 import _lib as L
         lib = L.load()
         layer = self.layers[0]
-        out = {}
+        rides = self.world == 1 and bool(self.shared_I) and layer.rides(self.M)   # shared expert inside the routed launches
+        out = {"shared_rides": rides}
         for what in ("routed", "shared"):
-            if what == "shared" and not self.shared_I:
+            if what == "shared" and (not self.shared_I or rides):
                 continue
             lib.sglb_profile_enable(1)
             for i in range(steps):
                 lay = self.layers[i % self.copies]
                 if what == "routed":
-                    routed = lay.experts(self.x, self.tw, self.ids)
+                    routed = lay.experts(self.x, self.tw, self.ids, with_shared=rides)
                 else:
                     lay.add_shared(self.x, routed)
             torch.cuda.synchronize()
@@ -416,13 +417,16 @@ def roofline_of(wl, ms_per_step, stage_us, hbm_peak, tc, peak_src, traffic_key=N
     fmt, E, H, I, M, topk = wl.fmt, wl.E, wl.H, wl.I, wl.M, wl.topk
     ab = algorithmic_bytes(fmt, E, H, I, M, topk, wl.ids, wl.shared_I)
     k_us = stage_us["routed"]["w13_gemm"]
+    rides = bool(stage_us.get("shared_rides"))
+    if rides:   # the shared expert's w13 tiles stream inside the same launch: its 2*H*I weight bytes and M more act rows
+        ab["w13"] += ab["shared"] * 2 / 3 + M * wl.shared_I * 2
     gbs = ab["w13"] / (k_us * 1e-6) / 1e9 if k_us > 0 else 0.0
     used = path_used(wl.args, fmt, M, topk, E, H, I)
     kdesc = KERNEL_DESC.get((used, fmt), "stream_gemm_kernel")
     if fmt == "mxfp4" and wl.args.no_mx4_native:
         kdesc = "umma_dq_kernel"
-    kname = (f"{kdesc}<stage 1> (tcgen05 w13 GEMM + silu_and_mul)" if used.startswith("umma")
-             else "stream_gemm_kernel<stage 1> (mma.sync w13 GEMM + silu_and_mul)")
+    kname = (f"{kdesc}<stage 1> (tcgen05 w13 GEMM + silu_and_mul" + (", shared expert's tiles riding along)" if rides else ")")
+             if used.startswith("umma") else "stream_gemm_kernel<stage 1> (mma.sync w13 GEMM + silu_and_mul)")
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
@@ -495,7 +499,7 @@ def describe(wl):
 
 
 # ---------------------------------------------------------------------------------------------------------------
-def ep_parity(args, world, rank, dev):
+def ep_parity(args, world, rank, dev, verbose=False):
     """Before anything is timed at N > 1: a small seeded layer through every exchange mode (fixed, exact, p2p, and the
     captured p2p graphs) on ragged token counts incl. a rank without tokens, compared BIT FOR BIT with the single-GPU
     fused_experts (+ shared_expert) over the full expert set on the same tokens.  Any mismatch fails the run."""
@@ -537,6 +541,9 @@ def ep_parity(args, world, rank, dev):
                 res["eq_1gpu"] &= same
                 if M:
                     res["max_diff"] = max(res["max_diff"], float((out.float() - ref.float()).abs().max()))
+            if verbose:
+                torch.cuda.synchronize()
+                print(f"[ep_parity] rank {rank} {fmt} Ms={Ms}: eager modes done, eq_1gpu={res['eq_1gpu']}", file=sys.stderr, flush=True)
             if max(Ms) == min(Ms):      # equal token counts: the captured graphs as well (fixed shape by construction)
                 gph = layer.graphed(M, H, dev)
                 if gph is None:

@@ -146,10 +146,27 @@ typedef struct sglb_moe_problem {
   const int32_t* slot_map;
   /* > 0: expected routed rows per expert for the AUTO path rule (default M*topk/E) */
   float rows_per_expert_hint;
+  /* The layer's shared expert riding along in the same launches (DeepSeek: fused_experts_cpu followed by
+   * shared_expert_cpu, test_moe_fp8_ext.py:60-67,118-124).  With shared_w13 != NULL the call returns
+   *   out = bf16(shared_mlp(x) + bf16(routed(x)) * shared_rsf)
+   * bit-identical to sglb_fused_experts followed by sglb_shared_expert on its result: every token is one more
+   * routed row of "expert E" whose weights are shared_w13 [2I,H] / shared_w2 [H,I] (same I, format and block
+   * sizes as the routed experts; scales as for E = 1), so the shared expert's 3*H*I weight bytes stream inside
+   * the routed GEMM launches instead of five small launches of their own.  Only where
+   * sglb_fused_experts_shared_rides(p) returns 1 (tcgen05 path, bf16 / int8 / fp8 tensor-native, plain silu,
+   * no slot_out); elsewhere call sglb_shared_expert. */
+  const void* shared_w13;
+  const void* shared_w2;
+  const void* shared_w13_scale;
+  const void* shared_w2_scale;
+  float shared_rsf;
 } sglb_moe_problem;
 
 size_t sglb_fused_experts_workspace_bytes(int64_t M, int topk, int E, int H, int I, int fmt);
 int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t stream);
+/* 1 if this problem (shape, format, path, options; the shared_* pointers themselves are not looked at) can carry
+ * the shared expert inside its launches, else 0 */
+int sglb_fused_experts_shared_rides(const sglb_moe_problem* p);
 
 /* ---- K6 shared_expert -----------------------------------------------------------------------------
  * shared_expert_cpu (test_shared_experts.py:68,78; test_moe_fp8_ext.py:60-61; test_moe_fp8.py:87-88):

@@ -28,6 +28,7 @@ class MoeProblem(C.Structure):
         ("w13_scale_tiles", _vp), ("w2_scale_tiles", _vp),
         ("w13_bias", _vp), ("w2_bias", _vp), ("act", _i32), ("alpha", _f32), ("limit", _f32),
         ("slot_out", _vp), ("slot_map", _vp), ("rows_per_expert_hint", _f32),
+        ("shared_w13", _vp), ("shared_w2", _vp), ("shared_w13_scale", _vp), ("shared_w2_scale", _vp), ("shared_rsf", _f32),
     ]
 
 
@@ -67,6 +68,7 @@ SIGNATURES = {
     "sglb_moe_align": (C.c_int, [_vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(AlignOut), _vp, _vp]),
     "sglb_fused_experts_workspace_bytes": (_sz, [_i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "sglb_fused_experts": (C.c_int, [C.POINTER(MoeProblem), _vp]),
+    "sglb_fused_experts_shared_rides": (C.c_int, [C.POINTER(MoeProblem)]),
     "sglb_shared_expert": (C.c_int, [C.POINTER(SharedProblem), _vp]),
     "sglb_linear_workspace_bytes": (_sz, [_i64, C.c_int, C.c_int, C.c_int]),
     "sglb_linear": (C.c_int, [C.POINTER(LinearProblem), _vp]),

@@ -13,6 +13,11 @@
 //   chunk_list      = (expert, row_start, rows<=chunk_rows) work items for the streaming GEMM
 //   tile_list       = (expert, row_start, rows<=tile_rows)  work items for the tcgen05 GEMM
 //   counters        = {num_valid, num_chunks, num_tiles, num_active_experts}
+//
+// Shared expert riding along (capi.cu, sglb_moe_problem.shared_w13): `shared_rows` = M extra rows are appended
+// BEHIND the routed ones, at sorted positions [S, S + M) with sorted_slot[S + m] = m * topk (so that the gather's
+// slot / topk gives token m), as ceil(M / tile_rows) tiles of expert id E at the end of tile_list (counted in
+// num_tiles).  Nothing else changes: slot_pos, expert_offset and the chunk list describe the routed slots only.
 #include "common.cuh"
 
 namespace sglb {
@@ -97,7 +102,7 @@ __global__ void __launch_bounds__(kAlignThreads)
                          int32_t* __restrict__ expert_count, int32_t* __restrict__ expert_offset,
                          int32_t* __restrict__ sorted_slot, int32_t* __restrict__ slot_pos,
                          int32_t* __restrict__ chunk_list, int32_t* __restrict__ tile_list,
-                         int32_t* __restrict__ counters) {
+                         int32_t* __restrict__ counters, int shared_rows, int topk) {
   extern __shared__ int smem_i[];
   int* block_total = smem_i;            // [E]
   int* base = block_total + E;          // [E]  expert_offset + slots in earlier blocks
@@ -160,7 +165,16 @@ __global__ void __launch_bounds__(kAlignThreads)
             list[3 * (first + i) + 2] = min(rows, tot - r0);
           }
         }
-        if (threadIdx.x == 0) counters[1 + pass] = (list != nullptr) ? ntot : 0;
+        int nsh = 0;  // the shared expert's tiles: expert id E, rows [S, S + shared_rows)
+        if (pass == 1 && list != nullptr && shared_rows > 0 && rows > 0) {
+          nsh = (shared_rows + rows - 1) / rows;
+          for (int i = threadIdx.x; i < nsh; i += kAlignThreads) {
+            list[3 * (ntot + i) + 0] = E;
+            list[3 * (ntot + i) + 1] = S + i * rows;
+            list[3 * (ntot + i) + 2] = min(rows, shared_rows - i * rows);
+          }
+        }
+        if (threadIdx.x == 0) counters[1 + pass] = (list != nullptr) ? ntot + nsh : 0;
         __syncthreads();
       }
       int act = (x < E && tot > 0) ? 1 : 0;
@@ -183,22 +197,12 @@ __global__ void __launch_bounds__(kAlignThreads)
   for (int p = total_valid + blockIdx.x * kAlignThreads + threadIdx.x; p < S;
        p += nb * kAlignThreads)
     sorted_slot[p] = S;
+  for (int m = blockIdx.x * kAlignThreads + threadIdx.x; m < shared_rows; m += nb * kAlignThreads)
+    sorted_slot[S + m] = m * topk;
 }
 
-}  // namespace sglb
-
-using namespace sglb;
-
-extern "C" size_t sglb_moe_align_scratch_bytes(int64_t M, int topk, int E) {
-  int64_t S = M * topk;
-  int64_t nb = ceil_div64(S > 0 ? S : 1, kAlignThreads);
-  return (size_t)(nb * E) * sizeof(int32_t);
-}
-
-extern "C" int sglb_moe_align(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows,
-                              int tile_rows, const sglb_align_out* out, void* scratch,
-                              sglb_stream_t stream_) {
-  cudaStream_t stream = (cudaStream_t)stream_;
+int moe_align_impl(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows, int tile_rows,
+                   const sglb_align_out* out, void* scratch, int shared_rows, cudaStream_t stream) {
   SGLB_CHECK(out != nullptr, "moe_align: null output struct");
   SGLB_CHECK(E >= 1 && E <= 1024, "moe_align: E=%d must be in [1,1024]", E);
   SGLB_CHECK(M >= 0 && topk >= 1, "moe_align: bad shape");
@@ -221,7 +225,23 @@ extern "C" int sglb_moe_align(const int32_t* topk_ids, int64_t M, int topk, int 
   SGLB_CUDA(launch_pdl(align_scatter_kernel, dim3(nb), dim3(kAlignThreads), smem, stream, topk_ids, S, E,
                        nb, (const int32_t*)scratch, chunk_rows, tile_rows, out->expert_count,
                        out->expert_offset, out->sorted_slot, out->slot_pos, out->chunk_list,
-                       out->tile_list, out->counters));
+                       out->tile_list, out->counters, shared_rows, topk));
   count_launch(nb > 1 ? 2 : 1);
   return SGLB_OK;
+}
+
+}  // namespace sglb
+
+using namespace sglb;
+
+extern "C" size_t sglb_moe_align_scratch_bytes(int64_t M, int topk, int E) {
+  int64_t S = M * topk;
+  int64_t nb = ceil_div64(S > 0 ? S : 1, kAlignThreads);
+  return (size_t)(nb * E) * sizeof(int32_t);
+}
+
+extern "C" int sglb_moe_align(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows,
+                              int tile_rows, const sglb_align_out* out, void* scratch,
+                              sglb_stream_t stream_) {
+  return moe_align_impl(topk_ids, M, topk, E, chunk_rows, tile_rows, out, scratch, 0, (cudaStream_t)stream_);
 }

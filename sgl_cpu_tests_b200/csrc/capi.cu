@@ -92,7 +92,7 @@ static MoeWorkspace carve(void* base, int64_t M, int topk, int E, int H, int I, 
   MoeWorkspace w;
   w.xq2 = nullptr;
   w.actq2 = nullptr;
-  const int64_t S = M * topk;
+  const int64_t S = M * topk + M;  // + M rows behind the routed ones: the shared expert riding along (align.cu)
   size_t off = 0;
   auto take = [&](size_t bytes) {
     void* p = base ? (char*)base + off : nullptr;
@@ -105,7 +105,7 @@ static MoeWorkspace carve(void* base, int64_t M, int topk, int E, int H, int I, 
   w.sorted_slot = (int32_t*)take(sizeof(int32_t) * S);
   w.slot_pos = (int32_t*)take(sizeof(int32_t) * S);
   w.chunk_list = (int32_t*)take(sizeof(int32_t) * 3 * max_items(S, E, kMinChunkRows));
-  w.tile_list = (int32_t*)take(sizeof(int32_t) * 3 * max_items(S, E, kMinTileRows));
+  w.tile_list = (int32_t*)take(sizeof(int32_t) * 3 * (max_items(S, E, kMinTileRows) + M / kMinTileRows + 1));
   w.align_scratch = (int32_t*)take(sglb_moe_align_scratch_bytes(M, topk, E));
   w.zero_ids = (int32_t*)take(sizeof(int32_t) * M);
   // +kTileRows rows of slack: the tcgen05 path reads whole 128-row tiles past the last expert
@@ -200,7 +200,9 @@ struct MlpExtra {
   float alpha = 1.f, limit = 0.f;
   int out_by_slot = 0;              // stage 2 writes row sorted_slot[p] (through out_map) of ic2_out
   const int32_t* out_map = nullptr;
-  bool any() const { return w13_bias || w2_bias || act != SGLB_ACT_SILU || out_by_slot; }
+  // the shared expert riding along as expert id E: M more rows behind the routed ones (align.cu)
+  const void *sh_w13 = nullptr, *sh_w2 = nullptr, *sh_s13 = nullptr, *sh_s2 = nullptr;
+  bool any() const { return w13_bias || w2_bias || act != SGLB_ACT_SILU || out_by_slot || sh_w13; }
 };
 
 // One GEMM stage on the tcgen05 path over the tile list of an existing alignment.
@@ -238,6 +240,11 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.act_limit = sa.act_limit;
   u.out_by_slot = sa.out_by_slot;
   u.out_map = sa.out_map;
+  u.Wsh = sa.Wsh;
+  u.Wsh_scale = sa.Wsh_scale;
+  u.shared_row0 = sa.shared_row0;
+  const int sh_tiles = sa.Wsh ? (int)ceil_div64(S / sa.topk, kTileRows) : 0;
+  u.max_tiles += sh_tiles;
   if (mx4_tiles) return launch_umma_mx4(stage, u, stream);
   if (f8_native) return pair ? launch_umma2_f8(stage, u, stream) : launch_umma_f8(stage, u, stream);
   if (pair) return launch_umma2_gemm(fmt, stage, u, stream);
@@ -246,7 +253,7 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
     const double M = (double)S / sa.topk;
     double active = E == 1 ? 1.0 : E * (1.0 - pow(1.0 - (double)(sa.topk < E ? sa.topk : E) / E, M));
     if (active < 1) active = 1;
-    if ((double)S / active <= 32.0) u.est_tiles = (int)(active + 0.5);
+    if ((double)S / active <= 32.0) u.est_tiles = (int)(active + 0.5) + sh_tiles;
   }
   return launch_umma_gemm(fmt, stage, u, stream);
 }
@@ -284,6 +291,10 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   a.row_scale = nullptr;
   a.scale_cols = fmt == SGLB_FMT_FP8_W8A16 ? ceil_div(H, bk) : H / 32;
   a.ebias = ex.w13_bias;
+  a.Wsh = ex.sh_w13;
+  a.Wsh_scale = ex.sh_s13;
+  a.shared_row0 = ex.sh_w13 ? (int)S : 0;
+  const int64_t act_rows = S + (ex.sh_w13 ? M : 0);  // rows of act / ic2 in use
   a.act = ex.act;
   a.act_alpha = ex.alpha;
   a.act_limit = ex.limit;
@@ -330,17 +341,19 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   a.row_scale = row_scale;
   a.scale_cols = fmt == SGLB_FMT_FP8_W8A16 ? ceil_div(I, bk) : I / 32;
   a.ebias = ex.w2_bias;
+  a.Wsh = ex.sh_w2;
+  a.Wsh_scale = ex.sh_s2;
   a.out_by_slot = ex.out_by_slot;
   a.out_map = ex.out_map;
   if (fmt == SGLB_FMT_INT8_W8A8) {
     StageTimer t(ST_QUANT_ACT, stream);
-    rc = launch_quant_rows_f32((const float*)ws.act, S, I, ws.actq, ws.acts, stream);
+    rc = launch_quant_rows_f32((const float*)ws.act, act_rows, I, ws.actq, ws.acts, stream);
     if (rc) return rc;
     a.X = ws.actq;
     a.Xscale = ws.acts;
   } else if (f8) {
     StageTimer t(ST_QUANT_ACT, stream);
-    rc = launch_split_rows_e4m3(ws.act, S, I, ws.actq, ws.actq2, ws.acts, stream);
+    rc = launch_split_rows_e4m3(ws.act, act_rows, I, ws.actq, ws.actq2, ws.acts, stream);
     if (rc) return rc;
     a.X = ws.actq;
     a.X2 = ws.actq2;
@@ -353,8 +366,11 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
                                 : dispatch_stream<2>(fmt, a, plan2, stream);
 }
 
+int moe_align_impl(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows, int tile_rows,
+                   const sglb_align_out* out, void* scratch, int shared_rows, cudaStream_t stream);
+
 static int run_align(const int32_t* ids, int64_t M, int topk, int E, int chunk_rows,
-                     const MoeWorkspace& ws, cudaStream_t stream, int tile_rows = kTileRows) {
+                     const MoeWorkspace& ws, cudaStream_t stream, int tile_rows = kTileRows, int shared_rows = 0) {
   sglb_align_out ao;
   ao.expert_count = ws.expert_count;
   ao.expert_offset = ws.expert_offset;
@@ -364,8 +380,7 @@ static int run_align(const int32_t* ids, int64_t M, int topk, int E, int chunk_r
   ao.tile_list = ws.tile_list;
   ao.counters = ws.counters;
   StageTimer t(ST_ALIGN, stream);
-  int rc = sglb_moe_align(ids, M, topk, E, chunk_rows, tile_rows, &ao, ws.align_scratch, stream);
-  return rc;
+  return moe_align_impl(ids, M, topk, E, chunk_rows, tile_rows, &ao, ws.align_scratch, shared_rows, stream);
 }
 
 }  // namespace sglb
@@ -428,6 +443,32 @@ extern "C" size_t sglb_fused_experts_workspace_bytes(int64_t M, int topk, int E,
   return carve(nullptr, M, topk, E, H, I, fmt).bytes;
 }
 
+namespace sglb {
+int launch_topk_reduce(const void* ic2, const int32_t* slot_pos, int64_t M, int topk, int H, const void* shared_y,
+                       float rsf, void* out, cudaStream_t stream);
+
+// AUTO path rule of fused_experts (also what sglb_fused_experts_shared_rides consults)
+static int auto_path(const sglb_moe_problem* p, bool mx4) {
+  const double rows_per_expert = p->rows_per_expert_hint > 0.f ? (double)p->rows_per_expert_hint : (double)p->M * p->topk / p->E;
+  // fp8 on the fp8 tensor cores streams weights faster than the mma.sync kernel at every batch size
+  // measured (DSV3 M = 16: 82 % vs 59 % of the HBM roofline): no ALU work per weight byte
+  const bool f8 = p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k);
+  return ((f8 || mx4 || rows_per_expert >= kUmmaMinRowsPerExpert) && umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I))
+             ? SGLB_PATH_UMMA
+             : SGLB_PATH_STREAM;
+}
+}  // namespace sglb
+
+extern "C" int sglb_fused_experts_shared_rides(const sglb_moe_problem* p) {
+  if (p == nullptr || p->M <= 0 || p->E < 1 || p->topk < 1) return 0;
+  if (p->slot_out != nullptr || p->act != SGLB_ACT_SILU) return 0;
+  const bool f8 = p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k);
+  if (!(p->fmt == SGLB_FMT_BF16 || p->fmt == SGLB_FMT_INT8_W8A8 || f8)) return 0;
+  if (!umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I)) return 0;
+  const int path = p->path == SGLB_PATH_AUTO ? auto_path(p, false) : p->path;
+  return path == SGLB_PATH_UMMA ? 1 : 0;
+}
+
 extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   SGLB_CHECK(p != nullptr, "fused_experts: null problem");
@@ -448,6 +489,18 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
   ex.limit = p->limit;
   ex.out_by_slot = p->slot_out != nullptr;
   ex.out_map = p->slot_map;
+  const bool ride = p->shared_w13 != nullptr;
+  if (ride) {
+    SGLB_CHECK(p->shared_w2 != nullptr, "fused_experts: shared_w13 without shared_w2");
+    SGLB_CHECK(p->fmt == SGLB_FMT_BF16 || (p->shared_w13_scale && p->shared_w2_scale), "fused_experts: the shared expert needs its scales");
+    SGLB_CHECK(sglb_fused_experts_shared_rides(p),
+               "fused_experts: the shared expert cannot ride along here (tcgen05 path with bf16 / int8 / tensor-native fp8 "
+               "weights, plain silu, no slot_out); call sglb_shared_expert");
+    ex.sh_w13 = p->shared_w13;
+    ex.sh_w2 = p->shared_w2;
+    ex.sh_s13 = p->shared_w13_scale;
+    ex.sh_s2 = p->shared_w2_scale;
+  }
   void* stage2_out = nullptr;  // set below: ws.ic2 (expert-sorted rows, reduced by K5) or the caller's slot rows
   const size_t need = sglb_fused_experts_workspace_bytes(p->M, p->topk, p->E, p->H, p->I, p->fmt);
   SGLB_CHECK(p->workspace && p->workspace_bytes >= need, "fused_experts: workspace too small (%zu < %zu)",
@@ -465,12 +518,7 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
                    umma_mx4_supported(p->H, p->I);
   const int mx4_cap = mx4 ? umma_mx4_tile_rows(rows_per_expert) : 0;
   if (path == SGLB_PATH_AUTO) {
-    // fp8 on the fp8 tensor cores streams weights faster than the mma.sync kernel at every batch size
-    // measured (DSV3 M = 16: 82 % vs 59 % of the HBM roofline): no ALU work per weight byte
-    const bool f8 = p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k);
-    path = ((f8 || mx4 || rows_per_expert >= kUmmaMinRowsPerExpert) && umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I))
-               ? SGLB_PATH_UMMA
-               : SGLB_PATH_STREAM;
+    path = auto_path(p, mx4);
     // bf16 prefill: the CTA-pair kernel wins once pair tiles fill up (Qwen3 M = 4096: 793 vs 705 TFLOP/s,
     // M = 8192: 940 vs 804); int8 stays on the single-CTA kernel (940 vs 805 TOP/s at M = 4096)
     // The pair kernel is NOT taken automatically any more: tests/test_gpu_fullsize.py (tools/dbg_perm.py) found
@@ -490,7 +538,7 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
                "fused_experts: the CTA-pair tcgen05 path has no expert bias / clamped swiglu / slot-addressed output");
     const bool use_mx4 = mx4 && path == SGLB_PATH_UMMA;
     rc = run_align(p->topk_ids, p->M, p->topk, p->E, 0, ws, stream,
-                   use_mx4 ? mx4_cap : (path == SGLB_PATH_UMMA2 ? umma2_tile_rows() : kTileRows));
+                   use_mx4 ? mx4_cap : (path == SGLB_PATH_UMMA2 ? umma2_tile_rows() : kTileRows), ride ? (int)p->M : 0);
     if (rc) return rc;
     rc = run_mlp(path, p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2,
                  p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, stage2_out, stream,
@@ -507,7 +555,9 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
   }
   if (p->slot_out) return SGLB_OK;  // the caller reduces the slot rows (expert-parallel combine)
   StageTimer t(ST_REDUCE, stream);
-  return sglb_topk_reduce(ws.ic2, ws.slot_pos, p->M, p->topk, p->H, p->out, stream);
+  // riding shared expert: its rows sit behind the routed ones; the reduce applies shared_expert_cpu's epilogue
+  const void* shared_y = ride ? (const void*)(ws.ic2 + (size_t)p->M * p->topk * p->H) : nullptr;
+  return launch_topk_reduce(ws.ic2, ws.slot_pos, p->M, p->topk, p->H, shared_y, p->shared_rsf, p->out, stream);
 }
 
 extern "C" int sglb_shared_expert(const sglb_shared_problem* p, sglb_stream_t stream_) {

@@ -85,7 +85,8 @@ __global__ void __launch_bounds__(256) quant_rows_kernel(const TIN* __restrict__
 // which GPU produced which slot.
 __global__ void __launch_bounds__(256)
     topk_reduce_kernel(const __nv_bfloat16* __restrict__ ic2, const int32_t* __restrict__ slot_pos,
-                       int topk, int H, __nv_bfloat16* __restrict__ out) {
+                       int topk, int H, const __nv_bfloat16* __restrict__ shared_y, float rsf,
+                       __nv_bfloat16* __restrict__ out) {
   pdl_wait();
   pdl_trigger();
   const int64_t m = blockIdx.y;
@@ -108,6 +109,10 @@ __global__ void __launch_bounds__(256)
     } else {
       for (int i = 0; i < 8 && h0 + i < H; ++i) acc[i] += __bfloat162float(src[i]);
     }
+  }
+  if (shared_y != nullptr) {  // shared_expert_cpu's epilogue on the rounded sum (shared_axpy_kernel's arithmetic)
+    const __nv_bfloat16* y = shared_y + (size_t)m * H + h0;
+    for (int i = 0; i < 8 && h0 + i < H; ++i) acc[i] = fmaf(bf16_round(acc[i]), rsf, __bfloat162float(y[i]));
   }
   __nv_bfloat16* dst = out + (size_t)m * H + h0;
   if (full) {
@@ -216,8 +221,9 @@ int launch_quant_rows_f32(const float* x, int64_t rows, int K, int8_t* q, float*
 }
 }  // namespace sglb
 
-extern "C" int sglb_topk_reduce(const void* ic2, const int32_t* slot_pos, int64_t M, int topk,
-                                int H, void* out, sglb_stream_t stream) {
+namespace sglb {
+int launch_topk_reduce(const void* ic2, const int32_t* slot_pos, int64_t M, int topk, int H, const void* shared_y,
+                       float rsf, void* out, cudaStream_t stream) {
   SGLB_CHECK(ic2 && slot_pos && out, "topk_reduce: null pointer");
   SGLB_CHECK(M < 65536ll * 32768ll, "topk_reduce: M too large");
   if (M == 0) return SGLB_OK;
@@ -225,12 +231,19 @@ extern "C" int sglb_topk_reduce(const void* ic2, const int32_t* slot_pos, int64_
   for (int64_t m0 = 0; m0 < M; m0 += 65535) {
     int64_t mm = M - m0 < 65535 ? M - m0 : 65535;
     dim3 grid((unsigned)ceil_div(ceil_div(H, 8), 256), (unsigned)mm);
-    SGLB_CUDA(launch_pdl(topk_reduce_kernel, grid, dim3(256), 0, (cudaStream_t)stream,
-                         (const __nv_bfloat16*)ic2, slot_pos + m0 * topk, topk, H,
+    SGLB_CUDA(launch_pdl(topk_reduce_kernel, grid, dim3(256), 0, stream, (const __nv_bfloat16*)ic2,
+                         slot_pos + m0 * topk, topk, H,
+                         shared_y ? (const __nv_bfloat16*)shared_y + m0 * H : (const __nv_bfloat16*)nullptr, rsf,
                          (__nv_bfloat16*)out + m0 * H));
     count_launch();
   }
   return SGLB_OK;
+}
+}  // namespace sglb
+
+extern "C" int sglb_topk_reduce(const void* ic2, const int32_t* slot_pos, int64_t M, int topk,
+                                int H, void* out, sglb_stream_t stream) {
+  return sglb::launch_topk_reduce(ic2, slot_pos, M, topk, H, nullptr, 1.f, out, (cudaStream_t)stream);
 }
 
 namespace sglb {

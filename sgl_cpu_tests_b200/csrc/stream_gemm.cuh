@@ -44,6 +44,9 @@ struct StreamArgs {
   float act_alpha, act_limit;
   int out_by_slot;         // stage 2: write routed row p to row sorted_slot[p] (through out_map if set) instead of p
   const int32_t* out_map;
+  const void* Wsh;         // tcgen05 paths only: the shared expert riding along (see UmmaArgs)
+  const void* Wsh_scale;
+  int shared_row0;
 };
 
 template <int FMT>

@@ -211,7 +211,10 @@ __device__ __forceinline__ void gather_role(const UmmaArgs& a, int total, int n_
       }
     };
     const int w0 = blockIdx.x;
-    WorkItem cur = get_item(a, w0 < total ? w0 : 0, n_blocks);
+    // no item for this CTA (fewer items than CTAs, or every id masked: then tile_list holds nothing at all and the
+    // lookahead below would chase uninitialised row indices)
+    if (w0 >= total) return;
+    WorkItem cur = get_item(a, w0, n_blocks);
     WorkItem nxt = get_item(a, w0 + step < total ? w0 + step : 0, n_blocks);
     int xr_cur[8];
     rows_of(cur, xr_cur);
@@ -284,7 +287,7 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
             if (kInt8 || kTokScale) xs_r[i] = a.Xscale[a.sorted_slot[p] / a.topk];
           } else {
             if (kInt8 || kTokScale) xs_r[i] = a.Xscale[p];
-            if (a.row_scale != nullptr) rs_r[i] = a.row_scale[a.sorted_slot[p]];
+            if (a.row_scale != nullptr && wi.e < a.E) rs_r[i] = a.row_scale[a.sorted_slot[p]];
           }
         }
       }
@@ -299,14 +302,14 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
         const int n = nbase + lane;
         float ws0 = 1.f, ws1 = 1.f;
         if (kInt8 && n < a.N) {
-          const float* ws = (const float*)a.Wscale + (size_t)wi.e * a.rows_per_expert;
+          const float* ws = wi.e < a.E ? (const float*)a.Wscale + (size_t)wi.e * a.rows_per_expert : (const float*)a.Wsh_scale;
           ws0 = ws[n];
           if (STAGE == 1) ws1 = ws[a.N + n];
         }
         float bias_n = 0.f;  // dense linears: f32 bias of output n (this lane's TMEM lane)
         if (STAGE == 2 && a.bias != nullptr && n < a.N) bias_n = a.bias[n];
         float eb0 = 0.f, eb1 = 0.f;  // per-expert bias of this lane's output(s)
-        if (a.ebias != nullptr && n < a.N) {
+        if (a.ebias != nullptr && n < a.N && wi.e < a.E) {
           const float* eb = a.ebias + (size_t)wi.e * a.rows_per_expert;
           eb0 = eb[n];
           if (STAGE == 1) eb1 = eb[a.N + n];

@@ -61,7 +61,8 @@ __device__ __forceinline__ uint32_t instr_desc_f8(int n) {
 
 template <int STAGE>
 __global__ void __launch_bounds__(kThreads, 1)
-    umma_f8_kernel(const __grid_constant__ CUtensorMap tmap_w, const UmmaArgs a) {
+    umma_f8_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_sh,
+                   const UmmaArgs a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t epi_base = smem_base + kStages * kStageBytes;
@@ -83,6 +84,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_w)) : "memory");
+    if (a.Wsh != nullptr) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_sh)) : "memory");
     for (int s = 0; s < kStages; ++s) {
       mbar_init(full_bar(s), 1 + kGatherThreadsF8);
       mbar_init(empty_bar(s), 1);
@@ -117,13 +119,15 @@ __global__ void __launch_bounds__(kThreads, 1)
           const WorkItem wi = get_item(a, w, n_blocks);
           const int wrow0 = STAGE == 1 ? wi.nb * kWSub : wi.nb * 2 * kWSub;
           const int wrow1 = STAGE == 1 ? a.N + wi.nb * kWSub : wrow0 + kWSub;
+          const CUtensorMap* tm = wi.e < a.E ? &tmap_w : &tmap_sh;  // the shared expert rides along as expert id E
+          const int we = wi.e < a.E ? wi.e : 0;
           for (int kb = 0; kb < num_kb; ++kb, ++it) {
             const int s = it % kStages;
             mbar_wait(empty_bar(s), ((it / kStages) & 1) ^ 1);
             if (elect_one()) {
               mbar_arrive_expect_tx(full_bar(s), 2 * kWTileBytes);
-              tma_load_3d(w_tile(s), &tmap_w, full_bar(s), kb * kRowBytes, wrow0, wi.e);
-              tma_load_3d(w_tile(s) + kWTileBytes, &tmap_w, full_bar(s), kb * kRowBytes, wrow1, wi.e);
+              tma_load_3d(w_tile(s), tm, full_bar(s), kb * kRowBytes, wrow0, we);
+              tma_load_3d(w_tile(s) + kWTileBytes, tm, full_bar(s), kb * kRowBytes, wrow1, we);
             }
             __syncwarp();
           }
@@ -224,10 +228,9 @@ __global__ void __launch_bounds__(kThreads, 1)
       const int wrow0 = STAGE == 1 ? wi.nb * kWSub : wi.nb * 2 * kWSub;
       const int wrow1 = STAGE == 1 ? a.N + wi.nb * kWSub : wrow0 + kWSub;
       // scale rows of this warp's 32 weight rows (block_n is a multiple of 32): one scalar per k block
-      const float* srow0 = (const float*)a.Wscale +
-                           ((size_t)wi.e * nblk_rows + min(wrow0 + q * 32, a.rows_per_expert - 1) / a.block_n) * a.scale_cols;
-      const float* srow1 = (const float*)a.Wscale +
-                           ((size_t)wi.e * nblk_rows + min(wrow1 + q * 32, a.rows_per_expert - 1) / a.block_n) * a.scale_cols;
+      const float* sbase = wi.e < a.E ? (const float*)a.Wscale + (size_t)wi.e * nblk_rows * a.scale_cols : (const float*)a.Wsh_scale;
+      const float* srow0 = sbase + (size_t)(min(wrow0 + q * 32, a.rows_per_expert - 1) / a.block_n) * a.scale_cols;
+      const float* srow1 = sbase + (size_t)(min(wrow1 + q * 32, a.rows_per_expert - 1) / a.block_n) * a.scale_cols;
       // per-token scalars: lane l keeps tokens l, l+32, l+64, l+96
       float xs_r[4], rs_r[4];
 #pragma unroll
@@ -240,7 +243,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             xs_r[i] = a.Xscale[a.sorted_slot[p] / a.topk];
           } else {
             xs_r[i] = a.Xscale[p];
-            if (a.row_scale != nullptr) rs_r[i] = a.row_scale[a.sorted_slot[p]];
+            if (a.row_scale != nullptr && wi.e < a.E) rs_r[i] = a.row_scale[a.sorted_slot[p]];
           }
         }
       }
@@ -312,7 +315,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           float bias_n = 0.f;
           if (STAGE == 2 && a.bias != nullptr && nbase + lane < a.N) bias_n = a.bias[nbase + lane];
           float eb0 = 0.f, eb1 = 0.f;  // per-expert bias of this lane's output(s)
-          if (a.ebias != nullptr && nbase + lane < a.N) {
+          if (a.ebias != nullptr && nbase + lane < a.N && wi.e < a.E) {
             const float* eb = a.ebias + (size_t)wi.e * a.rows_per_expert;
             eb0 = eb[nbase + lane];
             if (STAGE == 1) eb1 = eb[a.N + nbase + lane];
@@ -417,6 +420,11 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   CUtensorMap map;
   int rc = weight_tensor_map(a.W, (uint64_t)a.K, (uint64_t)a.rows_per_expert, (uint64_t)a.E, kRowBytes, kWSub, 1, &map);
   if (rc) return rc;
+  CUtensorMap map_sh = map;
+  if (a.Wsh != nullptr) {
+    rc = weight_tensor_map(a.Wsh, (uint64_t)a.K, (uint64_t)a.rows_per_expert, 1, kRowBytes, kWSub, 1, &map_sh);
+    if (rc) return rc;
+  }
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     SGLB_CUDA(cudaFuncSetAttribute(umma_f8_kernel<STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
@@ -425,7 +433,7 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   const int n_blocks = STAGE == 1 ? ceil_div(a.N, kWSub) : ceil_div(a.N, 2 * kWSub);
   const int64_t max_items = (int64_t)a.max_tiles * n_blocks;
   const int grid = (int)(max_items < sm_count() ? (max_items > 0 ? max_items : 1) : sm_count());
-  SGLB_CUDA(launch_pdl(umma_f8_kernel<STAGE>, dim3(grid), dim3(kThreads), kSmemBytes, stream, map, a));
+  SGLB_CUDA(launch_pdl(umma_f8_kernel<STAGE>, dim3(grid), dim3(kThreads), kSmemBytes, stream, map, map_sh, a));
   return SGLB_OK;
 }
 

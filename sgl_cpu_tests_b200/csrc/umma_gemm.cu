@@ -47,7 +47,8 @@ constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBufBytes + 10
 
 template <int FMT, int STAGE>
 __global__ void __launch_bounds__(kThreads, 1)
-    umma_moe_kernel(const __grid_constant__ CUtensorMap tmap_w, const UmmaArgs a) {
+    umma_moe_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_sh,
+                    const UmmaArgs a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B: 1 KB aligned
   const uint32_t epi_base = smem_base + kStages * kStageBytes;
@@ -70,6 +71,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_w)) : "memory");
+    if (a.Wsh != nullptr) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_sh)) : "memory");
     for (int s = 0; s < kStages; ++s) {
       mbar_init(full_bar(s), 1 + kGatherThreads);
       mbar_init(empty_bar(s), 1);
@@ -102,19 +104,22 @@ __global__ void __launch_bounds__(kThreads, 1)
       // The descriptor of the next item is fetched while this item streams: a dependent tile_list load at
       // every item start leaves the ring's freed slots unissued for its latency (one item is only ~11 us of
       // HBM time per SM for int8 at decode).
-      WorkItem nxt = get_item(a, blockIdx.x < total ? blockIdx.x : 0, n_blocks);
+      WorkItem nxt = {0, 0, 0, 0};
+      if ((int)blockIdx.x < total) nxt = get_item(a, blockIdx.x, n_blocks);
       for (int w = blockIdx.x; w < total; w += gridDim.x) {
         const WorkItem wi = nxt;
         if (w + (int)gridDim.x < total) nxt = get_item(a, w + gridDim.x, n_blocks);
         const int wrow0 = STAGE == 1 ? wi.nb * kWSub : wi.nb * 2 * kWSub;
         const int wrow1 = STAGE == 1 ? a.N + wi.nb * kWSub : wrow0 + kWSub;
+        const CUtensorMap* tm = wi.e < a.E ? &tmap_w : &tmap_sh;  // the shared expert rides along as expert id E
+        const int we = wi.e < a.E ? wi.e : 0;
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int s = it % kStages;
           mbar_wait(empty_bar(s), ((it / kStages) & 1) ^ 1);
           if (elect_one()) {
             mbar_arrive_expect_tx(full_bar(s), 2 * kWTileBytes);
-            tma_load_3d(w_tile(s), &tmap_w, full_bar(s), kb * kRowBytes, wrow0, wi.e);
-            tma_load_3d(w_tile(s) + kWTileBytes, &tmap_w, full_bar(s), kb * kRowBytes, wrow1, wi.e);
+            tma_load_3d(w_tile(s), tm, full_bar(s), kb * kRowBytes, wrow0, we);
+            tma_load_3d(w_tile(s) + kWTileBytes, tm, full_bar(s), kb * kRowBytes, wrow1, we);
           }
           __syncwarp();
         }
@@ -277,6 +282,11 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   int rc = weight_tensor_map(a.W, (uint64_t)a.K * EB, (uint64_t)a.rows_per_expert, (uint64_t)a.E, kRowBytes, kWSub, 1,
                              &map);
   if (rc) return rc;
+  CUtensorMap map_sh = map;
+  if (a.Wsh != nullptr) {
+    rc = weight_tensor_map(a.Wsh, (uint64_t)a.K * EB, (uint64_t)a.rows_per_expert, 1, kRowBytes, kWSub, 1, &map_sh);
+    if (rc) return rc;
+  }
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     SGLB_CUDA(cudaFuncSetAttribute(umma_moe_kernel<FMT, STAGE>,
@@ -300,7 +310,7 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
     return e ? atoi(e) : 0;
   }();
   if (forced_grid > 0 && forced_grid < grid) grid = forced_grid;
-  SGLB_CUDA(launch_pdl(umma_moe_kernel<FMT, STAGE>, dim3(grid), dim3(kThreads), kSmemBytes, stream, map, a));
+  SGLB_CUDA(launch_pdl(umma_moe_kernel<FMT, STAGE>, dim3(grid), dim3(kThreads), kSmemBytes, stream, map, map_sh, a));
   return SGLB_OK;
 }
 

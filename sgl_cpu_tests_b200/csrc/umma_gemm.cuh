@@ -34,6 +34,12 @@ struct UmmaArgs {
   float act_alpha, act_limit;
   int out_by_slot;         // stage 2: write routed row p to row sorted_slot[p] (through out_map if set) instead of p
   const int32_t* out_map;
+  // Shared expert riding along (umma_gemm.cu and umma_f8.cu only): tiles whose expert id is E (appended by moe_align,
+  // rows [shared_row0, shared_row0 + M) of X / out) take their weights from Wsh (one expert of the same shape, through
+  // a second tensor map) and their scales from Wsh_scale; they carry no per-expert bias and no topk weight.
+  const void* Wsh;         // nullptr = none
+  const void* Wsh_scale;
+  int shared_row0;         // = M * topk when Wsh is set, else 0
 };
 
 constexpr int kUmmaTileRows = 128;  // routed rows per tile (tile_rows handed to moe_align)

@@ -24,16 +24,29 @@ class MoELayer:
     shared_expert(x) + routed_scaling_factor * fused_experts(x, router(gating))   (shared given)
     fused_experts(x, router(gating))                                             (no shared expert)."""
 
-    def __init__(self, weights, fmt, router, shared=None, routed_scaling_factor=1.0, path=L.PATH_AUTO):
+    def __init__(self, weights, fmt, router, shared=None, routed_scaling_factor=1.0, path=L.PATH_AUTO, ride=True):
         self.w, self.fmt, self.router, self.shared, self.rsf, self.path = weights, fmt, router, shared, float(routed_scaling_factor), path
+        self.ride = ride    # let the shared expert ride along in the routed experts' launches where the kernels can
+
+    def rides(self, num_tokens):
+        """The shared expert's rows go through the routed experts' two GEMM launches (same result bit for bit, five
+        launches and a second pass of under-filled kernels fewer) when it has the experts' own shape and format."""
+        if self.shared is None or not self.ride:
+            return False
+        E, H, I = ops._weight_geometry(self.w["w1"], self.w["w2"], self.fmt, False)
+        s = self.shared
+        return ops.shared_rides(num_tokens, self.router.topk, E, H, I, self.fmt, self.w.get("block"), self.path,
+                                shared_I=s["w2"].shape[-1], shared_fmt=s.get("fmt", self.fmt)) \
+            and s.get("block") == self.w.get("block")
 
     def route(self, gating, out_w=None, out_ids=None):
         return self.router(gating, out_w, out_ids)
 
-    def experts(self, x, tw, ids, out=None):
+    def experts(self, x, tw, ids, out=None, with_shared=False):
         w = self.w
         return ops.fused_experts_impl(x, w["w1"], w["w2"], tw, ids, False, self.fmt, w.get("s1"), w.get("s2"), w.get("block"),
-                                      False, path=self.path, out=out)
+                                      False, path=self.path, out=out, shared=self.shared if with_shared else None,
+                                      routed_scaling_factor=self.rsf)
 
     def add_shared(self, x, routed, out=None):
         if self.shared is None:
@@ -44,6 +57,8 @@ class MoELayer:
 
     def forward(self, x, gating):
         tw, ids = self.route(gating)
+        if self.rides(x.shape[0]):
+            return self.experts(x, tw, ids, with_shared=True)
         return self.add_shared(x, self.experts(x, tw, ids))
 
     def graphed(self, num_tokens):
@@ -77,8 +92,13 @@ class GraphedLayer:
         side = torch.cuda.Stream(device=dev)
         key = (dev.index, side.cuda_stream)
 
+        self.rides = layer.rides(num_tokens)
+
         def call():
             layer.route(self.gating, self.topk_weights, self.topk_ids)
+            if self.rides:
+                layer.experts(self.hidden, self.topk_weights, self.topk_ids, out=self.out, with_shared=True)
+                return
             layer.experts(self.hidden, self.topk_weights, self.topk_ids, out=self.routed)
             if layer.shared is not None:
                 layer.add_shared(self.hidden, self.routed, out=self.out)

@@ -525,12 +525,16 @@ def _host_graph(M, topk, fmt, w13, w2d, s13, s2, block_size, path):
 
 def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, fmt, w1_scale, w2_scale,
                        block_size, is_vnni, path=L.PATH_AUTO, out=None, w1_bias=None, w2_bias=None, alpha=None,
-                       limit=None, slot_out=None, slot_map=None, rows_per_expert_hint=0.0):
+                       limit=None, slot_out=None, slot_map=None, rows_per_expert_hint=0.0, shared=None,
+                       routed_scaling_factor=1.0):
     """Format-explicit core behind every fused_experts_cpu signature vintage.  `out` (CUDA callers only):
     a [M, H] bf16 device tensor that receives the result instead of a fresh allocation.
     w1_bias [E, 2I] / w2_bias [E, H] / alpha / limit: the 17-argument vintage (gpt-oss expert biases and clamped
     swiglu; include/sglb200.h).  slot_out (CUDA callers): bf16 rows addressed by routed slot (through slot_map if
-    given) instead of the reduced [M, H] result -- the expert-parallel return path; returns slot_out."""
+    given) instead of the reduced [M, H] result -- the expert-parallel return path; returns slot_out.
+    shared (CUDA callers): dict(w1 [2I, H], w2 [H, I], s1, s2) -- the layer's shared expert riding along in the same
+    launches; the result is then shared_expert_cpu(x, ..., fused_experts_cpu(x, ...), routed_scaling_factor), bit for
+    bit (include/sglb200.h, sglb_moe_problem.shared_w13).  Only where shared_rides(...) says so."""
     if hidden_states.dim() != 2 or hidden_states.dtype != torch.bfloat16:
         raise RuntimeError("fused_experts: hidden_states must be a 2-D bfloat16 tensor")
     if w1.dtype not in _WDT[fmt] or w2.dtype != w1.dtype:
@@ -558,7 +562,8 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
     with torch.cuda.device(dev):
         w13 = _resident_weight(w1, is_vnni, dev)
         w2d = _resident_weight(w2, is_vnni, dev)
-        extras = w1_bias is not None or w2_bias is not None or alpha is not None or limit is not None or slot_out is not None
+        extras = (w1_bias is not None or w2_bias is not None or alpha is not None or limit is not None or slot_out is not None
+                  or shared is not None)
         if not on_cuda and _HOST_GRAPH and M <= _HOST_GRAPH_MAX_TOKENS and out is None and not extras:
             if fmt == L.FMT_MXFP4:
                 gs13, gs2 = _resident_mx_scale(w1_scale, is_vnni, dev), _resident_mx_scale(w2_scale, is_vnni, dev)
@@ -618,6 +623,16 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
             out = x
         else:
             out = torch.empty_like(x)
+        sh = [None] * 4
+        if shared is not None:
+            sw1, sw2 = shared["w1"], shared["w2"]
+            if not (on_cuda and sw1.is_cuda and sw2.is_cuda) or tuple(sw1.shape) != (2 * I, H) or tuple(sw2.shape) != (H, I) \
+                    or sw1.dtype != w13.dtype or not (sw1.is_contiguous() and sw2.is_contiguous()):
+                raise RuntimeError("fused_experts: a riding shared expert needs CUDA tensors w1 [2I, H], w2 [H, I] of the experts' "
+                                   "own I and dtype")
+            sh = [sw1, sw2, shared.get("s1"), shared.get("s2")]
+            if fmt != L.FMT_BF16 and (sh[2] is None or sh[3] is None or sh[2].dtype != torch.float32 or not sh[2].is_cuda):
+                raise RuntimeError("fused_experts: a riding shared expert needs its f32 CUDA scales")
         nws = lib.sglb_fused_experts_workspace_bytes(M, topk, E, H, I, fmt)
         with _launch_lock:
             ws = _workspace(nws, dev)
@@ -629,7 +644,9 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
                              w13_bias=_ptr(b13), w2_bias=_ptr(b2), act=act,
                              alpha=float(1.702 if alpha is None else alpha), limit=float(0.0 if limit is None else limit),
                              slot_out=_ptr(slot_out), slot_map=_ptr(slot_map),
-                             rows_per_expert_hint=float(rows_per_expert_hint))
+                             rows_per_expert_hint=float(rows_per_expert_hint),
+                             shared_w13=_ptr(sh[0]), shared_w2=_ptr(sh[1]), shared_w13_scale=_ptr(sh[2]),
+                             shared_w2_scale=_ptr(sh[3]), shared_rsf=float(routed_scaling_factor))
             L.check(lib.sglb_fused_experts(p, _stream()))
         if slot_out is not None:
             return slot_out
@@ -642,6 +659,16 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
             hidden_states.copy_(out)  # D2H into the caller's buffer ("fused moe mutates content in hs")
             return hidden_states
         return out.cpu()
+
+
+def shared_rides(M, topk, E, H, I, fmt, block_size=None, path=L.PATH_AUTO, shared_I=None, shared_fmt=None):
+    """True where fused_experts_impl(shared=...) can carry the layer's shared expert inside the routed experts'
+    launches (sglb_fused_experts_shared_rides + the shape conditions: same I and format as the routed experts)."""
+    if M <= 0 or (shared_I is not None and shared_I != I) or (shared_fmt is not None and shared_fmt != fmt):
+        return False
+    bn, bk = (int(block_size[0]), int(block_size[1])) if (fmt == L.FMT_FP8_W8A16 and block_size is not None) else (0, 0)
+    p = L.MoeProblem(M=M, topk=topk, E=E, H=H, I=I, fmt=fmt, path=path, block_n=bn, block_k=bk, act=L.ACT_SILU)
+    return bool(L.load().sglb_fused_experts_shared_rides(p))
 
 
 class GraphedExperts:

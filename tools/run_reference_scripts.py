@@ -138,7 +138,8 @@ def own_timing(shape_lines):
         parts = []
         for fmt in ("bf16", "int8", "fp8"):
             ws = [bench.make_weights(fmt, E, H, I, dev, gen) for _ in range(2)]
-            x, tw, ids = bench.make_batch(M, E, topk, H, dev, gen)
+            x, gating = bench.make_batch(M, E, H, dev, gen)
+            tw, ids = K.grouped_topk(x, gating, topk, False, 1, 1)      # bench_moe.py:33-41: plain top-k of the gate
 
             def step(i):
                 w = ws[i % 2]
