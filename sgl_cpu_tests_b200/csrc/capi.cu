@@ -60,6 +60,8 @@ int launch_shared_axpy(const void* y, const void* fused, float rsf, int64_t n, v
                        cudaStream_t stream);
 int launch_quant_rows_f32(const float* x, int64_t rows, int K, int8_t* q, float* scale,
                           cudaStream_t stream);
+int launch_gather_rows(const int32_t* sorted_slot, int64_t S, int topk, int row_bytes, const void* x, const void* x2, void* y,
+                       void* y2, cudaStream_t stream);
 
 // ---- workspace carving -------------------------------------------------------------------------
 struct MoeWorkspace {
@@ -73,6 +75,7 @@ struct MoeWorkspace {
   int8_t* actq;               // [S, I]
   float* acts;                // [S]
   int8_t *xq2, *actq2;        // fp8 tensor-native path: lo pieces (xq / actq hold the hi pieces)
+  int8_t *xsorted, *xsorted2; // CTA-pair path: the stage-1 rows in expert-sorted order (bf16 / s8 / e4m3 hi, lo)
   size_t bytes;
 };
 
@@ -130,6 +133,10 @@ static MoeWorkspace carve(void* base, int64_t M, int topk, int E, int H, int I, 
     w.actq = nullptr;
     w.acts = nullptr;
   }
+  // the CTA-pair kernels take the stage-1 rows pre-gathered (one row per routed slot)
+  const size_t eb = fmt == SGLB_FMT_BF16 ? 2 : 1;
+  w.xsorted = (int8_t*)take((size_t)M * topk * H * eb);
+  w.xsorted2 = fmt == SGLB_FMT_FP8_W8A16 ? (int8_t*)take((size_t)M * topk * H) : nullptr;
   w.bytes = off;
   return w;
 }
@@ -243,6 +250,7 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.Wsh = sa.Wsh;
   u.Wsh_scale = sa.Wsh_scale;
   u.shared_row0 = sa.shared_row0;
+  u.x_rows = (int)(sa.gather ? S / sa.topk : S);  // token rows when gathered, else the sorted rows themselves
   const int sh_tiles = sa.Wsh ? (int)ceil_div64(S / sa.topk, kTileRows) : 0;
   u.max_tiles += sh_tiles;
   if (mx4_tiles) return launch_umma_mx4(stage, u, stream);
@@ -319,6 +327,15 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
     a.Xscale = ws.xs;
   } else {
     a.X = hidden;
+  }
+  if (pair) {  // routed rows into expert-sorted order: the pair kernels read them as plain TMA boxes
+    StageTimer t(ST_QUANT_X, stream);
+    rc = launch_gather_rows(ws.sorted_slot, S, topk, H * (fmt == SGLB_FMT_BF16 ? 2 : 1), a.X, a.X2, ws.xsorted,
+                            a.X2 ? ws.xsorted2 : nullptr, stream);
+    if (rc) return rc;
+    a.X = ws.xsorted;
+    if (a.X2) a.X2 = ws.xsorted2;
+    a.gather = 0;
   }
   {
     StageTimer t(ST_GEMM1, stream);
@@ -453,9 +470,19 @@ static int auto_path(const sglb_moe_problem* p, bool mx4) {
   // fp8 on the fp8 tensor cores streams weights faster than the mma.sync kernel at every batch size
   // measured (DSV3 M = 16: 82 % vs 59 % of the HBM roofline): no ALU work per weight byte
   const bool f8 = p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k);
-  return ((f8 || mx4 || rows_per_expert >= kUmmaMinRowsPerExpert) && umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I))
-             ? SGLB_PATH_UMMA
-             : SGLB_PATH_STREAM;
+  const int path = ((f8 || mx4 || rows_per_expert >= kUmmaMinRowsPerExpert) && umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I))
+                       ? SGLB_PATH_UMMA
+                       : SGLB_PATH_STREAM;
+  // Prefill: the CTA-pair kernels (M = 256 MMAs, routed rows pre-gathered into sorted order and fed by TMA) once
+  // pair tiles fill up.  Measured (tools/pair_check.py, r2i; bit-identical to the single-CTA kernels): bf16 Qwen3
+  // M = 4096 / 8192: 785 / 928 vs 732 / 829 TFLOP/s; fp8 DSV3 M = 8192: 806 vs 698; slower for int8 (744 vs 858
+  // TOP/s) and for fp8 layers with little work per gathered row (Qwen3 I = 768: 562 vs 588, I = 384: 415 vs 468).
+  // Not with expert biases / clamped swiglu / slot-addressed output (single-CTA epilogues only).
+  const bool plain = !p->w13_bias && !p->w2_bias && p->act == SGLB_ACT_SILU && !p->slot_out;
+  if (path == SGLB_PATH_UMMA && !mx4 && plain && rows_per_expert >= kPairMinRowsPerExpert &&
+      (p->fmt == SGLB_FMT_BF16 || (f8 && (double)p->H * p->I >= 8.0e6)))
+    return SGLB_PATH_UMMA2;
+  return path;
 }
 }  // namespace sglb
 
@@ -465,6 +492,7 @@ extern "C" int sglb_fused_experts_shared_rides(const sglb_moe_problem* p) {
   const bool f8 = p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k);
   if (!(p->fmt == SGLB_FMT_BF16 || p->fmt == SGLB_FMT_INT8_W8A8 || f8)) return 0;
   if (!umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I)) return 0;
+  // where AUTO takes the CTA-pair kernels for the routed experts (prefill) the shared expert stays a call of its own
   const int path = p->path == SGLB_PATH_AUTO ? auto_path(p, false) : p->path;
   return path == SGLB_PATH_UMMA ? 1 : 0;
 }
@@ -519,14 +547,6 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
   const int mx4_cap = mx4 ? umma_mx4_tile_rows(rows_per_expert) : 0;
   if (path == SGLB_PATH_AUTO) {
     path = auto_path(p, mx4);
-    // bf16 prefill: the CTA-pair kernel wins once pair tiles fill up (Qwen3 M = 4096: 793 vs 705 TFLOP/s,
-    // M = 8192: 940 vs 804); int8 stays on the single-CTA kernel (940 vs 805 TOP/s at M = 4096)
-    // The pair kernel is NOT taken automatically any more: tests/test_gpu_fullsize.py (tools/dbg_perm.py) found
-    // it not bit-reproducible from run to run at 256 rows per expert (a few rows per call off by up to 6e-2,
-    // inside the reference tolerance but a race: the relay / remote-arrive chain of umma_pair.cuh orders the
-    // peer CTA's cp.async rows at CTA scope only).  It stays available as SGLB_PATH_UMMA2 until that is fixed.
-    if (false && path == SGLB_PATH_UMMA && p->fmt == SGLB_FMT_BF16 && rows_per_expert >= kPairMinRowsPerExpert)
-      path = SGLB_PATH_UMMA2;
   }
   if (path == SGLB_PATH_UMMA || path == SGLB_PATH_UMMA2) {
     SGLB_CHECK(umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I),

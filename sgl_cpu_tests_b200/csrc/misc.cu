@@ -125,6 +125,24 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// ---- routed rows into expert-sorted order (CTA-pair kernels read them as plain TMA boxes) -------------------------
+// y[p] = x[sorted_slot[p] / topk] for the valid positions p (sentinel entries = S are skipped); x2 / y2: a second
+// array gathered the same way (the lo pieces of the fp8 split) or nullptr.
+__global__ void __launch_bounds__(128)
+    gather_rows_kernel(const int32_t* __restrict__ sorted_slot, int S, int topk, int row_bytes, const char* __restrict__ x,
+                       const char* __restrict__ x2, char* __restrict__ y, char* __restrict__ y2) {
+  pdl_wait();
+  pdl_trigger();
+  const int p = blockIdx.x;
+  const int slot = sorted_slot[p];
+  if (slot >= S) return;
+  const size_t src = (size_t)(slot / topk) * row_bytes, dst = (size_t)p * row_bytes;
+  for (int i = threadIdx.x * 16; i < row_bytes; i += 128 * 16) {
+    *reinterpret_cast<int4*>(y + dst + i) = *reinterpret_cast<const int4*>(x + src + i);
+    if (x2 != nullptr) *reinterpret_cast<int4*>(y2 + dst + i) = *reinterpret_cast<const int4*>(x2 + src + i);
+  }
+}
+
 // ---- shared expert epilogue: out = y + fused_out * rsf ------------------------------------------
 __global__ void __launch_bounds__(256)
     shared_axpy_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ fused,
@@ -247,6 +265,15 @@ extern "C" int sglb_topk_reduce(const void* ic2, const int32_t* slot_pos, int64_
 }
 
 namespace sglb {
+int launch_gather_rows(const int32_t* sorted_slot, int64_t S, int topk, int row_bytes, const void* x, const void* x2, void* y,
+                       void* y2, cudaStream_t stream) {
+  SGLB_CHECK(row_bytes % 16 == 0, "gather_rows: rows must be whole 16-byte pieces (%d bytes)", row_bytes);
+  if (S == 0) return SGLB_OK;
+  SGLB_CUDA(launch_pdl(gather_rows_kernel, dim3((unsigned)S), dim3(128), 0, stream, sorted_slot, (int)S, topk, row_bytes,
+                       (const char*)x, (const char*)x2, (char*)y, (char*)y2));
+  count_launch();
+  return SGLB_OK;
+}
 int launch_shared_axpy(const void* y, const void* fused, float rsf, int64_t n, void* out,
                        cudaStream_t stream) {
   if (n == 0) return SGLB_OK;

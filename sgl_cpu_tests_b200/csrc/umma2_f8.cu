@@ -9,9 +9,10 @@
 // the warps holding `up` pass their finished accumulators to the `gate` warps through shared memory.
 //
 // Roles (12 warps; setmaxnreg: 56 registers for the producer warpgroup, 216 for the epilogue):
-//   warp 0      TMA producer (cta_group::2 loads, bytes counted on the leader's full barrier)
-//   warp 1      leader: MMA issuer; peer: relay (routed rows landed -> leader's full barrier)
-//   warps 2-3   gather producers, hi and lo pieces of this CTA's half of the routed rows
+//   warp 0      TMA producer, weights (cta_group::2 loads, bytes counted on the leader's full barrier)
+//   warp 1      leader: MMA issuer; peer: idle
+//   warps 2-3   idle (the routed rows arrive in expert-sorted order: warp 0 loads this CTA's hi and lo halves as two
+//               2-D TMA boxes counted on the leader's full barrier, umma2_gemm.cu header)
 //   warps 4-11  epilogue: acc += scale * partial per k block (128 f32 registers per thread), fused output
 #include <type_traits>
 
@@ -25,7 +26,6 @@ namespace {
 
 constexpr int kStagesP = 4;
 constexpr int kStageBytesP = kWTileBytes + 2 * kXTileBytes;  // 48 KB: A half + X hi + X lo (this CTA's rows)
-constexpr int kGatherThreadsP = 64;
 constexpr int kFirstEpiWarpP = 4;
 constexpr int kThreadsP = (kFirstEpiWarpP + kEpiWarps) * 32;  // 384
 constexpr int kXchgBytesP = 4 * 2 * 2048;
@@ -47,7 +47,8 @@ __device__ __forceinline__ uint32_t instr_desc_pair_f8(int n) {
 
 template <int STAGE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
-    umma2_f8_kernel(const __grid_constant__ CUtensorMap tmap_w, const UmmaArgs a) {
+    umma2_f8_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_xh,
+                    const __grid_constant__ CUtensorMap tmap_xl, const UmmaArgs a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t epi_base = smem_base + kStagesP * kStageBytesP;
@@ -57,7 +58,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
   auto xh_tile = [&](int s) { return smem_base + s * kStageBytesP + kWTileBytes; };
   auto xl_tile = [&](int s) { return smem_base + s * kStageBytesP + kWTileBytes + kXTileBytes; };
   auto full_bar = [&](int s) { return bar_base + 8 * s; };
-  auto xfull_bar = [&](int s) { return bar_base + 8 * (kStagesP + s); };
   auto empty_bar = [&](int s) { return bar_base + 8 * (2 * kStagesP + s); };
   auto pfull_bar = [&](int b) { return bar_base + 8 * (3 * kStagesP + b); };
   auto pempty_bar = [&](int b) { return bar_base + 8 * (3 * kStagesP + 2 + b); };
@@ -73,9 +73,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_w)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_xh)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_xl)) : "memory");
     for (int s = 0; s < kStagesP; ++s) {
-      mbar_init(full_bar(s), 2);
-      mbar_init(xfull_bar(s), kGatherThreadsP);
+      mbar_init(full_bar(s), 1);  // the leader's expect_tx arrive; everything else is TMA bytes
       mbar_init(empty_bar(s), 1);
     }
     for (int b = 0; b < 2; ++b) {
@@ -106,12 +107,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
       uint32_t it = 0;
       for (int w = cluster_id; w < total; w += num_clusters) {
         const PairItem wi = get_pair_item(a, w, n_blocks);
+        const int n_eff = (wi.rows + 15) & ~15;
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int s = it % kStagesP;
           mbar_wait(empty_bar(s), ((it / kStagesP) & 1) ^ 1);
           if (elect_one()) {
             const uint32_t lbar = mapa(full_bar(s), 0);
-            if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2 * kWTileBytes);
+            // both CTAs' weight halves + both CTAs' hi and lo routed-row boxes (whole 128-row boxes)
+            if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2 * kWTileBytes + 4 * kXTileBytes);
+            const int r0 = wi.row_start + (int)rank * (n_eff >> 1);
+            tma_load_2d_pair(xh_tile(s), &tmap_xh, lbar, kb * kRowBytes, r0);
+            tma_load_2d_pair(xl_tile(s), &tmap_xl, lbar, kb * kRowBytes, r0);
             if constexpr (STAGE == 1) {
               const int g0 = wi.nb * kWSub + (int)rank * 64;
               tma_load_3d_pair(w_tile(s), &tmap_w, lbar, kb * kRowBytes, g0, wi.e);
@@ -140,8 +146,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
             }
             const int s = it % kStagesP;
             mbar_wait(full_bar(s), (it / kStagesP) & 1);
-            mbar_wait(xfull_bar(s), (it / kStagesP) & 1);
-            fence_proxy_async();
             tc_fence_after();
             const uint32_t acc = tmem_base + pb * kAccCols;
             const bool last = (kb % G) == G - 1 || kb == num_kb - 1;
@@ -161,51 +165,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
             if (last) ++gi;
           }
         }
-      } else {
-        // ================= relay (peer) =================
-        uint32_t it = 0;
-        for (int w = cluster_id; w < total; w += num_clusters) {
-          for (int kb = 0; kb < num_kb; ++kb, ++it) {
-            const int s = it % kStagesP;
-            mbar_wait(xfull_bar(s), (it / kStagesP) & 1);
-            fence_proxy_async();
-            if (elect_one()) mbar_arrive_cluster_release(mapa(full_bar(s), 0));
-            __syncwarp();
-          }
-        }
-      }
-    } else {
-      // ================= gather producers: hi and lo pieces of this CTA's routed rows =================
-      const int g = threadIdx.x - 64;
-      const int c = g & 7, rbase = g >> 3;
-      const uint32_t dst0 = rbase * kRowBytes + ((c ^ (rbase & 7)) << 4);
-      const char* xh = (const char*)a.X + c * 16;
-      const char* xl = (const char*)a.X2 + c * 16;
-      uint32_t it = 0;
-      for (int w = cluster_id; w < total; w += num_clusters) {
-        const PairItem wi = get_pair_item(a, w, n_blocks);
-        const int half = ((wi.rows + 15) & ~15) >> 1;
-        uint32_t off[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int r = (int)rank * half + rbase + 8 * j;
-          const int p = wi.row_start + min(r, wi.rows - 1);
-          const int xr = a.gather ? (a.sorted_slot[p] / a.topk) : p;
-          off[j] = (uint32_t)xr * (uint32_t)a.K;
-        }
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
-          const int s = it % kStagesP;
-          mbar_wait(empty_bar(s), ((it / kStagesP) & 1) ^ 1);
-          const uint32_t dh = xh_tile(s) + dst0, dl = xl_tile(s) + dst0;
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            if (rbase + 8 * j < half) {
-              cp_async16(dh + j * 8 * kRowBytes, xh + off[j] + kb * kRowBytes);
-              cp_async16(dl + j * 8 * kRowBytes, xl + off[j] + kb * kRowBytes);
-            }
-          }
-          cp_async_arrive_noinc(xfull_bar(s));
-        }
       }
     }
   } else {
@@ -224,6 +183,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
     const uint32_t pempty_l0 = mapa(pempty_bar(0), 0), pempty_l1 = mapa(pempty_bar(1), 0);
     const int nblk_rows = ceil_div(a.rows_per_expert, a.block_n);
     uint32_t gi = 0;
+    uint32_t xi = 0;  // exchange-buffer parity over all chunks of this warp pair, across items (umma2_gemm.cu)
     for (int w = cluster_id; w < total; w += num_clusters) {
       const PairItem wi = get_pair_item(a, w, n_blocks);
       const int n_eff = (wi.rows + 15) & ~15;
@@ -299,7 +259,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
         if (c0 >= n_eff) continue;
         const float xsel = sel8(xs_r, c), rsel = sel8(rs_r, c);
         if constexpr (STAGE == 1) {
-          float* xb = xbuf + (c & 1) * 512;
+          float* xb = xbuf + (xi++ & 1) * 512;
           if (is_up) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
@@ -353,6 +313,12 @@ int launch_pair_f8(const UmmaArgs& a, cudaStream_t stream) {
   int rc = weight_tensor_map(a.W, (uint64_t)a.K, (uint64_t)a.rows_per_expert, (uint64_t)a.E, kRowBytes,
                              STAGE == 1 ? 64 : kWSub, 1, &map);
   if (rc) return rc;
+  CUtensorMap map_xh, map_xl;
+  SGLB_CHECK(a.gather == 0, "CTA-pair tcgen05 path: routed rows must be in expert-sorted order (gather = 0)");
+  rc = rows_tensor_map(a.X, (uint64_t)a.K, (uint64_t)a.x_rows, kUmmaTileRows, &map_xh);
+  if (rc) return rc;
+  rc = rows_tensor_map(a.X2, (uint64_t)a.K, (uint64_t)a.x_rows, kUmmaTileRows, &map_xl);
+  if (rc) return rc;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     SGLB_CUDA(cudaFuncSetAttribute(umma2_f8_kernel<STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesP));
@@ -372,7 +338,7 @@ int launch_pair_f8(const UmmaArgs& a, cudaStream_t stream) {
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  SGLB_CUDA(cudaLaunchKernelEx(&cfg, umma2_f8_kernel<STAGE>, map, a));
+  SGLB_CUDA(cudaLaunchKernelEx(&cfg, umma2_f8_kernel<STAGE>, map, map_xh, map_xl, a));
   return SGLB_OK;
 }
 

@@ -15,10 +15,18 @@
 // (two 64-row TMA boxes into one 128-row operand tile); the epilogue warps that hold `up` hand
 // their values to the warps that hold `gate` through shared memory.
 //
+// Routed rows come through the TMA unit as well: the caller hands both stages rows that are ALREADY in
+// expert-sorted order (stage 1: capi.cu gathers the token rows once per call, gather_rows_kernel; stage 2: act is
+// produced in that order), so each CTA's half of a tile is one 2-D TMA box whose bytes are counted on the LEADER's
+// full barrier like the weights'.  History: the first version gathered with cp.async and relayed "my half is in
+// place" to the leader with a remote mbarrier arrive; rows written through the generic proxy in one CTA and read by
+// a tensor core driven from the other need a cluster-scope release on that arrive (without it 1-20 rows per 4096
+// differed from run to run; with it the membar cost ~1 us per stage).  TMA tile::gather4 (four arbitrary rows per
+// instruction, tools/gather4_probe.cu) removes the proxy problem but 32-64 instructions of 4 x 128 B per stage
+// run at half the speed of the single-CTA kernel (tools/pair_check.py, r2i).  One box per stage does not.
+//
 // Barriers (s = smem stage, b = TMEM buffer; "L" lives in the leader CTA only):
-//   full[s]  L   weights of both CTAs landed (TMA cta_group::2 complete_tx on the leader's barrier)
-//                + the peer's routed rows are in place (one remote arrive from the peer's relay warp)
-//   xfull[s]     this CTA's routed rows landed (cp.async arrivals of its 128 gather threads)
+//   full[s]  L   weights and routed rows of both CTAs landed (TMA cta_group::2 complete_tx on the leader's barrier)
 //   empty[s]     tcgen05.commit multicast to both CTAs: stage may be refilled
 //   tfull[b]     tcgen05.commit multicast: accumulators complete
 //   tempty[b] L  one arrive per epilogue warp of both CTAs: buffer drained
@@ -32,14 +40,15 @@ namespace {
 
 constexpr int kStages2 = 5;
 constexpr int kStageBytes2 = kWTileBytes + kXTileBytes;       // 32 KB: A half (128 rows) + B half (<= 128 rows)
-constexpr int kFirstEpiWarp2 = 6;
+constexpr int kFirstEpiWarp2 = 4;                             // warp 0: TMA (weights + routed rows), 1: MMA issuer, 2-3 idle
 constexpr int kThreads2 = (kFirstEpiWarp2 + kEpiWarps) * 32;  // 448
 constexpr int kXchgBytes = 4 * 2 * 2048;                      // 4 warp pairs x 2 buffers x (16 tokens x 32 lanes f32)
 constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + kEpiWarps * kEpiBufBytes + kXchgBytes + 1024 + 256;
 
 template <int FMT, int STAGE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
-    umma2_moe_kernel(const __grid_constant__ CUtensorMap tmap_w, const UmmaArgs a) {
+    umma2_moe_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
+                     const UmmaArgs a) {
   extern __shared__ uint8_t smem_raw[];
   constexpr bool kInt8 = FMT == SGLB_FMT_INT8_W8A8;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -49,7 +58,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
   auto w_tile = [&](int s) { return smem_base + s * kStageBytes2; };
   auto x_tile = [&](int s) { return smem_base + s * kStageBytes2 + kWTileBytes; };
   auto full_bar = [&](int s) { return bar_base + 8 * s; };
-  auto xfull_bar = [&](int s) { return bar_base + 8 * (kStages2 + s); };
   auto empty_bar = [&](int s) { return bar_base + 8 * (2 * kStages2 + s); };
   auto tfull_bar = [&](int b) { return bar_base + 8 * (3 * kStages2 + b); };
   auto tempty_bar = [&](int b) { return bar_base + 8 * (3 * kStages2 + 2 + b); };
@@ -66,9 +74,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_w)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_x)) : "memory");
     for (int s = 0; s < kStages2; ++s) {
-      mbar_init(full_bar(s), 2);                 // leader's expect_tx arrive + the peer's relay
-      mbar_init(xfull_bar(s), kGatherThreads);
+      mbar_init(full_bar(s), 1);                 // the leader's expect_tx arrive; everything else is TMA bytes
       mbar_init(empty_bar(s), 1);
     }
     for (int b = 0; b < 2; ++b) {
@@ -97,12 +105,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
     uint32_t it = 0;
     for (int w = cluster_id; w < total; w += num_clusters) {
       const PairItem wi = get_pair_item(a, w, n_blocks);
+      const int n_eff = (wi.rows + 15) & ~15;
       for (int kb = 0; kb < num_kb; ++kb, ++it) {
         const int s = it % kStages2;
         mbar_wait(empty_bar(s), ((it / kStages2) & 1) ^ 1);
         if (elect_one()) {
           const uint32_t lbar = mapa(full_bar(s), 0);
-          if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2 * kWTileBytes);
+          // both CTAs' weight halves + both CTAs' routed-row boxes (whole 128-row boxes: rows past the tile's half
+          // belong to the next tile or are zero-filled past the array, and are never multiplied: N = n_eff)
+          if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2 * kWTileBytes + 2 * kXTileBytes);
+          tma_load_2d_pair(x_tile(s), &tmap_x, lbar, kb * kRowBytes, wi.row_start + (int)rank * (n_eff >> 1));
           if constexpr (STAGE == 1) {  // 64 gate rows + the matching 64 up rows
             const int g0 = wi.nb * kWSub + (int)rank * 64;
             tma_load_3d_pair(w_tile(s), &tmap_w, lbar, kb * kRowBytes, g0, wi.e);
@@ -129,8 +141,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int s = it % kStages2;
           mbar_wait(full_bar(s), (it / kStages2) & 1);
-          mbar_wait(xfull_bar(s), (it / kStages2) & 1);
-          fence_proxy_async();  // this CTA's routed rows were written by cp.async (generic proxy)
           tc_fence_after();
           if (elect_one()) {
 #pragma unroll
@@ -145,46 +155,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
           __syncwarp();
         }
       }
-    } else {
-      // ================= relay (peer CTA): routed rows in place -> leader's full barrier =================
-      uint32_t it = 0;
-      for (int w = cluster_id; w < total; w += num_clusters) {
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
-          const int s = it % kStages2;
-          mbar_wait(xfull_bar(s), (it / kStages2) & 1);
-          fence_proxy_async();
-          if (elect_one()) mbar_arrive_cluster_release(mapa(full_bar(s), 0));
-          __syncwarp();
-        }
-      }
     }
   } else if (warp < kFirstEpiWarp2) {
-    // ================= gather producers: this CTA's half of the routed rows =================
-    const int g = threadIdx.x - 64;
-    const int c = g & 7, rbase = g >> 3;
-    const uint32_t dst0 = rbase * kRowBytes + ((c ^ (rbase & 7)) << 4);
-    uint32_t it = 0;
-    for (int w = cluster_id; w < total; w += num_clusters) {
-      const PairItem wi = get_pair_item(a, w, n_blocks);
-      const int half = ((wi.rows + 15) & ~15) >> 1;
-      const char* src[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int r = (int)rank * half + rbase + 16 * j;
-        const int p = wi.row_start + min(r, wi.rows - 1);
-        const int xr = a.gather ? (a.sorted_slot[p] / a.topk) : p;
-        src[j] = (const char*)a.X + (size_t)xr * k_bytes + c * 16;
-      }
-      for (int kb = 0; kb < num_kb; ++kb, ++it) {
-        const int s = it % kStages2;
-        mbar_wait(empty_bar(s), ((it / kStages2) & 1) ^ 1);
-        const uint32_t dst = x_tile(s) + dst0;
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (rbase + 16 * j < half) cp_async16(dst + j * 16 * kRowBytes, src[j] + kb * kRowBytes);
-        cp_async_arrive_noinc(xfull_bar(s));
-      }
-    }
+    // idle
   } else {
     // ================= epilogue =================
     // warp (q, par): TMEM lanes [32q, 32q+32) of this CTA, 16-column (= 16-token) chunks of parity par.
@@ -202,6 +175,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
     float* xbuf = reinterpret_cast<float*>(smem_raw + (xchg_base + pair_idx * 4096 - smem_u32(smem_raw)));
     const uint32_t tempty_l0 = mapa(tempty_bar(0), 0), tempty_l1 = mapa(tempty_bar(1), 0);
     uint32_t li = 0;
+    // Exchange-buffer parity runs over ALL chunks this warp pair processes, not per item: with a per-item counter a
+    // ragged tile with an odd number of chunks is followed by a chunk in the SAME buffer, and the `up` warp -- which
+    // has nothing left to do for the item once it has passed the last barrier, and whose next accumulators are
+    // usually ready -- overwrote values the `gate` warp was still reading (the run-to-run differences that round 1
+    // blamed on the relay alone; tools/pair_check.py).
+    uint32_t ci = 0;
     for (int w = cluster_id; w < total; w += num_clusters, ++li) {
       const PairItem wi = get_pair_item(a, w, n_blocks);
       const int n_eff = (wi.rows + 15) & ~15;
@@ -235,7 +214,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
       mbar_wait(tfull_bar(buf), (li >> 1) & 1);
       tc_fence_after();
       const uint32_t acc = tmem_base + lane_off + buf * kAccCols;
-      int ci = 0;
 #pragma unroll 1
       for (int c0 = 16 * par; c0 < n_eff; c0 += 32, ++ci) {  // n_eff is uniform over the CTA
         const float xsel = sel8(xs_r, c0 >> 5), rsel = sel8(rs_r, c0 >> 5);
@@ -307,6 +285,10 @@ int launch_pair(const UmmaArgs& a, cudaStream_t stream) {
   int rc = weight_tensor_map(a.W, (uint64_t)a.K * EB, (uint64_t)a.rows_per_expert, (uint64_t)a.E, kRowBytes,
                              STAGE == 1 ? 64 : kWSub, 1, &map);
   if (rc) return rc;
+  CUtensorMap map_x;
+  SGLB_CHECK(a.gather == 0, "CTA-pair tcgen05 path: routed rows must be in expert-sorted order (gather = 0)");
+  rc = rows_tensor_map(a.X, (uint64_t)a.K * EB, (uint64_t)a.x_rows, kUmmaTileRows, &map_x);
+  if (rc) return rc;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     SGLB_CUDA(cudaFuncSetAttribute(umma2_moe_kernel<FMT, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -327,7 +309,7 @@ int launch_pair(const UmmaArgs& a, cudaStream_t stream) {
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  SGLB_CUDA(cudaLaunchKernelEx(&cfg, umma2_moe_kernel<FMT, STAGE>, map, a));
+  SGLB_CUDA(cudaLaunchKernelEx(&cfg, umma2_moe_kernel<FMT, STAGE>, map, map_x, a));
   return SGLB_OK;
 }
 

@@ -403,6 +403,8 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
 // host helpers shared by the two tcgen05 translation units (defined in umma_gemm.cu)
 int weight_tensor_map(const void* W, uint64_t kbytes, uint64_t rows, uint64_t E, uint32_t box_bytes,
                       uint32_t box_rows, int swizzle128, CUtensorMap* out);
+// Routed-row map (rows already in expert-sorted order): bytes {K_bytes, rows}, box {128, box_rows}, 128-B swizzle
+int rows_tensor_map(const void* X, uint64_t kbytes, uint64_t rows, uint32_t box_rows, CUtensorMap* out);
 int sm_count();
 
 }  // namespace sglb

@@ -263,6 +263,21 @@ int weight_tensor_map(const void* W, uint64_t kbytes, uint64_t rows, uint64_t E,
   return SGLB_OK;
 }
 
+int rows_tensor_map(const void* X, uint64_t kbytes, uint64_t rows, uint32_t box_rows, CUtensorMap* out) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  SGLB_CHECK(enc != nullptr, "tcgen05 path: cuTensorMapEncodeTiled is not available from this driver");
+  SGLB_CHECK(((uintptr_t)X & 15) == 0 && kbytes % 16 == 0, "tcgen05 path: routed rows must be 16-byte aligned");
+  const cuuint64_t gdim[2] = {kbytes, rows};
+  const cuuint64_t gstride[1] = {kbytes};
+  const cuuint32_t box[2] = {kRowBytes, box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(X), gdim, gstride, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  SGLB_CHECK(r == CUDA_SUCCESS, "tcgen05 path: cuTensorMapEncodeTiled (routed rows) failed (CUresult %d)", (int)r);
+  return SGLB_OK;
+}
+
 int sm_count() {
   static int n = [] {
     int dev = 0, v = 0;

@@ -40,6 +40,7 @@ struct UmmaArgs {
   const void* Wsh;         // nullptr = none
   const void* Wsh_scale;
   int shared_row0;         // = M * topk when Wsh is set, else 0
+  int x_rows;              // rows of X (CTA-pair kernels: bound of the TMA gather map)
 };
 
 constexpr int kUmmaTileRows = 128;  // routed rows per tile (tile_rows handed to moe_align)

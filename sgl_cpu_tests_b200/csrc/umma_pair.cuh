@@ -54,6 +54,17 @@ __device__ __forceinline__ void tma_load_3d_pair(uint32_t dst, const CUtensorMap
       "l"(reinterpret_cast<uint64_t>(map)), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+// 2-D TMA tile of routed rows (rows [r0, r0 + box rows) x 128 bytes at byte column c0 of a [rows, K] array, 128-B
+// swizzle), bytes counted on a barrier of the pair's LEADER CTA like the weights': the routed rows of both CTAs reach
+// shared memory through the async proxy and complete on the barrier the MMA issuer waits on -- no generic-proxy
+// writes, no relay warp, no cluster-scope fence (umma2_gemm.cu header).
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, uint32_t leader_bar, int c0, int r0) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          dst),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(leader_bar), "r"(c0), "r"(r0)
+      : "memory");
+}
 template <int FMT>
 __device__ __forceinline__ void umma_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                           uint32_t accumulate) {

@@ -148,3 +148,20 @@ def test_fused_experts_full_size_properties(K, fmt, E, topk, H, I, M):
     got = out[rows.to(DEV)].float().cpu()
     scale = max(1e-6, float(ref.float().abs().max()))
     torch.testing.assert_close(got / scale, ref.float() / scale, **TOL)
+
+
+@pytest.mark.parametrize("fmt", ["bf16", "int8", "fp8"])
+def test_pair_kernels_equal_single_cta_bitwise_at_scale(K, fmt):
+    """CTA-pair kernels (umma2_*.cu) over many ragged tiles per cluster: bit-identical to the single-CTA kernels and
+    from run to run.  Small cases (one item per cluster) never reuse a TMEM buffer or the gate/up exchange buffer
+    across items; this size does (tools/pair_check.py found the exchange-buffer race that way)."""
+    E, topk, H, I, M = 128, 8, 2048, 768, 4096
+    fmt_id = {"bf16": K.FMT_BF16, "int8": K.FMT_INT8_W8A8, "fp8": K.FMT_FP8_W8A16}[fmt]
+    layer = make_layer(fmt, E, H, I)
+    g = torch.Generator(device=DEV).manual_seed(9)
+    x = torch.randn(M, H, device=DEV, generator=g, dtype=torch.bfloat16) / (4 if fmt != "fp8" else math.sqrt(H))
+    tw, ids = routing(M, E, topk, 9)
+    ids[::5, 0] = -1
+    ref = call(K, layer, fmt_id, x, tw, ids, path=K.PATH_UMMA)
+    for _ in range(6):
+        assert torch.equal(call(K, layer, fmt_id, x, tw, ids, path=K.PATH_UMMA2), ref)

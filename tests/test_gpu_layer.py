@@ -43,7 +43,9 @@ def test_riding_shared_expert_is_bit_identical(K, fmt, M):
     sep, *_ = build(K, fmt, E, topk, H, I, I, 11, False, path=K.PATH_UMMA)
     assert ride.rides(M) and not sep.rides(M)
     g = torch.Generator(device=dev).manual_seed(100 + M)
-    x = (torch.randn(M, H, device=dev, generator=g) / 4).bfloat16()
+    # outputs of O(1), as in the reference's scripts (test_moe_fp8_ext.py:33-35 scales its operands the same way):
+    # the op rounds the shared MLP and the sum to bf16, so two ulps at |out| > 2 already exceed rtol = atol = 1e-2
+    x = (torch.randn(M, H, device=dev, generator=g) / 16).bfloat16()
     gating = torch.randn(M, E, device=dev, generator=g).bfloat16()
     n0 = K.launch_count()
     a = ride.forward(x, gating)
