@@ -65,6 +65,12 @@ int sglb_profile_read(float* ms_out, int* calls_out, int n);
  * the kernel (csrc/umma_dq.cu).  Process-wide switch, used by the parity tests to cover both. */
 void sglb_set_fp8_native(int on);
 
+/* Decode chain fusion (default 1): up to 8192 routed slots per call, fused_experts runs align + the stage-1 operand
+ * preparation as ONE prologue launch, quantises the int8 activation inside the stage-2 producer and performs the
+ * top-k reduce inside the stage-2 epilogue (last arriver per token, slot order) -- 3 launches for bf16 / int8 instead
+ * of 4-7, results bit-identical.  0 = the separate launches (kept for the parity tests and for prefill). */
+void sglb_set_chain_fusion(int on);
+
 /* ---- K1 router ------------------------------------------------------------------------------
  * grouped_topk_cpu          (test_grouped_topk.py:61-69, test_moe.py:61-70)  : bias == NULL
  * biased_grouped_topk_cpu   (test_biased_grouped_topk.py:71-80)              : bias != NULL

@@ -57,6 +57,7 @@ SIGNATURES = {
     "sglb_launch_count": (C.c_uint64, []),
     "sglb_profile_enable": (None, [C.c_int]),
     "sglb_set_fp8_native": (None, [C.c_int]),
+    "sglb_set_chain_fusion": (None, [C.c_int]),
     "sglb_set_mx4_native": (None, [C.c_int]),
     "sglb_mx4_scale_tiles_bytes": (_sz, [_i64, C.c_int, C.c_int, C.c_int]),
     "sglb_mx4_tile_scales": (C.c_int, [_vp, _vp, _i64, C.c_int, C.c_int, C.c_int, _vp]),

@@ -19,6 +19,7 @@
 // slot / topk gives token m), as ceil(M / tile_rows) tiles of expert id E at the end of tile_list (counted in
 // num_tiles).  Nothing else changes: slot_pos, expert_offset and the chunk list describe the routed slots only.
 #include "common.cuh"
+#include "rowops.cuh"
 
 namespace sglb {
 
@@ -96,20 +97,39 @@ __global__ void __launch_bounds__(kAlignThreads) align_count_kernel(const int32_
   for (int x = threadIdx.x; x < E; x += kAlignThreads) block_hist[(size_t)blockIdx.x * E + x] = hist[x];
 }
 
-__global__ void __launch_bounds__(kAlignThreads)
-    align_scatter_kernel(const int32_t* __restrict__ ids, int S, int E, int nb,
-                         const int32_t* __restrict__ block_hist, int chunk_rows, int tile_rows,
-                         int32_t* __restrict__ expert_count, int32_t* __restrict__ expert_offset,
-                         int32_t* __restrict__ sorted_slot, int32_t* __restrict__ slot_pos,
-                         int32_t* __restrict__ chunk_list, int32_t* __restrict__ tile_list,
-                         int32_t* __restrict__ counters, int shared_rows, int topk) {
-  extern __shared__ int smem_i[];
+// Body of one align block (blockIdx.x < nb).  block_hist: per-block expert histograms from align_count_kernel, or
+// nullptr -- then a block counts the slots of the other blocks itself (the single-launch prologue, nb <= 8).
+__device__ __forceinline__ void align_block(int* smem_i, const int32_t* __restrict__ ids, int S, int E, int nb,
+                                            const int32_t* __restrict__ block_hist, int chunk_rows, int tile_rows,
+                                            int32_t* __restrict__ expert_count, int32_t* __restrict__ expert_offset,
+                                            int32_t* __restrict__ sorted_slot, int32_t* __restrict__ slot_pos,
+                                            int32_t* __restrict__ chunk_list, int32_t* __restrict__ tile_list,
+                                            int32_t* __restrict__ counters, int shared_rows, int topk) {
   int* block_total = smem_i;            // [E]
   int* base = block_total + E;          // [E]  expert_offset + slots in earlier blocks
   int* warp_sums = base + E;            // [33]
   uint16_t* warp_cnt = reinterpret_cast<uint16_t*>(warp_sums + 34);  // [32*E]
-  pdl_wait();
-  pdl_trigger();
+  int* all_tot = reinterpret_cast<int*>(warp_cnt + 32 * E);          // [E]  (self-counting only)
+  int* all_before = all_tot + E;                                     // [E]
+  const bool self_count = nb > 1 && block_hist == nullptr;
+  if (self_count) {
+    for (int x = threadIdx.x; x < E; x += kAlignThreads) {
+      all_tot[x] = 0;
+      all_before[x] = 0;
+    }
+    __syncthreads();
+    for (int b = 0; b < nb; ++b) {
+      const int sl = b * kAlignThreads + threadIdx.x;
+      if (sl < S) {
+        const int ee = ids[sl];
+        if (ee >= 0 && ee < E) {
+          atomicAdd(&all_tot[ee], 1);
+          if (b < (int)blockIdx.x) atomicAdd(&all_before[ee], 1);
+        }
+      }
+    }
+    __syncthreads();
+  }
 
   const int slot = blockIdx.x * kAlignThreads + threadIdx.x;
   int e = -1;
@@ -126,6 +146,9 @@ __global__ void __launch_bounds__(kAlignThreads)
     if (x < E) {
       if (nb == 1) {
         tot = block_total[x];
+      } else if (self_count) {
+        tot = all_tot[x];
+        before = all_before[x];
       } else {
         for (int b = 0; b < nb; ++b) {
           int c = block_hist[(size_t)b * E + x];
@@ -201,6 +224,65 @@ __global__ void __launch_bounds__(kAlignThreads)
     sorted_slot[S + m] = m * topk;
 }
 
+__global__ void __launch_bounds__(kAlignThreads)
+    align_scatter_kernel(const int32_t* __restrict__ ids, int S, int E, int nb,
+                         const int32_t* __restrict__ block_hist, int chunk_rows, int tile_rows,
+                         int32_t* __restrict__ expert_count, int32_t* __restrict__ expert_offset,
+                         int32_t* __restrict__ sorted_slot, int32_t* __restrict__ slot_pos,
+                         int32_t* __restrict__ chunk_list, int32_t* __restrict__ tile_list,
+                         int32_t* __restrict__ counters, int shared_rows, int topk) {
+  extern __shared__ int smem_i[];
+  pdl_wait();
+  pdl_trigger();
+  align_block(smem_i, ids, S, E, nb, block_hist, chunk_rows, tile_rows, expert_count, expert_offset, sorted_slot, slot_pos,
+              chunk_list, tile_list, counters, shared_rows, topk);
+}
+
+// ---- prologue of the fused decode chain: ONE launch in front of the two GEMMs --------------------------------
+// Blocks [0, nb): the align pass above (each block counts the other blocks' slots itself, nb <= kPrologueMaxAlignBlocks).
+// Blocks [nb, nb + ceil(M / 4)): four token rows per block, 256 threads each:
+//   * activation operand of stage 1: per-row int8 quantisation (mode 1, quant_row_int8) or the e4m3 hi / lo split
+//     (mode 2, split_row_e4m3) -- the device functions the stand-alone kernels run, so the bytes are identical;
+//   * state of the fused top-k reduce: tok_valid[m], red_cnt[m, :] = topk - valid (masked slots never arrive);
+//   * zeroes row_amax (int8: maxed by the stage-1 epilogue).
+__global__ void __launch_bounds__(kAlignThreads)
+    moe_prologue_kernel(const int32_t* __restrict__ ids, int S, int E, int nb, int chunk_rows, int tile_rows,
+                        int32_t* __restrict__ expert_count, int32_t* __restrict__ expert_offset,
+                        int32_t* __restrict__ sorted_slot, int32_t* __restrict__ slot_pos, int32_t* __restrict__ chunk_list,
+                        int32_t* __restrict__ tile_list, int32_t* __restrict__ counters, int shared_rows, int topk,
+                        const PrologueRows pr) {
+  extern __shared__ int smem_i[];
+  pdl_wait();
+  pdl_trigger();
+  if ((int)blockIdx.x < nb) {
+    align_block(smem_i, ids, S, E, nb, nullptr, chunk_rows, tile_rows, expert_count, expert_offset, sorted_slot, slot_pos,
+                chunk_list, tile_list, counters, shared_rows, topk);
+    return;
+  }
+  const int rb = blockIdx.x - nb, nrb = gridDim.x - nb;
+  const int grp = threadIdx.x >> 8, t = threadIdx.x & 255;
+  if (pr.row_amax != nullptr)
+    for (int i = rb * kAlignThreads + threadIdx.x; i < pr.amax_rows; i += nrb * kAlignThreads) pr.row_amax[i] = 0u;
+  const int m = rb * 4 + grp;
+  if (m >= pr.M) return;  // whole 256-thread group
+  if (pr.red_cnt != nullptr) {
+    int valid = 0;
+    for (int j = 0; j < topk; ++j) {
+      const int e = ids[(size_t)m * topk + j];
+      valid += (e >= 0 && e < E) ? 1 : 0;
+    }
+    if (t == 0) pr.tok_valid[m] = valid;
+    for (int b = t; b < pr.red_blocks; b += 256) pr.red_cnt[(size_t)m * pr.red_blocks + b] = topk - valid;
+  }
+  float* red_s = reinterpret_cast<float*>(smem_i) + grp * 8;
+  if (pr.mode == 1)
+    quant_row_int8<__nv_bfloat16>(pr.x + (size_t)m * pr.K, pr.K, (int8_t*)pr.q + (size_t)m * pr.K, pr.xs + m, t, red_s,
+                                  1 + grp);
+  else if (pr.mode == 2)
+    split_row_e4m3(pr.x + (size_t)m * pr.K, pr.K, (uint8_t*)pr.q + (size_t)m * pr.K, (uint8_t*)pr.q2 + (size_t)m * pr.K,
+                   pr.xs + m, t, red_s, 1 + grp);
+}
+
 int moe_align_impl(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows, int tile_rows,
                    const sglb_align_out* out, void* scratch, int shared_rows, cudaStream_t stream) {
   SGLB_CHECK(out != nullptr, "moe_align: null output struct");
@@ -227,6 +309,28 @@ int moe_align_impl(const int32_t* topk_ids, int64_t M, int topk, int E, int chun
                        out->expert_offset, out->sorted_slot, out->slot_pos, out->chunk_list,
                        out->tile_list, out->counters, shared_rows, topk));
   count_launch(nb > 1 ? 2 : 1);
+  return SGLB_OK;
+}
+
+// One launch: align + stage-1 operand preparation + fused-reduce state (see moe_prologue_kernel).
+int moe_prologue_impl(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows, int tile_rows,
+                      const sglb_align_out* out, int shared_rows, const PrologueRows& pr, cudaStream_t stream) {
+  SGLB_CHECK(E >= 1 && E <= 1024, "moe_prologue: E=%d must be in [1,1024]", E);
+  const int S = (int)(M * topk);
+  const int nb = S > 0 ? ceil_div(S, kAlignThreads) : 1;
+  SGLB_CHECK(nb <= kPrologueMaxAlignBlocks, "moe_prologue: M*topk=%d too large for the single-launch prologue", S);
+  const size_t smem = (size_t)(4 * E + 34) * sizeof(int) + (size_t)32 * E * sizeof(uint16_t);
+  SGLB_CHECK(smem <= 96 * 1024, "moe_prologue: E=%d needs too much shared memory", E);
+  static bool attr_set = false;
+  if (!attr_set) {
+    SGLB_CUDA(cudaFuncSetAttribute(moe_prologue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    attr_set = true;
+  }
+  const int nrb = (int)ceil_div64(M, 4);
+  SGLB_CUDA(launch_pdl(moe_prologue_kernel, dim3(nb + nrb), dim3(kAlignThreads), smem, stream, topk_ids, S, E, nb,
+                       chunk_rows, tile_rows, out->expert_count, out->expert_offset, out->sorted_slot, out->slot_pos,
+                       out->chunk_list, out->tile_list, out->counters, shared_rows, topk, pr));
+  count_launch();
   return SGLB_OK;
 }
 

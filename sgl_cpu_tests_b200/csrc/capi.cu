@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include "common.cuh"
+#include "rowops.cuh"
 #include "stream_gemm.cuh"
 #include "umma_gemm.cuh"
 
@@ -33,6 +34,8 @@ struct StageEvents {
 static bool g_profile = false;
 static bool g_mx4_native = true;  // mxfp4: block-scaled tensor-native kernel (umma_mx4.cu) when scale tiles are given
 static bool g_f8_native = true;  // fp8: tensor-native kernel (umma_f8.cu) vs dequantising kernel (umma_dq.cu)
+// decode chain fusion: single-launch prologue, int8 act quantisation and the top-k reduce inside the GEMM kernels
+static bool g_chain_fusion = true;
 static std::vector<StageEvents> g_events;
 static size_t g_events_used = 0;
 
@@ -76,6 +79,9 @@ struct MoeWorkspace {
   float* acts;                // [S]
   int8_t *xq2, *actq2;        // fp8 tensor-native path: lo pieces (xq / actq hold the hi pieces)
   int8_t *xsorted, *xsorted2; // CTA-pair path: the stage-1 rows in expert-sorted order (bf16 / s8 / e4m3 hi, lo)
+  // fused decode chain (M * topk <= kFuseMaxSlots): per-token valid slots, arrival counters, per-row max |act|
+  int32_t *tok_valid, *red_cnt;
+  uint32_t* row_amax;
   size_t bytes;
 };
 
@@ -86,6 +92,9 @@ constexpr double kUmmaMinRowsPerExpert = 4.0;
 constexpr double kPairMinRowsPerExpert = 128.0;
 constexpr int kTileRows = kUmmaTileRows;
 constexpr int kMinTileRows = 16;  // smallest tile_rows any path hands to moe_align (sizes tile_list)
+// Decode chain fusion applies up to this many routed slots (the single-launch prologue's align blocks)
+constexpr int64_t kFuseMaxSlots = (int64_t)kPrologueMaxAlignBlocks * 1024;
+static int red_blocks_max(int H) { return ceil_div(H, 32) + 8; }  // counters per token: stream path, 32 columns per warp
 
 static int64_t max_items(int64_t S, int E, int rows) {
   return (S < E ? S : E) + S / rows + 1;
@@ -137,6 +146,10 @@ static MoeWorkspace carve(void* base, int64_t M, int topk, int E, int H, int I, 
   const size_t eb = fmt == SGLB_FMT_BF16 ? 2 : 1;
   w.xsorted = (int8_t*)take((size_t)M * topk * H * eb);
   w.xsorted2 = fmt == SGLB_FMT_FP8_W8A16 ? (int8_t*)take((size_t)M * topk * H) : nullptr;
+  const bool fusable = M * topk <= kFuseMaxSlots;
+  w.tok_valid = (int32_t*)take(fusable ? sizeof(int32_t) * M : 0);
+  w.red_cnt = (int32_t*)take(fusable ? sizeof(int32_t) * M * red_blocks_max(H) : 0);
+  w.row_amax = (uint32_t*)take(fusable ? sizeof(uint32_t) * (S + kTileRows) : 0);
   w.bytes = off;
   return w;
 }
@@ -209,6 +222,10 @@ struct MlpExtra {
   const int32_t* out_map = nullptr;
   // the shared expert riding along as expert id E: M more rows behind the routed ones (align.cu)
   const void *sh_w13 = nullptr, *sh_w2 = nullptr, *sh_s13 = nullptr, *sh_s2 = nullptr;
+  // fused decode chain: the prologue prepared the stage-1 operand; the stage-2 kernel finishes tokens into final_out
+  bool fused = false;
+  void* final_out = nullptr;
+  float shared_rsf = 1.f;
   bool any() const { return w13_bias || w2_bias || act != SGLB_ACT_SILU || out_by_slot || sh_w13; }
 };
 
@@ -251,6 +268,9 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.Wsh_scale = sa.Wsh_scale;
   u.shared_row0 = sa.shared_row0;
   u.x_rows = (int)(sa.gather ? S / sa.topk : S);  // token rows when gathered, else the sorted rows themselves
+  u.red = sa.red;
+  u.row_amax = sa.row_amax;
+  u.Xraw = sa.Xraw;
   const int sh_tiles = sa.Wsh ? (int)ceil_div64(S / sa.topk, kTileRows) : 0;
   u.max_tiles += sh_tiles;
   if (mx4_tiles) return launch_umma_mx4(stage, u, stream);
@@ -264,6 +284,15 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
     if ((double)S / active <= 32.0) u.est_tiles = (int)(active + 0.5) + sh_tiles;
   }
   return launch_umma_gemm(fmt, stage, u, stream);
+}
+
+// Counters per token of the fused top-k reduce: one per output-column block a stage-2 CTA (tcgen05: 256 columns) or
+// warp (streaming kernel: 32 columns) completes.
+static int stage2_red_blocks(int path, int64_t M, int topk, int E, int H) {
+  if (path != SGLB_PATH_STREAM) return ceil_div(H, 2 * 128);
+  const StreamPlan p2 = make_plan(M, topk, E, H, 2);
+  const int wn = p2.cfg == 0 ? 8 : (p2.cfg == 1 ? 2 : 1);
+  return ceil_div(H, 32 * wn) * wn;
 }
 
 // Two grouped GEMMs over an existing alignment (path = SGLB_PATH_STREAM or SGLB_PATH_UMMA).
@@ -312,16 +341,23 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   const bool umma = path == SGLB_PATH_UMMA || pair;
   const bool mx4 = umma && !pair && fmt == SGLB_FMT_MXFP4 && s13_tiles && s2_tiles && mx4_cap > 0;
   const bool f8 = mx4 || (umma && fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(H, I, bn, bk));
+  // fused decode chain: the single-launch prologue already prepared the stage-1 operand (run_prologue)
+  const bool fused_int8 = ex.fused && fmt == SGLB_FMT_INT8_W8A8 && path == SGLB_PATH_UMMA;
   if (fmt == SGLB_FMT_INT8_W8A8) {
-    StageTimer t(ST_QUANT_X, stream);
-    rc = sglb_quant_rows_int8(hidden, M, H, ws.xq, ws.xs, stream);
-    if (rc) return rc;
+    if (!ex.fused) {
+      StageTimer t(ST_QUANT_X, stream);
+      rc = sglb_quant_rows_int8(hidden, M, H, ws.xq, ws.xs, stream);
+      if (rc) return rc;
+    }
     a.X = ws.xq;
     a.Xscale = ws.xs;
+    if (fused_int8) a.row_amax = ws.row_amax;  // the stage-1 epilogue leaves max |act| per row for stage 2
   } else if (f8) {
-    StageTimer t(ST_QUANT_X, stream);
-    rc = launch_split_rows_e4m3(hidden, M, H, ws.xq, ws.xq2, ws.xs, stream);
-    if (rc) return rc;
+    if (!ex.fused) {
+      StageTimer t(ST_QUANT_X, stream);
+      rc = launch_split_rows_e4m3(hidden, M, H, ws.xq, ws.xq2, ws.xs, stream);
+      if (rc) return rc;
+    }
     a.X = ws.xq;
     a.X2 = ws.xq2;
     a.Xscale = ws.xs;
@@ -362,12 +398,29 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   a.Wsh_scale = ex.sh_s2;
   a.out_by_slot = ex.out_by_slot;
   a.out_map = ex.out_map;
-  if (fmt == SGLB_FMT_INT8_W8A8) {
+  if (ex.fused) {
+    a.red.cnt = ws.red_cnt;
+    a.red.slot_pos = ws.slot_pos;
+    a.red.tok_valid = ws.tok_valid;
+    a.red.out = ex.final_out;
+    a.red.M = (int)M;
+    a.red.blocks = stage2_red_blocks(path, M, topk, E, H);
+    a.red.need = topk + (ex.sh_w13 ? 1 : 0);
+    a.red.shared_row0 = ex.sh_w13 ? (int)S : -1;
+    a.red.rsf = ex.shared_rsf;
+  }
+  if (fused_int8) {
+    // no quantisation launch: the gather warps of the stage-2 kernel quantise the f32 act rows on the way in
+    a.X = nullptr;
+    a.Xscale = nullptr;
+    a.Xraw = (const float*)ws.act;
+  } else if (fmt == SGLB_FMT_INT8_W8A8) {
     StageTimer t(ST_QUANT_ACT, stream);
     rc = launch_quant_rows_f32((const float*)ws.act, act_rows, I, ws.actq, ws.acts, stream);
     if (rc) return rc;
     a.X = ws.actq;
     a.Xscale = ws.acts;
+    a.row_amax = nullptr;
   } else if (f8) {
     StageTimer t(ST_QUANT_ACT, stream);
     rc = launch_split_rows_e4m3(ws.act, act_rows, I, ws.actq, ws.actq2, ws.acts, stream);
@@ -398,6 +451,39 @@ static int run_align(const int32_t* ids, int64_t M, int topk, int E, int chunk_r
   ao.counters = ws.counters;
   StageTimer t(ST_ALIGN, stream);
   return moe_align_impl(ids, M, topk, E, chunk_rows, tile_rows, &ao, ws.align_scratch, shared_rows, stream);
+}
+
+int moe_prologue_impl(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows, int tile_rows,
+                      const sglb_align_out* out, int shared_rows, const PrologueRows& pr, cudaStream_t stream);
+
+// Fused decode chain: align + stage-1 operand preparation (mode 1 int8 rows, 2 e4m3 hi / lo split) + the state of the
+// fused top-k reduce, in ONE launch.
+static int run_prologue(const int32_t* ids, const void* hidden, int64_t M, int topk, int E, int H, int mode, int red_blocks,
+                        int chunk_rows, int tile_rows, int shared_rows, const MoeWorkspace& ws, cudaStream_t stream) {
+  sglb_align_out ao;
+  ao.expert_count = ws.expert_count;
+  ao.expert_offset = ws.expert_offset;
+  ao.sorted_slot = ws.sorted_slot;
+  ao.slot_pos = ws.slot_pos;
+  ao.chunk_list = ws.chunk_list;
+  ao.tile_list = ws.tile_list;
+  ao.counters = ws.counters;
+  PrologueRows pr;
+  memset(&pr, 0, sizeof(pr));
+  pr.mode = mode;
+  pr.x = (const __nv_bfloat16*)hidden;
+  pr.M = (int)M;
+  pr.K = H;
+  pr.q = ws.xq;
+  pr.q2 = ws.xq2;
+  pr.xs = ws.xs;
+  pr.tok_valid = ws.tok_valid;
+  pr.red_cnt = ws.red_cnt;
+  pr.red_blocks = red_blocks;
+  pr.row_amax = ws.row_amax;
+  pr.amax_rows = (int)(M * topk + M);
+  StageTimer t(ST_ALIGN, stream);
+  return moe_prologue_impl(ids, M, topk, E, chunk_rows, tile_rows, &ao, shared_rows, pr, stream);
 }
 
 }  // namespace sglb
@@ -432,6 +518,7 @@ extern "C" int sglb_profile_read(float* ms_out, int* calls_out, int n) {
 }
 
 extern "C" void sglb_set_fp8_native(int on) { g_f8_native = on != 0; }
+extern "C" void sglb_set_chain_fusion(int on) { g_chain_fusion = on != 0; }
 extern "C" void sglb_set_mx4_native(int on) { g_mx4_native = on != 0; }
 extern "C" size_t sglb_mx4_scale_tiles_bytes(int64_t E, int rows, int split, int K) {
   if (E <= 0 || rows <= 0 || K <= 0) return 0;
@@ -548,6 +635,14 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
   if (path == SGLB_PATH_AUTO) {
     path = auto_path(p, mx4);
   }
+  // Decode chain fusion (bit-identical to the separate launches): one prologue launch, int8 act quantisation inside the
+  // stage-2 producer, top-k reduce inside the stage-2 epilogue.  Not for the CTA-pair kernels (prefill) and not when
+  // the caller reduces the slot rows itself (expert parallel).
+  const bool fuse = g_chain_fusion && !p->slot_out && p->M * p->topk <= kFuseMaxSlots && p->H % 8 == 0 &&
+                    (path == SGLB_PATH_UMMA || path == SGLB_PATH_STREAM);
+  ex.fused = fuse;
+  ex.final_out = p->out;
+  ex.shared_rsf = p->shared_rsf;
   if (path == SGLB_PATH_UMMA || path == SGLB_PATH_UMMA2) {
     SGLB_CHECK(umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I),
                "fused_experts: tcgen05 path does not support fmt=%d H=%d I=%d", p->fmt, p->H, p->I);
@@ -557,8 +652,15 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     SGLB_CHECK(path == SGLB_PATH_UMMA || !ex.any(),
                "fused_experts: the CTA-pair tcgen05 path has no expert bias / clamped swiglu / slot-addressed output");
     const bool use_mx4 = mx4 && path == SGLB_PATH_UMMA;
-    rc = run_align(p->topk_ids, p->M, p->topk, p->E, 0, ws, stream,
-                   use_mx4 ? mx4_cap : (path == SGLB_PATH_UMMA2 ? umma2_tile_rows() : kTileRows), ride ? (int)p->M : 0);
+    const int tile_rows = use_mx4 ? mx4_cap : (path == SGLB_PATH_UMMA2 ? umma2_tile_rows() : kTileRows);
+    if (fuse) {
+      const bool f8 = use_mx4 || (p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k));
+      const int mode = p->fmt == SGLB_FMT_INT8_W8A8 ? 1 : (f8 ? 2 : 0);
+      rc = run_prologue(p->topk_ids, p->hidden, p->M, p->topk, p->E, p->H, mode,
+                        stage2_red_blocks(path, p->M, p->topk, p->E, p->H), 0, tile_rows, ride ? (int)p->M : 0, ws, stream);
+    } else {
+      rc = run_align(p->topk_ids, p->M, p->topk, p->E, 0, ws, stream, tile_rows, ride ? (int)p->M : 0);
+    }
     if (rc) return rc;
     rc = run_mlp(path, p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2,
                  p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, stage2_out, stream,
@@ -566,7 +668,11 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     if (rc) return rc;
   } else {
     StreamPlan plan = make_plan(p->M, p->topk, p->E, p->I, 1);
-    rc = run_align(p->topk_ids, p->M, p->topk, p->E, 8 * plan.ng, ws, stream);
+    if (fuse)
+      rc = run_prologue(p->topk_ids, p->hidden, p->M, p->topk, p->E, p->H, p->fmt == SGLB_FMT_INT8_W8A8 ? 1 : 0,
+                        stage2_red_blocks(path, p->M, p->topk, p->E, p->H), 8 * plan.ng, kTileRows, 0, ws, stream);
+    else
+      rc = run_align(p->topk_ids, p->M, p->topk, p->E, 8 * plan.ng, ws, stream);
     if (rc) return rc;
     rc = run_mlp(SGLB_PATH_STREAM, p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2,
                  p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, stage2_out, stream, nullptr,
@@ -574,6 +680,7 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     if (rc) return rc;
   }
   if (p->slot_out) return SGLB_OK;  // the caller reduces the slot rows (expert-parallel combine)
+  if (fuse) return SGLB_OK;         // the stage-2 kernel finished the tokens itself
   StageTimer t(ST_REDUCE, stream);
   // riding shared expert: its rows sit behind the routed ones; the reduce applies shared_expert_cpu's epilogue
   const void* shared_y = ride ? (const void*)(ws.ic2 + (size_t)p->M * p->topk * p->H) : nullptr;

@@ -136,6 +136,62 @@ __device__ __forceinline__ int64_t out_row_of(int p, const int32_t* sorted_slot,
   return out_map != nullptr ? out_map[s] : s;
 }
 
+// ---- fused top-k reduce (decode chain fusion, capi.cu) ---------------------------------------------------------
+// The stage-2 GEMM kernels finish a token themselves: every (routed row, output-column block) a CTA / warp completes is
+// counted on red_cnt[token, block]; whoever brings the count to `need` (= topk, + 1 with a riding shared expert; the
+// prologue pre-counts masked slots) adds the token's slot rows of that block IN SLOT ORDER j = 0..topk-1 in f32 and
+// rounds once -- topk_reduce_kernel's arithmetic (misc.cu), so the result is bit-identical to the separate launch.
+// Rows written by other SMs are read through L2 (ld.global.cg) after a device-scope fence.
+struct FusedReduce {
+  int32_t* cnt;              // [M, blocks]; nullptr = no fusion (the caller launches topk_reduce)
+  const int32_t* slot_pos;   // [M * topk]: sorted position of each slot or -1
+  const int32_t* tok_valid;  // [M]: valid slots per token (0 and no shared rider -> the row is zero-filled)
+  void* out;                 // [M, N] bf16
+  int M;
+  int blocks;                // counters per token
+  int need;                  // arrivals that complete a (token, block)
+  int shared_row0;           // riding shared expert: its stage-2 rows sit at ic2[shared_row0 + token]; -1 = none
+  float rsf;
+};
+// 8 consecutive columns [col0, col0 + 8) of token t.  ic2: the stage-2 output rows (bf16, row stride N).
+__device__ __forceinline__ void fused_reduce_cols8(const FusedReduce& r, const __nv_bfloat16* ic2, int topk, int N, int t,
+                                                   int col0) {
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int j = 0; j < topk; ++j) {
+    const int p = r.slot_pos[(size_t)t * topk + j];
+    if (p < 0) continue;
+    const int4 v = __ldcg(reinterpret_cast<const int4*>(ic2 + (size_t)p * N + col0));
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      acc[2 * i] += bf16_bits_to_float(w[i] & 0xffffu);
+      acc[2 * i + 1] += bf16_bits_to_float(w[i] >> 16);
+    }
+  }
+  if (r.shared_row0 >= 0) {
+    const int4 v = __ldcg(reinterpret_cast<const int4*>(ic2 + (size_t)(r.shared_row0 + t) * N + col0));
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      acc[2 * i] = fmaf(bf16_round(acc[2 * i]), r.rsf, bf16_bits_to_float(w[i] & 0xffffu));
+      acc[2 * i + 1] = fmaf(bf16_round(acc[2 * i + 1]), r.rsf, bf16_bits_to_float(w[i] >> 16));
+    }
+  }
+  uint32_t o[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) o[i] = pack_bf16x2(acc[2 * i], acc[2 * i + 1]);
+  *reinterpret_cast<int4*>((__nv_bfloat16*)r.out + (size_t)t * N + col0) = make_int4(o[0], o[1], o[2], o[3]);
+}
+// rows of tokens without any valid slot (and no shared rider) are zero: nobody ever arrives for them
+__device__ __forceinline__ void fused_reduce_zero_rows(const FusedReduce& r, int N, int worker, int workers, int lane) {
+  if (r.cnt == nullptr || r.shared_row0 >= 0) return;
+  for (int t = worker; t < r.M; t += workers) {
+    if (r.tok_valid[t] != 0) continue;
+    for (int c = lane * 8; c < N; c += 32 * 8)
+      *reinterpret_cast<int4*>((__nv_bfloat16*)r.out + (size_t)t * N + c) = make_int4(0, 0, 0, 0);
+  }
+}
+
 // ---- legacy warp MMA (decode / weight-streaming path) ----------------------------------------
 // D(16x8,f32) += A(16x16,bf16,row) * B(16x8,bf16,col)
 __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2,

@@ -1,32 +1,13 @@
 // Small HBM-bound kernels around the GEMMs: per-row int8 quantisation, the topk reduce (K5), the
 // shared-expert axpy epilogue and the prepack re-tiling kernels (K7).
 #include "common.cuh"
+#include "rowops.cuh"
 
 namespace sglb {
 
 
 
-// ---- per-row dynamic int8 quantisation (test_moe_int8.py:23-31) ---------------------------------
-// One CTA per row.  absmax is taken over the bf16 values, scale = absmax.clamp_min(1e-7)/127,
-// q = rint(x * (127/absmax)) -- the same two f32 expressions the reference oracle evaluates.
-template <typename TIN>
-__device__ __forceinline__ void load8(const TIN* p, float (&v)[8]);
-template <>
-__device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[8]) {
-  int4 r = *reinterpret_cast<const int4*>(p);
-  const uint32_t* w = reinterpret_cast<const uint32_t*>(&r);
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    v[2 * j] = bf16_bits_to_float(w[j] & 0xffffu);
-    v[2 * j + 1] = bf16_bits_to_float(w[j] >> 16);
-  }
-}
-template <>
-__device__ __forceinline__ void load8<float>(const float* p, float (&v)[8]) {
-  float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
-  v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w, v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
-}
-
+// ---- per-row dynamic int8 quantisation: one CTA per row (the row function lives in rowops.cuh) ----------
 template <typename TIN>
 __global__ void __launch_bounds__(256) quant_rows_kernel(const TIN* __restrict__ x, int K,
                                                          int8_t* __restrict__ q,
@@ -34,50 +15,8 @@ __global__ void __launch_bounds__(256) quant_rows_kernel(const TIN* __restrict__
   pdl_wait();
   pdl_trigger();
   const int64_t row = blockIdx.x;
-  const TIN* xr = x + row * K;
-  int8_t* qr = q + row * K;
   __shared__ float warp_max_s[8];
-  float amax = 0.f;
-  const bool vec = (K % 8 == 0);
-  if (vec) {
-    for (int i = threadIdx.x * 8; i < K; i += 256 * 8) {
-      float v[8];
-      load8<TIN>(xr + i, v);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(v[j]));
-    }
-  } else {
-    for (int i = threadIdx.x; i < K; i += 256) amax = fmaxf(amax, fabsf(load_as_float<TIN>(xr + i)));
-  }
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
-  if ((threadIdx.x & 31) == 0) warp_max_s[threadIdx.x >> 5] = amax;
-  __syncthreads();
-  amax = warp_max_s[0];
-#pragma unroll
-  for (int w = 1; w < 8; ++w) amax = fmaxf(amax, warp_max_s[w]);
-  amax = fmaxf(amax, 1e-7f);
-  // torch evaluates `127 / absmax` (Tensor.__rtruediv__) as reciprocal(absmax) * 127: two roundings
-  const float inv = __fmul_rn(__frcp_rn(amax), 127.0f);
-  if (threadIdx.x == 0) scale[row] = amax / 127.0f;
-  if (vec) {
-    for (int i = threadIdx.x * 8; i < K; i += 256 * 8) {
-      float v[8];
-      load8<TIN>(xr + i, v);
-      uint32_t o[2];
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        int q0 = __float2int_rn(v[4 * j] * inv), q1 = __float2int_rn(v[4 * j + 1] * inv);
-        int q2 = __float2int_rn(v[4 * j + 2] * inv), q3 = __float2int_rn(v[4 * j + 3] * inv);
-        o[j] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) |
-               ((uint32_t)(q3 & 0xff) << 24);
-      }
-      *reinterpret_cast<uint2*>(qr + i) = make_uint2(o[0], o[1]);
-    }
-  } else {
-    for (int i = threadIdx.x; i < K; i += 256)
-      qr[i] = (int8_t)__float2int_rn(load_as_float<TIN>(xr + i) * inv);
-  }
+  quant_row_int8<TIN>(x + row * K, K, q + row * K, scale + row, threadIdx.x, warp_max_s, 0);
 }
 
 // ---- K5: out[m,:] = sum over the token's valid slots, in slot order j = 0..topk-1 ----------------

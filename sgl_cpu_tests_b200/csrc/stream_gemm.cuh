@@ -47,6 +47,9 @@ struct StreamArgs {
   const void* Wsh;         // tcgen05 paths only: the shared expert riding along (see UmmaArgs)
   const void* Wsh_scale;
   int shared_row0;
+  FusedReduce red;         // stage 2: fused top-k reduce, one counter per (token, 32-column warp block); cnt == nullptr = off
+  uint32_t* row_amax;      // tcgen05 int8 path only (see UmmaArgs)
+  const float* Xraw;
 };
 
 template <int FMT>
@@ -98,6 +101,9 @@ __global__ void __launch_bounds__(WN* WK * 32)
 
   pdl_wait();
   pdl_trigger();
+  if constexpr (STAGE == 2)
+    fused_reduce_zero_rows(a.red, a.N, (blockIdx.y * gridDim.x + blockIdx.x) * (WN * WK) + (threadIdx.x >> 5),
+                           gridDim.x * gridDim.y * (WN * WK), threadIdx.x & 31);
   const int chunk = blockIdx.y;
   if (chunk >= a.counters[1]) return;
   const int e = a.chunk_list[3 * chunk + 0];
@@ -368,6 +374,29 @@ __global__ void __launch_bounds__(WN* WK * 32)
         }
       }
     }
+  // ---- fused top-k reduce (decode chain fusion): this warp finished 32 columns of the chunk's rows ----
+  if constexpr (STAGE == 2) {
+    if (a.red.cnt != nullptr) {  // kernel-uniform
+      __threadfence();
+      __syncwarp();
+      bool done = false;
+      int tok = 0;
+      if (lane < rows) {
+        tok = a.sorted_slot[row_start + lane] / a.topk;
+        __threadfence();
+        done = atomicAdd(a.red.cnt + (size_t)tok * a.red.blocks + (blockIdx.x * WN + wn), 1) + 1 == a.red.need;
+        if (done) __threadfence();
+      }
+      unsigned mask = __ballot_sync(0xffffffffu, done);
+      const int col0 = nbase[0] + lane * 8;
+      while (mask) {
+        const int srcl = __ffs(mask) - 1;
+        mask &= mask - 1;
+        const int tkn = __shfl_sync(0xffffffffu, tok, srcl);
+        if (lane < 4 && col0 < a.N) fused_reduce_cols8(a.red, (const __nv_bfloat16*)a.out, a.topk, a.N, tkn, col0);
+      }
+    }
+  }
 }
 
 // Host-side launcher shared by the per-format translation units.

@@ -241,6 +241,93 @@ __device__ __forceinline__ void gather_role(const UmmaArgs& a, int total, int n_
     }
 }
 
+// ---- int8 stage 2 in the fused decode chain: the gather warps quantise f32 act rows on the way in ----------
+// Same thread -> (row, 16-byte chunk) map as gather_role.  A chunk is 16 s8 of K = 64 bytes of f32 act; the row's
+// scale comes from a.row_amax (maxed by the stage-1 epilogue): inv = rcp(max(amax, 1e-7)) * 127 and
+// q = rint(v * inv), the two f32 expressions of quant_rows_kernel (misc.cu), so the operand bytes are the ones the
+// separate quantisation launch would have written.
+__device__ __forceinline__ void gather_quant_role(const UmmaArgs& a, int total, int n_blocks, int num_kb, int g,
+                                                  uint32_t x_tile0, uint32_t x_stride, uint32_t xfull0, uint32_t xempty0,
+                                                  int nstages) {
+  const int c = g & 7, rbase = g >> 3;
+  const uint32_t dst0 = rbase * kRowBytes + ((c ^ (rbase & 7)) << 4);
+  uint32_t it = 0;
+  for (int w = blockIdx.x; w < total; w += gridDim.x) {
+    const WorkItem wi = get_item(a, w, n_blocks);
+    const int n_eff = (wi.rows + 15) & ~15;
+    const float* src[8];
+    float inv[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int p = wi.row_start + min(rbase + 16 * j, wi.rows - 1);
+      src[j] = a.Xraw + (size_t)p * a.K + c * 16;
+      inv[j] = 0.f;
+      if (rbase + 16 * j < n_eff) inv[j] = __fmul_rn(__frcp_rn(fmaxf(__uint_as_float(a.row_amax[p]), 1e-7f)), 127.0f);
+    }
+    for (int kb = 0; kb < num_kb; ++kb, ++it) {
+      const int s = it % nstages;
+      mbar_wait(xempty0 + 8 * s, ((it / nstages) & 1) ^ 1);
+      const uint32_t dst = x_tile0 + s * x_stride + dst0;
+#pragma unroll
+      for (int j0 = 0; j0 < 8; j0 += 2) {  // two rows (eight 16-byte loads) in flight
+        if (rbase + 16 * j0 < n_eff) {     // monotone in j0
+          float4 v[2][4];
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj)
+            if (rbase + 16 * (j0 + jj) < n_eff) {
+              const float4* p4 = reinterpret_cast<const float4*>(src[j0 + jj] + kb * kRowBytes);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) v[jj][i] = __ldcg(p4 + i);
+            }
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj)
+            if (rbase + 16 * (j0 + jj) < n_eff) {
+              const float sc = inv[j0 + jj];
+              uint32_t o[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const int q0 = __float2int_rn(v[jj][i].x * sc), q1 = __float2int_rn(v[jj][i].y * sc);
+                const int q2 = __float2int_rn(v[jj][i].z * sc), q3 = __float2int_rn(v[jj][i].w * sc);
+                o[i] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) |
+                       ((uint32_t)(q3 & 0xff) << 24);
+              }
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (j0 + jj) * 16 * kRowBytes), "r"(o[0]),
+                           "r"(o[1]), "r"(o[2]), "r"(o[3])
+                           : "memory");
+            }
+        }
+      }
+      fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
+      mbar_arrive(xfull0 + 8 * s);
+    }
+  }
+}
+
+// ---- fused top-k reduce of one finished stage-2 work item (all kEpiWarps epilogue warps call it) -----------
+// Warp ew owns rows [16 ew, 16 ew + 16) of the tile: lane l < 16 counts the arrival of row 16 ew + l on
+// red.cnt[token, nb]; completed tokens are reduced by the whole warp, 8 columns per lane (256 per block).
+__device__ __forceinline__ void fused_reduce_item(const UmmaArgs& a, const WorkItem& wi, int ew, int lane) {
+  __threadfence();  // this thread's ic2 stores, device scope
+  asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");  // every epilogue warp has stored its part of the item
+  const int r = ew * 16 + lane;
+  bool done = false;
+  int tok = 0;
+  if (lane < 16 && r < wi.rows) {
+    tok = a.sorted_slot[wi.row_start + r] / a.topk;
+    __threadfence();  // cumulative: the other warps' stores observed through the barrier
+    done = atomicAdd(a.red.cnt + (size_t)tok * a.red.blocks + wi.nb, 1) + 1 == a.red.need;
+    if (done) __threadfence();
+  }
+  unsigned mask = __ballot_sync(0xffffffffu, done);
+  const int col0 = wi.nb * 2 * kWSub + lane * 8;
+  while (mask) {
+    const int srcl = __ffs(mask) - 1;
+    mask &= mask - 1;
+    const int t = __shfl_sync(0xffffffffu, tok, srcl);
+    if (col0 < a.N) fused_reduce_cols8(a.red, (const __nv_bfloat16*)a.out, a.topk, a.N, t, col0);
+  }
+}
+
 // ---- epilogue warps -------------------------------------------------------------------------------------
 // kEpiWarps warps; `ew` = index among them, `warp` = warp index in the CTA (its TMEM lane quadrant is
 // warp & 3).  INT8: s32 accumulators with activation / weight scales; otherwise f32 accumulators.
@@ -268,6 +355,7 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
     constexpr int NRD = 16 / TPI;                      // read instructions per chunk
     uint8_t* ebuf = smem_raw + (epi_base + ew * kEpiBufBytes - smem_u32(smem_raw));
     const int rd_tok = lane / SEGS, rd_seg = lane % SEGS;
+    if constexpr (STAGE == 2) fused_reduce_zero_rows(a.red, a.N, blockIdx.x * kEpiWarps + ew, gridDim.x * kEpiWarps, lane);
     uint32_t li = 0;
     for (int w = blockIdx.x; w < total; w += gridDim.x, ++li) {
       const WorkItem wi = get_item(a, w, n_blocks);
@@ -286,7 +374,11 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
           if constexpr (STAGE == 1) {
             if (kInt8 || kTokScale) xs_r[i] = a.Xscale[a.sorted_slot[p] / a.topk];
           } else {
-            if (kInt8 || kTokScale) xs_r[i] = a.Xscale[p];
+            if constexpr (kInt8) {  // fused chain: the row's scale is quant_rows_kernel's amax / 127
+              xs_r[i] = a.Xraw != nullptr ? fmaxf(__uint_as_float(a.row_amax[p]), 1e-7f) / 127.0f : a.Xscale[p];
+            } else if (kTokScale) {
+              xs_r[i] = a.Xscale[p];
+            }
             if (a.row_scale != nullptr && wi.e < a.E) rs_r[i] = a.row_scale[a.sorted_slot[p]];
           }
         }
@@ -384,10 +476,21 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
           for (int i = 0; i < NRD; ++i) {
             const int tok = rd_tok + TPI * i;
             const int4 piece = *reinterpret_cast<const int4*>(ebuf + tok * ROWB + rd_seg * 16);
-            if (c0 + tok < wi.rows && nn < a.N) {
+            const bool live = c0 + tok < wi.rows && nn < a.N;
+            if (live) {
               const int64_t orow = STAGE == 2 ? out_row_of(wi.row_start + c0 + tok, a.sorted_slot, a.out_by_slot, a.out_map)
                                               : (int64_t)(wi.row_start + c0 + tok);
               *reinterpret_cast<int4*>((char*)a.out + ((size_t)orow * a.N + nn) * OB) = piece;
+            }
+            if constexpr (kInt8 && STAGE == 1) {
+              // fused chain: max |act| of the row, for the quantisation the stage-2 gather warps perform
+              if (a.row_amax != nullptr) {  // warp-uniform
+                const float4 f = *reinterpret_cast<const float4*>(&piece);
+                float m = live ? fmaxf(fmaxf(fabsf(f.x), fabsf(f.y)), fmaxf(fabsf(f.z), fabsf(f.w))) : 0.f;
+#pragma unroll
+                for (int off = 1; off < SEGS; off <<= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+                if (rd_seg == 0 && c0 + tok < wi.rows) atomicMax(a.row_amax + wi.row_start + c0 + tok, __float_as_uint(m));
+              }
             }
           }
           __syncwarp();
@@ -395,6 +498,9 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
       }
       tc_fence_before();
       mbar_arrive(tempty_bar(buf));
+      if constexpr (STAGE == 2) {
+        if (a.red.cnt != nullptr) fused_reduce_item(a, wi, ew, lane);  // kernel-uniform
+      }
     }
 }
 

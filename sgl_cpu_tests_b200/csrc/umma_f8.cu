@@ -30,6 +30,7 @@
 
 #include <type_traits>
 
+#include "rowops.cuh"
 #include "umma_common.cuh"
 
 namespace sglb {
@@ -221,6 +222,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     uint8_t* ebuf = smem_raw + (epi_base + ew * kEpiBufBytes - smem_u32(smem_raw));
     const int rd_tok = lane / SEGS, rd_seg = lane % SEGS;
     const int nblk_rows = ceil_div(a.rows_per_expert, a.block_n);
+    if constexpr (STAGE == 2) fused_reduce_zero_rows(a.red, a.N, blockIdx.x * kEpiWarps + ew, gridDim.x * kEpiWarps, lane);
     uint32_t gi = 0;
     for (int w = blockIdx.x; w < total; w += gridDim.x) {
       const WorkItem wi = get_item(a, w, n_blocks);
@@ -350,6 +352,9 @@ __global__ void __launch_bounds__(kThreads, 1)
           __syncwarp();
         }
       }
+      if constexpr (STAGE == 2) {
+        if (a.red.cnt != nullptr) fused_reduce_item(a, wi, ew, lane);  // fused decode chain (kernel-uniform)
+      }
     }
   }
 
@@ -362,57 +367,15 @@ __global__ void __launch_bounds__(kThreads, 1)
   }
 }
 
-// ---- bf16 rows -> (hi, lo) e4m3 pieces + per-row power-of-two factor --------------------------------
-// x' = x * 2^(7 - e), e = floor(log2(max|x|)) so max|x'| is in [128, 256) (e4m3 max 448);
-// hi = RN_e4m3(x'), lo = RN_e4m3(x' - hi), rexp = 2^(e - 7):  x ~= (hi + lo) * rexp.
+// ---- bf16 rows -> (hi, lo) e4m3 pieces + per-row power-of-two factor: one CTA per row (rowops.cuh) ----
 __global__ void __launch_bounds__(256) split_rows_e4m3_kernel(const __nv_bfloat16* __restrict__ x, int K,
                                                               uint8_t* __restrict__ hi, uint8_t* __restrict__ lo,
                                                               float* __restrict__ rexp) {
   pdl_wait();
   pdl_trigger();
   const int64_t row = blockIdx.x;
-  const __nv_bfloat16* xr = x + row * K;
   __shared__ float warp_max_s[8];
-  float amax = 0.f;
-  for (int i = threadIdx.x * 8; i < K; i += 256 * 8) {
-    const int4 r = *reinterpret_cast<const int4*>(xr + i);
-    const uint32_t* wv = reinterpret_cast<const uint32_t*>(&r);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      amax = fmaxf(amax, fabsf(bf16_bits_to_float(wv[j] & 0xffffu)));
-      amax = fmaxf(amax, fabsf(bf16_bits_to_float(wv[j] >> 16)));
-    }
-  }
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
-  if ((threadIdx.x & 31) == 0) warp_max_s[threadIdx.x >> 5] = amax;
-  __syncthreads();
-  amax = warp_max_s[0];
-#pragma unroll
-  for (int w = 1; w < 8; ++w) amax = fmaxf(amax, warp_max_s[w]);
-  int e = (int)((__float_as_uint(amax) >> 23) & 0xff) - 127;  // floor(log2) of a normal float
-  if (!(amax > 0.f) || e < -100) e = -100;                   // all-zero / denormal rows: any factor works
-  if (e > 120) e = 120;
-  const float up = __uint_as_float((uint32_t)(127 + 7 - e) << 23);
-  if (threadIdx.x == 0) rexp[row] = __uint_as_float((uint32_t)(127 + e - 7) << 23);
-  for (int i = threadIdx.x * 8; i < K; i += 256 * 8) {
-    const int4 r = *reinterpret_cast<const int4*>(xr + i);
-    const uint32_t* wv = reinterpret_cast<const uint32_t*>(&r);
-    uint32_t oh[2] = {0, 0}, ol[2] = {0, 0};
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float2 v = make_float2(bf16_bits_to_float(wv[j] & 0xffffu) * up, bf16_bits_to_float(wv[j] >> 16) * up);
-      const __nv_fp8x2_storage_t h = __nv_cvt_float2_to_fp8x2(v, __NV_SATFINITE, __NV_E4M3);
-      const __half2_raw hr = __nv_cvt_fp8x2_to_halfraw2(h, __NV_E4M3);
-      const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&hr));
-      const __nv_fp8x2_storage_t l =
-          __nv_cvt_float2_to_fp8x2(make_float2(v.x - hf.x, v.y - hf.y), __NV_SATFINITE, __NV_E4M3);
-      oh[j >> 1] |= (uint32_t)h << (16 * (j & 1));
-      ol[j >> 1] |= (uint32_t)l << (16 * (j & 1));
-    }
-    *reinterpret_cast<uint2*>(hi + row * K + i) = make_uint2(oh[0], oh[1]);
-    *reinterpret_cast<uint2*>(lo + row * K + i) = make_uint2(ol[0], ol[1]);
-  }
+  split_row_e4m3(x + row * K, K, hi + row * K, lo + row * K, rexp + row, threadIdx.x, warp_max_s, 0);
 }
 
 template <int STAGE>

@@ -162,8 +162,12 @@ __global__ void __launch_bounds__(kThreads, 1)
       }
     }
   } else if (warp < 6) {
-    gather_role<false>(a, total, n_blocks, num_kb, k_bytes, threadIdx.x - 64, x_tile(0), kStageBytes, full_bar(0),
-                empty_bar(0), kStages);
+    if (FMT == SGLB_FMT_INT8_W8A8 && STAGE == 2 && a.Xraw != nullptr)  // fused decode chain: quantise on the way in
+      gather_quant_role(a, total, n_blocks, num_kb, threadIdx.x - 64, x_tile(0), kStageBytes, full_bar(0), empty_bar(0),
+                        kStages);
+    else
+      gather_role<false>(a, total, n_blocks, num_kb, k_bytes, threadIdx.x - 64, x_tile(0), kStageBytes, full_bar(0),
+                         empty_bar(0), kStages);
   } else {
     epilogue_role<FMT == SGLB_FMT_INT8_W8A8, STAGE, false>(a, total, n_blocks, smem_raw, epi_base, tfull_bar(0),
                                                     tempty_bar(0), tmem_base, warp, warp - kFirstEpiWarp, lane);

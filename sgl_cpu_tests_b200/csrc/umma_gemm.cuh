@@ -41,6 +41,12 @@ struct UmmaArgs {
   const void* Wsh_scale;
   int shared_row0;         // = M * topk when Wsh is set, else 0
   int x_rows;              // rows of X (CTA-pair kernels: bound of the TMA gather map)
+  // ---- decode chain fusion (capi.cu: fewer launches per call, bit-identical results) ----
+  FusedReduce red;         // stage 2: the epilogue finishes tokens itself (common.cuh); red.cnt == nullptr = off
+  uint32_t* row_amax;      // int8: f32 bits of max |act| per act row.  Stage 1: the epilogue atomically maxes into it
+                           // (zeroed by the prologue); stage 2 with Xraw set: the quantisation scale of each row
+  const float* Xraw;       // stage 2, int8 (umma_gemm.cu only): f32 act rows [*, K]; the gather warps quantise them into
+                           // the operand tile with quant_rows_kernel's arithmetic (X / Xscale are unused)
 };
 
 constexpr int kUmmaTileRows = 128;  // routed rows per tile (tile_rows handed to moe_align)

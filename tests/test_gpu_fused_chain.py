@@ -1,0 +1,167 @@
+"""Decode chain fusion (capi.cu, sglb_set_chain_fusion): the single-launch prologue (align + stage-1 operand
+preparation), the int8 activation quantised inside the stage-2 producer and the top-k reduce performed by the stage-2
+epilogue must give the SAME BITS as the chain of separate launches (align, quant_x, w13, quant_act, w2, topk_reduce),
+which in turn is what the oracle tests hold to the reference (tests/test_gpu_parity.py).  Covered: every weight
+format, the streaming and the tcgen05 path, ragged token counts, -1 / duplicate ids
+(test_moe_offloading_cpu.py:57-68), a token with every id masked, every id masked, the riding shared expert, inplace
+output (out aliases the hidden states), graph replay, and the launch count."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def K():
+    import sgl_cpu_tests_b200 as K
+    assert torch.cuda.is_available()
+    return K
+
+
+def fusion(on):
+    from sgl_cpu_tests_b200 import _lib as L
+    L.load().sglb_set_chain_fusion(1 if on else 0)
+
+
+def weights(fmt, E, H, I, seed):
+    import bench
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev).manual_seed(seed)
+    return bench.make_weights(fmt, E, H, I, dev, g), bench.FMT_ID[fmt], g
+
+
+def run(K, x, w, fid, tw, ids, path, inplace=False):
+    return K.fused_experts_impl(x.clone(), w["w1"], w["w2"], tw, ids, inplace, fid, w["s1"], w["s2"], w["block"], False, path=path)
+
+
+def both(K, x, w, fid, tw, ids, path, inplace=False):
+    try:
+        fusion(False)
+        n0 = K.launch_count()
+        ref = run(K, x, w, fid, tw, ids, path, inplace)
+        n1 = K.launch_count()
+        fusion(True)
+        out = run(K, x, w, fid, tw, ids, path, inplace)
+        n2 = K.launch_count()
+    finally:
+        fusion(True)
+    return ref, out, n1 - n0, n2 - n1
+
+
+def routing(M, E, topk, g, dev):
+    gating = torch.randn(M, E, device=dev, generator=g)
+    tw, ids = torch.topk(torch.softmax(gating, -1), topk, dim=-1)
+    return tw.float().contiguous(), ids.int().contiguous()
+
+
+@pytest.mark.parametrize("fmt", ["bf16", "int8", "fp8", "mxfp4"])
+@pytest.mark.parametrize("path", ["stream", "umma"])
+@pytest.mark.parametrize("M", [1, 5, 37, 130, 300])
+def test_fused_chain_is_bit_identical(K, fmt, path, M):
+    E, topk, H, I = 16, 4, 1024, 512
+    dev = torch.device("cuda", 0)
+    w, fid, g = weights(fmt, E, H, I, 3)
+    x = (torch.randn(M, H, device=dev, generator=g) / 8).bfloat16()
+    tw, ids = routing(M, E, topk, g, dev)
+    p = K.PATH_STREAM if path == "stream" else K.PATH_UMMA
+    ref, out, n_sep, n_fused = both(K, x, w, fid, tw, ids, p)
+    assert torch.isfinite(ref.float()).all() and ref.float().abs().max() > 0
+    assert torch.equal(out, ref), f"{fmt} {path} M={M}: max diff {(out.float() - ref.float()).abs().max()}"
+    assert n_fused < n_sep, (n_fused, n_sep)
+    if fmt in ("bf16", "int8") and path == "umma":
+        assert n_fused == 3, n_fused  # prologue, w13, w2 (<= 3 launches per call)
+
+
+@pytest.mark.parametrize("fmt", ["bf16", "int8", "fp8"])
+@pytest.mark.parametrize("path", ["stream", "umma", "auto"])
+def test_fused_chain_masked_and_duplicate_ids(K, fmt, path):
+    E, topk, H, I, M = 8, 4, 512, 256, 77
+    dev = torch.device("cuda", 0)
+    w, fid, g = weights(fmt, E, H, I, 5)
+    x = (torch.randn(M, H, device=dev, generator=g) / 4).bfloat16()
+    tw, ids = routing(M, E, topk, g, dev)
+    tw = torch.randn(M, topk, device=dev, generator=g)  # negative weights too (moe_offload fixture)
+    p = {"stream": K.PATH_STREAM, "umma": K.PATH_UMMA, "auto": K.PATH_AUTO}[path]
+    cases = []
+    a = ids.clone(); a[::3, 0] = -1; a[5, :] = -1; a[76, :] = -1; cases.append(a)   # masked slots, two fully masked tokens
+    b = ids.clone(); b[:, 1] = b[:, 0]; cases.append(b)                              # duplicate ids inside a token
+    cases.append(torch.full_like(ids, -1))                                           # nothing routed at all
+    c = torch.zeros_like(ids); c[:, 1:] = -1; cases.append(c)                        # one expert takes every token
+    for masked in cases:
+        ref, out, _, _ = both(K, x, w, fid, tw, masked, p)
+        assert torch.equal(out, ref), f"{fmt} {path}: max diff {(out.float() - ref.float()).abs().max()}"
+
+
+@pytest.mark.parametrize("fmt", ["bf16", "int8", "fp8"])
+def test_fused_chain_inplace_and_qwen_shape(K, fmt):
+    """out aliases hidden_states (inplace=True, test_moe.py:79-92): the fused reduce writes rows of `out` while other
+    CTAs still run stage 2 -- which never reads the hidden states."""
+    E, topk, H, I, M = 128, 8, 2048, 768, 128
+    dev = torch.device("cuda", 0)
+    w, fid, g = weights(fmt, E, H, I, 7)
+    x = (torch.randn(M, H, device=dev, generator=g) / 8).bfloat16()
+    tw, ids = routing(M, E, topk, g, dev)
+    for M_ in (128, 16, 1):
+        ref, out, _, _ = both(K, x[:M_], w, fid, tw[:M_].contiguous(), ids[:M_].contiguous(), K.PATH_AUTO, inplace=True)
+        assert torch.equal(out, ref), f"{fmt} M={M_}: max diff {(out.float() - ref.float()).abs().max()}"
+
+
+@pytest.mark.parametrize("fmt", ["bf16", "int8", "fp8"])
+@pytest.mark.parametrize("M", [1, 37, 300])
+def test_fused_chain_with_riding_shared_expert(K, fmt, M):
+    from test_gpu_layer import build
+    E, topk, H, I = 16, 4, 1024, 512
+    dev = torch.device("cuda", 0)
+    layer, w, sh, bias = build(K, fmt, E, topk, H, I, I, 11, True, path=K.PATH_UMMA)
+    assert layer.rides(M)
+    g = torch.Generator(device=dev).manual_seed(100 + M)
+    x = (torch.randn(M, H, device=dev, generator=g) / 16).bfloat16()
+    gating = torch.randn(M, E, device=dev, generator=g).bfloat16()
+    try:
+        fusion(False)
+        ref = layer.forward(x, gating)
+        fusion(True)
+        out = layer.forward(x, gating)
+        tw, ids = layer.route(gating)
+        ids[::2, 1] = -1
+        fusion(False)
+        ref_m = layer.experts(x, tw, ids, with_shared=True)
+        fusion(True)
+        out_m = layer.experts(x, tw, ids, with_shared=True)
+    finally:
+        fusion(True)
+    assert torch.equal(out, ref), (out.float() - ref.float()).abs().max()
+    assert torch.equal(out_m, ref_m), (out_m.float() - ref_m.float()).abs().max()
+
+
+def test_fused_chain_graph_replay_and_repeatability(K):
+    """Counters and row maxima are re-armed by every prologue: repeated calls and graph replays give the same bits."""
+    E, topk, H, I, M = 32, 4, 1024, 512, 64
+    dev = torch.device("cuda", 0)
+    for fmt in ("int8", "fp8"):
+        w, fid, g = weights(fmt, E, H, I, 9)
+        x = (torch.randn(M, H, device=dev, generator=g) / 8).bfloat16()
+        tw, ids = routing(M, E, topk, g, dev)
+        fusion(False)
+        try:
+            ref = run(K, x, w, fid, tw, ids, K.PATH_AUTO)
+        finally:
+            fusion(True)
+        for _ in range(5):
+            assert torch.equal(run(K, x, w, fid, tw, ids, K.PATH_AUTO), ref)
+        ge = K.GraphedExperts(M, w["w1"], w["w2"], topk, fid, w["s1"], w["s2"], w["block"])
+        for _ in range(4):
+            assert torch.equal(ge(x, tw, ids), ref)
+
+
+def test_many_align_blocks_in_the_prologue(K):
+    """M * topk > 1024: the prologue's align blocks count each other's slots themselves (no align_count launch)."""
+    E, topk, H, I, M = 64, 8, 512, 256, 1000   # 8000 slots -> 8 align blocks
+    dev = torch.device("cuda", 0)
+    for fmt in ("bf16", "int8"):
+        w, fid, g = weights(fmt, E, H, I, 13)
+        x = (torch.randn(M, H, device=dev, generator=g) / 8).bfloat16()
+        tw, ids = routing(M, E, topk, g, dev)
+        ids[::7, 3] = -1
+        ref, out, _, _ = both(K, x, w, fid, tw, ids, K.PATH_UMMA)
+        assert torch.equal(out, ref), (out.float() - ref.float()).abs().max()
