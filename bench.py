@@ -78,6 +78,8 @@ def parse():
     ap.add_argument("--bias-scale", type=float, default=None, help="std of the router's correction bias (default: by shape)")
     ap.add_argument("--path", default="auto", choices=list(PATHS), help="GEMM path (auto = by rows/expert)")
     ap.add_argument("--no-mx4-native", action="store_true", help="mxfp4: dequantising kernels instead of the block-scaled tensor cores")
+    ap.add_argument("--fusion", type=int, default=1, choices=[0, 1, 2],
+                    help="decode chain fusion level (include/sglb200.h sglb_set_chain_fusion; 1 = the library default)")
     ap.add_argument("--block-k", type=int, default=128, help="fp8 scale block along K (experiments; the layer's is 128)")
     ap.add_argument("--launch", default="auto", choices=["auto", "eager", "graph"],
                     help="how the value leg launches a step: eager C-ABI calls, or one CUDA-graph replay per step "
@@ -637,6 +639,7 @@ def run_b200(args):
     hbm_peak, tc, peak_src = peaks()
     lib = L.load()
     lib.sglb_set_mx4_native(0 if args.no_mx4_native else 1)
+    lib.sglb_set_chain_fusion(args.fusion)
 
     parity = None
     if world > 1:

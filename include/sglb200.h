@@ -65,11 +65,13 @@ int sglb_profile_read(float* ms_out, int* calls_out, int n);
  * the kernel (csrc/umma_dq.cu).  Process-wide switch, used by the parity tests to cover both. */
 void sglb_set_fp8_native(int on);
 
-/* Decode chain fusion (default 1): up to 8192 routed slots per call, fused_experts runs align + the stage-1 operand
- * preparation as ONE prologue launch, quantises the int8 activation inside the stage-2 producer and performs the
- * top-k reduce inside the stage-2 epilogue (last arriver per token, slot order) -- 3 launches for bf16 / int8 instead
- * of 4-7, results bit-identical.  0 = the separate launches (kept for the parity tests and for prefill). */
-void sglb_set_chain_fusion(int on);
+/* Decode chain fusion level, for calls of up to 8192 routed slots.  0 = every step its own launch (align_count,
+ * align_scatter, activation preparation, w13, activation preparation, w2, topk_reduce).  1 (default) = align + the
+ * stage-1 operand preparation (int8 rows / e4m3 hi-lo split of the hidden states) as ONE prologue launch.  2 =
+ * additionally the int8 activation quantised inside the stage-2 producer and the top-k reduce performed inside the
+ * stage-2 kernel (3 launches per call for bf16 / int8) -- measured slower on B200 and kept as an experiment
+ * (DESIGN.md 4c).  Results are bit-identical at every level (tests/test_gpu_fused_chain.py). */
+void sglb_set_chain_fusion(int level);
 
 /* ---- K1 router ------------------------------------------------------------------------------
  * grouped_topk_cpu          (test_grouped_topk.py:61-69, test_moe.py:61-70)  : bias == NULL

@@ -34,8 +34,12 @@ struct StageEvents {
 static bool g_profile = false;
 static bool g_mx4_native = true;  // mxfp4: block-scaled tensor-native kernel (umma_mx4.cu) when scale tiles are given
 static bool g_f8_native = true;  // fp8: tensor-native kernel (umma_f8.cu) vs dequantising kernel (umma_dq.cu)
-// decode chain fusion: single-launch prologue, int8 act quantisation and the top-k reduce inside the GEMM kernels
-static bool g_chain_fusion = true;
+// Decode chain fusion level (sglb_set_chain_fusion).  1 (default): align + stage-1 operand preparation in ONE prologue
+// launch.  2: also the int8 act quantisation inside the stage-2 producer and the top-k reduce inside the stage-2 kernel
+// (3 launches per call) -- bit-identical, but measured SLOWER on B200 (gpurun r2n: Qwen3 int8 M = 128 step 0.130 ->
+// 0.158 ms, bf16 0.204 -> 0.222 ms): under a saturated HBM every dependent global round trip costs 2-3 us, and the
+// fence -> arrival atomic -> slot rows chain of a 4-9 us work item does not fit behind it.  Kept as an experiment.
+static int g_chain_fusion = 1;
 static std::vector<StageEvents> g_events;
 static size_t g_events_used = 0;
 
@@ -224,6 +228,7 @@ struct MlpExtra {
   const void *sh_w13 = nullptr, *sh_w2 = nullptr, *sh_s13 = nullptr, *sh_s2 = nullptr;
   // fused decode chain: the prologue prepared the stage-1 operand; the stage-2 kernel finishes tokens into final_out
   bool fused = false;
+  bool fused_reduce = false;  // bf16 / int8 on umma_gemm.cu (reducer warp) and the streaming kernels
   void* final_out = nullptr;
   float shared_rsf = 1.f;
   bool any() const { return w13_bias || w2_bias || act != SGLB_ACT_SILU || out_by_slot || sh_w13; }
@@ -342,7 +347,7 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   const bool mx4 = umma && !pair && fmt == SGLB_FMT_MXFP4 && s13_tiles && s2_tiles && mx4_cap > 0;
   const bool f8 = mx4 || (umma && fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(H, I, bn, bk));
   // fused decode chain: the single-launch prologue already prepared the stage-1 operand (run_prologue)
-  const bool fused_int8 = ex.fused && fmt == SGLB_FMT_INT8_W8A8 && path == SGLB_PATH_UMMA;
+  const bool fused_int8 = ex.fused_reduce && fmt == SGLB_FMT_INT8_W8A8 && path == SGLB_PATH_UMMA;  // level 2
   if (fmt == SGLB_FMT_INT8_W8A8) {
     if (!ex.fused) {
       StageTimer t(ST_QUANT_X, stream);
@@ -398,7 +403,7 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   a.Wsh_scale = ex.sh_s2;
   a.out_by_slot = ex.out_by_slot;
   a.out_map = ex.out_map;
-  if (ex.fused) {
+  if (ex.fused_reduce) {
     a.red.cnt = ws.red_cnt;
     a.red.slot_pos = ws.slot_pos;
     a.red.tok_valid = ws.tok_valid;
@@ -458,7 +463,7 @@ int moe_prologue_impl(const int32_t* topk_ids, int64_t M, int topk, int E, int c
 
 // Fused decode chain: align + stage-1 operand preparation (mode 1 int8 rows, 2 e4m3 hi / lo split) + the state of the
 // fused top-k reduce, in ONE launch.
-static int run_prologue(const int32_t* ids, const void* hidden, int64_t M, int topk, int E, int H, int mode, int red_blocks,
+static int run_prologue(const int32_t* ids, const void* hidden, int64_t M, int topk, int E, int H, int mode, int red_blocks,  // red_blocks 0: no fused reduce
                         int chunk_rows, int tile_rows, int shared_rows, const MoeWorkspace& ws, cudaStream_t stream) {
   sglb_align_out ao;
   ao.expert_count = ws.expert_count;
@@ -477,8 +482,8 @@ static int run_prologue(const int32_t* ids, const void* hidden, int64_t M, int t
   pr.q = ws.xq;
   pr.q2 = ws.xq2;
   pr.xs = ws.xs;
-  pr.tok_valid = ws.tok_valid;
-  pr.red_cnt = ws.red_cnt;
+  pr.tok_valid = red_blocks > 0 ? ws.tok_valid : nullptr;
+  pr.red_cnt = red_blocks > 0 ? ws.red_cnt : nullptr;
   pr.red_blocks = red_blocks;
   pr.row_amax = ws.row_amax;
   pr.amax_rows = (int)(M * topk + M);
@@ -518,7 +523,7 @@ extern "C" int sglb_profile_read(float* ms_out, int* calls_out, int n) {
 }
 
 extern "C" void sglb_set_fp8_native(int on) { g_f8_native = on != 0; }
-extern "C" void sglb_set_chain_fusion(int on) { g_chain_fusion = on != 0; }
+extern "C" void sglb_set_chain_fusion(int level) { g_chain_fusion = level < 0 ? 0 : (level > 2 ? 2 : level); }
 extern "C" void sglb_set_mx4_native(int on) { g_mx4_native = on != 0; }
 extern "C" size_t sglb_mx4_scale_tiles_bytes(int64_t E, int rows, int split, int K) {
   if (E <= 0 || rows <= 0 || K <= 0) return 0;
@@ -635,12 +640,17 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
   if (path == SGLB_PATH_AUTO) {
     path = auto_path(p, mx4);
   }
-  // Decode chain fusion (bit-identical to the separate launches): one prologue launch, int8 act quantisation inside the
-  // stage-2 producer, top-k reduce inside the stage-2 epilogue.  Not for the CTA-pair kernels (prefill) and not when
-  // the caller reduces the slot rows itself (expert parallel).
-  const bool fuse = g_chain_fusion && !p->slot_out && p->M * p->topk <= kFuseMaxSlots && p->H % 8 == 0 &&
+  // Decode chain fusion (bit-identical to the separate launches): one prologue launch; at level 2 also the int8 act
+  // quantisation inside the stage-2 producer and the top-k reduce inside the stage-2 kernel.  Not for the CTA-pair
+  // kernels (prefill) and not when the caller reduces the slot rows itself (expert parallel).
+  const bool fuse = g_chain_fusion >= 1 && !p->slot_out && p->M * p->topk <= kFuseMaxSlots && p->H % 8 == 0 &&
                     (path == SGLB_PATH_UMMA || path == SGLB_PATH_STREAM);
+  // The reduce moves into the stage-2 kernel where a warp off the critical path can take it: the reducer warp of
+  // umma_gemm.cu (bf16 / int8) and the finishing warps of the streaming kernel.  The fp8 / mxfp4 tensor-native kernels
+  // keep the separate launch (their epilogue warps promote partial sums all through an item).
+  const bool fuse_reduce = fuse && g_chain_fusion >= 2 && (path == SGLB_PATH_STREAM || p->fmt == SGLB_FMT_BF16 || p->fmt == SGLB_FMT_INT8_W8A8);
   ex.fused = fuse;
+  ex.fused_reduce = fuse_reduce;
   ex.final_out = p->out;
   ex.shared_rsf = p->shared_rsf;
   if (path == SGLB_PATH_UMMA || path == SGLB_PATH_UMMA2) {
@@ -657,7 +667,8 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
       const bool f8 = use_mx4 || (p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k));
       const int mode = p->fmt == SGLB_FMT_INT8_W8A8 ? 1 : (f8 ? 2 : 0);
       rc = run_prologue(p->topk_ids, p->hidden, p->M, p->topk, p->E, p->H, mode,
-                        stage2_red_blocks(path, p->M, p->topk, p->E, p->H), 0, tile_rows, ride ? (int)p->M : 0, ws, stream);
+                        fuse_reduce ? stage2_red_blocks(path, p->M, p->topk, p->E, p->H) : 0, 0, tile_rows,
+                        ride ? (int)p->M : 0, ws, stream);
     } else {
       rc = run_align(p->topk_ids, p->M, p->topk, p->E, 0, ws, stream, tile_rows, ride ? (int)p->M : 0);
     }
@@ -680,7 +691,7 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     if (rc) return rc;
   }
   if (p->slot_out) return SGLB_OK;  // the caller reduces the slot rows (expert-parallel combine)
-  if (fuse) return SGLB_OK;         // the stage-2 kernel finished the tokens itself
+  if (fuse_reduce) return SGLB_OK;  // the stage-2 kernel finished the tokens itself
   StageTimer t(ST_REDUCE, stream);
   // riding shared expert: its rows sit behind the routed ones; the reduce applies shared_expert_cpu's epilogue
   const void* shared_y = ride ? (const void*)(ws.ic2 + (size_t)p->M * p->topk * p->H) : nullptr;

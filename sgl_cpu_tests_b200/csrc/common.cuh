@@ -157,20 +157,31 @@ struct FusedReduce {
 __device__ __forceinline__ void fused_reduce_cols8(const FusedReduce& r, const __nv_bfloat16* ic2, int topk, int N, int t,
                                                    int col0) {
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  for (int j = 0; j < topk; ++j) {
-    const int p = r.slot_pos[(size_t)t * topk + j];
-    if (p < 0) continue;
-    const int4 v = __ldcg(reinterpret_cast<const int4*>(ic2 + (size_t)p * N + col0));
-    const uint32_t* w = reinterpret_cast<const uint32_t*>(&v);
+  int4 sv = make_int4(0, 0, 0, 0);  // the riding shared expert's row travels with the first pass
+  if (r.shared_row0 >= 0) sv = __ldcg(reinterpret_cast<const int4*>(ic2 + (size_t)(r.shared_row0 + t) * N + col0));
+  // eight slots per pass: the positions, then the rows, are fetched together (two L2 round trips per pass instead of
+  // two per slot); the additions keep the slot order
+  for (int j0 = 0; j0 < topk; j0 += 8) {
+    int p[8];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      acc[2 * i] += bf16_bits_to_float(w[i] & 0xffffu);
-      acc[2 * i + 1] += bf16_bits_to_float(w[i] >> 16);
+    for (int i = 0; i < 8; ++i) p[i] = j0 + i < topk ? r.slot_pos[(size_t)t * topk + j0 + i] : -1;
+    int4 v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      v[i] = p[i] >= 0 ? __ldcg(reinterpret_cast<const int4*>(ic2 + (size_t)p[i] * N + col0)) : make_int4(0, 0, 0, 0);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (p[i] < 0) continue;
+      const uint32_t* w = reinterpret_cast<const uint32_t*>(&v[i]);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        acc[2 * q] += bf16_bits_to_float(w[q] & 0xffffu);
+        acc[2 * q + 1] += bf16_bits_to_float(w[q] >> 16);
+      }
     }
   }
   if (r.shared_row0 >= 0) {
-    const int4 v = __ldcg(reinterpret_cast<const int4*>(ic2 + (size_t)(r.shared_row0 + t) * N + col0));
-    const uint32_t* w = reinterpret_cast<const uint32_t*>(&v);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(&sv);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       acc[2 * i] = fmaf(bf16_round(acc[2 * i]), r.rsf, bf16_bits_to_float(w[i] & 0xffffu));

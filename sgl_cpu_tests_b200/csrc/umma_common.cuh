@@ -264,37 +264,54 @@ __device__ __forceinline__ void gather_quant_role(const UmmaArgs& a, int total, 
       inv[j] = 0.f;
       if (rbase + 16 * j < n_eff) inv[j] = __fmul_rn(__frcp_rn(fmaxf(__uint_as_float(a.row_amax[p]), 1e-7f)), 127.0f);
     }
+    // rows j = 0, 1 (all there is at decode: tiles of up to 32 rows): the 64 bytes of k block kb + 1 are requested
+    // before k block kb is converted, so an L2 round trip never sits between two stages
+    auto load_pair = [&](float4 (&v)[2][4], int j0, int kb) {
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj)
+        if (rbase + 16 * (j0 + jj) < n_eff) {
+          const float4* p4 = reinterpret_cast<const float4*>(src[j0 + jj] + kb * kRowBytes);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) v[jj][i] = __ldcg(p4 + i);
+        }
+    };
+    auto store_pair = [&](const float4 (&v)[2][4], int j0, uint32_t dst) {
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj)
+        if (rbase + 16 * (j0 + jj) < n_eff) {
+          const float sc = inv[j0 + jj];
+          uint32_t o[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int q0 = __float2int_rn(v[jj][i].x * sc), q1 = __float2int_rn(v[jj][i].y * sc);
+            const int q2 = __float2int_rn(v[jj][i].z * sc), q3 = __float2int_rn(v[jj][i].w * sc);
+            o[i] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) |
+                   ((uint32_t)(q3 & 0xff) << 24);
+          }
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (j0 + jj) * 16 * kRowBytes), "r"(o[0]),
+                       "r"(o[1]), "r"(o[2]), "r"(o[3])
+                       : "memory");
+        }
+    };
+    float4 nxt[2][4];
+    load_pair(nxt, 0, 0);
     for (int kb = 0; kb < num_kb; ++kb, ++it) {
       const int s = it % nstages;
+      float4 cur[2][4];
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) cur[jj][i] = nxt[jj][i];
+      if (kb + 1 < num_kb) load_pair(nxt, 0, kb + 1);
       mbar_wait(xempty0 + 8 * s, ((it / nstages) & 1) ^ 1);
       const uint32_t dst = x_tile0 + s * x_stride + dst0;
+      store_pair(cur, 0, dst);
 #pragma unroll
-      for (int j0 = 0; j0 < 8; j0 += 2) {  // two rows (eight 16-byte loads) in flight
-        if (rbase + 16 * j0 < n_eff) {     // monotone in j0
+      for (int j0 = 2; j0 < 8; j0 += 2) {
+        if (rbase + 16 * j0 < n_eff) {  // larger tiles (skewed routing): plain load -> convert -> store
           float4 v[2][4];
-#pragma unroll
-          for (int jj = 0; jj < 2; ++jj)
-            if (rbase + 16 * (j0 + jj) < n_eff) {
-              const float4* p4 = reinterpret_cast<const float4*>(src[j0 + jj] + kb * kRowBytes);
-#pragma unroll
-              for (int i = 0; i < 4; ++i) v[jj][i] = __ldcg(p4 + i);
-            }
-#pragma unroll
-          for (int jj = 0; jj < 2; ++jj)
-            if (rbase + 16 * (j0 + jj) < n_eff) {
-              const float sc = inv[j0 + jj];
-              uint32_t o[4];
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const int q0 = __float2int_rn(v[jj][i].x * sc), q1 = __float2int_rn(v[jj][i].y * sc);
-                const int q2 = __float2int_rn(v[jj][i].z * sc), q3 = __float2int_rn(v[jj][i].w * sc);
-                o[i] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) |
-                       ((uint32_t)(q3 & 0xff) << 24);
-              }
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (j0 + jj) * 16 * kRowBytes), "r"(o[0]),
-                           "r"(o[1]), "r"(o[2]), "r"(o[3])
-                           : "memory");
-            }
+          load_pair(v, j0, kb);
+          store_pair(v, j0, dst);
         }
       }
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
@@ -303,28 +320,46 @@ __device__ __forceinline__ void gather_quant_role(const UmmaArgs& a, int total, 
   }
 }
 
-// ---- fused top-k reduce of one finished stage-2 work item (all kEpiWarps epilogue warps call it) -----------
-// Warp ew owns rows [16 ew, 16 ew + 16) of the tile: lane l < 16 counts the arrival of row 16 ew + l on
-// red.cnt[token, nb]; completed tokens are reduced by the whole warp, 8 columns per lane (256 per block).
-__device__ __forceinline__ void fused_reduce_item(const UmmaArgs& a, const WorkItem& wi, int ew, int lane) {
-  __threadfence();  // this thread's ic2 stores, device scope
-  asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");  // every epilogue warp has stored its part of the item
-  const int r = ew * 16 + lane;
-  bool done = false;
-  int tok = 0;
-  if (lane < 16 && r < wi.rows) {
-    tok = a.sorted_slot[wi.row_start + r] / a.topk;
-    __threadfence();  // cumulative: the other warps' stores observed through the barrier
-    done = atomicAdd(a.red.cnt + (size_t)tok * a.red.blocks + wi.nb, 1) + 1 == a.red.need;
-    if (done) __threadfence();
-  }
-  unsigned mask = __ballot_sync(0xffffffffu, done);
-  const int col0 = wi.nb * 2 * kWSub + lane * 8;
-  while (mask) {
-    const int srcl = __ffs(mask) - 1;
-    mask &= mask - 1;
-    const int t = __shfl_sync(0xffffffffu, tok, srcl);
-    if (col0 < a.N) fused_reduce_cols8(a.red, (const __nv_bfloat16*)a.out, a.topk, a.N, t, col0);
+// ---- fused top-k reduce: a dedicated reducer warp (stage 2 of umma_gemm.cu in the fused decode chain) -------
+// The epilogue warps only ARRIVE on red_full[b] after the stores of a work item (and wait on red_empty[b] before they
+// reuse the slot two items later), so the L2 round trips of the reduce -- fence, arrival atomics, the slot rows --
+// never sit on the path that frees TMEM.  The reducer counts each routed row of the tile on red.cnt[token, nb];
+// tokens it completes are reduced by the whole warp, 8 columns per lane (256 per block).  Barriers at red_bar0:
+// full[0], full[1], empty[0], empty[1].
+__device__ __forceinline__ void reducer_role(const UmmaArgs& a, int total, int n_blocks, uint32_t red_bar0, int lane) {
+  uint32_t li = 0;
+  for (int w = blockIdx.x; w < total; w += gridDim.x, ++li) {
+    const WorkItem wi = get_item(a, w, n_blocks);
+    const int b = li & 1;
+    int tok[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {  // before the wait: the dependent tile_list -> sorted_slot loads hide under the item
+      const int r = lane + 32 * i;
+      tok[i] = r < wi.rows ? a.sorted_slot[wi.row_start + r] / a.topk : -1;
+    }
+    mbar_wait_relaxed(red_bar0 + 8 * b, (li >> 1) & 1);  // every epilogue thread has issued its stores of the item
+    __threadfence();  // cumulative over the stores observed through the barrier (the grid-sync pattern)
+    int old[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      old[i] = tok[i] >= 0 ? atomicAdd(a.red.cnt + (size_t)tok[i] * a.red.blocks + wi.nb, 1) : -2;
+    bool any = false;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) any |= old[i] + 1 == a.red.need;
+    if (any) __threadfence();
+    const int col0 = wi.nb * 2 * kWSub + lane * 8;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      unsigned mask = __ballot_sync(0xffffffffu, old[i] + 1 == a.red.need);
+      while (mask) {
+        const int srcl = __ffs(mask) - 1;
+        mask &= mask - 1;
+        const int t = __shfl_sync(0xffffffffu, tok[i], srcl);
+        if (col0 < a.N) fused_reduce_cols8(a.red, (const __nv_bfloat16*)a.out, a.topk, a.N, t, col0);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(red_bar0 + 8 * (2 + b));
   }
 }
 
@@ -339,7 +374,7 @@ template <bool kInt8, int STAGE, bool kRelaxed, bool kTokScale = false, int kAcc
           int kSubStride = kWSub, bool kConcat = false>
 __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int n_blocks, uint8_t* smem_raw,
                                               uint32_t epi_base, uint32_t tfull0, uint32_t tempty0,
-                                              uint32_t tmem_base, int warp, int ew, int lane) {
+                                              uint32_t tmem_base, int warp, int ew, int lane, uint32_t red_bar0 = 0) {
   auto tfull_bar = [&](int b) { return tfull0 + 8 * b; };
   auto tempty_bar = [&](int b) { return tempty0 + 8 * b; };
     // ================= epilogue =================
@@ -361,6 +396,9 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
       const WorkItem wi = get_item(a, w, n_blocks);
       const int n_eff = (wi.rows + 15) & ~15;
       const int buf = li & 1;
+      if constexpr (STAGE == 2) {  // fused reduce: the reducer warp must be done with the item two back
+        if (red_bar0 != 0) mbar_wait_relaxed(red_bar0 + 8 * (2 + buf), ((li >> 1) & 1) ^ 1);
+      }
       // Per-token scalars of this tile (activation scale, topk weight): lane l keeps tokens
       // l, l+32, l+64, l+96.  Fetched before the accumulator wait so the dependent loads
       // (sorted_slot -> scale) hide under the MMAs; broadcast with shuffles in the column loop.
@@ -499,7 +537,7 @@ __device__ __forceinline__ void epilogue_role(const UmmaArgs& a, int total, int 
       tc_fence_before();
       mbar_arrive(tempty_bar(buf));
       if constexpr (STAGE == 2) {
-        if (a.red.cnt != nullptr) fused_reduce_item(a, wi, ew, lane);  // kernel-uniform
+        if (red_bar0 != 0) mbar_arrive(red_bar0 + 8 * buf);  // this thread's stores of the item are issued (release)
       }
     }
 }

@@ -222,7 +222,6 @@ __global__ void __launch_bounds__(kThreads, 1)
     uint8_t* ebuf = smem_raw + (epi_base + ew * kEpiBufBytes - smem_u32(smem_raw));
     const int rd_tok = lane / SEGS, rd_seg = lane % SEGS;
     const int nblk_rows = ceil_div(a.rows_per_expert, a.block_n);
-    if constexpr (STAGE == 2) fused_reduce_zero_rows(a.red, a.N, blockIdx.x * kEpiWarps + ew, gridDim.x * kEpiWarps, lane);
     uint32_t gi = 0;
     for (int w = blockIdx.x; w < total; w += gridDim.x) {
       const WorkItem wi = get_item(a, w, n_blocks);
@@ -351,9 +350,6 @@ __global__ void __launch_bounds__(kThreads, 1)
           }
           __syncwarp();
         }
-      }
-      if constexpr (STAGE == 2) {
-        if (a.red.cnt != nullptr) fused_reduce_item(a, wi, ew, lane);  // fused decode chain (kernel-uniform)
       }
     }
   }

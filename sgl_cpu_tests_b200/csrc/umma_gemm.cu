@@ -42,11 +42,13 @@ constexpr int kStages = 4;
 constexpr int kStageBytes = 2 * kWTileBytes + kXTileBytes;  // 48 KB
 constexpr int kFirstEpiWarp = 6;
 constexpr int kThreads = (kFirstEpiWarp + kEpiWarps) * 32;  // 448
+constexpr int kReducerWarp = kFirstEpiWarp + kEpiWarps;     // 14: present only in the fused decode chain (stage 2)
+constexpr int kThreadsFused = kThreads + 32;
 constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBufBytes + 1024 /*alignment slack*/ +
                            256 /*barriers*/;
 
 template <int FMT, int STAGE>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreadsFused, 1)
     umma_moe_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_sh,
                     const UmmaArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -60,6 +62,8 @@ __global__ void __launch_bounds__(kThreads, 1)
   auto tfull_bar = [&](int b) { return bar_base + 8 * (2 * kStages + b); };
   auto tempty_bar = [&](int b) { return bar_base + 8 * (2 * kStages + 2 + b); };
   const uint32_t tmem_slot = bar_base + 8 * (2 * kStages + 4);
+  const uint32_t red_bar0 = bar_base + 128;  // fused reduce: full[2], empty[2] between the epilogue and the reducer warp
+  const bool fused_reduce = STAGE == 2 && a.red.cnt != nullptr;  // then the block has kThreadsFused threads
   uint32_t* tmem_slot_ptr =
       reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
@@ -79,6 +83,8 @@ __global__ void __launch_bounds__(kThreads, 1)
     for (int b = 0; b < 2; ++b) {
       mbar_init(tfull_bar(b), 1);
       mbar_init(tempty_bar(b), kEpiThreads);
+      mbar_init(red_bar0 + 8 * b, kEpiThreads);
+      mbar_init(red_bar0 + 8 * (2 + b), 1);
     }
     fence_barrier_init();
   }
@@ -168,9 +174,12 @@ __global__ void __launch_bounds__(kThreads, 1)
     else
       gather_role<false>(a, total, n_blocks, num_kb, k_bytes, threadIdx.x - 64, x_tile(0), kStageBytes, full_bar(0),
                          empty_bar(0), kStages);
-  } else {
+  } else if (warp < kReducerWarp) {
     epilogue_role<FMT == SGLB_FMT_INT8_W8A8, STAGE, false>(a, total, n_blocks, smem_raw, epi_base, tfull_bar(0),
-                                                    tempty_bar(0), tmem_base, warp, warp - kFirstEpiWarp, lane);
+                                                    tempty_bar(0), tmem_base, warp, warp - kFirstEpiWarp, lane,
+                                                    fused_reduce ? red_bar0 : 0u);
+  } else {
+    if constexpr (STAGE == 2) reducer_role(a, total, n_blocks, red_bar0, lane);
   }
 
   tc_fence_before();
@@ -329,7 +338,8 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
     return e ? atoi(e) : 0;
   }();
   if (forced_grid > 0 && forced_grid < grid) grid = forced_grid;
-  SGLB_CUDA(launch_pdl(umma_moe_kernel<FMT, STAGE>, dim3(grid), dim3(kThreads), kSmemBytes, stream, map, map_sh, a));
+  const int threads = STAGE == 2 && a.red.cnt != nullptr ? kThreadsFused : kThreads;  // + the reducer warp
+  SGLB_CUDA(launch_pdl(umma_moe_kernel<FMT, STAGE>, dim3(grid), dim3(threads), kSmemBytes, stream, map, map_sh, a));
   return SGLB_OK;
 }
 

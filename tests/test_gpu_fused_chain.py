@@ -1,6 +1,6 @@
 """Decode chain fusion (capi.cu, sglb_set_chain_fusion): the single-launch prologue (align + stage-1 operand
-preparation), the int8 activation quantised inside the stage-2 producer and the top-k reduce performed by the stage-2
-epilogue must give the SAME BITS as the chain of separate launches (align, quant_x, w13, quant_act, w2, topk_reduce),
+preparation; level 1, the default) and, at level 2, the int8 activation quantised inside the stage-2 producer and the
+top-k reduce performed inside the stage-2 kernel must give the SAME BITS as the chain of separate launches (align, quant_x, w13, quant_act, w2, topk_reduce),
 which in turn is what the oracle tests hold to the reference (tests/test_gpu_parity.py).  Covered: every weight
 format, the streaming and the tcgen05 path, ragged token counts, -1 / duplicate ids
 (test_moe_offloading_cpu.py:57-68), a token with every id masked, every id masked, the riding shared expert, inplace
@@ -18,9 +18,13 @@ def K():
     return K
 
 
-def fusion(on):
+DEFAULT_LEVEL = 1
+
+
+def fusion(level):
+    """0: separate launches; 1 (default): single-launch prologue; 2: + in-kernel int8 quantisation and top-k reduce."""
     from sgl_cpu_tests_b200 import _lib as L
-    L.load().sglb_set_chain_fusion(1 if on else 0)
+    L.load().sglb_set_chain_fusion(DEFAULT_LEVEL if level is True else int(level))
 
 
 def weights(fmt, E, H, I, seed):
@@ -35,17 +39,24 @@ def run(K, x, w, fid, tw, ids, path, inplace=False):
 
 
 def both(K, x, w, fid, tw, ids, path, inplace=False):
+    """Separate launches vs level 2; level 1 is checked against the same reference on the way."""
     try:
-        fusion(False)
+        fusion(0)
         n0 = K.launch_count()
         ref = run(K, x, w, fid, tw, ids, path, inplace)
         n1 = K.launch_count()
-        fusion(True)
+        fusion(1)
+        mid = run(K, x, w, fid, tw, ids, path, inplace)
+        n1b = K.launch_count()
+        assert torch.equal(mid, ref), f"level 1: max diff {(mid.float() - ref.float()).abs().max()}"
+        assert n1b - n1 <= n1 - n0
+        fusion(2)
+        n1c = K.launch_count()
         out = run(K, x, w, fid, tw, ids, path, inplace)
         n2 = K.launch_count()
     finally:
         fusion(True)
-    return ref, out, n1 - n0, n2 - n1
+    return ref, out, n1 - n0, n2 - n1c
 
 
 def routing(M, E, topk, g, dev):
@@ -118,20 +129,19 @@ def test_fused_chain_with_riding_shared_expert(K, fmt, M):
     x = (torch.randn(M, H, device=dev, generator=g) / 16).bfloat16()
     gating = torch.randn(M, E, device=dev, generator=g).bfloat16()
     try:
-        fusion(False)
+        fusion(0)
         ref = layer.forward(x, gating)
-        fusion(True)
-        out = layer.forward(x, gating)
         tw, ids = layer.route(gating)
         ids[::2, 1] = -1
-        fusion(False)
         ref_m = layer.experts(x, tw, ids, with_shared=True)
-        fusion(True)
-        out_m = layer.experts(x, tw, ids, with_shared=True)
+        for level in (1, 2):
+            fusion(level)
+            out = layer.forward(x, gating)
+            out_m = layer.experts(x, tw, ids, with_shared=True)
+            assert torch.equal(out, ref), (level, (out.float() - ref.float()).abs().max())
+            assert torch.equal(out_m, ref_m), (level, (out_m.float() - ref_m.float()).abs().max())
     finally:
         fusion(True)
-    assert torch.equal(out, ref), (out.float() - ref.float()).abs().max()
-    assert torch.equal(out_m, ref_m), (out_m.float() - ref_m.float()).abs().max()
 
 
 def test_fused_chain_graph_replay_and_repeatability(K):
@@ -142,16 +152,18 @@ def test_fused_chain_graph_replay_and_repeatability(K):
         w, fid, g = weights(fmt, E, H, I, 9)
         x = (torch.randn(M, H, device=dev, generator=g) / 8).bfloat16()
         tw, ids = routing(M, E, topk, g, dev)
-        fusion(False)
+        fusion(0)
         try:
             ref = run(K, x, w, fid, tw, ids, K.PATH_AUTO)
+            for level in (1, 2):
+                fusion(level)
+                for _ in range(5):
+                    assert torch.equal(run(K, x, w, fid, tw, ids, K.PATH_AUTO), ref)
+                ge = K.GraphedExperts(M, w["w1"], w["w2"], topk, fid, w["s1"], w["s2"], w["block"])
+                for _ in range(4):
+                    assert torch.equal(ge(x, tw, ids), ref)
         finally:
             fusion(True)
-        for _ in range(5):
-            assert torch.equal(run(K, x, w, fid, tw, ids, K.PATH_AUTO), ref)
-        ge = K.GraphedExperts(M, w["w1"], w["w2"], topk, fid, w["s1"], w["s2"], w["block"])
-        for _ in range(4):
-            assert torch.equal(ge(x, tw, ids), ref)
 
 
 def test_many_align_blocks_in_the_prologue(K):

@@ -511,7 +511,7 @@ def test_graphed_experts_matches_eager(K, fmt):
         s1, s2 = (torch.rand(E, 2 * I) * 1e-2).to(dev), (torch.rand(E, H) * 1e-2).to(dev)
         f = K.FMT_INT8_W8A8
     g = K.GraphedExperts(M, w1, w2, topk, f, s1, s2)
-    assert g.kernels_per_replay >= 4
+    assert g.kernels_per_replay >= 3  # fused decode chain: prologue, w13, w2
     for seed in (1, 2):
         torch.manual_seed(seed)
         x = (torch.randn(M, H) / 4).bfloat16().to(dev)
