@@ -33,19 +33,33 @@ __global__ void __launch_bounds__(256)
   if (h0 >= H) return;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   const bool full = (h0 + 8 <= H) && (H % 8 == 0);
-  for (int j = 0; j < topk; ++j) {
-    const int p = slot_pos[m * topk + j];
-    if (p < 0) continue;
-    const __nv_bfloat16* src = ic2 + (size_t)p * H + h0;
-    if (full) {
-      int4 v = *reinterpret_cast<const int4*>(src);
-      const uint32_t* w = reinterpret_cast<const uint32_t*>(&v);
+  if (full) {
+    // eight slots per pass: the positions, then the rows, are requested together (two dependent round trips per pass
+    // instead of two per slot -- at decode this kernel is nothing but latency); the additions keep the slot order
+    for (int j0 = 0; j0 < topk; j0 += 8) {
+      int p[8];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        acc[2 * i] += bf16_bits_to_float(w[i] & 0xffffu);
-        acc[2 * i + 1] += bf16_bits_to_float(w[i] >> 16);
+      for (int i = 0; i < 8; ++i) p[i] = j0 + i < topk ? slot_pos[m * topk + j0 + i] : -1;
+      int4 v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        v[i] = p[i] >= 0 ? *reinterpret_cast<const int4*>(ic2 + (size_t)p[i] * H + h0) : make_int4(0, 0, 0, 0);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (p[i] < 0) continue;
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(&v[i]);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          acc[2 * q] += bf16_bits_to_float(w[q] & 0xffffu);
+          acc[2 * q + 1] += bf16_bits_to_float(w[q] >> 16);
+        }
       }
-    } else {
+    }
+  } else {
+    for (int j = 0; j < topk; ++j) {
+      const int p = slot_pos[m * topk + j];
+      if (p < 0) continue;
+      const __nv_bfloat16* src = ic2 + (size_t)p * H + h0;
       for (int i = 0; i < 8 && h0 + i < H; ++i) acc[i] += __bfloat162float(src[i]);
     }
   }

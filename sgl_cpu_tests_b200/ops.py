@@ -312,14 +312,16 @@ def _resident_mx_scale(s, is_vnni, dev):
     return sd
 
 
-def _mx4_tiles(s_dev, split):
+def _mx4_tiles(s_dev, shape, split):
     """e8m0 scales [E, rows, K/32] on the device -> the 512-byte tiles the block-scaled tensor-core kernel
-    copies into TMEM (csrc/umma_mx4.cu); built once per scale tensor and cached."""
-    key = _registry_key(s_dev, False, ("mx4tiles", split))
+    copies into TMEM (csrc/umma_mx4.cu); built once per scale tensor and cached.  Keyed on (and dropped with) the
+    resident scale tensor itself, not on the reshaped view of it made here: a temporary view dies with the call and
+    would take the entry with it (found in the gpt-oss launch list: two re-tiling launches, 137 us, per step)."""
+    key = _registry_key(s_dev, False, ("mx4tiles", tuple(shape), split))
     hit = _registry_get(key)
     if hit is not None:
         return hit
-    E, rows, G = _rows_k(s_dev, False)
+    E, rows, G = shape
     lib = L.load()
     tiles = torch.empty(lib.sglb_mx4_scale_tiles_bytes(E, rows, split, 32 * G), dtype=torch.uint8, device=s_dev.device)
     L.check(lib.sglb_mx4_tile_scales(s_dev.data_ptr(), tiles.data_ptr(), E, rows, split, 32 * G, _stream()))
@@ -593,8 +595,8 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
                 w13p, w2p = _mx4_weight(w13), _mx4_weight(w2d)
                 if w13p is not None and w2p is not None:
                     w13, w2d = w13p, w2p
-                    t13 = _mx4_tiles(s13.view(E, 2 * I, H // 32), I)
-                    t2 = _mx4_tiles(s2.view(E, H, I // 32), 0)
+                    t13 = _mx4_tiles(s13, (E, 2 * I, H // 32), I)
+                    t2 = _mx4_tiles(s2, (E, H, I // 32), 0)
         elif fmt != L.FMT_BF16:
             s13 = _resident_aux(w1_scale, dev, torch.float32)
             s2 = _resident_aux(w2_scale, dev, torch.float32)

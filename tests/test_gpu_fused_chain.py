@@ -177,3 +177,21 @@ def test_many_align_blocks_in_the_prologue(K):
         ids[::7, 3] = -1
         ref, out, _, _ = both(K, x, w, fid, tw, ids, K.PATH_UMMA)
         assert torch.equal(out, ref), (out.float() - ref.float()).abs().max()
+
+
+def test_mxfp4_scale_tiles_are_built_once(K):
+    """The e8m0 scale tiles of the block-scaled kernel are a per-weight cache (ops._mx4_tiles): a second call with the
+    same weights must not re-tile them (regression: the cache was keyed on a temporary view and re-tiled every call,
+    two extra launches = 137 us per gpt-oss step)."""
+    E, topk, H, I, M = 16, 4, 1024, 512, 64
+    dev = torch.device("cuda", 0)
+    w, fid, g = weights("mxfp4", E, H, I, 21)
+    x = (torch.randn(M, H, device=dev, generator=g) / 8).bfloat16()
+    tw, ids = routing(M, E, topk, g, dev)
+    counts = []
+    for _ in range(3):
+        n0 = K.launch_count()
+        run(K, x, w, fid, tw, ids, K.PATH_AUTO)
+        counts.append(K.launch_count() - n0)
+    assert counts[1] == counts[2] <= 5, counts   # prologue, w13, split, w2, reduce
+    assert counts[0] >= counts[1]
