@@ -65,7 +65,7 @@ int sglb_profile_read(float* ms_out, int* calls_out, int n);
  * the kernel (csrc/umma_dq.cu).  Process-wide switch, used by the parity tests to cover both. */
 void sglb_set_fp8_native(int on);
 
-/* Decode chain fusion level, for calls of up to 8192 routed slots.  0 = every step its own launch (align_count,
+/* Decode chain fusion level, for calls of up to 16384 routed slots.  0 = every step its own launch (align_count,
  * align_scatter, activation preparation, w13, activation preparation, w2, topk_reduce).  1 (default) = align + the
  * stage-1 operand preparation (int8 rows / e4m3 hi-lo split of the hidden states) as ONE prologue launch.  2 =
  * additionally the int8 activation quantised inside the stage-2 producer and the top-k reduce performed inside the

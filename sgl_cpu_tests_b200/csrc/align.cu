@@ -265,15 +265,18 @@ __global__ void __launch_bounds__(kAlignThreads)
     for (int i = rb * kAlignThreads + threadIdx.x; i < pr.amax_rows; i += nrb * kAlignThreads) pr.row_amax[i] = 0u;
   const int m = rb * 4 + grp;
   if (m >= pr.M) return;  // whole 256-thread group
+  int valid = 0;
+  for (int j = 0; j < topk; ++j) {
+    const int e = ids[(size_t)m * topk + j];
+    valid += (e >= 0 && e < E) ? 1 : 0;
+  }
   if (pr.red_cnt != nullptr) {
-    int valid = 0;
-    for (int j = 0; j < topk; ++j) {
-      const int e = ids[(size_t)m * topk + j];
-      valid += (e >= 0 && e < E) ? 1 : 0;
-    }
     if (t == 0) pr.tok_valid[m] = valid;
     for (int b = t; b < pr.red_blocks; b += 256) pr.red_cnt[(size_t)m * pr.red_blocks + b] = topk - valid;
   }
+  // a token no routed slot points at is never gathered (an expert-parallel rank: most received rows); with a riding
+  // shared expert every token row is an operand
+  if (valid == 0 && shared_rows == 0) return;
   float* red_s = reinterpret_cast<float*>(smem_i) + grp * 8;
   if (pr.mode == 1)
     quant_row_int8<__nv_bfloat16>(pr.x + (size_t)m * pr.K, pr.K, (int8_t*)pr.q + (size_t)m * pr.K, pr.xs + m, t, red_s,

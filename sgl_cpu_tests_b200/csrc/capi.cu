@@ -66,7 +66,7 @@ struct StageTimer {
 int launch_shared_axpy(const void* y, const void* fused, float rsf, int64_t n, void* out,
                        cudaStream_t stream);
 int launch_quant_rows_f32(const float* x, int64_t rows, int K, int8_t* q, float* scale,
-                          cudaStream_t stream);
+                          cudaStream_t stream, const int32_t* n_valid = nullptr, int always_from = 0);
 int launch_gather_rows(const int32_t* sorted_slot, int64_t S, int topk, int row_bytes, const void* x, const void* x2, void* y,
                        void* y2, cudaStream_t stream);
 
@@ -229,6 +229,7 @@ struct MlpExtra {
   // fused decode chain: the prologue prepared the stage-1 operand; the stage-2 kernel finishes tokens into final_out
   bool fused = false;
   bool fused_reduce = false;  // bf16 / int8 on umma_gemm.cu (reducer warp) and the streaming kernels
+  double rpe_hint = 0.0;      // expected routed rows per expert when the ids are mostly masked (expert parallel)
   void* final_out = nullptr;
   float shared_rsf = 1.f;
   bool any() const { return w13_bias || w2_bias || act != SGLB_ACT_SILU || out_by_slot || sh_w13; }
@@ -237,7 +238,7 @@ struct MlpExtra {
 // One GEMM stage on the tcgen05 path over the tile list of an existing alignment.
 static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64_t S, const MoeWorkspace& ws,
                           cudaStream_t stream, bool f8_native = false, bool pair = false,
-                          const void* mx4_tiles = nullptr, int mx4_cap = 0) {
+                          const void* mx4_tiles = nullptr, int mx4_cap = 0, double rpe_hint = 0.0) {
   UmmaArgs u;
   memset(&u, 0, sizeof(u));
   u.W = sa.W;
@@ -278,16 +279,21 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.Xraw = sa.Xraw;
   const int sh_tiles = sa.Wsh ? (int)ceil_div64(S / sa.topk, kTileRows) : 0;
   u.max_tiles += sh_tiles;
+  if (!pair) {
+    // Expected number of tiles when the call is weight-streaming bound (up to 64 rows per active expert: every item
+    // then costs its weight bytes); the launchers size the persistent grid to whole waves of it (persistent_grid).
+    // rpe = expected routed rows per expert: the caller's hint (an expert-parallel rank, whose ids are mostly masked)
+    // or S / E; experts hit ~ Poisson.
+    const double rpe = rpe_hint > 0.0 ? rpe_hint : (double)S / E;
+    double active = E == 1 ? 1.0 : E * (1.0 - exp(-rpe));
+    if (active < 1) active = 1;
+    const double rows_active = rpe * E / active;
+    const int cap = mx4_tiles ? mx4_cap : kTileRows;
+    if (rows_active <= 64.0) u.est_tiles = (int)(active * ceil(rows_active / cap) + 0.5) + sh_tiles;
+  }
   if (mx4_tiles) return launch_umma_mx4(stage, u, stream);
   if (f8_native) return pair ? launch_umma2_f8(stage, u, stream) : launch_umma_f8(stage, u, stream);
   if (pair) return launch_umma2_gemm(fmt, stage, u, stream);
-  if (fmt == SGLB_FMT_BF16 || fmt == SGLB_FMT_INT8_W8A8) {
-    // expected number of tiles when the call is weight-streaming bound (few rows per active expert)
-    const double M = (double)S / sa.topk;
-    double active = E == 1 ? 1.0 : E * (1.0 - pow(1.0 - (double)(sa.topk < E ? sa.topk : E) / E, M));
-    if (active < 1) active = 1;
-    if ((double)S / active <= 32.0) u.est_tiles = (int)(active + 0.5) + sh_tiles;
-  }
   return launch_umma_gemm(fmt, stage, u, stream);
 }
 
@@ -380,7 +386,7 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
   }
   {
     StageTimer t(ST_GEMM1, stream);
-    rc = umma ? run_umma_stage(fmt, 1, a, E, S, ws, stream, f8, pair, mx4 ? s13_tiles : nullptr, mx4_cap)
+    rc = umma ? run_umma_stage(fmt, 1, a, E, S, ws, stream, f8, pair, mx4 ? s13_tiles : nullptr, mx4_cap, ex.rpe_hint)
                                 : dispatch_stream<1>(fmt, a, plan, stream);
   }
   if (rc) return rc;
@@ -421,14 +427,14 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
     a.Xraw = (const float*)ws.act;
   } else if (fmt == SGLB_FMT_INT8_W8A8) {
     StageTimer t(ST_QUANT_ACT, stream);
-    rc = launch_quant_rows_f32((const float*)ws.act, act_rows, I, ws.actq, ws.acts, stream);
+    rc = launch_quant_rows_f32((const float*)ws.act, act_rows, I, ws.actq, ws.acts, stream, ws.counters, (int)S);
     if (rc) return rc;
     a.X = ws.actq;
     a.Xscale = ws.acts;
     a.row_amax = nullptr;
   } else if (f8) {
     StageTimer t(ST_QUANT_ACT, stream);
-    rc = launch_split_rows_e4m3(ws.act, act_rows, I, ws.actq, ws.actq2, ws.acts, stream);
+    rc = launch_split_rows_e4m3(ws.act, act_rows, I, ws.actq, ws.actq2, ws.acts, stream, ws.counters, (int)S);
     if (rc) return rc;
     a.X = ws.actq;
     a.X2 = ws.actq2;
@@ -437,7 +443,7 @@ static int run_mlp(int path, int fmt, int64_t M, int topk, int E, int H, int I, 
     a.X = ws.act;
   }
   StageTimer t(ST_GEMM2, stream);
-  return umma ? run_umma_stage(fmt, 2, a, E, S, ws, stream, f8, pair, mx4 ? s2_tiles : nullptr, mx4_cap)
+  return umma ? run_umma_stage(fmt, 2, a, E, S, ws, stream, f8, pair, mx4 ? s2_tiles : nullptr, mx4_cap, ex.rpe_hint)
                                 : dispatch_stream<2>(fmt, a, plan2, stream);
 }
 
@@ -609,6 +615,7 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
   ex.limit = p->limit;
   ex.out_by_slot = p->slot_out != nullptr;
   ex.out_map = p->slot_map;
+  ex.rpe_hint = p->rows_per_expert_hint > 0.f ? (double)p->rows_per_expert_hint : 0.0;
   const bool ride = p->shared_w13 != nullptr;
   if (ride) {
     SGLB_CHECK(p->shared_w2 != nullptr, "fused_experts: shared_w13 without shared_w2");
@@ -641,14 +648,14 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     path = auto_path(p, mx4);
   }
   // Decode chain fusion (bit-identical to the separate launches): one prologue launch; at level 2 also the int8 act
-  // quantisation inside the stage-2 producer and the top-k reduce inside the stage-2 kernel.  Not for the CTA-pair
-  // kernels (prefill) and not when the caller reduces the slot rows itself (expert parallel).
-  const bool fuse = g_chain_fusion >= 1 && !p->slot_out && p->M * p->topk <= kFuseMaxSlots && p->H % 8 == 0 &&
+  // quantisation inside the stage-2 producer and the top-k reduce inside the stage-2 kernel (not when the caller
+  // reduces the slot rows itself: expert parallel).  Not for the CTA-pair kernels (prefill).
+  const bool fuse = g_chain_fusion >= 1 && p->M * p->topk <= kFuseMaxSlots && p->H % 8 == 0 &&
                     (path == SGLB_PATH_UMMA || path == SGLB_PATH_STREAM);
   // The reduce moves into the stage-2 kernel where a warp off the critical path can take it: the reducer warp of
   // umma_gemm.cu (bf16 / int8) and the finishing warps of the streaming kernel.  The fp8 / mxfp4 tensor-native kernels
   // keep the separate launch (their epilogue warps promote partial sums all through an item).
-  const bool fuse_reduce = fuse && g_chain_fusion >= 2 && (path == SGLB_PATH_STREAM || p->fmt == SGLB_FMT_BF16 || p->fmt == SGLB_FMT_INT8_W8A8);
+  const bool fuse_reduce = fuse && g_chain_fusion >= 2 && !p->slot_out && (path == SGLB_PATH_STREAM || p->fmt == SGLB_FMT_BF16 || p->fmt == SGLB_FMT_INT8_W8A8);
   ex.fused = fuse;
   ex.fused_reduce = fuse_reduce;
   ex.final_out = p->out;

@@ -11,12 +11,18 @@ namespace sglb {
 template <typename TIN>
 __global__ void __launch_bounds__(256) quant_rows_kernel(const TIN* __restrict__ x, int K,
                                                          int8_t* __restrict__ q,
-                                                         float* __restrict__ scale) {
+                                                         float* __restrict__ scale, const int32_t* __restrict__ n_valid,
+                                                         int always_from, int64_t rows) {
   pdl_wait();
   pdl_trigger();
-  const int64_t row = blockIdx.x;
   __shared__ float warp_max_s[8];
-  quant_row_int8<TIN>(x + row * K, K, q + row * K, scale + row, threadIdx.x, warp_max_s, 0);
+  const int nv = n_valid != nullptr ? *n_valid : 0;
+  for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+    // act rows in expert-sorted order: [*n_valid, always_from) hold nothing (masked slots), see split_rows_e4m3_kernel
+    if (n_valid != nullptr && row >= nv && row < always_from) continue;
+    quant_row_int8<TIN>(x + row * K, K, q + row * K, scale + row, threadIdx.x, warp_max_s, 0);
+    __syncthreads();  // warp_max_s is reused by the next row
+  }
 }
 
 // ---- K5: out[m,:] = sum over the token's valid slots, in slot order j = 0..topk-1 ----------------
@@ -175,8 +181,8 @@ extern "C" int sglb_quant_rows_int8(const void* x_bf16, int64_t rows, int K, int
   SGLB_CHECK(x_bf16 && q && scale, "quant_rows: null pointer");
   SGLB_CHECK(K > 0 && rows >= 0, "quant_rows: bad shape");
   if (rows == 0) return SGLB_OK;
-  SGLB_CUDA(launch_pdl(quant_rows_kernel<__nv_bfloat16>, dim3((unsigned)rows), dim3(256), 0,
-                       (cudaStream_t)stream, (const __nv_bfloat16*)x_bf16, K, q, scale));
+  SGLB_CUDA(launch_pdl(quant_rows_kernel<__nv_bfloat16>, dim3((unsigned)(rows < 16 * 148 ? rows : 16 * 148)), dim3(256), 0,
+                       (cudaStream_t)stream, (const __nv_bfloat16*)x_bf16, K, q, scale, (const int32_t*)nullptr, 0, rows));
   count_launch();
   return SGLB_OK;
 }
@@ -184,9 +190,10 @@ extern "C" int sglb_quant_rows_int8(const void* x_bf16, int64_t rows, int K, int
 namespace sglb {
 // f32 rows (the int8 path keeps silu_and_mul in f32 until it is re-quantised, test_moe_int8.py:84-90)
 int launch_quant_rows_f32(const float* x, int64_t rows, int K, int8_t* q, float* scale,
-                          cudaStream_t stream) {
+                          cudaStream_t stream, const int32_t* n_valid, int always_from) {
   if (rows == 0) return SGLB_OK;
-  SGLB_CUDA(launch_pdl(quant_rows_kernel<float>, dim3((unsigned)rows), dim3(256), 0, stream, x, K, q, scale));
+  SGLB_CUDA(launch_pdl(quant_rows_kernel<float>, dim3((unsigned)(rows < 16 * 148 ? rows : 16 * 148)), dim3(256), 0, stream, x,
+                       K, q, scale, n_valid, always_from, rows));
   count_launch();
   return SGLB_OK;
 }

@@ -8,7 +8,7 @@
 
 namespace sglb {
 
-constexpr int kPrologueMaxAlignBlocks = 8;  // align blocks (1024 slots each) the single-launch prologue handles
+constexpr int kPrologueMaxAlignBlocks = 16;  // align blocks (1024 slots each) the single-launch prologue handles
 
 struct PrologueRows {
   int mode;                 // 0: nothing to prepare (bf16), 1: int8 per-row quantisation, 2: e4m3 hi / lo split

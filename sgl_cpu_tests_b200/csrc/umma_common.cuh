@@ -551,4 +551,20 @@ int weight_tensor_map(const void* W, uint64_t kbytes, uint64_t rows, uint64_t E,
 int rows_tensor_map(const void* X, uint64_t kbytes, uint64_t rows, uint32_t box_rows, CUtensorMap* out);
 int sm_count();
 
+// Persistent grid of the tcgen05 kernels: one CTA per SM, at most one per work item.  In the weight-streaming regime
+// (capi.cu sets est_items only there) every item costs the same, so the grid is sized to WHOLE WAVES of the expected
+// item count -- Qwen3 w13 at M = 128 is 768 items: 128 CTAs x 6 instead of 148 CTAs x 5.2; an expert-parallel rank of
+// 8 streams DeepSeek-V3's w13 as 512 items: 128 CTAs x 4 instead of 148 x 3.46.  Measured (SGLB_GRID experiment,
+// DESIGN 4a): 96..148 CTAs stream at the same rate, the partial last wave costs its full length.
+inline int persistent_grid(int64_t max_items, int64_t est_items) {
+  const int sms = sm_count();
+  int grid = (int)(max_items < sms ? (max_items > 0 ? max_items : 1) : sms);
+  if (est_items > 0) {
+    const int64_t waves = (est_items + sms - 1) / sms;
+    const int64_t even = (est_items + waves - 1) / waves;
+    if (even < grid && even >= (sms * 3) / 4) grid = (int)even;
+  }
+  return grid;
+}
+
 }  // namespace sglb

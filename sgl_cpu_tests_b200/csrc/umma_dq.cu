@@ -330,7 +330,7 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   }
   const int n_blocks = STAGE == 1 ? ceil_div(a.N, kWSub) : ceil_div(a.N, 2 * kWSub);
   const int64_t max_items = (int64_t)a.max_tiles * n_blocks;
-  const int grid = (int)(max_items < sm_count() ? (max_items > 0 ? max_items : 1) : sm_count());
+  const int grid = persistent_grid(max_items, (int64_t)a.est_tiles * n_blocks);
   SGLB_CUDA(launch_pdl(umma_dq_kernel<FMT, STAGE>, dim3(grid), dim3(kThreads), smem_bytes<FMT>(), stream, map, a));
   return SGLB_OK;
 }

@@ -364,14 +364,22 @@ __global__ void __launch_bounds__(kThreads, 1)
 }
 
 // ---- bf16 rows -> (hi, lo) e4m3 pieces + per-row power-of-two factor: one CTA per row (rowops.cuh) ----
+// n_valid / always_from (act rows in expert-sorted order): rows [*n_valid, always_from) hold nothing -- masked slots
+// sort behind the valid ones (an expert-parallel rank sees world x cap slots of which ~1/world are its own) -- and are
+// skipped; rows from always_from on are the riding shared expert's.
 __global__ void __launch_bounds__(256) split_rows_e4m3_kernel(const __nv_bfloat16* __restrict__ x, int K,
                                                               uint8_t* __restrict__ hi, uint8_t* __restrict__ lo,
-                                                              float* __restrict__ rexp) {
+                                                              float* __restrict__ rexp, const int32_t* __restrict__ n_valid,
+                                                              int always_from, int64_t rows) {
   pdl_wait();
   pdl_trigger();
-  const int64_t row = blockIdx.x;
   __shared__ float warp_max_s[8];
-  split_row_e4m3(x + row * K, K, hi + row * K, lo + row * K, rexp + row, threadIdx.x, warp_max_s, 0);
+  const int nv = n_valid != nullptr ? *n_valid : 0;
+  for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+    if (n_valid != nullptr && row >= nv && row < always_from) continue;
+    split_row_e4m3(x + row * K, K, hi + row * K, lo + row * K, rexp + row, threadIdx.x, warp_max_s, 0);
+    __syncthreads();  // warp_max_s is reused by the next row
+  }
 }
 
 template <int STAGE>
@@ -391,7 +399,7 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   }
   const int n_blocks = STAGE == 1 ? ceil_div(a.N, kWSub) : ceil_div(a.N, 2 * kWSub);
   const int64_t max_items = (int64_t)a.max_tiles * n_blocks;
-  const int grid = (int)(max_items < sm_count() ? (max_items > 0 ? max_items : 1) : sm_count());
+  const int grid = persistent_grid(max_items, (int64_t)a.est_tiles * n_blocks);
   SGLB_CUDA(launch_pdl(umma_f8_kernel<STAGE>, dim3(grid), dim3(kThreads), kSmemBytes, stream, map, map_sh, a));
   return SGLB_OK;
 }
@@ -409,11 +417,14 @@ int launch_umma_f8(int stage, const UmmaArgs& a, cudaStream_t stream) {
 }
 
 int launch_split_rows_e4m3(const void* x_bf16, int64_t rows, int K, void* hi, void* lo, float* rexp,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, const int32_t* n_valid, int always_from) {
   SGLB_CHECK(K % 8 == 0, "split_rows_e4m3: K must be a multiple of 8 (K=%d)", K);
   if (rows == 0) return SGLB_OK;
-  SGLB_CUDA(launch_pdl(split_rows_e4m3_kernel, dim3((unsigned)rows), dim3(256), 0, stream,
-                       (const __nv_bfloat16*)x_bf16, K, (uint8_t*)hi, (uint8_t*)lo, rexp));
+  // one CTA per row up to 16 waves of the machine, then rows are strided (an expert-parallel rank launches over
+  // world x cap x topk slots of which ~1/world hold a row)
+  const int64_t grid = rows < 16 * 148 ? rows : 16 * 148;
+  SGLB_CUDA(launch_pdl(split_rows_e4m3_kernel, dim3((unsigned)grid), dim3(256), 0, stream,
+                       (const __nv_bfloat16*)x_bf16, K, (uint8_t*)hi, (uint8_t*)lo, rexp, n_valid, always_from, rows));
   count_launch();
   return SGLB_OK;
 }

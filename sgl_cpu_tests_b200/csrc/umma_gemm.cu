@@ -323,16 +323,7 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   }
   const int n_blocks = STAGE == 1 ? ceil_div(a.N, kWSub) : ceil_div(a.N, 2 * kWSub);
   const int64_t max_items = (int64_t)a.max_tiles * n_blocks;
-  int grid = (int)(max_items < sm_count() ? (max_items > 0 ? max_items : 1) : sm_count());
-  // Weight-streaming regime (capi.cu sets est_tiles only there): every item costs the same, so the grid is
-  // sized to whole waves -- Qwen3 w13 at M = 128 is 768 items: 128 CTAs x 6 instead of 148 CTAs x 5.2.  Measured
-  // (SGLB_GRID experiment): 96..148 CTAs stream at the same rate, the partial last wave costs 2-4 %.
-  if (a.est_tiles > 0) {
-    const int64_t items = (int64_t)a.est_tiles * n_blocks;
-    const int64_t waves = (items + sm_count() - 1) / sm_count();
-    const int64_t even = (items + waves - 1) / waves;
-    if (even < grid && even >= (sm_count() * 3) / 4) grid = (int)even;
-  }
+  int grid = persistent_grid(max_items, (int64_t)a.est_tiles * n_blocks);  // whole waves in the streaming regime
   static const int forced_grid = [] {
     const char* e = getenv("SGLB_GRID");  // experiments: persistent grid size
     return e ? atoi(e) : 0;

@@ -73,6 +73,6 @@ int launch_umma_mx4(int stage, const UmmaArgs& a, cudaStream_t stream);
 size_t mx4_scale_tiles_bytes(int64_t E, int rows, int split, int K);
 int launch_mx4_tile_scales(const void* src, void* dst, int64_t E, int rows, int split, int K, cudaStream_t stream);
 int launch_split_rows_e4m3(const void* x_bf16, int64_t rows, int K, void* hi, void* lo, float* rexp,
-                           cudaStream_t stream);
+                           cudaStream_t stream, const int32_t* n_valid = nullptr, int always_from = 0);
 
 }  // namespace sglb

@@ -229,20 +229,32 @@ class PeerExchange:
         except Exception:  # interpreter shutdown
             pass
 
-    def enqueue(self, x, tw, ids, E, backend, par, rsf=1.0, out=None, hint=0.0):
-        """dispatch -> (shared expert on a side stream) -> wait -> local experts into y -> combine, all
-        asynchronous on the current stream; `par` selects the buffer set."""
+    def start_shared(self, x, backend):
+        """Forks the replicated shared expert's MLP onto the side stream at THIS point of the current stream.  It needs
+        nothing but the local hidden states, so a caller that also routes (GraphedEP) forks it before the router: the
+        router, the dispatch kernel and the flag wait keep only a few SMs busy for ~120 us (2 x B200, r2g), which is
+        about what the shared MLP of 256 tokens takes; forked after the dispatch (round 2's first version) most of it
+        ran behind the persistent expert kernels and showed up as combine time (8 GPUs, r2r: combine 186 us)."""
+        if backend.shared is None or x.shape[0] == 0:
+            return None
+        self.side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.side):
+            return backend.shared_mlp(x)
+
+    _NOT_STARTED = object()
+
+    def enqueue(self, x, tw, ids, E, backend, par, rsf=1.0, out=None, hint=0.0, shared_y=_NOT_STARTED):
+        """(shared expert on a side stream) -> dispatch -> wait -> local experts into y -> combine, all
+        asynchronous on the current stream; `par` selects the buffer set.  shared_y: the result of an earlier
+        start_shared() on this stream, else the fork happens here."""
         lib = L.load()
         main = torch.cuda.current_stream()
         s = main.cuda_stream
         M = x.shape[0]
+        if shared_y is PeerExchange._NOT_STARTED:
+            shared_y = self.start_shared(x, backend)
         L.check(lib.sglb_ep_p2p_dispatch(ops._ptr(x), ops._ptr(ids), ops._ptr(tw), M, self.topk, E, self.world,
                                          self.rank, self.H, self.cap, self.peers, par, s))
-        shared_y = None
-        if backend.shared is not None and M > 0:   # overlaps the exchange and the routed experts
-            self.side.wait_stream(main)
-            with torch.cuda.stream(self.side):
-                shared_y = backend.shared_mlp(x)
         L.check(lib.sglb_ep_p2p_wait_dispatch(self.base, self.world, self.cap, self.H, self.topk, s))
         backend.experts_into(self.recv_x[par], self.recv_tw[par], self.recv_ids[par], self.y[par], hint)
         if out is None:
@@ -288,9 +300,11 @@ class GraphedEP:
         self.graphs = [None, None]
 
         def enqueue(par):
+            shared_y = px.start_shared(self.hidden, B)   # under the router and the exchange
             if router is not None:
                 router(self.gating, self.topk_weights, self.topk_ids)
-            px.enqueue(self.hidden, self.topk_weights, self.topk_ids, layer.E, B, par, layer.rsf, self.out, hint)
+            px.enqueue(self.hidden, self.topk_weights, self.topk_ids, layer.E, B, par, layer.rsf, self.out, hint,
+                       shared_y=shared_y)
 
         with torch.cuda.device(device):
             key = (device.index, cap_stream.cuda_stream)

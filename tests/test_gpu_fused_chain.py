@@ -168,9 +168,9 @@ def test_fused_chain_graph_replay_and_repeatability(K):
 
 def test_many_align_blocks_in_the_prologue(K):
     """M * topk > 1024: the prologue's align blocks count each other's slots themselves (no align_count launch)."""
-    E, topk, H, I, M = 64, 8, 512, 256, 1000   # 8000 slots -> 8 align blocks
+    E, topk, H, I = 64, 8, 512, 256
     dev = torch.device("cuda", 0)
-    for fmt in ("bf16", "int8"):
+    for fmt, M in (("bf16", 1000), ("int8", 1000), ("fp8", 2000)):   # 8000 / 16000 slots -> 8 / 16 align blocks
         w, fid, g = weights(fmt, E, H, I, 13)
         x = (torch.randn(M, H, device=dev, generator=g) / 8).bfloat16()
         tw, ids = routing(M, E, topk, g, dev)
