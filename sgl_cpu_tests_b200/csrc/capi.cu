@@ -34,6 +34,7 @@ struct StageEvents {
 static bool g_profile = false;
 static bool g_mx4_native = true;  // mxfp4: block-scaled tensor-native kernel (umma_mx4.cu) when scale tiles are given
 static bool g_f8_native = true;  // fp8: tensor-native kernel (umma_f8.cu) vs dequantising kernel (umma_dq.cu)
+static bool g_f8_small_tiles = true;  // fp8 decode: 32-row tiles on the deep-ring configuration (SGLB_F8_SMALL_TILES=0: off)
 // Decode chain fusion level (sglb_set_chain_fusion).  1 (default): align + stage-1 operand preparation in ONE prologue
 // launch.  2: also the int8 act quantisation inside the stage-2 producer and the top-k reduce inside the stage-2 kernel
 // (3 launches per call) -- bit-identical, but measured SLOWER on B200 (gpurun r2n: Qwen3 int8 M = 128 step 0.130 ->
@@ -256,7 +257,9 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.E = E;
   u.topk = sa.topk;
   u.gather = sa.gather;
-  u.max_tiles = (int)max_items(S, E, mx4_tiles ? mx4_cap : (pair ? umma2_tile_rows() : kTileRows));
+  // mx4_cap: row capacity of the tiles when it is not the default (mxfp4 kernel: 16..112; fp8 deep-ring variant: 32)
+  const int tile_cap = mx4_cap > 0 ? mx4_cap : (pair ? umma2_tile_rows() : kTileRows);
+  u.max_tiles = (int)max_items(S, E, tile_cap);
   u.block_n = sa.block_n;
   u.block_k = sa.block_k;
   u.scale_cols = sa.scale_cols;
@@ -277,7 +280,7 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.red = sa.red;
   u.row_amax = sa.row_amax;
   u.Xraw = sa.Xraw;
-  const int sh_tiles = sa.Wsh ? (int)ceil_div64(S / sa.topk, kTileRows) : 0;
+  const int sh_tiles = sa.Wsh ? (int)ceil_div64(S / sa.topk, tile_cap) : 0;
   u.max_tiles += sh_tiles;
   if (!pair) {
     // Expected number of tiles when the call is weight-streaming bound (up to 64 rows per active expert: every item
@@ -288,8 +291,7 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
     double active = E == 1 ? 1.0 : E * (1.0 - exp(-rpe));
     if (active < 1) active = 1;
     const double rows_active = rpe * E / active;
-    const int cap = mx4_tiles ? mx4_cap : kTileRows;
-    if (rows_active <= 64.0) u.est_tiles = (int)(active * ceil(rows_active / cap) + 0.5) + sh_tiles;
+    if (rows_active <= 64.0) u.est_tiles = (int)(active * ceil(rows_active / tile_cap) + 0.5) + sh_tiles;
   }
   if (mx4_tiles) return launch_umma_mx4(stage, u, stream);
   if (f8_native) return pair ? launch_umma2_f8(stage, u, stream) : launch_umma_f8(stage, u, stream);
@@ -528,7 +530,10 @@ extern "C" int sglb_profile_read(float* ms_out, int* calls_out, int n) {
   return SGLB_OK;
 }
 
-extern "C" void sglb_set_fp8_native(int on) { g_f8_native = on != 0; }
+extern "C" void sglb_set_fp8_native(int on) {
+  g_f8_native = (on & 1) != 0;
+  g_f8_small_tiles = (on & 2) == 0;  // bit 1 set: keep 128-row tiles at decode too (A/B experiments, parity tests)
+}
 extern "C" void sglb_set_chain_fusion(int level) { g_chain_fusion = level < 0 ? 0 : (level > 2 ? 2 : level); }
 extern "C" void sglb_set_mx4_native(int on) { g_mx4_native = on != 0; }
 extern "C" size_t sglb_mx4_scale_tiles_bytes(int64_t E, int rows, int split, int K) {
@@ -669,7 +674,16 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     SGLB_CHECK(path == SGLB_PATH_UMMA || !ex.any(),
                "fused_experts: the CTA-pair tcgen05 path has no expert bias / clamped swiglu / slot-addressed output");
     const bool use_mx4 = mx4 && path == SGLB_PATH_UMMA;
-    const int tile_rows = use_mx4 ? mx4_cap : (path == SGLB_PATH_UMMA2 ? umma2_tile_rows() : kTileRows);
+    // fp8 tensor-native kernel, decode: 32-row tiles run the deep-ring configuration (umma_f8.cu F8Cfg<32>) -- when an
+    // expert practically never gets more rows (Poisson(12) > 32: 1e-6; a longer expert is split and streams twice) and
+    // a riding shared expert fits one tile
+    const bool f8n = p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k);
+    const int f8_cap = (path == SGLB_PATH_UMMA && f8n && g_f8_small_tiles && rows_per_expert <= 12.0 &&
+                        (!ride || p->M <= umma_f8_small_tile_rows()))
+                           ? umma_f8_small_tile_rows()
+                           : 0;
+    const int cap_arg = use_mx4 ? mx4_cap : f8_cap;
+    const int tile_rows = cap_arg > 0 ? cap_arg : (path == SGLB_PATH_UMMA2 ? umma2_tile_rows() : kTileRows);
     if (fuse) {
       const bool f8 = use_mx4 || (p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k));
       const int mode = p->fmt == SGLB_FMT_INT8_W8A8 ? 1 : (f8 ? 2 : 0);
@@ -682,7 +696,7 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     if (rc) return rc;
     rc = run_mlp(path, p->fmt, p->M, p->topk, p->E, p->H, p->I, p->hidden, p->w13, p->w2,
                  p->w13_scale, p->w2_scale, p->block_n, p->block_k, p->topk_weights, ws, stage2_out, stream,
-                 use_mx4 ? p->w13_scale_tiles : nullptr, use_mx4 ? p->w2_scale_tiles : nullptr, mx4_cap, ex);
+                 use_mx4 ? p->w13_scale_tiles : nullptr, use_mx4 ? p->w2_scale_tiles : nullptr, cap_arg, ex);
     if (rc) return rc;
   } else {
     StreamPlan plan = make_plan(p->M, p->topk, p->E, p->I, 1);

@@ -87,36 +87,59 @@ __device__ __forceinline__ float sigmoid_f64(float x) {
 
 // PER = ceil(E/32) rounded up to a compiled size.  Lane l owns experts l, l+32, ...
 template <int PER, typename TG, typename TB, bool BIASED>
-__global__ void __launch_bounds__(128) router_kernel(const TG* __restrict__ gating,
+__global__ void __launch_bounds__(256) router_kernel(const TG* __restrict__ gating,
                                                     const TB* __restrict__ bias, int64_t M, int E,
                                                     int topk, int G, int topk_group, int renorm,
                                                     int n_shared, float routed_scale,
                                                     const void* __restrict__ non_padded, int non_padded_i64,
                                                     float* __restrict__ out_w,
-                                                    int32_t* __restrict__ out_id) {
-  const int lane = threadIdx.x & 31;
-  const int64_t tok = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (tok >= M) return;
-  if (non_padded != nullptr) {
+                                                    int32_t* __restrict__ out_id, int wpt) {
+  // wpt = warps per token.  The f64 sigmoid is ~120 f64 instructions and the f64 pipe issues one warp instruction in
+  // ~35 clk per scheduler (measured: one warp with 8 sigmoids per lane = 18 us, whatever M), so at decode sizes a
+  // token's experts are spread over wpt warps of the block (each lane evaluates PER / wpt sigmoids, values meet in
+  // shared memory) and warp 0 of the token runs the selection on exactly the values the one-warp form computes.
+  extern __shared__ float sig_sm[];  // [tokens per block][E], wpt > 1 only
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const bool multi = BIASED && wpt > 1;
+  const int tpb = multi ? (int)(blockDim.x >> 5) / wpt : (int)(blockDim.x >> 5);
+  const int slot = multi ? warp / wpt : warp, sub = multi ? warp % wpt : 0;
+  const int64_t tok = (int64_t)blockIdx.x * tpb + slot;
+  bool padded = false;
+  if (tok < M && non_padded != nullptr) {
     const int64_t n_valid = non_padded_i64 ? *reinterpret_cast<const int64_t*>(non_padded)
                                            : (int64_t) * reinterpret_cast<const int32_t*>(non_padded);
-    if (tok >= n_valid) {  // padded row: every slot masked
-      if (lane < topk) {
-        out_w[tok * topk + lane] = 0.f;
-        out_id[tok * topk + lane] = -1;
-      }
-      return;
-    }
+    padded = tok >= n_valid;
   }
-  const TG* row = gating + tok * E;
   const float NEG = -INFINITY;
-
   float s[PER];  // weight source: softmax prob or sigmoid
   float c[PER];  // choice score
+  if (tok < M && !padded) {
+    const TG* row = gating + tok * E;
 #pragma unroll
-  for (int k = 0; k < PER; ++k) {
-    int e = lane + 32 * k;
-    s[k] = (e < E) ? load_as_float<TG>(row + e) : NEG;
+    for (int k = 0; k < PER; ++k) {
+      int e = lane + 32 * k;
+      s[k] = (e < E) ? load_as_float<TG>(row + e) : NEG;
+    }
+  }
+  if (multi) {
+    if (tok < M && !padded) {
+      const int per_w = PER / wpt;  // host guarantees PER % wpt == 0
+#pragma unroll
+      for (int k = 0; k < PER; ++k) {
+        const int e = lane + 32 * k;
+        if (k / per_w == sub && e < E) sig_sm[slot * E + e] = sigmoid_f64(s[k]);
+      }
+    }
+    __syncthreads();
+    if (sub != 0) return;
+  }
+  if (tok >= M) return;
+  if (padded) {  // padded row: every slot masked
+    if (lane < topk) {
+      out_w[tok * topk + lane] = 0.f;
+      out_id[tok * topk + lane] = -1;
+    }
+    return;
   }
   if (!BIASED) {
     float mx = NEG;
@@ -141,7 +164,7 @@ __global__ void __launch_bounds__(128) router_kernel(const TG* __restrict__ gati
     for (int k = 0; k < PER; ++k) {
       int e = lane + 32 * k;
       if (e < E) {
-        s[k] = sigmoid_f64(s[k]);  // bit-reproducible on the CPU: see the file header
+        s[k] = multi ? sig_sm[slot * E + e] : sigmoid_f64(s[k]);  // bit-reproducible on the CPU: see the file header
         c[k] = s[k] + load_as_float<TB>(bias + e);
       } else {
         s[k] = 0.f;
@@ -152,15 +175,21 @@ __global__ void __launch_bounds__(128) router_kernel(const TG* __restrict__ gati
 
   // ---- group scores: lane g ends up holding the score of group g (G <= 32) ----
   const int gs = E / G;
+  // group of each expert this lane owns, computed once: an integer division by a run-time value is ~25 dependent
+  // instructions, and the kernel is one long dependency chain per warp (ncu r2x: 970 warp instructions at 16 clk each)
+  int grp[PER];
+#pragma unroll
+  for (int k = 0; k < PER; ++k) grp[k] = (lane + 32 * k) / gs;
   uint32_t group_mask = 0xffffffffu;
   if (G > 1 && topk_group < G) {
     float my_group_score = NEG;
+#pragma unroll 4  // the butterflies of different groups are independent: let them overlap
     for (int g = 0; g < G; ++g) {
       float m1 = NEG, m2 = NEG;  // top-2 of the group (biased) / max (softmax)
 #pragma unroll
       for (int k = 0; k < PER; ++k) {
         int e = lane + 32 * k;
-        if (e < E && e / gs == g) {
+        if (e < E && grp[k] == g) {
           float v = c[k];
           if (v > m1) {
             m2 = m1;
@@ -201,7 +230,7 @@ __global__ void __launch_bounds__(128) router_kernel(const TG* __restrict__ gati
   for (int k = 0; k < PER; ++k) {
     int e = lane + 32 * k;
     taken[k] = !(e < E);
-    if (e < E && !((group_mask >> (e / gs)) & 1u)) c[k] = BIASED ? NEG : 0.0f;
+    if (e < E && !((group_mask >> grp[k]) & 1u)) c[k] = BIASED ? NEG : 0.0f;
   }
 
   // ---- top-k by repeated warp argmax ----
@@ -255,13 +284,22 @@ static int launch_router(const void* gating, const void* bias, int64_t M, int E,
                          int topk_group, int renorm, int n_shared, float routed_scale,
                          const void* non_padded, int non_padded_i64, float* out_w,
                          int32_t* out_id, cudaStream_t stream) {
-  const int warps = 4;
-  dim3 grid((unsigned)ceil_div64(M, warps)), block(warps * 32);
   const int per = ceil_div(E, 32);
+  const int per_c = per <= 1 ? 1 : (per <= 2 ? 2 : (per <= 4 ? 4 : (per <= 8 ? 8 : (per <= 16 ? 16 : 32))));  // compiled PER
+  // biased router at decode sizes: up to 8 warps per token (see the kernel), as long as ~2048 warps are not exceeded
+  int wpt = 1;
+  if (BIASED) {
+    wpt = 8;
+    while (wpt > 1 && (M * wpt > 2048 || per_c % wpt != 0)) wpt /= 2;
+  }
+  const int warps = wpt > 1 ? 8 : 4;
+  const int tpb = warps / wpt;
+  dim3 grid((unsigned)ceil_div64(M, tpb)), block(warps * 32);
+  const size_t smem = wpt > 1 ? sizeof(float) * tpb * E : 0;
 #define SGLB_ROUTER_CASE(P)                                                                      \
-  router_kernel<P, TG, TB, BIASED><<<grid, block, 0, stream>>>(                                  \
+  router_kernel<P, TG, TB, BIASED><<<grid, block, smem, stream>>>(                               \
       (const TG*)gating, (const TB*)bias, M, E, topk, G, topk_group, renorm, n_shared, routed_scale, \
-      non_padded, non_padded_i64, out_w, out_id)
+      non_padded, non_padded_i64, out_w, out_id, wpt)
   if (per <= 1) SGLB_ROUTER_CASE(1);
   else if (per <= 2) SGLB_ROUTER_CASE(2);
   else if (per <= 4) SGLB_ROUTER_CASE(4);

@@ -39,12 +39,22 @@ using namespace ummak;
 
 namespace {
 
-constexpr int kStages = 3;
-constexpr int kStageBytes = 2 * kWTileBytes + 2 * kXTileBytes;  // 64 KB: W gate/up + X hi + X lo
+// Two shared-memory configurations (template parameter XROWS = routed rows an operand slot holds = row capacity of the
+// tiles moe_align hands out):
+//   XROWS = 128: stage = W gate/up 32 KB + X hi + X lo 2 x 16 KB = 64 KB, 3 stages (prefill and general decode)
+//   XROWS = 32:  stage = 32 KB + 2 x 4 KB = 40 KB, 5 stages: 160 KB instead of 96 KB of weight bytes in flight per SM.
+// At ~2.2 us of loaded HBM latency 96 KB in flight is ~43 GB/s per SM -- enough when all 148 SMs stream, the cap when a
+// decode call has fewer work items than SMs (DeepSeek-V3 at M = 1: 144 items); capi.cu picks 32 when tiles are small.
+template <int XROWS>
+struct F8Cfg {
+  static constexpr int kXBytes = XROWS * kRowBytes;
+  static constexpr int kStages = XROWS == 128 ? 3 : 5;
+  static constexpr int kStageBytes = 2 * kWTileBytes + 2 * kXBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBufBytes + 1024 + 256;
+};
 constexpr int kGatherThreadsF8 = 64;
 constexpr int kFirstEpiWarp = 4;
 constexpr int kThreads = (kFirstEpiWarp + kEpiWarps) * 32;  // 384
-constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBufBytes + 1024 + 256;
 constexpr int kProducerRegs = 56, kEpilogueRegs = 216;  // 128*56 + 256*216 <= 384*168
 
 __device__ __forceinline__ void umma_f8(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
@@ -60,10 +70,12 @@ __device__ __forceinline__ uint32_t instr_desc_f8(int n) {
   return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kWSub >> 4) << 24);
 }
 
-template <int STAGE>
+template <int STAGE, int XROWS>
 __global__ void __launch_bounds__(kThreads, 1)
     umma_f8_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_sh,
                    const UmmaArgs a) {
+  constexpr int kStages = F8Cfg<XROWS>::kStages, kStageBytes = F8Cfg<XROWS>::kStageBytes;
+  constexpr int kXTileBytes = F8Cfg<XROWS>::kXBytes;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t epi_base = smem_base + kStages * kStageBytes;
@@ -187,9 +199,9 @@ __global__ void __launch_bounds__(kThreads, 1)
       for (int w = blockIdx.x; w < total; w += gridDim.x) {
         const WorkItem wi = get_item(a, w, n_blocks);
         const int n_eff = (wi.rows + 15) & ~15;
-        uint32_t off[16];
+        uint32_t off[XROWS / 8];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
+        for (int j = 0; j < XROWS / 8; ++j) {
           const int r = rbase + 8 * j;
           const int p = wi.row_start + min(r, wi.rows - 1);
           const int xr = a.gather ? (a.sorted_slot[p] / a.topk) : p;
@@ -200,7 +212,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           mbar_wait(empty_bar(s), ((it / kStages) & 1) ^ 1);
           const uint32_t dh = xh_tile(s) + dst0, dl = xl_tile(s) + dst0;
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
+          for (int j = 0; j < XROWS / 8; ++j) {
             if (rbase + 8 * j < n_eff) {
               cp_async16(dh + j * 8 * kRowBytes, xh + off[j] + kb * kRowBytes);
               cp_async16(dl + j * 8 * kRowBytes, xl + off[j] + kb * kRowBytes);
@@ -382,8 +394,9 @@ __global__ void __launch_bounds__(256) split_rows_e4m3_kernel(const __nv_bfloat1
   }
 }
 
-template <int STAGE>
+template <int STAGE, int XROWS>
 int launch_one(const UmmaArgs& a, cudaStream_t stream) {
+  constexpr int kSmemBytes = F8Cfg<XROWS>::kSmemBytes;
   CUtensorMap map;
   int rc = weight_tensor_map(a.W, (uint64_t)a.K, (uint64_t)a.rows_per_expert, (uint64_t)a.E, kRowBytes, kWSub, 1, &map);
   if (rc) return rc;
@@ -394,13 +407,13 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   }
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
-    SGLB_CUDA(cudaFuncSetAttribute(umma_f8_kernel<STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    SGLB_CUDA(cudaFuncSetAttribute(umma_f8_kernel<STAGE, XROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr_set = true;
   }
   const int n_blocks = STAGE == 1 ? ceil_div(a.N, kWSub) : ceil_div(a.N, 2 * kWSub);
   const int64_t max_items = (int64_t)a.max_tiles * n_blocks;
   const int grid = persistent_grid(max_items, (int64_t)a.est_tiles * n_blocks);
-  SGLB_CUDA(launch_pdl(umma_f8_kernel<STAGE>, dim3(grid), dim3(kThreads), kSmemBytes, stream, map, map_sh, a));
+  SGLB_CUDA(launch_pdl(umma_f8_kernel<STAGE, XROWS>, dim3(grid), dim3(kThreads), kSmemBytes, stream, map, map_sh, a));
   return SGLB_OK;
 }
 
@@ -410,8 +423,13 @@ int umma_f8_supported(int H, int I, int block_n, int block_k) {
   return H % kRowBytes == 0 && I % kRowBytes == 0 && block_k % kRowBytes == 0 && block_n % 32 == 0;
 }
 
+int umma_f8_small_tile_rows() { return 32; }
+
+// a.tile_cap: row capacity of the tiles in tile_list -- 0 / 128 (general) or umma_f8_small_tile_rows() (deep ring)
 int launch_umma_f8(int stage, const UmmaArgs& a, cudaStream_t stream) {
-  int rc = stage == 1 ? launch_one<1>(a, stream) : launch_one<2>(a, stream);
+  int rc;
+  if (a.tile_cap == 32) rc = stage == 1 ? launch_one<1, 32>(a, stream) : launch_one<2, 32>(a, stream);
+  else rc = stage == 1 ? launch_one<1, 128>(a, stream) : launch_one<2, 128>(a, stream);
   if (rc == SGLB_OK) count_launch();
   return rc;
 }

@@ -195,3 +195,50 @@ def test_mxfp4_scale_tiles_are_built_once(K):
         counts.append(K.launch_count() - n0)
     assert counts[1] == counts[2] <= 5, counts   # prologue, w13, split, w2, reduce
     assert counts[0] >= counts[1]
+
+
+@pytest.mark.parametrize("M", [1, 16, 40])
+def test_fp8_small_tile_deep_ring_is_bit_identical(K, M):
+    """fp8 decode takes 32-row tiles on a 5-stage ring (umma_f8.cu F8Cfg<32>) when experts get few rows; the per-row
+    arithmetic does not depend on the tile a row lands in, so the result equals the 128-row configuration bit for bit
+    -- also when one expert receives more than 32 rows and is split into several tiles."""
+    from sgl_cpu_tests_b200 import _lib as L
+    E, topk, H, I = 16, 4, 1024, 512
+    dev = torch.device("cuda", 0)
+    w, fid, g = weights("fp8", E, H, I, 31)
+    x = (torch.randn(M, H, device=dev, generator=g) / 8).bfloat16()
+    tw, ids = routing(M, E, topk, g, dev)
+    skew = ids.clone()
+    skew[:, 0] = 3                                       # expert 3 takes a row of every token: 40 rows > 32
+    skew[:, 1:] = torch.where(skew[:, 1:] == 3, torch.full_like(skew[:, 1:], 4), skew[:, 1:])
+    lib = L.load()
+    for case in (ids, skew):
+        try:
+            lib.sglb_set_fp8_native(3)                   # 128-row tiles
+            ref = run(K, x, w, fid, tw, case, K.PATH_UMMA)
+            lib.sglb_set_fp8_native(1)                   # default: 32-row tiles where rows per expert <= 12
+            out = run(K, x, w, fid, tw, case, K.PATH_UMMA)
+        finally:
+            lib.sglb_set_fp8_native(1)
+        assert torch.isfinite(ref.float()).all() and ref.float().abs().max() > 0
+        assert torch.equal(out, ref), (out.float() - ref.float()).abs().max()
+
+
+def test_fp8_small_tiles_with_riding_shared_expert(K):
+    from sgl_cpu_tests_b200 import _lib as L
+    from test_gpu_layer import build
+    E, topk, H, I, M = 16, 4, 1024, 512, 20
+    dev = torch.device("cuda", 0)
+    layer, *_ = build(K, "fp8", E, topk, H, I, I, 11, True, path=K.PATH_UMMA)
+    g = torch.Generator(device=dev).manual_seed(5)
+    x = (torch.randn(M, H, device=dev, generator=g) / 16).bfloat16()
+    gating = torch.randn(M, E, device=dev, generator=g).bfloat16()
+    lib = L.load()
+    try:
+        lib.sglb_set_fp8_native(3)
+        ref = layer.forward(x, gating)
+        lib.sglb_set_fp8_native(1)
+        out = layer.forward(x, gating)
+    finally:
+        lib.sglb_set_fp8_native(1)
+    assert torch.equal(out, ref), (out.float() - ref.float()).abs().max()
