@@ -105,10 +105,50 @@ def _to_host(dev_tensor):
     return dev_tensor.cpu()
 
 
+# ---- first upload of a large pageable host tensor (weights): pipelined through two pinned staging buffers ------
+# `tensor.to(device)` from pageable memory runs at ~8 GB/s (the driver stages through a small internal buffer on one
+# thread); a multi-threaded memcpy into pinned memory (torch's parallel CPU copy) overlapped with the DMA of the previous
+# chunk reaches PCIe rate.  DeepSeek-V3's 11.3 GB layer, or the 84 GB of weight clones bench_moe.py touches once.
+_STAGE_BYTES = 64 << 20
+_UPLOAD_MIN_BYTES = 256 << 20
+_stage = {}
+
+
+def _upload_staged(t, dev):
+    src = t.detach().contiguous().view(torch.uint8).reshape(-1)
+    n = src.numel()
+    dst = torch.empty(t.shape, dtype=t.dtype, device=dev)
+    dflat = dst.view(torch.uint8).reshape(-1)
+    if "buf" not in _stage:
+        _stage["buf"] = [torch.empty(_STAGE_BYTES, dtype=torch.uint8, pin_memory=True) for _ in range(2)]
+        _stage["ev"] = [None, None]
+    bufs, evs = _stage["buf"], _stage["ev"]
+    with _launch_lock:
+        for i, o in enumerate(range(0, n, _STAGE_BYTES)):
+            m = min(_STAGE_BYTES, n - o)
+            b = i & 1
+            if evs[b] is not None:
+                evs[b].synchronize()      # the DMA that read this staging buffer has finished
+            bufs[b][:m].copy_(src[o:o + m])
+            dflat[o:o + m].copy_(bufs[b][:m], non_blocking=True)
+            evs[b] = torch.cuda.Event()
+            evs[b].record()
+        for e in evs:
+            if e is not None:
+                e.synchronize()
+    return dst
+
+
 def _to_dev(t, dev, dtype=None):
     if t is None:
         return None
     if t.device != dev:
+        if (_PIN_HOST and t.device.type == "cpu" and _nbytes(t) >= _UPLOAD_MIN_BYTES and t.is_contiguous()
+                and not t.is_pinned()):
+            t = _upload_staged(t, dev)
+            if dtype is not None and t.dtype != dtype:
+                t = t.to(dtype)
+            return t
         _maybe_pin(t)
         # pinned host memory: stream-ordered async copy (every entry point ends with a blocking D2H of
         # its result or returns device tensors ordered on the same stream, so the source stays valid)
@@ -190,6 +230,11 @@ def _registry_drop(key):
     if ent is not None:
         _registry_bytes -= _nbytes(ent[1])
         _registry_host_bytes -= ent[2]
+        # a cached host-tensor graph keeps the device tensors it was captured over alive: evicting a weight must take
+        # its graphs along, or the cap above bounds nothing (bench_moe.py: 60 weight sets, 169 GB held by graphs)
+        ptr = ent[1].data_ptr()
+        for gk in [gk for gk in _host_graphs if ptr in gk[3:7]]:
+            _host_graphs.pop(gk, None)
 
 
 def _registry_get(key, t=None):

@@ -242,3 +242,18 @@ def test_fp8_small_tiles_with_riding_shared_expert(K):
     finally:
         lib.sglb_set_fp8_native(1)
     assert torch.equal(out, ref), (out.float() - ref.float()).abs().max()
+
+
+def test_staged_upload_of_large_pageable_tensors_is_exact(K):
+    """ops._upload_staged (first upload of a large pageable host tensor through two pinned staging buffers): every byte
+    arrives, also when the size is not a multiple of the staging buffer."""
+    from sgl_cpu_tests_b200 import ops
+    dev = torch.device("cuda", 0)
+    n = ops._UPLOAD_MIN_BYTES + 3 * ops._STAGE_BYTES // 2 + 12345 * 2
+    t = torch.randint(-2 ** 15, 2 ** 15 - 1, (n // 2,), dtype=torch.int16).view(torch.bfloat16)
+    assert not t.is_pinned()
+    d = ops._to_dev(t, dev)
+    assert d.dtype == t.dtype and d.shape == t.shape
+    assert torch.equal(d.view(torch.int16).cpu(), t.view(torch.int16))
+    f8 = torch.randint(0, 255, (ops._UPLOAD_MIN_BYTES + 7,), dtype=torch.uint8).view(torch.float8_e4m3fn)
+    assert torch.equal(ops._to_dev(f8, dev).view(torch.uint8).cpu(), f8.view(torch.uint8))
