@@ -129,6 +129,7 @@ __global__ void __launch_bounds__(128)
   if (any_mine) {
     const int4* src = reinterpret_cast<const int4*>(x + (size_t)m * H);
     int4* dst = reinterpret_cast<int4*>(pb + L.x[par] + slot * H * 2);
+#pragma unroll 4  // four 16-byte loads in flight per thread before the first peer store
     for (int i = threadIdx.x; i < H / 8; i += 128) dst[i] = src[i];
   }
   __threadfence_system();
@@ -182,16 +183,30 @@ __global__ void __launch_bounds__(256)
   const int h0 = (blockIdx.y * 256 + threadIdx.x) * 8;
   if (h0 >= H) return;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  for (int j = 0; j < topk; ++j) {  // slot order: the single-GPU reduction order
-    const int e = ids[m * topk + j];
-    if (e < 0 || e >= E_local * world) continue;
-    const char* src = peers.base[e / E_local] + L.y[par] + ((((size_t)rank * cap + m) * topk + j) * H + h0) * 2;
-    const int4 v = ld_peer16(src);
-    const uint32_t* wv = reinterpret_cast<const uint32_t*>(&v);
+  // slot order: the single-GPU reduction order.  Eight slots per pass: their peer loads are all in flight before the
+  // first addition (one NVLink round trip per pass instead of one per slot).
+  for (int j0 = 0; j0 < topk; j0 += 8) {
+    int e[8];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      acc[2 * i] += bf16_bits_to_float(wv[i] & 0xffffu);
-      acc[2 * i + 1] += bf16_bits_to_float(wv[i] >> 16);
+    for (int i = 0; i < 8; ++i) {
+      e[i] = j0 + i < topk ? ids[m * topk + j0 + i] : -1;
+      if (e[i] >= E_local * world) e[i] = -1;
+    }
+    int4 v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      v[i] = e[i] >= 0 ? ld_peer16(peers.base[e[i] / E_local] + L.y[par] +
+                                   ((((size_t)rank * cap + m) * topk + j0 + i) * H + h0) * 2)
+                       : make_int4(0, 0, 0, 0);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (e[i] < 0) continue;
+      const uint32_t* wv = reinterpret_cast<const uint32_t*>(&v[i]);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        acc[2 * q] += bf16_bits_to_float(wv[q] & 0xffffu);
+        acc[2 * q + 1] += bf16_bits_to_float(wv[q] >> 16);
+      }
     }
   }
   if (shared_y != nullptr) {  // shared_expert_cpu's epilogue on the rounded sum (misc.cu shared_axpy_kernel)
