@@ -1006,7 +1006,7 @@ def run_reference(args):
     cpu_call(c)
     one = time.perf_counter() - t0
     total = args.steps + args.warmup
-    budget = 420.0
+    budget = 180.0   # seconds for the whole arm: the driver runs it at N = 1 and again for every N of the scaling run
     m = M
     steps, warmup = args.steps, args.warmup
     if one * total > budget:   # the step cost is per active expert, not per token: fewer repetitions before fewer tokens

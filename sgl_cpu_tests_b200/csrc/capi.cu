@@ -493,7 +493,7 @@ static int run_prologue(const int32_t* ids, const void* hidden, int64_t M, int t
   pr.tok_valid = red_blocks > 0 ? ws.tok_valid : nullptr;
   pr.red_cnt = red_blocks > 0 ? ws.red_cnt : nullptr;
   pr.red_blocks = red_blocks;
-  pr.row_amax = ws.row_amax;
+  pr.row_amax = red_blocks > 0 ? ws.row_amax : nullptr;  // level 2 only: maxed by the stage-1 epilogue (int8)
   pr.amax_rows = (int)(M * topk + M);
   StageTimer t(ST_ALIGN, stream);
   return moe_prologue_impl(ids, M, topk, E, chunk_rows, tile_rows, &ao, shared_rows, pr, stream);
