@@ -4,6 +4,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <string.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "rowops.cuh"
@@ -277,6 +278,14 @@ static int run_umma_stage(int fmt, int stage, const StreamArgs& sa, int E, int64
   u.Wsh_scale = sa.Wsh_scale;
   u.shared_row0 = sa.shared_row0;
   u.x_rows = (int)(sa.gather ? S / sa.topk : S);  // token rows when gathered, else the sorted rows themselves
+  static const int l2_hints = [] {
+    // experiment, off: L2 eviction hints on the TMA loads of the CTA-pair fp8 kernel (weights evict-first, routed rows
+    // evict-last).  Measured at DSV3 M = 8192 (r3g): w13 4251 -> 4180 us, w2 2060 -> 2090 us, whole step 8.01 -> 8.70 ms
+    // -- the pinned lines cost the kernels around the GEMMs more than the GEMMs gain.
+    const char* e = getenv("SGLB_L2_HINTS");
+    return e ? atoi(e) : 0;
+  }();
+  u.l2_hints = l2_hints;
   u.red = sa.red;
   u.row_amax = sa.row_amax;
   u.Xraw = sa.Xraw;

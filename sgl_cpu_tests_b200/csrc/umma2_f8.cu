@@ -104,6 +104,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kProducerRegsP));
     if (warp == 0) {
       // ================= TMA producer =================
+      const bool l2_hints = a.l2_hints != 0;
       uint32_t it = 0;
       for (int w = cluster_id; w < total; w += num_clusters) {
         const PairItem wi = get_pair_item(a, w, n_blocks);
@@ -116,6 +117,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
             // both CTAs' weight halves + both CTAs' hi and lo routed-row boxes (whole 128-row boxes)
             if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2 * kWTileBytes + 4 * kXTileBytes);
             const int r0 = wi.row_start + (int)rank * (n_eff >> 1);
+            if (l2_hints) {
+              tma_load_2d_pair_hint(xh_tile(s), &tmap_xh, lbar, kb * kRowBytes, r0, kL2EvictLast);
+              tma_load_2d_pair_hint(xl_tile(s), &tmap_xl, lbar, kb * kRowBytes, r0, kL2EvictLast);
+              if constexpr (STAGE == 1) {
+                const int g0 = wi.nb * kWSub + (int)rank * 64;
+                tma_load_3d_pair_hint(w_tile(s), &tmap_w, lbar, kb * kRowBytes, g0, wi.e, kL2EvictFirst);
+                tma_load_3d_pair_hint(w_tile(s) + kWTileBytes / 2, &tmap_w, lbar, kb * kRowBytes, a.N + g0, wi.e, kL2EvictFirst);
+              } else {
+                tma_load_3d_pair_hint(w_tile(s), &tmap_w, lbar, kb * kRowBytes, wi.nb * 2 * kWSub + (int)rank * kWSub, wi.e,
+                                      kL2EvictFirst);
+              }
+            } else {
             tma_load_2d_pair(xh_tile(s), &tmap_xh, lbar, kb * kRowBytes, r0);
             tma_load_2d_pair(xl_tile(s), &tmap_xl, lbar, kb * kRowBytes, r0);
             if constexpr (STAGE == 1) {
@@ -124,6 +137,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsP, 1)
               tma_load_3d_pair(w_tile(s) + kWTileBytes / 2, &tmap_w, lbar, kb * kRowBytes, a.N + g0, wi.e);
             } else {
               tma_load_3d_pair(w_tile(s), &tmap_w, lbar, kb * kRowBytes, wi.nb * 2 * kWSub + (int)rank * kWSub, wi.e);
+            }
             }
           }
           __syncwarp();

@@ -45,6 +45,7 @@ struct UmmaArgs {
   FusedReduce red;         // stage 2: the epilogue finishes tokens itself (common.cuh); red.cnt == nullptr = off
   uint32_t* row_amax;      // int8: f32 bits of max |act| per act row.  Stage 1: the epilogue atomically maxes into it
                            // (zeroed by the prologue); stage 2 with Xraw set: the quantisation scale of each row
+  int l2_hints;            // CTA-pair fp8 kernel: TMA loads carry L2 eviction hints (weights first, routed rows last)
   const float* Xraw;       // stage 2, int8 (umma_gemm.cu only): f32 act rows [*, K]; the gather warps quantise them into
                            // the operand tile with quant_rows_kernel's arithmetic (X / Xscale are unused)
 };
