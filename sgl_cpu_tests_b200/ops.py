@@ -96,6 +96,16 @@ def _maybe_pin(t):
         weakref.finalize(t, _unpin, ptr)
 
 
+_copy_streams = {}
+
+
+def _copy_stream(dev):
+    st = _copy_streams.get(dev.index)
+    if st is None:
+        st = _copy_streams[dev.index] = torch.cuda.Stream(device=dev)
+    return st
+
+
 def _to_host(dev_tensor):
     """Device result -> a fresh host tensor; large results land in torch's cached pinned pool (DMA at full rate)."""
     if _PIN_HOST and _nbytes(dev_tensor) >= _PIN_MIN_BYTES:
@@ -926,7 +936,22 @@ def shared_expert_impl(hs, w1, w2, fused_out, rsf, inplace, fmt, s1, s2, block, 
     lib = L.load()
     with torch.cuda.device(dev):
         x = _to_dev(hs, dev)
-        fo = _to_dev(fused_out, dev)
+        # A pinned host `fused_out` is only needed by the final axpy: its upload runs on a copy stream UNDER the MLP's
+        # GEMMs (the reference's API hands the routed result from op to op through host memory; at DeepSeek-V3's 256
+        # tokens that is 3.7 MB = about as long as the shared MLP itself).
+        fo_event = None
+        if (fused_out is not None and not on_cuda and out is None and fused_out.is_contiguous()
+                and (fused_out.is_pinned() or fused_out.data_ptr() in _pinned)):
+            side = _copy_stream(dev)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                fo = torch.empty(fused_out.shape, dtype=fused_out.dtype, device=dev)
+                fo.copy_(fused_out, non_blocking=True)
+                fo_event = torch.cuda.Event()
+                fo_event.record(side)
+            fo.record_stream(torch.cuda.current_stream())
+        else:
+            fo = _to_dev(fused_out, dev)
         w1d = _resident_weight(w1, bool(is_vnni), dev)
         w2d = _resident_weight(w2, bool(is_vnni), dev)
         s1d = _resident_aux(s1, dev, torch.float32)
@@ -941,9 +966,12 @@ def shared_expert_impl(hs, w1, w2, fused_out, rsf, inplace, fmt, s1, s2, block, 
             ws = _workspace(nws, dev)
             p = L.SharedProblem(M=M, H=H, I=I, fmt=fmt, path=L.PATH_AUTO, hidden=x.data_ptr(), w1=w1d.data_ptr(),
                                 w2=w2d.data_ptr(), w1_scale=_ptr(s1d), w2_scale=_ptr(s2d), block_n=bn, block_k=bk,
-                                fused_out=_ptr(fo), routed_scaling_factor=float(rsf), out=out.data_ptr(),
-                                workspace=ws.data_ptr(), workspace_bytes=ws.numel())
+                                fused_out=None if fo_event is not None else _ptr(fo), routed_scaling_factor=float(rsf),
+                                out=out.data_ptr(), workspace=ws.data_ptr(), workspace_bytes=ws.numel())
             L.check(lib.sglb_shared_expert(p, _stream()))
+            if fo_event is not None:   # out = bf16(fma(fused_out, rsf, mlp)): the epilogue sglb_shared_expert fuses
+                torch.cuda.current_stream().wait_event(fo_event)
+                L.check(lib.sglb_shared_axpy(out.data_ptr(), fo.data_ptr(), float(rsf), out.numel(), out.data_ptr(), _stream()))
         if on_cuda:
             if inplace and out is not hs:
                 hs.copy_(out)

@@ -257,3 +257,26 @@ def test_staged_upload_of_large_pageable_tensors_is_exact(K):
     assert torch.equal(d.view(torch.int16).cpu(), t.view(torch.int16))
     f8 = torch.randint(0, 255, (ops._UPLOAD_MIN_BYTES + 7,), dtype=torch.uint8).view(torch.float8_e4m3fn)
     assert torch.equal(ops._to_dev(f8, dev).view(torch.uint8).cpu(), f8.view(torch.uint8))
+
+
+@pytest.mark.parametrize("fmt", ["bf16", "fp8"])
+def test_shared_expert_pinned_fused_out_overlapped_upload(K, fmt):
+    """A pinned host fused_experts_out is uploaded on a copy stream under the MLP and added by a separate axpy launch
+    (ops.shared_expert_impl): same bits as the fused epilogue taken with pageable tensors."""
+    import bench
+    H, I, M = 1024, 512, 100
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev).manual_seed(17)
+    sh = bench.make_shared(fmt, H, I, dev, g)
+    fid = bench.FMT_ID[fmt]
+    x = (torch.randn(M, H, device=dev, generator=g) / 8).bfloat16().cpu()
+    fo = (torch.randn(M, H, device=dev, generator=g) / 4).bfloat16().cpu()
+    c = lambda t: None if t is None else t.cpu()
+    args = (c(sh["w1"]), c(sh["w2"]))
+    ref = K.shared_expert_impl(x.clone(), *args, fo.clone(), 2.5, False, fid, c(sh["s1"]), c(sh["s2"]), sh["block"], False)
+    out = K.shared_expert_impl(x.clone().pin_memory(), *args, fo.clone().pin_memory(), 2.5, False, fid, c(sh["s1"]), c(sh["s2"]),
+                               sh["block"], False)
+    assert torch.equal(out, ref), (out.float() - ref.float()).abs().max()
+    xin = x.clone().pin_memory()
+    out2 = K.shared_expert_impl(xin, *args, fo.clone().pin_memory(), 2.5, True, fid, c(sh["s1"]), c(sh["s2"]), sh["block"], False)
+    assert out2 is xin and torch.equal(out2, ref)
