@@ -223,7 +223,7 @@ def dist_env():
 
 
 def path_used(args, fmt, M, topk, E, H, I):
-    """Mirrors the SGLB_PATH_AUTO rule of capi.cu (rows/expert >= 4 and a supported shape)."""
+    """Mirrors the SGLB_PATH_AUTO rule of capi.cu (rows/expert >= 2 or at most 32 slots, and a supported shape)."""
     if args.path != "auto":
         return args.path
     rpe = M * topk / E
@@ -239,7 +239,7 @@ def path_used(args, fmt, M, topk, E, H, I):
     else:
         eb = {"bf16": 2, "int8": 1}[fmt]
         ok = (H * eb) % 128 == 0 and (I * eb) % 128 == 0
-    return "umma" if ok and M * topk / E >= 4.0 else "stream"
+    return "umma" if ok and (M * topk / E >= 2.0 or M * topk <= 32) else "stream"
 
 
 PATH_DESC = {"stream": "stream (mma.sync weight streaming)", "umma": "umma (tcgen05 + TMEM + TMA)",

@@ -92,9 +92,12 @@ struct MoeWorkspace {
 };
 
 constexpr int kMinChunkRows = 8;
-// Measured on B200 (Qwen3 shape): the persistent TMA-fed tcgen05 kernel streams weights faster than the
-// mma.sync kernel from about 4 routed rows per expert upwards and ties below.
-constexpr double kUmmaMinRowsPerExpert = 4.0;
+// Measured on B200 (Qwen3 / bench_moe.py shapes, r3i): the persistent TMA-fed tcgen05 kernel streams weights faster than
+// the mma.sync kernel from 2 routed rows per expert upwards (M = 32 / 48: 110.6 vs 114.6 / 116.6 vs 122.5 us) and for a
+// handful of slots (M = 1: 32.0 vs 37.2 us; M = 4: 103 vs 109 us bf16); in between the streaming kernel wins (M = 16:
+// 88 vs 96 us).
+constexpr double kUmmaMinRowsPerExpert = 2.0;
+constexpr int64_t kUmmaTinySlots = 32;
 constexpr double kPairMinRowsPerExpert = 128.0;
 constexpr int kTileRows = kUmmaTileRows;
 constexpr int kMinTileRows = 16;  // smallest tile_rows any path hands to moe_align (sizes tile_list)
@@ -582,7 +585,7 @@ static int auto_path(const sglb_moe_problem* p, bool mx4) {
   // fp8 on the fp8 tensor cores streams weights faster than the mma.sync kernel at every batch size
   // measured (DSV3 M = 16: 82 % vs 59 % of the HBM roofline): no ALU work per weight byte
   const bool f8 = p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k);
-  const int path = ((f8 || mx4 || rows_per_expert >= kUmmaMinRowsPerExpert) && umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I))
+  const int path = ((f8 || mx4 || rows_per_expert >= kUmmaMinRowsPerExpert || p->M * p->topk <= kUmmaTinySlots) && umma_supported(p->fmt, p->M, p->topk, p->E, p->H, p->I))
                        ? SGLB_PATH_UMMA
                        : SGLB_PATH_STREAM;
   // Prefill: the CTA-pair kernels (M = 256 MMAs, routed rows pre-gathered into sorted order and fed by TMA) once
