@@ -686,14 +686,20 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     SGLB_CHECK(path == SGLB_PATH_UMMA || !ex.any(),
                "fused_experts: the CTA-pair tcgen05 path has no expert bias / clamped swiglu / slot-addressed output");
     const bool use_mx4 = mx4 && path == SGLB_PATH_UMMA;
-    // fp8 tensor-native kernel, decode: 32-row tiles run the deep-ring configuration (umma_f8.cu F8Cfg<32>) -- when an
-    // expert practically never gets more rows (Poisson(12) > 32: 1e-6; a longer expert is split and streams twice) and
-    // a riding shared expert fits one tile
+    // fp8 tensor-native kernel, decode: 32- or 80-row tiles run the deep-ring configurations (umma_f8.cu F8Cfg) -- when
+    // an expert rarely gets more rows (Poisson(12) > 32: 1e-6; Poisson(64) > 80: 2 %; a longer expert is split and
+    // streams twice) and a riding shared expert fits one tile
     const bool f8n = p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k);
-    const int f8_cap = (path == SGLB_PATH_UMMA && f8n && g_f8_small_tiles && rows_per_expert <= 12.0 &&
-                        (!ride || p->M <= umma_f8_small_tile_rows()))
-                           ? umma_f8_small_tile_rows()
-                           : 0;
+    int f8_cap = 0;
+    static const int small_env = [] {
+      const char* e = getenv("SGLB_F8_SMALL_TILES");  // experiments: 0 = 128-row tiles only, 1 = 32-row only, 2 = 32 and 80
+      return e ? atoi(e) : 2;
+    }();
+    if (path == SGLB_PATH_UMMA && f8n && g_f8_small_tiles && small_env > 0) {
+      if (rows_per_expert <= 12.0 && (!ride || p->M <= umma_f8_small_tile_rows())) f8_cap = umma_f8_small_tile_rows();
+      else if (small_env > 1 && rows_per_expert <= 40.0 && (!ride || p->M <= umma_f8_mid_tile_rows()))
+        f8_cap = umma_f8_mid_tile_rows();
+    }
     const int cap_arg = use_mx4 ? mx4_cap : f8_cap;
     const int tile_rows = cap_arg > 0 ? cap_arg : (path == SGLB_PATH_UMMA2 ? umma2_tile_rows() : kTileRows);
     if (fuse) {

@@ -42,13 +42,17 @@ namespace {
 // Two shared-memory configurations (template parameter XROWS = routed rows an operand slot holds = row capacity of the
 // tiles moe_align hands out):
 //   XROWS = 128: stage = W gate/up 32 KB + X hi + X lo 2 x 16 KB = 64 KB, 3 stages (prefill and general decode)
-//   XROWS = 32:  stage = 32 KB + 2 x 4 KB = 40 KB, 5 stages: 160 KB instead of 96 KB of weight bytes in flight per SM.
+//   XROWS = 80:  stage = 32 KB + 2 x 10 KB = 52 KB, 4 stages: 128 KB of weight bytes in flight per SM
+//   XROWS = 32:  stage = 32 KB + 2 x 4 KB = 40 KB, 5 stages: 160 KB instead of 96 KB in flight.
 // At ~2.2 us of loaded HBM latency 96 KB in flight is ~43 GB/s per SM -- enough when all 148 SMs stream, the cap when a
-// decode call has fewer work items than SMs (DeepSeek-V3 at M = 1: 144 items); capi.cu picks 32 when tiles are small.
+// decode call has fewer work items than SMs (DeepSeek-V3 at M = 1: 144 items) or sizes its grid to whole waves (an
+// expert-parallel rank of 8: 128 CTAs, 33 GB/s per SM measured); capi.cu picks the smallest capacity the expected rows
+// per expert fit with two standard deviations to spare (a longer expert is split and streams its weights twice).
 template <int XROWS>
 struct F8Cfg {
   static constexpr int kXBytes = XROWS * kRowBytes;
-  static constexpr int kStages = XROWS == 128 ? 3 : 5;
+  static constexpr int kStages = XROWS == 128 ? 3 : (XROWS == 80 ? 4 : 5);
+  static_assert(XROWS == 128 || XROWS == 80 || XROWS == 32, "operand slot rows");
   static constexpr int kStageBytes = 2 * kWTileBytes + 2 * kXBytes;
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBufBytes + 1024 + 256;
 };
@@ -424,11 +428,13 @@ int umma_f8_supported(int H, int I, int block_n, int block_k) {
 }
 
 int umma_f8_small_tile_rows() { return 32; }
+int umma_f8_mid_tile_rows() { return 80; }
 
 // a.tile_cap: row capacity of the tiles in tile_list -- 0 / 128 (general) or umma_f8_small_tile_rows() (deep ring)
 int launch_umma_f8(int stage, const UmmaArgs& a, cudaStream_t stream) {
   int rc;
   if (a.tile_cap == 32) rc = stage == 1 ? launch_one<1, 32>(a, stream) : launch_one<2, 32>(a, stream);
+  else if (a.tile_cap == 80) rc = stage == 1 ? launch_one<1, 80>(a, stream) : launch_one<2, 80>(a, stream);
   else rc = stage == 1 ? launch_one<1, 128>(a, stream) : launch_one<2, 128>(a, stream);
   if (rc == SGLB_OK) count_launch();
   return rc;

@@ -25,7 +25,7 @@ struct UmmaArgs {
   int scale_cols;          // fp8: ceil(K/bk); mxfp4: K/32
   const void* X2;          // fp8 / mxfp4 tensor-native paths: lo pieces of the routed rows (X = hi pieces, e4m3)
   const void* Wsf;         // mxfp4 tensor-native path: e8m0 scales re-tiled for tcgen05.cp (umma_mx4.cu)
-  int tile_cap;            // row capacity of the tiles in tile_list when not 128: mxfp4 kernel 16..112, fp8 deep ring 32
+  int tile_cap;            // row capacity of the tiles in tile_list when not 128: mxfp4 kernel 16..112, fp8 deep rings 32 / 80
   const float* bias;       // stage 2 optional f32 [N] added after row_scale (dense linears, E = 1)
   int est_tiles;           // umma_gemm.cu, decode regime: expected tile count (0 = unknown), sizes the persistent grid
   const float* ebias;      // per-expert f32 bias [E, rows_per_expert] or nullptr (gpt-oss w1_bias / w2_bias): added to
@@ -67,6 +67,7 @@ int launch_umma_dq(int fmt, int stage, const UmmaArgs& a, cudaStream_t stream);
 int umma_f8_supported(int H, int I, int block_n, int block_k);
 int launch_umma_f8(int stage, const UmmaArgs& a, cudaStream_t stream);
 int umma_f8_small_tile_rows();  // tile capacity of the deep-ring decode configuration (UmmaArgs.tile_cap)
+int umma_f8_mid_tile_rows();    // 80-row tiles, 4-stage ring
 // mxfp4 on the block-scaled fp8/fp4 tensor cores (umma_mx4.cu): weights e2m1 via TMA, e8m0 scales in TMEM
 int umma_mx4_supported(int H, int I);
 int umma_mx4_tile_rows(double rows_per_expert);

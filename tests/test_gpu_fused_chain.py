@@ -197,9 +197,10 @@ def test_mxfp4_scale_tiles_are_built_once(K):
     assert counts[0] >= counts[1]
 
 
-@pytest.mark.parametrize("M", [1, 16, 40])
+@pytest.mark.parametrize("M", [1, 16, 40, 100, 250])
 def test_fp8_small_tile_deep_ring_is_bit_identical(K, M):
-    """fp8 decode takes 32-row tiles on a 5-stage ring (umma_f8.cu F8Cfg<32>) when experts get few rows; the per-row
+    """fp8 decode takes 32-row tiles on a 5-stage ring (umma_f8.cu F8Cfg<32>; M = 100, 250 here: 80-row tiles on a
+    4-stage ring, F8Cfg<80>) when experts get few rows; the per-row
     arithmetic does not depend on the tile a row lands in, so the result equals the 128-row configuration bit for bit
     -- also when one expert receives more than 32 rows and is split into several tiles."""
     from sgl_cpu_tests_b200 import _lib as L
