@@ -706,11 +706,23 @@ def run_b200(args):
         per_rank_bytes = e_local * (3 * H * I * bw + scale_bytes(fmt, H, I)) + (3 * H * wl.shared_I * bw + scale_bytes(fmt, H, wl.shared_I) if wl.shared_I else 0) \
             + 2 * M * H * 2 + M * topk * 8
         gbs = per_rank_bytes / (ms_per_step * 1e-3) / 1e9
-        out["roofline"] = {"bound": "hbm", "kernel": "whole step of one rank (all local experts assumed active)", "achieved": gbs,
-                           "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak, "peak_source": peak_src, "traffic": None,
-                           "algorithmic_bytes": per_rank_bytes,
-                           "exchange_bytes_per_rank": {"dispatch_rows": int(M * H * 2), "return_slot_rows": int(M * topk * H * 2),
-                                                       "note": "upper bounds: a row travels once per owner rank, a slot row once"}}
+        xbytes = {"dispatch_rows": int(M * H * 2), "return_slot_rows": int(M * topk * H * 2),
+                  "note": "upper bounds: a row travels once per owner rank, a slot row once"}
+        # a rank computes the routed rows it RECEIVES (M * topk on average: every rank sends as many tokens) + its own
+        # tokens through the replicated shared expert; the bound is whichever roof asks for more time
+        fl = flops(M, topk, H, I, wl.shared_I)
+        roof_dt = "int8" if fmt == "int8" else "bf16"
+        t_hbm, t_tc = per_rank_bytes / (hbm_peak * 1e9), (fl / (tc[roof_dt] * 1e12) if tc.get(roof_dt) else 0.0)
+        if t_tc > t_hbm:
+            tf = fl / (ms_per_step * 1e-3) / 1e12
+            out["roofline"] = {"bound": "tensor", "kernel": "whole step of one rank (received routed rows + local shared expert)",
+                               "achieved": tf, "peak": tc[roof_dt], "unit": "TFLOP/s" if roof_dt == "bf16" else "TOP/s",
+                               "frac": tf / tc[roof_dt], "peak_source": peak_src, "traffic": None, "algorithmic_flops": fl,
+                               "hbm_gbs": gbs, "exchange_bytes_per_rank": xbytes}
+        else:
+            out["roofline"] = {"bound": "hbm", "kernel": "whole step of one rank (all local experts assumed active)", "achieved": gbs,
+                               "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak, "peak_source": peak_src, "traffic": None,
+                               "algorithmic_bytes": per_rank_bytes, "exchange_bytes_per_rank": xbytes}
         del ids_local
         try:
             ph = ep_phases(wl, 10)
