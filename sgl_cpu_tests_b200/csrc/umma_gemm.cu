@@ -47,8 +47,10 @@ constexpr int kThreadsFused = kThreads + 32;
 constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBufBytes + 1024 /*alignment slack*/ +
                            256 /*barriers*/;
 
-template <int FMT, int STAGE>
-__global__ void __launch_bounds__(kThreadsFused, 1)
+// RED: the level-2 chain-fusion variant of stage 2 with the reducer warp (its own instantiation, so that the default
+// kernels keep the register budget of a 448-thread block)
+template <int FMT, int STAGE, bool RED = false>
+__global__ void __launch_bounds__(RED ? kThreadsFused : kThreads, 1)
     umma_moe_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_sh,
                     const UmmaArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -63,7 +65,7 @@ __global__ void __launch_bounds__(kThreadsFused, 1)
   auto tempty_bar = [&](int b) { return bar_base + 8 * (2 * kStages + 2 + b); };
   const uint32_t tmem_slot = bar_base + 8 * (2 * kStages + 4);
   const uint32_t red_bar0 = bar_base + 128;  // fused reduce: full[2], empty[2] between the epilogue and the reducer warp
-  const bool fused_reduce = STAGE == 2 && a.red.cnt != nullptr;  // then the block has kThreadsFused threads
+  constexpr bool fused_reduce = RED;  // then the block has kThreadsFused threads
   uint32_t* tmem_slot_ptr =
       reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
@@ -168,7 +170,7 @@ __global__ void __launch_bounds__(kThreadsFused, 1)
       }
     }
   } else if (warp < 6) {
-    if (FMT == SGLB_FMT_INT8_W8A8 && STAGE == 2 && a.Xraw != nullptr)  // fused decode chain: quantise on the way in
+    if (RED && FMT == SGLB_FMT_INT8_W8A8 && a.Xraw != nullptr)  // fused decode chain: quantise on the way in
       gather_quant_role(a, total, n_blocks, num_kb, threadIdx.x - 64, x_tile(0), kStageBytes, full_bar(0), empty_bar(0),
                         kStages);
     else
@@ -179,7 +181,7 @@ __global__ void __launch_bounds__(kThreadsFused, 1)
                                                     tempty_bar(0), tmem_base, warp, warp - kFirstEpiWarp, lane,
                                                     fused_reduce ? red_bar0 : 0u);
   } else {
-    if constexpr (STAGE == 2) reducer_role(a, total, n_blocks, red_bar0, lane);
+    if constexpr (RED) reducer_role(a, total, n_blocks, red_bar0, lane);
   }
 
   tc_fence_before();
@@ -303,8 +305,11 @@ int sm_count() {
 
 namespace {
 
-template <int FMT, int STAGE>
+template <int FMT, int STAGE, bool RED = false>
 int launch_one(const UmmaArgs& a, cudaStream_t stream) {
+  if constexpr (STAGE == 2 && !RED) {
+    if (a.red.cnt != nullptr || a.Xraw != nullptr) return launch_one<FMT, 2, true>(a, stream);
+  }
   constexpr int EB = FMT == SGLB_FMT_INT8_W8A8 ? 1 : 2;
   CUtensorMap map;
   int rc = weight_tensor_map(a.W, (uint64_t)a.K * EB, (uint64_t)a.rows_per_expert, (uint64_t)a.E, kRowBytes, kWSub, 1,
@@ -317,7 +322,7 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
   }
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
-    SGLB_CUDA(cudaFuncSetAttribute(umma_moe_kernel<FMT, STAGE>,
+    SGLB_CUDA(cudaFuncSetAttribute(umma_moe_kernel<FMT, STAGE, RED>,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr_set = true;
   }
@@ -329,8 +334,8 @@ int launch_one(const UmmaArgs& a, cudaStream_t stream) {
     return e ? atoi(e) : 0;
   }();
   if (forced_grid > 0 && forced_grid < grid) grid = forced_grid;
-  const int threads = STAGE == 2 && a.red.cnt != nullptr ? kThreadsFused : kThreads;  // + the reducer warp
-  SGLB_CUDA(launch_pdl(umma_moe_kernel<FMT, STAGE>, dim3(grid), dim3(threads), kSmemBytes, stream, map, map_sh, a));
+  const int threads = RED ? kThreadsFused : kThreads;  // + the reducer warp
+  SGLB_CUDA(launch_pdl(umma_moe_kernel<FMT, STAGE, RED>, dim3(grid), dim3(threads), kSmemBytes, stream, map, map_sh, a));
   return SGLB_OK;
 }
 
