@@ -63,7 +63,8 @@ int sglb_profile_read(float* ms_out, int* calls_out, int n);
 /* fp8 w8a16 on the tcgen05 path: 1 (default) = weights stay e4m3 and run on the fp8 tensor cores with
  * the activations split into two e4m3 pieces (csrc/umma_f8.cu); 0 = weights dequantised to bf16 in
  * the kernel (csrc/umma_dq.cu).  Process-wide switch, used by the parity tests to cover both.  Bit 1 (on = 3)
- * additionally keeps 128-row tiles at decode instead of the 32-row deep-ring configuration (umma_f8.cu F8Cfg). */
+ * additionally keeps 128-row tiles at decode instead of the 32-row deep-ring configuration (umma_f8.cu F8Cfg); bit 2
+ * (on = 5) also takes the 80-row configuration (an experiment: it bets on balanced routing, capi.cu). */
 void sglb_set_fp8_native(int on);
 
 /* Decode chain fusion level, for calls of up to 16384 routed slots.  0 = every step its own launch (align_count,

@@ -36,6 +36,7 @@ static bool g_profile = false;
 static bool g_mx4_native = true;  // mxfp4: block-scaled tensor-native kernel (umma_mx4.cu) when scale tiles are given
 static bool g_f8_native = true;  // fp8: tensor-native kernel (umma_f8.cu) vs dequantising kernel (umma_dq.cu)
 static bool g_f8_small_tiles = true;  // fp8 decode: 32-row tiles on the deep-ring configuration (SGLB_F8_SMALL_TILES=0: off)
+static bool g_f8_mid_tiles = false;   // fp8: 80-row tiles on the 4-stage ring (experiment: SGLB_F8_SMALL_TILES=2 / set_fp8_native bit 2)
 // Decode chain fusion level (sglb_set_chain_fusion).  1 (default): align + stage-1 operand preparation in ONE prologue
 // launch.  2: also the int8 act quantisation inside the stage-2 producer and the top-k reduce inside the stage-2 kernel
 // (3 launches per call) -- bit-identical, but measured SLOWER on B200 (gpurun r2n: Qwen3 int8 M = 128 step 0.130 ->
@@ -545,6 +546,7 @@ extern "C" int sglb_profile_read(float* ms_out, int* calls_out, int n) {
 extern "C" void sglb_set_fp8_native(int on) {
   g_f8_native = (on & 1) != 0;
   g_f8_small_tiles = (on & 2) == 0;  // bit 1 set: keep 128-row tiles at decode too (A/B experiments, parity tests)
+  g_f8_mid_tiles = (on & 4) != 0;    // bit 2 set: also the 80-row configuration
 }
 extern "C" void sglb_set_chain_fusion(int level) { g_chain_fusion = level < 0 ? 0 : (level > 2 ? 2 : level); }
 extern "C" void sglb_set_mx4_native(int on) { g_mx4_native = on != 0; }
@@ -692,12 +694,18 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     const bool f8n = p->fmt == SGLB_FMT_FP8_W8A16 && g_f8_native && umma_f8_supported(p->H, p->I, p->block_n, p->block_k);
     int f8_cap = 0;
     static const int small_env = [] {
-      const char* e = getenv("SGLB_F8_SMALL_TILES");  // experiments: 0 = 128-row tiles only, 1 = 32-row only, 2 = 32 and 80
-      return e ? atoi(e) : 2;
+      const char* e = getenv("SGLB_F8_SMALL_TILES");  // 0 = 128-row tiles only, 1 (default) = 32-row at decode, 2 = also 80-row
+      return e ? atoi(e) : 1;
     }();
+    // Smaller tiles are a bet on balanced routing: an expert with more rows than the capacity is split and streams its
+    // weights once per tile.  32-row tiles are therefore taken only up to 512 routed slots, where even the worst case
+    // (every slot on one expert: 16 tiles of it) moves a fraction of what a balanced call streams; the 80-row
+    // configuration gains 2 % on balanced routing (DSV3 M = 512: 0.931 -> 0.950) and can lose 60 % on a collapsed one,
+    // so it stays an experiment switch.
     if (path == SGLB_PATH_UMMA && f8n && g_f8_small_tiles && small_env > 0) {
-      if (rows_per_expert <= 12.0 && (!ride || p->M <= umma_f8_small_tile_rows())) f8_cap = umma_f8_small_tile_rows();
-      else if (small_env > 1 && rows_per_expert <= 40.0 && (!ride || p->M <= umma_f8_mid_tile_rows()))
+      if (rows_per_expert <= 12.0 && p->M * p->topk <= 512 && (!ride || p->M <= umma_f8_small_tile_rows()))
+        f8_cap = umma_f8_small_tile_rows();
+      else if ((small_env > 1 || g_f8_mid_tiles) && rows_per_expert <= 40.0 && (!ride || p->M <= umma_f8_mid_tile_rows()))
         f8_cap = umma_f8_mid_tile_rows();
     }
     const int cap_arg = use_mx4 ? mx4_cap : f8_cap;

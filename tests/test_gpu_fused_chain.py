@@ -217,7 +217,7 @@ def test_fp8_small_tile_deep_ring_is_bit_identical(K, M):
         try:
             lib.sglb_set_fp8_native(3)                   # 128-row tiles
             ref = run(K, x, w, fid, tw, case, K.PATH_UMMA)
-            lib.sglb_set_fp8_native(1)                   # default: 32-row tiles where rows per expert <= 12
+            lib.sglb_set_fp8_native(5)                   # 32-row tiles (up to 512 slots, <= 12 rows per expert) and 80-row tiles
             out = run(K, x, w, fid, tw, case, K.PATH_UMMA)
         finally:
             lib.sglb_set_fp8_native(1)
