@@ -6,7 +6,7 @@
  * torch.  A call returns SGLB_OK or a negative status; sglb_last_error() then holds a
  * thread-local message (the Python layer turns it into RuntimeError, the way the reference's
  * TORCH_CHECK surfaces).  The library keeps no global state apart from that message: the caller
- * owns all buffers including the workspace.
+ * owns all buffers including the workspace (one exception, stated there: sglb_moe_align_static).
  *
  * Each entry point cites the reference interface it stands behind (paths are relative to the
  * reference checkout, /root/reference in the build container).
@@ -111,6 +111,28 @@ size_t sglb_moe_align_scratch_bytes(int64_t M, int topk, int E);
 int64_t sglb_moe_align_max_items(int64_t M, int topk, int E, int rows);
 int sglb_moe_align(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows,
                    int tile_rows, const sglb_align_out* out, void* scratch, sglb_stream_t stream);
+
+/* ---- K2 for callers that cannot allocate device memory ---------------------------------------------------
+ * No counterpart in the reference (its align pass is internal to fused_experts_cpu and runs on host memory).
+ * sglb_moe_align wants a caller-owned scratch buffer once a batch has more than 1024 routed slots.  A caller
+ * that cannot supply one -- an engine that gave every free byte of HBM to its own pools at start-up, a plugin
+ * that must not call cudaMalloc or its host's allocator, a step where an allocation's implicit device
+ * synchronisation is unacceptable -- calls this variant instead: same inputs, same outputs, bit-identical
+ * results, and the scratch lives in a 1 MiB array inside the library's device image (resident on every GPU
+ * that loads the library until the process exits).  The call allocates nothing, on the device or through any
+ * library.
+ *   limit      ceil(M*topk/1024) * E * 4 bytes <= sglb_moe_align_static_max_bytes() (= 1 MiB; e.g. 131072
+ *              tokens x top-8 over 256 experts); larger problems return SGLB_ERR_INVALID with a message.
+ *   set-up     the first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ *              that device current -- the one holding the buffers, as for every other entry point) and caches
+ *              it; make that first call before starting any stream capture.
+ *   sharing    every call on a device uses the same array and leaves its histograms behind.  Nothing needs
+ *              clearing between calls (each call overwrites what it later reads), but two calls that can run
+ *              at the same time on one GPU -- different streams, or different host threads -- race on it and
+ *              give wrong indices: keep calls to this entry point ordered per device. */
+size_t sglb_moe_align_static_max_bytes(void);
+int sglb_moe_align_static(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows,
+                          int tile_rows, const sglb_align_out* out, sglb_stream_t stream);
 
 /* ---- K3-K5 fused_experts ------------------------------------------------------------------------
  * fused_experts_cpu (test_moe.py:79-92, test_moe_int8.py:129, test_moe_fp8_ext.py:118,

@@ -67,6 +67,8 @@ SIGNATURES = {
     "sglb_moe_align_scratch_bytes": (_sz, [_i64, C.c_int, C.c_int]),
     "sglb_moe_align_max_items": (_i64, [_i64, C.c_int, C.c_int, C.c_int]),
     "sglb_moe_align": (C.c_int, [_vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(AlignOut), _vp, _vp]),
+    "sglb_moe_align_static_max_bytes": (_sz, []),
+    "sglb_moe_align_static": (C.c_int, [_vp, _i64, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(AlignOut), _vp]),
     "sglb_fused_experts_workspace_bytes": (_sz, [_i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "sglb_fused_experts": (C.c_int, [C.POINTER(MoeProblem), _vp]),
     "sglb_fused_experts_shared_rides": (C.c_int, [C.POINTER(MoeProblem)]),

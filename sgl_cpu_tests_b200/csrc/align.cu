@@ -18,6 +18,8 @@
 // BEHIND the routed ones, at sorted positions [S, S + M) with sorted_slot[S + m] = m * topk (so that the gather's
 // slot / topk gives token m), as ceil(M / tile_rows) tiles of expert id E at the end of tile_list (counted in
 // num_tiles).  Nothing else changes: slot_pos, expert_offset and the chunk list describe the routed slots only.
+#include <mutex>
+
 #include "common.cuh"
 #include "rowops.cuh"
 
@@ -350,5 +352,63 @@ extern "C" size_t sglb_moe_align_scratch_bytes(int64_t M, int topk, int E) {
 extern "C" int sglb_moe_align(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows,
                               int tile_rows, const sglb_align_out* out, void* scratch,
                               sglb_stream_t stream_) {
+  return moe_align_impl(topk_ids, M, topk, E, chunk_rows, tile_rows, out, scratch, 0, (cudaStream_t)stream_);
+}
+
+// ---- moe_align for callers that cannot allocate device memory -------------------------------------------------
+// sglb_moe_align needs a caller-provided scratch buffer (the per-block expert histograms that align_count_kernel
+// hands to align_scatter_kernel) as soon as a batch has more than 1024 routed slots.  Some callers have nowhere
+// to get one: a serving loop that handed all free HBM to its KV-cache pool at start-up, a plugin that is
+// forbidden from touching the host's caching allocator, code that runs where cudaMalloc would implicitly
+// synchronise the device in the middle of a latency-critical step.  For them the same two kernels run over a
+// buffer that is part of this library's device image: the array below.  It costs kAlignStaticBytes of HBM on
+// every GPU that loads libsglb200.so, from load until the process exits, whether or not the entry point is used.
+//
+// In host code the NAME g_align_static_scratch is only a handle for the runtime -- it is not a device address,
+// and a kernel handed `g_align_static_scratch` from the host would fault (or, on a machine where the GPU can reach
+// host memory, quietly scribble over the wrong bytes).  The device address is looked up once per device with
+// cudaGetSymbolAddress, with that device current, and cached.
+constexpr size_t kAlignStaticBytes = (size_t)1 << 20;  // 262144 histogram entries: blocks(M*topk / 1024) * E
+constexpr int kAlignStaticMaxDevices = 64;
+static __device__ __align__(256) int32_t g_align_static_scratch[kAlignStaticBytes / sizeof(int32_t)];
+
+namespace {
+std::mutex g_align_static_mu;
+int32_t* g_align_static_ptr[kAlignStaticMaxDevices] = {};  // device address of the array, per device ordinal
+
+// Device address of g_align_static_scratch on the CURRENT device (first use on a device does the look-up).
+int align_static_scratch(int32_t** ptr) {
+  int dev = -1;
+  SGLB_CUDA(cudaGetDevice(&dev));
+  SGLB_CHECK(dev >= 0 && dev < kAlignStaticMaxDevices, "moe_align_static: device ordinal %d not supported (max %d)", dev,
+             kAlignStaticMaxDevices - 1);
+  std::lock_guard<std::mutex> lock(g_align_static_mu);
+  if (g_align_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    SGLB_CUDA(cudaGetSymbolAddress(&p, g_align_static_scratch));
+    SGLB_CHECK(p != nullptr, "moe_align_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+    g_align_static_ptr[dev] = (int32_t*)p;
+  }
+  *ptr = g_align_static_ptr[dev];
+  return SGLB_OK;
+}
+}  // namespace
+
+extern "C" size_t sglb_moe_align_static_max_bytes(void) { return kAlignStaticBytes; }
+
+extern "C" int sglb_moe_align_static(const int32_t* topk_ids, int64_t M, int topk, int E, int chunk_rows,
+                                     int tile_rows, const sglb_align_out* out, sglb_stream_t stream_) {
+  SGLB_CHECK(M >= 0 && topk >= 1 && E >= 1, "moe_align_static: bad shape M=%lld topk=%d E=%d", (long long)M, topk, E);
+  SGLB_CHECK(M * (int64_t)topk < (1ll << 30), "moe_align_static: M*topk too large");
+  const size_t need = sglb_moe_align_scratch_bytes(M, topk, E);
+  SGLB_CHECK(need <= kAlignStaticBytes,
+             "moe_align_static: M=%lld topk=%d E=%d needs %zu bytes of scratch, the built-in buffer holds %zu "
+             "(ceil(M*topk/1024)*E*4 must not exceed it); use sglb_moe_align with a caller-owned scratch buffer",
+             (long long)M, topk, E, need, kAlignStaticBytes);
+  int32_t* scratch = nullptr;
+  if (int rc = align_static_scratch(&scratch)) return rc;
+  // Nothing in the buffer has to start at zero: align_count_kernel stores every histogram entry of the
+  // ceil(M*topk/1024) blocks this call uses before align_scatter_kernel reads them, and entries past those
+  // (leftovers of an earlier, larger call) are never read.
   return moe_align_impl(topk_ids, M, topk, E, chunk_rows, tile_rows, out, scratch, 0, (cudaStream_t)stream_);
 }
