@@ -54,6 +54,13 @@ const char* sglb_last_error(void);
 /* number of kernels this library has launched in the calling process (bench.py reports it) */
 uint64_t sglb_launch_count(void);
 
+/* Page-locking of caller-owned HOST memory, for host layers that stage CPU tensors (the reference's scripts pass CPU
+ * tensors: test_moe.py:96-99, bench_moe.py:52).  No counterpart in the reference.  host_ptr is a HOST pointer.  A
+ * failure (read-only or file-backed mapping, locked-memory limit) returns SGLB_ERR_CUDA with a message and leaves no
+ * pending CUDA error behind. */
+int sglb_host_register(void* host_ptr, size_t bytes);
+int sglb_host_unregister(void* host_ptr);
+
 /* Optional per-stage timing with CUDA events on the launching stream (used by bench.py for the
  * roofline figure).  Stages: 0 align, 1 quant_x, 2 w13 GEMM, 3 quant_act, 4 w2 GEMM, 5 topk reduce.
  * sglb_profile_read sums ms and sample counts per stage since the last read; synchronise first. */

@@ -55,6 +55,8 @@ SIGNATURES = {
     "sglb_version": (C.c_int, []),
     "sglb_last_error": (C.c_char_p, []),
     "sglb_launch_count": (C.c_uint64, []),
+    "sglb_host_register": (C.c_int, [_vp, _sz]),
+    "sglb_host_unregister": (C.c_int, [_vp]),
     "sglb_profile_enable": (None, [C.c_int]),
     "sglb_set_fp8_native": (None, [C.c_int]),
     "sglb_set_chain_fusion": (None, [C.c_int]),

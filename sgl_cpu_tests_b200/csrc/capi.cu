@@ -520,6 +520,29 @@ extern "C" int sglb_version(void) { return 100; }
 extern "C" const char* sglb_last_error(void) { return g_err; }
 extern "C" uint64_t sglb_launch_count(void) { return g_launches.load(); }
 
+// Page-locks / releases a caller-owned HOST range for the host layer's staging (ops.py::_maybe_pin).  A failed
+// registration (read-only or file-backed mapping, RLIMIT_MEMLOCK, ...) is reported and its error is cleared here, in
+// this library's runtime, so it cannot surface later from an unrelated launch check.
+extern "C" int sglb_host_register(void* host_ptr, size_t bytes) {
+  SGLB_CHECK(host_ptr != nullptr && bytes > 0, "host_register: empty range");
+  cudaError_t e = cudaHostRegister(host_ptr, bytes, cudaHostRegisterDefault);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    set_error("cudaHostRegister(%p, %zu) failed: %s", host_ptr, bytes, cudaGetErrorString(e));
+    return SGLB_ERR_CUDA;
+  }
+  return SGLB_OK;
+}
+extern "C" int sglb_host_unregister(void* host_ptr) {
+  cudaError_t e = cudaHostUnregister(host_ptr);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    set_error("cudaHostUnregister(%p) failed: %s", host_ptr, cudaGetErrorString(e));
+    return SGLB_ERR_CUDA;
+  }
+  return SGLB_OK;
+}
+
 extern "C" void sglb_profile_enable(int on) {
   g_profile = on != 0;
   g_events_used = 0;
@@ -728,7 +751,8 @@ extern "C" int sglb_fused_experts(const sglb_moe_problem* p, sglb_stream_t strea
     StreamPlan plan = make_plan(p->M, p->topk, p->E, p->I, 1);
     if (fuse)
       rc = run_prologue(p->topk_ids, p->hidden, p->M, p->topk, p->E, p->H, p->fmt == SGLB_FMT_INT8_W8A8 ? 1 : 0,
-                        stage2_red_blocks(path, p->M, p->topk, p->E, p->H), 8 * plan.ng, kTileRows, 0, ws, stream);
+                        fuse_reduce ? stage2_red_blocks(path, p->M, p->topk, p->E, p->H) : 0, 8 * plan.ng, kTileRows, 0, ws,
+                        stream);
     else
       rc = run_align(p->topk_ids, p->M, p->topk, p->E, 8 * plan.ng, ws, stream);
     if (rc) return rc;

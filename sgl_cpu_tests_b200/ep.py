@@ -161,6 +161,9 @@ class PeerExchange:
         lib = L.load()
         world, rank = comm.world, comm.rank
         self.world, self.rank, self.cap, self.H, self.topk = world, rank, cap, H, topk
+        self.comm, self.device = comm, device
+        self.base, self._opened, self._closed = None, [], False
+        self.pins = 0      # GraphedEP objects whose captured graphs address this region (EPMoE never evicts those)
         # every rank must have built the same geometry: offsets into a peer's region are computed locally
         geo = comm.all_gather_object((world, cap, H, topk))
         if any(g != geo[0] for g in geo):
@@ -180,7 +183,6 @@ class PeerExchange:
         gathered = comm.all_gather_object((status, bytes(handle.raw)))
         self.base = base.value
         self.peers = (C.c_void_p * world)()
-        self._opened = []
         if all(g[0] == "ok" for g in gathered):
             for r in range(world):
                 if r == rank:
@@ -215,17 +217,34 @@ class PeerExchange:
         self.side = torch.cuda.Stream(device=device)
 
     def close(self):
+        """COLLECTIVE: every rank of the group calls it, at the same point of the program.  A rank's combine waits for
+        its peers' experts, not for their combines, so a peer may still be reading this rank's `y` rows over NVLink when
+        this rank is done; and CUDA IPC requires every importer to close its mapping before the exporter frees.
+        Order: this device idle -> everybody idle -> unmap the peers -> everybody unmapped -> free the own region."""
+        if getattr(self, "_closed", True):
+            return
+        self._closed = True
         lib = L.load()
+        torch.cuda.synchronize(self.device)
+        self.comm.all_gather_object("idle")          # no kernel of any rank touches any region from here on
         for p in self._opened:
             lib.sglb_p2p_close(p)
         self._opened = []
-        if getattr(self, "base", None):
+        self.comm.all_gather_object("unmapped")      # nobody holds a mapping of this rank's region any more
+        if self.base:
             lib.sglb_p2p_free(self.base)
             self.base = None
 
     def __del__(self):
+        # Not collective, so the exported region is NOT freed here (a peer may still read it; it goes with the process).
+        # Dropping this process's own mappings of the peers is safe once the local device is idle.
         try:
-            self.close()
+            if not getattr(self, "_closed", True) and self._opened:
+                torch.cuda.synchronize(self.device)
+                lib = L.load()
+                for p in self._opened:
+                    lib.sglb_p2p_close(p)
+                self._opened = []
         except Exception:  # interpreter shutdown
             pass
 
@@ -279,6 +298,7 @@ class GraphedEP:
 
     def __init__(self, layer, px, num_tokens, H, device, router=None):
         self.layer, self.px, self.router = layer, px, router
+        px.pins += 1       # the graphs below bake in addresses inside px's region: released by close() only
         topk = layer.topk
         self.hidden = torch.zeros(num_tokens, H, dtype=torch.bfloat16, device=device)
         self.gating = torch.zeros(num_tokens, layer.E, dtype=torch.bfloat16, device=device) if router is not None else None
@@ -336,7 +356,16 @@ class GraphedEP:
                             ops._workspaces[k] = v
             torch.cuda.current_stream().wait_stream(cap_stream)
 
+    def close(self):
+        """Drops the graphs and lets the layer evict / close the peer region again.  Call it on every rank at the same
+        point of the program (explicitly: garbage collection runs at different times on different ranks)."""
+        if self.graphs is not None:
+            self.graphs = None
+            self.px.pins -= 1
+
     def __call__(self, hidden_states=None, topk_weights=None, topk_ids=None, gating=None):
+        if self.graphs is None:
+            raise RuntimeError("GraphedEP: called after close()")
         if hidden_states is not None:
             self.hidden.copy_(hidden_states, non_blocking=True)
         if gating is not None:
@@ -356,9 +385,12 @@ class EPMoE:
     weights: dict(w1=[E/n, 2I, H], w2=[E/n, H, I], s1, s2, block) -- this rank's experts only.
     shared:  dict(w1=[2Is, H], w2=[H, Is], s1, s2, block[, fmt]) -- the replicated shared expert; with it
              forward returns shared_expert(x) + routed(x) * routed_scaling_factor (shared_expert_cpu's contract).
-    capacity: rows reserved per (source, destination) pair.  A GROUP-WIDE constant >= every rank's token count;
-             if omitted it is agreed once, at the first call, as the next power of two of the maximum token count
-             over the ranks (one all-reduce).  Ranks may hold different -- also zero -- token counts.
+    capacity: rows reserved per (source, destination) pair.  A GROUP-WIDE constant >= every rank's token count (the
+             caller's promise: the check against it is rank-local, a rank that breaks it raises alone).  If omitted
+             it is agreed by the group on every call (one all-reduce + host read per call) as the next power of two
+             of the largest token count seen so far, and grows on all ranks together.  Ranks may hold different --
+             also zero -- token counts.
+    close(): collective, like forward.
     forward(x[M,H] bf16, topk_weights[M,k] f32, topk_ids[M,k] i32 with GLOBAL expert ids) -> [M,H] bf16,
     bit-identical to the single-GPU fused_experts (+ shared_expert) on the same tokens when both sides run the
     same GEMM kernel variant (pass `path`; SGLB_PATH_AUTO picks the kernel from the batch size).
@@ -377,6 +409,7 @@ class EPMoE:
                                                                        path, shared)
         self.rsf = float(routed_scaling_factor)
         self.capacity = None if capacity is None else int(capacity)
+        self._auto_capacity = capacity is None
         self.last_mode = None
         self._peer = {}          # (cap, H) -> PeerExchange
         self._peer_failed = False
@@ -394,17 +427,26 @@ class EPMoE:
     def _agreed_capacity(self, M, device, capacity):
         if capacity is not None:
             return int(capacity)
-        if self.capacity is None:
+        if self._auto_capacity:
+            # Agreed on EVERY call (one all-reduce + host read): a batch larger than anything seen so far makes the
+            # whole group grow together, instead of one rank raising while its peers wait in the exchange for it.
+            # Latency-critical callers pass `capacity` (constructor or call) or use graphed(), and skip this.
             mx = self.comm.max_int(M, device)
-            self.capacity = max(16, 1 << max(0, mx - 1).bit_length())
+            if self.capacity is None or mx > self.capacity:
+                self.capacity = max(16, 1 << max(0, mx - 1).bit_length())
         return self.capacity
 
     def _peer_exchange(self, cap, H, device):
         key = (cap, H)
         if key not in self._peer:
             try:
-                while len(self._peer) >= 2:     # bounded: each entry pins an IPC-mapped region on every rank
-                    self._peer.pop(next(iter(self._peer))).close()
+                # bounded: each entry pins an IPC-mapped region on every rank.  Oldest first, but never a region that a
+                # live GraphedEP captured graphs over (same decision on every rank: close() is collective)
+                while len(self._peer) >= 2:
+                    victim = next((k for k, v in self._peer.items() if v.pins == 0), None)
+                    if victim is None:
+                        break
+                    self._peer.pop(victim).close()
                 self._peer[key] = PeerExchange(self.comm, cap, H, self.topk, device)
             except RuntimeError:
                 self._peer_failed = True     # decided identically on every rank (see PeerExchange.__init__)

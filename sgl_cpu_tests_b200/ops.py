@@ -55,16 +55,22 @@ def _ptr(t):
 # rotates `inputs[idx]`); a 56 MB activation (M = 3929, H = 7168) crosses PCIe at ~8 GB/s from pageable memory and at
 # ~25 GB/s once registered.  A contiguous host tensor of at least _PIN_MIN_BYTES seen for the second time at the same
 # address is registered with cudaHostRegister and unregistered when the tensor object dies.  SGLB_PIN_HOST=0 disables.
+# The registration goes through libsglb200 (sglb_host_register): a refused range -- a read-only or file-backed mapping
+# such as an mmap'ed checkpoint, the locked-memory limit -- is then cleared inside the library instead of staying
+# pending in torch's runtime, where the next launch check would report it as an unrelated CUDA error.  At most
+# SGLB_PIN_HOST_GB (default 8) of caller memory are page-locked at a time; refused ranges are not tried again.
 _PIN_HOST = os.environ.get("SGLB_PIN_HOST", "1") != "0"
 _PIN_MIN_BYTES = 4 << 20
+_PIN_MAX_BYTES = int(float(os.environ.get("SGLB_PIN_HOST_GB", "8")) * (1 << 30))
 _pin_seen = {}
 _pinned = {}
+_pin_refused = set()
 
 
 def _unpin(ptr):
     if _pinned.pop(ptr, None) is not None:
         try:
-            torch.cuda.cudart().cudaHostUnregister(ptr)
+            L.load().sglb_host_unregister(ptr)
         except Exception:  # interpreter / context shutdown
             pass
 
@@ -76,7 +82,7 @@ def _maybe_pin(t):
     if n < _PIN_MIN_BYTES:
         return
     ptr = t.data_ptr()
-    if ptr in _pinned:
+    if ptr in _pinned or (ptr, n) in _pin_refused or sum(_pinned.values()) + n > _PIN_MAX_BYTES:
         return
     seen = _pin_seen.get((ptr, n), 0) + 1
     if seen < 2:
@@ -87,13 +93,13 @@ def _maybe_pin(t):
     _pin_seen.pop((ptr, n), None)
     if t.is_pinned():
         return
-    try:
-        rc = torch.cuda.cudart().cudaHostRegister(ptr, n, 0)
-    except Exception:
-        return
-    if int(rc) == 0:
+    if L.load().sglb_host_register(ptr, n) == L.OK:
         _pinned[ptr] = n
         weakref.finalize(t, _unpin, ptr)
+    else:
+        if len(_pin_refused) > 256:
+            _pin_refused.clear()
+        _pin_refused.add((ptr, n))
 
 
 _copy_streams = {}
@@ -423,6 +429,19 @@ def _resident_mx_scale(s, is_vnni, dev):
     return sd
 
 
+# A CUDA graph bakes in the addresses of everything its kernels touch, including the registry-owned tensors DERIVED
+# from a weight (mxfp4 scale tiles, padded mxfp4 weights).  While a graph is being captured the helpers below hand
+# every tensor they return to this sink, and the graph object keeps them alive: the registry may evict the entry,
+# the memory stays valid for as long as a graph can replay over it.
+_capture_sink = None
+
+
+def _note_captured(t):
+    if _capture_sink is not None and t is not None:
+        _capture_sink.append(t)
+    return t
+
+
 def _mx4_tiles(s_dev, shape, split):
     """e8m0 scales [E, rows, K/32] on the device -> the 512-byte tiles the block-scaled tensor-core kernel
     copies into TMEM (csrc/umma_mx4.cu); built once per scale tensor and cached.  Keyed on (and dropped with) the
@@ -431,13 +450,13 @@ def _mx4_tiles(s_dev, shape, split):
     key = _registry_key(s_dev, False, ("mx4tiles", tuple(shape), split))
     hit = _registry_get(key)
     if hit is not None:
-        return hit
+        return _note_captured(hit)
     E, rows, G = shape
     lib = L.load()
     tiles = torch.empty(lib.sglb_mx4_scale_tiles_bytes(E, rows, split, 32 * G), dtype=torch.uint8, device=s_dev.device)
     L.check(lib.sglb_mx4_tile_scales(s_dev.data_ptr(), tiles.data_ptr(), E, rows, split, 32 * G, _stream()))
     _registry_put(key, (None, None), tiles, s_dev)   # dropped when the keyed scale tensor dies
-    return tiles
+    return _note_captured(tiles)
 
 
 def _mx4_weight(w_dev):
@@ -454,12 +473,12 @@ def _mx4_weight(w_dev):
     key = _registry_key(w_dev, False, "mx4pad")
     hit = _registry_get(key)
     if hit is not None:
-        return hit
+        return _note_captured(hit)
     buf = torch.zeros(w_dev.numel() + 64, dtype=torch.uint8, device=w_dev.device)
     padded = buf[:w_dev.numel()].view(w_dev.shape)
     padded.copy_(w_dev)
     _registry_put(key, (None, None), padded, w_dev)
-    return padded
+    return _note_captured(padded)
 
 
 # ---- K1: routers -----------------------------------------------------------------------------------------
@@ -833,8 +852,14 @@ class GraphedExperts:
                         self.kernels_per_replay = launch_count() - n0
                     side.synchronize()
                     self.graph = torch.cuda.CUDAGraph()
-                    with torch.cuda.graph(self.graph, stream=side):
-                        call()
+                    global _capture_sink
+                    derived = _capture_sink = []
+                    try:
+                        with torch.cuda.graph(self.graph, stream=side):
+                            call()
+                    finally:
+                        _capture_sink = None
+                    self._keep = self._keep + tuple(derived)   # scale tiles / padded weights the graph addresses
                 finally:
                     _workspaces.pop(key, None)
             torch.cuda.current_stream().wait_stream(side)

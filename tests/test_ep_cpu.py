@@ -152,6 +152,50 @@ def test_ep_two_ranks_gloo():
             assert loose_err <= 1e-2
 
 
+def _regrow_main(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from sgl_cpu_tests_b200 import ep
+        E, topk, H, I = 8, 3, 32, 16
+        el = E // world
+        layer = None
+        # a warm-up sized batch first, then one that only rank 0 outgrows the agreed capacity with, then a small one
+        for step, Ms in enumerate([(3, 2), (20, 5), (1, 1)]):
+            w1, w2, _, _, xs, tws, idss = make_case(11 + step, Ms, E, topk, H, I)
+            local = dict(w1=w1[rank * el:(rank + 1) * el], w2=w2[rank * el:(rank + 1) * el])
+            if layer is None:
+                layer = ep.EPMoE(local, "bf16", E, topk, backend=OracleBackend(local, "bf16", el, topk, None))
+            else:
+                layer.backend = OracleBackend(local, "bf16", el, topk, None)
+            x, tw, ids = xs[rank], tws[rank], idss[rank]
+            out = layer.forward(x, tw, ids, mode="fixed")
+            ref = O.reduce_slots(slot_rows_rowwise(x, w1, w2, tw, ids), ids, E)
+            q.put((rank, step, bool(torch.equal(out, ref)), layer.capacity))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ep_auto_capacity_grows_on_every_rank_together():
+    """A later batch larger than the capacity agreed at the first call must not raise on one rank while the other
+    enters the exchange: without an explicit capacity the group re-agrees per call and grows together."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_regrow_main, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(6)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    caps = {0: 16, 1: 32, 2: 32}
+    for rank, step, equal, cap in res:
+        assert cap == caps[step], (rank, step, cap)
+        assert equal, (rank, step)
+
+
 def test_ep_oracle_layout_single_process():
     """plan / pack / ret_index / combine contracts, world = 4, both segment layouts: the exchange composed in one
     process reproduces reduce_slots(slot_rows) exactly."""

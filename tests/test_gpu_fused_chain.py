@@ -197,6 +197,49 @@ def test_mxfp4_scale_tiles_are_built_once(K):
     assert counts[0] >= counts[1]
 
 
+def test_graph_outlives_eviction_of_the_mxfp4_scale_tiles(K):
+    """A captured graph addresses the registry-owned scale tiles of an mxfp4 weight.  The registry may evict them
+    (LRU, clear_weight_cache): the graph object must keep them alive itself, and a replay after the eviction --
+    with the freed-looking memory scribbled over by new allocations -- must still give the eager result."""
+    from sgl_cpu_tests_b200 import ops
+    E, topk, H, I, M = 16, 4, 1024, 512, 64
+    dev = torch.device("cuda", 0)
+    w, fid, g = weights("mxfp4", E, H, I, 23)
+    x = (torch.randn(M, H, device=dev, generator=g) / 8).bfloat16()
+    tw, ids = routing(M, E, topk, g, dev)
+    ref = run(K, x, w, fid, tw, ids, K.PATH_AUTO).clone()
+    gph = K.GraphedExperts(M, w["w1"], w["w2"], topk, fid, w["s1"], w["s2"], w["block"])
+    tiles = [t for t in gph._keep if t is not None and t.dtype == torch.uint8 and t.dim() == 1]
+    assert len(tiles) >= 2, "the graph does not hold the scale tiles it was captured over"
+    ops.clear_weight_cache()
+    torch.cuda.synchronize()
+    junk = [torch.full((t.numel(),), 0xff, dtype=torch.uint8, device=dev) for t in tiles for _ in range(4)]
+    out = gph(x, tw, ids)
+    torch.cuda.synchronize()
+    assert torch.equal(out, ref)
+    del junk
+
+
+def test_refused_host_registration_leaves_no_cuda_error_behind(K):
+    """ops._maybe_pin page-locks large recurring host buffers through sglb_host_register.  A range the driver refuses
+    (here: one that is already registered) must be skipped quietly: no exception, no pending CUDA error that the next
+    torch launch check would trip over."""
+    from sgl_cpu_tests_b200 import _lib as L
+    lib = L.load()
+    t = torch.empty(8 << 20, dtype=torch.uint8)
+    assert lib.sglb_host_register(t.data_ptr(), t.numel()) == 0
+    try:
+        assert lib.sglb_host_register(t.data_ptr(), t.numel()) != 0      # already registered: refused
+        assert b"cudaHostRegister" in lib.sglb_last_error()
+        y = torch.ones(1024, device="cuda") * 2                           # a torch launch + its error check
+        torch.cuda.synchronize()
+        assert float(y.sum()) == 2048.0
+    finally:
+        assert lib.sglb_host_unregister(t.data_ptr()) == 0
+    assert lib.sglb_host_unregister(t.data_ptr()) != 0                    # not registered any more: reported, cleared
+    torch.cuda.synchronize()
+
+
 @pytest.mark.parametrize("M", [1, 16, 40, 100, 250])
 def test_fp8_small_tile_deep_ring_is_bit_identical(K, M):
     """fp8 decode takes 32-row tiles on a 5-stage ring (umma_f8.cu F8Cfg<32>; M = 100, 250 here: 80-row tiles on a
