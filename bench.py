@@ -73,6 +73,8 @@ def parse():
     ap.add_argument("--no-configs", action="store_true", help="skip the other BASELINE configurations ('configs')")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle check of the timed step ('parity_check')")
+    ap.add_argument("--parity-tokens", type=int, default=32, help="tokens of the headline step compared with the oracle")
     ap.add_argument("--no-router", action="store_true", help="routing precomputed outside the step (experiments)")
     ap.add_argument("--no-shared", action="store_true", help="leave the shared expert out of the step (experiments)")
     ap.add_argument("--bias-scale", type=float, default=None, help="std of the router's correction bias (default: by shape)")
@@ -474,10 +476,75 @@ def roofline_of(wl, ms_per_step, stage_us, hbm_peak, tc, peak_src, traffic_key=N
     return roof, step
 
 
+def step_parity(wl, step, tokens):
+    """Checks the step that is about to be timed -- same layer objects, same launch mode (graph replay or eager) --
+    against the CPU oracle: router ids on EVERY token (torch.equal; weights bit-equal for the biased router, 1e-5 for
+    the softmax one), then the layer output of `tokens` evenly spaced tokens against the oracle restricted to the
+    experts those tokens use (the reference's tolerance, rtol = atol = 1e-2; int8: mean relative error < 1e-2 as in
+    tests/test_gpu_parity.py).  The oracle is used here as the checker only; nothing of it is timed or shipped.
+    Sequence matched: test_biased_grouped_topk.py:67-80 -> test_moe_fp8_ext.py:118 -> :60-61."""
+    from oracle import moe_oracle as O
+    t0 = time.time()
+    out = step(0).clone()           # step 0 runs weight copy 0
+    torch.cuda.synchronize()
+    res = {"tokens": 0, "launch_checked": "graph" if hasattr(step, "graphs") else "eager"}
+    gating = wl.gating.cpu()
+    if wl.with_router:
+        if wl.biased:
+            tw_o, ids_o = O.biased_grouped_topk(gating, wl.bias.cpu(), wl.topk, wl.renorm, wl.G, wl.tg)
+        else:
+            tw_o, ids_o = O.grouped_topk(gating, wl.topk, wl.renorm, wl.G, wl.tg)
+        tw_g, ids_g = wl.router(wl.gating)
+        res["ids_equal"] = bool(torch.equal(ids_g.cpu(), ids_o))
+        res["weights_equal"] = bool(torch.equal(tw_g.cpu(), tw_o) if wl.biased else
+                                    torch.allclose(tw_g.cpu(), tw_o, rtol=1e-5, atol=1e-7))
+        res["router_tokens"] = int(gating.shape[0])
+    else:
+        tw_o, ids_o = wl.tw.cpu(), wl.ids.cpu()
+        res["ids_equal"] = res["weights_equal"] = None
+    n = min(tokens, wl.M)
+    idx = torch.linspace(0, wl.M - 1, n).round().long().unique()
+    ids_s, tw_s = ids_o[idx], tw_o[idx]
+    used = torch.unique(ids_s[ids_s >= 0]).long()
+    remap = torch.full((wl.E,), -1, dtype=torch.int32)
+    remap[used] = torch.arange(used.numel(), dtype=torch.int32)
+    ids_r = torch.where(ids_s >= 0, remap[ids_s.clamp_min(0).long()], ids_s)
+    w = wl.weights[0]
+    du = used.to(wl.dev)
+    sub = {k: (w[k][du].cpu() if torch.is_tensor(w[k]) else w[k]) for k in ("w1", "w2", "s1", "s2", "block")}
+    x = wl.x[idx.to(wl.dev)].cpu()
+    ref = O.fused_experts_lean(x, sub["w1"], sub["w2"], tw_s, ids_r, wl.fmt, sub["s1"], sub["s2"], sub["block"])
+    if wl.shared_I:
+        sh = {k: (v.cpu() if torch.is_tensor(v) else v) for k, v in wl.shared[0].items()}
+        ref = O.shared_expert(x, sh["w1"], sh["w2"], ref, wl.rsf, wl.fmt, sh["s1"], sh["s2"], sh["block"])
+    got, ref = out[idx.to(wl.dev)].float().cpu(), ref.float()
+    res["tokens"] = int(idx.numel())
+    res["experts_checked"] = int(used.numel())
+    res["max_diff"] = float((got - ref).abs().max())
+    res["mean_rel"] = float((got - ref).abs().mean() / ref.abs().mean().clamp_min(1e-30))
+    if wl.fmt == "int8":
+        res["criterion"] = "mean relative error < 1e-2 (tests/test_gpu_parity.py, int8)"
+        res["outputs_ok"] = bool(torch.isfinite(got).all()) and res["mean_rel"] < 1e-2
+    else:
+        res["criterion"] = "allclose rtol = atol = 1e-2 (utils.py:3-25 of the reference)"
+        res["outputs_ok"] = bool(torch.isfinite(got).all() and torch.allclose(got, ref, rtol=1e-2, atol=1e-2))
+    if wl.fmt == "mxfp4":
+        res["note"] = "parity unpinned: the reference has no fused-mxfp4 call site, the oracle is composed from test_mxfp4.py:65-128"
+    res["ok"] = bool(res["outputs_ok"] and res["ids_equal"] is not False and res["weights_equal"] is not False)
+    res["seconds"] = round(time.time() - t0, 2)
+    return res
+
+
 def measure_config(args, name, shape, fmt, M, dev, gen, hbm_peak, tc, peak_src, steps=10, e2e=True):
     """One entry of `configs`: the layer of `shape` in `fmt` at M tokens, measured like the headline."""
     wl = Workload(args, shape, fmt, M, dev, gen, router=not args.no_router, shared=not args.no_shared)
     step, graphed = wl.make_step()
+    par = None
+    if not args.no_parity:
+        try:
+            par = step_parity(wl, step, 4)
+        except Exception as e:  # noqa: BLE001
+            par = {"ok": False, "error": f"{type(e).__name__}: {e}"}
     ms = time_steps(step, steps, 3) / steps
     prof = wl.stage_profile(max(3, steps // 2))
     roof, srf = roofline_of(wl, ms, prof, hbm_peak, tc, peak_src)
@@ -488,6 +555,8 @@ def measure_config(args, name, shape, fmt, M, dev, gen, hbm_peak, tc, peak_src, 
            "active_experts": roof["active_experts"]}
     if fmt == "mxfp4":
         ent["parity"] = "unpinned (the reference has no fused-mxfp4 call site; composed oracle)"
+    if par is not None:
+        ent["parity_check"] = par
     if e2e and not args.no_e2e:
         ent["e2e"] = run_e2e(args, wl, 1, 0, min(steps, 10))
     del step, wl
@@ -655,6 +724,14 @@ def run_b200(args):
     E, topk, H, I = wl.E, wl.topk, wl.H, wl.I
     step, graphed = wl.make_step()
 
+    # ---- the step that gets timed, checked against the oracle first (N = 1; N > 1 has ep_parity above) ----
+    step_par = None
+    if world == 1 and not args.no_parity:
+        step_par = step_parity(wl, step, args.parity_tokens)
+        if not step_par["ok"]:
+            print(json.dumps({"error": "the timed step differs from the oracle", "parity_check": step_par}))
+            raise SystemExit(3)
+
     # ---- headline: device-resident inputs ----
     clocks = ClockSampler(local)
     for i in range(args.warmup):
@@ -693,6 +770,8 @@ def run_b200(args):
         "windows_ms_per_step": [w / args.steps for w in windows],
         "clocks": clk, "gpu_launches": int(launches),
     }
+    if step_par is not None:
+        out["parity_check"] = step_par
     if world > 1:
         out["per_rank_ms_per_step"] = [p / args.steps for p in per_rank]
         out["config"]["exchange"] = {"p2p": "NVLink peer memory (ep_p2p.cu: stores into the owners' buffers, per-slot rows read back with peer loads; no NCCL on the data path)",
@@ -792,6 +871,11 @@ def run_b200(args):
                     cfgs.append({"name": name, "M": m, "error": f"{type(e).__name__}: {e}"})
                     torch.cuda.empty_cache()
         out["configs"] = cfgs
+        bad = [c["name"] + f" M={c['M']}" for c in cfgs if c.get("parity_check") and not c["parity_check"].get("ok")]
+        if bad:
+            print(json.dumps({"error": "timed configs differ from the oracle", "configs": bad,
+                              "parity_checks": [c.get("parity_check") for c in cfgs]}))
+            raise SystemExit(3)
 
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(shape, fmt, M, budget_s=25.0)

@@ -165,3 +165,31 @@ def test_pair_kernels_equal_single_cta_bitwise_at_scale(K, fmt):
     ref = call(K, layer, fmt_id, x, tw, ids, path=K.PATH_UMMA)
     for _ in range(6):
         assert torch.equal(call(K, layer, fmt_id, x, tw, ids, path=K.PATH_UMMA2), ref)
+
+
+@pytest.mark.parametrize("M", [1, 256])
+def test_deepseek_v3_layer_as_bench_times_it(M):
+    """The step bench.py's headline times, at its real size: biased_grouped_topk (G 8, topk_group 2) -> 256 fp8
+    block-128 experts (H 7168, I 2048) -> shared expert I 2048 riding in the same launches -> one CUDA-graph replay,
+    against the oracle (router ids and weights bit-equal on every token; layer output of up to 32 tokens within
+    rtol = atol = 1e-2 against the oracle restricted to the experts they use).  Reference sequence:
+    test_biased_grouped_topk.py:67-80 -> test_moe_fp8_ext.py:118 -> :60-61."""
+    import argparse
+    import bench
+    dev = torch.device("cuda", 0)
+    args = argparse.Namespace(bias_scale=None, path="auto", launch="graph", ep_mode=None)
+    g = torch.Generator(device=dev).manual_seed(1111)
+    wl = bench.Workload(args, "dsv3", "fp8", M, dev, g, copies=1)
+    wl.copies = 1
+    try:
+        if M == 256:
+            assert wl.layers[0].rides(M), "the shared expert must ride inside the routed launches at the headline size"
+        step = wl.graph_step()
+        res = bench.step_parity(wl, step, 32)
+        assert res["launch_checked"] == "graph" and res["router_tokens"] == M
+        assert res["ids_equal"] and res["weights_equal"], res
+        assert res["outputs_ok"] and res["ok"], res
+        assert res["tokens"] == min(32, M)
+    finally:
+        wl.layers = wl.weights = wl.shared = None
+        torch.cuda.empty_cache()
