@@ -455,6 +455,39 @@ def fused_experts_lean(a, w1, w2, topk_weight, topk_ids, fmt, w1_scale=None, w2_
 
 
 # ---------------------------------------------------------------------------------------------------
+# CPU-baseline variant with the weight-only formats dequantised ONCE (bench.py's "pre-dequantised bf16" figure)
+#
+# The literal oracles above re-dequantise every active expert to f32 on every call: fine for a checker, unfair as a
+# timed CPU baseline (no CPU kernel would do that per call).  This variant hoists the dequantisation out of the
+# step -- weights become bf16-resident, which is what test_moe_fp8_ext.py:70-91 itself feeds its GEMMs ("dequantised
+# to the activation dtype") -- and runs the reference's bf16 oracle, torch_naive_moe (test_moe.py:22-54: bf16
+# matmuls, oneDNN / AMX on a Xeon that has it), on them.  Same algorithm, bf16 GEMM rounding instead of f32.
+
+
+def dequantise_to_bf16(w, scale, fmt, block_size=None):
+    """[E, N, K'] (or 2-D) quantised weights -> bf16 [E, N, K], one expert at a time (bounded temporaries)."""
+    if fmt in ("bf16", "int8"):
+        raise ValueError("only the weight-only formats (fp8, mxfp4) have a pre-dequantised form")
+    squeeze = w.dim() == 2
+    if squeeze:
+        w, scale = w.unsqueeze(0), scale.unsqueeze(0)
+    K = w.shape[2] * (2 if fmt == "mxfp4" else 1)
+    out = torch.empty(w.shape[0], w.shape[1], K, dtype=torch.bfloat16)
+    for i in range(w.shape[0]):
+        if fmt == "fp8":
+            out[i] = scaled_weight(w[i], scale[i], block_size[0], block_size[1]).bfloat16()
+        else:
+            out[i] = mxfp4_dequantize(w[i], torch.bfloat16, scale[i])
+    return out[0] if squeeze else out
+
+
+def shared_expert_resident_bf16(a, w1_bf16, w2_bf16, fused_out, routed_scaling_factor):
+    """shared_expert on bf16-resident weights: bf16 GEMMs, f32 epilogue (test_shared_experts.py:34-40 in a.dtype)."""
+    ic1 = silu_and_mul(a @ w1_bf16.t())
+    return ((ic1 @ w2_bf16.t()).float() + fused_out.float() * routed_scaling_factor).to(a.dtype)
+
+
+# ---------------------------------------------------------------------------------------------------
 # shared expert
 
 

@@ -1,5 +1,6 @@
 """The CPU oracle against fixtures produced by the reference's own oracle code
 (tests/golden/make_golden.py).  No GPU, no CUDA library."""
+import pytest
 import torch
 
 from oracle import moe_oracle as O
@@ -245,3 +246,37 @@ def test_sigmoid_f64_c_restatement_bit_equal(tmp_path):
     exact = torch.sigmoid(x.double())
     ulp = torch.maximum(exact.float().abs(), torch.tensor(2.0 ** -126)) * 2.0 ** -23
     assert ((got.double() - exact).abs() <= ulp.double()).all()
+
+
+@pytest.mark.parametrize("fmt", ["fp8", "mxfp4"])
+def test_predequantised_bf16_baseline_matches_the_literal_oracle(fmt):
+    """bench.py's second CPU figure (weights dequantised once to bf16, then the reference's bf16 oracle) computes the
+    same layer as the literal per-call-dequantising oracle, up to bf16 GEMM rounding."""
+    torch.manual_seed(5)
+    M, E, topk, H, I = 24, 8, 3, 256, 128
+    a = (torch.randn(M, H) / 16).bfloat16()
+    if fmt == "fp8":
+        w1 = (torch.randn(E, 2 * I, H) * 100).clamp(-400, 400).to(torch.float8_e4m3fn)
+        w2 = (torch.randn(E, H, I) * 100).clamp(-400, 400).to(torch.float8_e4m3fn)
+        s1, s2, block = torch.randn(E, 2 * I // 128, H // 128) * 1e-3, torch.randn(E, H // 128, I // 128) * 1e-3, [128, 128]
+    else:
+        w1 = torch.randint(0, 256, (E, 2 * I, H // 2), dtype=torch.uint8)
+        w2 = torch.randint(0, 256, (E, H, I // 2), dtype=torch.uint8)
+        s1 = torch.randint(118, 122, (E, 2 * I, H // 32), dtype=torch.uint8)
+        s2 = torch.randint(118, 122, (E, H, I // 32), dtype=torch.uint8)
+        block = None
+    tw, ids = torch.topk(torch.softmax(torch.randn(M, E), dim=-1), topk)
+    ids = ids.to(torch.int32)
+    ids[0, 0] = -1
+    lit = O.fused_experts_lean(a, w1, w2, tw, ids, fmt, s1, s2, block)
+    d1, d2 = O.dequantise_to_bf16(w1, s1, fmt, block), O.dequantise_to_bf16(w2, s2, fmt, block)
+    assert d1.shape == (E, 2 * I, H) and d1.dtype == torch.bfloat16
+    res = O.torch_naive_moe(a, d1, d2, tw, ids)
+    scale = float(lit.float().abs().max())
+    assert float((res.float() - lit.float()).abs().max()) <= 3e-2 * scale
+    assert torch.allclose(res.float(), lit.float(), rtol=5e-2, atol=3e-2 * scale)
+    sh_lit = O.shared_expert(a, w1[0], w2[0], lit, 2.5, fmt, s1[0], s2[0], block) if fmt == "fp8" else None
+    if sh_lit is not None:
+        sh = O.shared_expert_resident_bf16(a, d1[0], d2[0], lit, 2.5)
+        scale = float(sh_lit.float().abs().max())
+        assert float((sh.float() - sh_lit.float()).abs().max()) <= 3e-2 * scale
