@@ -906,7 +906,7 @@ def run_e2e(args, wl, world, rank, steps):
     ring = [xh.clone().pin_memory() for _ in range(steps + 3 if use_ring else 1)] if world == 1 else []
     per_op = {"router": 0.0, "fused_experts": 0.0, "shared_expert": 0.0}
     calls = [0]
-    h2d = d2h = 0
+    h2d = d2h = shared_uploads = 0
     if world > 1:
         layer = wl.layers[0]
         twh, idh = pin(wl.tw), pin(wl.ids)
@@ -966,7 +966,7 @@ def run_e2e(args, wl, world, rank, steps):
         h2d += xh.numel() * 2 + M * topk * 8
         d2h += xh.numel() * 2
         if sh is not None:
-            h2d += 2 * xh.numel() * 2
+            shared_uploads = 2 * xh.numel() * 2      # hidden_states and fused_experts_out, unless still in HBM (below)
             d2h += xh.numel() * 2
         api = ("torch.ops.sgl_kernel." + ("biased_grouped_topk_cpu -> " if wl.biased else "grouped_topk_cpu -> ") * int(wl.with_router)
                + "fused_experts_cpu" + (" -> shared_expert_cpu" if sh is not None else "")
@@ -979,11 +979,16 @@ def run_e2e(args, wl, world, rank, steps):
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
+    from sgl_cpu_tests_b200 import ops as _ops
+    hits0 = _ops.shadow_hits
     t0 = time.perf_counter()
     for _ in range(steps):
         call()
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
+    reused = (_ops.shadow_hits - hits0) / steps      # tensors per step shared_expert_cpu found still in HBM (ops._shadow_get)
+    if shared_uploads:
+        h2d += int(shared_uploads * max(0.0, 2.0 - reused) / 2.0)
     if world > 1:
         import torch.distributed as dist
         t = torch.tensor([dt], device=wl.dev)
@@ -993,6 +998,7 @@ def run_e2e(args, wl, world, rank, steps):
     return {"value": M * world * steps / dt, "unit": "tokens/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
             "ms_per_step": dt / steps * 1e3, "steps": steps, "api": api,
             "per_op_ms": {k: v / steps * 1e3 for k, v in per_op.items()} if world == 1 else None,
+            "tensors_reused_in_hbm_per_step": reused,
             "note": "fixed token count per call: host-tensor calls replay a cached CUDA graph per (M, weights)"}
 
 

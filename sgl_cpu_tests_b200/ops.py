@@ -102,6 +102,40 @@ def _maybe_pin(t):
         _pin_refused.add((ptr, n))
 
 
+# ---- device shadows of the last host-tensor fused_experts call ---------------------------------------------------
+# The reference's API hands tensors from op to op through host memory: shared_expert_cpu(hidden_states, ...,
+# fused_experts_out, ...) right after fused_experts_cpu(hidden_states, ...) (test_moe_fp8_ext.py:60-61,118).  Both of
+# those tensors were in HBM a moment ago -- hidden_states uploaded, the result produced there -- so the second op need
+# not upload them again.  The last host-tensor fused_experts call leaves (host tensor -> device tensor) for its input
+# and its result; a hit requires the SAME tensor object (weak reference), an unchanged torch version counter, the
+# same Python thread and the same CUDA stream, and every new host-tensor fused_experts call drops both entries
+# before it touches the (static, graph-owned) device buffers they point to.  What it cannot see, as for the weight
+# registry: writes that bypass the version counter (numpy views, `t.data.copy_()`) between the two ops.
+# SGLB_SHADOW=0 disables.
+_SHADOW = os.environ.get("SGLB_SHADOW", "1") != "0"
+_shadow = {}
+shadow_hits = 0   # for tests / bench
+
+
+def _shadow_put(kind, host_t, dev_t):
+    if _SHADOW and host_t is not None and not host_t.is_cuda and host_t.is_contiguous():
+        _shadow[kind] = (weakref.ref(host_t), host_t._version, dev_t, threading.get_ident(), _stream())
+
+
+def _shadow_get(host_t, dev):
+    """The device twin of `host_t` left by the last host-tensor fused_experts call, or None.  Call under _launch_lock
+    and keep it until the kernels reading the twin are enqueued."""
+    global shadow_hits
+    if not _shadow or host_t is None or host_t.is_cuda:
+        return None
+    for ref, ver, d, tid, st in list(_shadow.values()):
+        if (ref() is host_t and host_t._version == ver and tid == threading.get_ident() and st == _stream()
+                and d.device == dev and d.shape == host_t.shape and d.dtype == host_t.dtype):
+            shadow_hits += 1
+            return d
+    return None
+
+
 _copy_streams = {}
 
 
@@ -291,6 +325,7 @@ def invalidate(tensor=None):
 
 def clear_weight_cache():
     global _registry_bytes, _registry_host_bytes
+    _shadow.clear()
     _host_graphs.clear()
     _host_graph_seen.clear()
     _registry.clear()
@@ -714,6 +749,7 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
             with _launch_lock:
                 g = _host_graph(M, topk, fmt, w13, w2d, gs13, gs2, block_size, path)
                 if g is not None:
+                    _shadow.clear()      # the static buffers below are about to be rewritten
                     _maybe_pin(hidden_states)
                     g.hidden.copy_(hidden_states, non_blocking=True)
                     g.topk_weights.copy_(topk_weights, non_blocking=True)
@@ -721,8 +757,14 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
                     g.graph.replay()
                     if inplace:
                         hidden_states.copy_(g.out)  # blocking D2H into the caller's buffer
+                        _shadow_put("out", hidden_states, g.out)   # hidden_states now holds the result
                         return hidden_states
-                    return _to_host(g.out)
+                    h = _to_host(g.out)
+                    _shadow_put("x", hidden_states, g.hidden)
+                    _shadow_put("out", h, g.out)
+                    return h
+        if not on_cuda:
+            _shadow.clear()
         x = _to_dev(hidden_states, dev)
         tw = _to_dev(topk_weights, dev, torch.float32)
         ids = _to_dev(topk_ids, dev, torch.int32)
@@ -798,8 +840,12 @@ def fused_experts_impl(hidden_states, w1, w2, topk_weights, topk_ids, inplace, f
             return out
         if inplace:
             hidden_states.copy_(out)  # D2H into the caller's buffer ("fused moe mutates content in hs")
+            _shadow_put("out", hidden_states, out)
             return hidden_states
-        return _to_host(out)
+        h = _to_host(out)
+        _shadow_put("x", hidden_states, x)
+        _shadow_put("out", h, out)
+        return h
 
 
 def shared_rides(M, topk, E, H, I, fmt, block_size=None, path=L.PATH_AUTO, shared_I=None, shared_fmt=None):
@@ -959,13 +1005,18 @@ def shared_expert_impl(hs, w1, w2, fused_out, rsf, inplace, fmt, s1, s2, block, 
     on_cuda = hs.is_cuda
     dev = hs.device if on_cuda else _device()
     lib = L.load()
-    with torch.cuda.device(dev):
-        x = _to_dev(hs, dev)
+    with torch.cuda.device(dev), _launch_lock:     # the lock spans shadow look-up .. enqueue (see _shadow_get)
+        x = _shadow_get(hs, dev) if not on_cuda else None
+        if x is None:
+            x = _to_dev(hs, dev)
+        fo_shadow = _shadow_get(fused_out, dev) if (not on_cuda and out is None) else None
         # A pinned host `fused_out` is only needed by the final axpy: its upload runs on a copy stream UNDER the MLP's
         # GEMMs (the reference's API hands the routed result from op to op through host memory; at DeepSeek-V3's 256
         # tokens that is 3.7 MB = about as long as the shared MLP itself).
         fo_event = None
-        if (fused_out is not None and not on_cuda and out is None and fused_out.is_contiguous()
+        if fo_shadow is not None:       # still in HBM from the fused_experts call that produced it: no upload at all
+            fo = fo_shadow
+        elif (fused_out is not None and not on_cuda and out is None and fused_out.is_contiguous()
                 and (fused_out.is_pinned() or fused_out.data_ptr() in _pinned)):
             side = _copy_stream(dev)
             side.wait_stream(torch.cuda.current_stream())

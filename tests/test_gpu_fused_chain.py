@@ -220,6 +220,58 @@ def test_graph_outlives_eviction_of_the_mxfp4_scale_tiles(K):
     del junk
 
 
+@pytest.mark.parametrize("fmt", ["bf16", "fp8"])
+def test_shared_expert_reuses_the_device_twins_of_the_previous_fused_experts_call(K, fmt):
+    """Host tensors, the reference's call sequence (test_moe_fp8_ext.py:118 then :60-61): shared_expert_cpu gets the
+    hidden_states that fused_experts_cpu just uploaded and the result it just produced.  Both are still in HBM, so
+    the second op must not upload them again -- and must give the bits of the plain path.  A hit needs the same
+    tensor objects at an unchanged version: an in-place update of either, or an older call's tensors, must miss."""
+    from sgl_cpu_tests_b200 import ops
+    E, topk, H, I, M = 16, 4, 1024, 512, 48
+    dev = torch.device("cuda", 0)
+    w, fid, g = weights(fmt, E, H, I, 41)
+    sh = {k: (v[0].contiguous() if torch.is_tensor(v) else v) for k, v in weights(fmt, 1, H, I, 43)[0].items()}
+    tw_d, ids_d = routing(M, E, topk, g, dev)
+    tw, ids = tw_d.cpu(), ids_d.cpu()
+    xs = [(torch.randn(M, H, generator=torch.Generator().manual_seed(s)) / 16).bfloat16() for s in (1, 2)]
+
+    def fused(x):
+        return K.fused_experts_impl(x, w["w1"], w["w2"], tw, ids, False, fid, w["s1"], w["s2"], w["block"], False)
+
+    def shared(x, fo):
+        return K.shared_expert_impl(x, sh["w1"], sh["w2"], fo, 2.5, False, fid, sh["s1"], sh["s2"], sh["block"], False)
+
+    assert ops._SHADOW
+    for _ in range(3):                       # the third call replays the cached host-tensor graph (static buffers)
+        out1 = fused(xs[0])
+        ops._SHADOW = False
+        try:
+            ref1 = shared(xs[0], out1)       # plain path: both tensors uploaded
+        finally:
+            ops._SHADOW = True
+        h0 = ops.shadow_hits
+        got1 = shared(xs[0], out1)
+        assert ops.shadow_hits == h0 + 2, "hidden_states and fused_experts_out should both have been found in HBM"
+        assert torch.equal(got1, ref1)
+    # an older call's tensors: the static buffers now hold call 2's data, call 1's tensors must miss
+    out1 = fused(xs[0])
+    out2 = fused(xs[1])
+    h0 = ops.shadow_hits
+    assert torch.equal(shared(xs[0], out1), ref1)
+    assert ops.shadow_hits == h0
+    # an in-place update through torch bumps the version counter: miss, and the new values are used
+    out2.mul_(2)
+    xs[1].add_(0.25)
+    h0 = ops.shadow_hits
+    got = shared(xs[1], out2)
+    assert ops.shadow_hits == h0
+    ops._SHADOW = False
+    try:
+        assert torch.equal(got, shared(xs[1], out2))
+    finally:
+        ops._SHADOW = True
+
+
 def test_refused_host_registration_leaves_no_cuda_error_behind(K):
     """ops._maybe_pin page-locks large recurring host buffers through sglb_host_register.  A range the driver refuses
     (here: one that is already registered) must be skipped quietly: no exception, no pending CUDA error that the next
